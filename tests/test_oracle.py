@@ -1,0 +1,258 @@
+"""CPU tests of the oracle itself (no GPU).
+
+What is pinned by the reference (tests/golden/*.json, produced by oracle/gen_golden.py
+from the reference's own unmodified code):
+  * rational arithmetic known answers  (Source/numOprts.c:37-129)
+  * the initial tableau of each model  (Source/simplex.c:91-260, Source/matrix.c:19-91,
+    SURVEY.md App. B)
+What is NOT pinned by the reference -- it has no pivot loop (Source/simplex.c:57-63) -- and
+is therefore checked against hand-derived sequences and against
+invariants: pivot sequences, statuses, iteration counts.
+"""
+from fractions import Fraction
+
+import numpy as np
+import pytest
+
+import helpers as H
+import oracle_lib as O
+
+
+# --------------------------------------------------------------------- App. A KATs
+@pytest.mark.parametrize("kat", [k for k in H.load_kat() if not k["has_m"]],
+                         ids=lambda k: f"{k['op']}:{k['a']}:{k['b']}")
+def test_rational_kat_matches_reference(kat):
+    L = O.lib()
+    a = O.rat_parse(kat["a"])
+    if kat["op"] in ("parse", "dec"):
+        r = a
+    else:
+        b = O.rat_parse(kat["b"])
+        r = getattr(L, "lpo_rat_" + kat["op"])(a, b)
+    assert r.valid == kat["valid"]
+    if kat["valid"]:
+        assert (r.num, r.den) == (kat["num"], kat["den"])     # same representation, sign on den kept
+        assert L.lpo_rat_to_double(r) == kat["dec"]
+
+
+def test_rational_cmp_handles_negative_denominator():
+    L = O.lib()
+    assert L.lpo_rat_cmp(O.rat(1, -2), O.rat(-1, 3)) < 0
+    assert L.lpo_rat_cmp(O.rat(1, -2), O.rat(-1, 2)) == 0
+    assert L.lpo_rat_cmp(O.rat(3, 4), O.rat(2, 3)) > 0
+
+
+# ------------------------------------------------------- App. B tableaux -> App. C runs
+def _run_exact(name, method):
+    d = H.load_dumps()[name]
+    T, basis, n_art, n = H.tableau_from_dump(d, method)
+    return d, T, basis, n_art, n, O.solve_rat(H.frac_pairs(T), basis, method=method, n_art=n_art)
+
+
+def _run_f64(name, method):
+    d = H.load_dumps()[name]
+    T, basis, n_art, n = H.tableau_from_dump(d, method)
+    return O.solve_f64(H.frac_f64(T), basis, method=method, n_art=n_art)
+
+
+def test_reference_rejects_shipped_testdata():
+    # Source/testdata.txt:2 says "ma:"; WriteIn only accepts max/min (Source/dataReader.c:455)
+    assert H.load_dumps()["testdata_asshipped.txt"] == {"parsed": 0}
+
+
+def test_testdata_front_end_dump_is_appendix_b1():
+    d = H.load_dumps()["testdata_fixed.txt"]
+    assert (d["m"], d["n"], d["valid"]) == (2, 4, 1)
+    assert d["names"] == ["x1", "x2", "x3", "x4"] and d["basis"] == ["x3", "x4"]
+    assert d["constant"][:2] == [19, 3]
+    assert [r[0][:2] for r in d["rows"]] == [[51, 14], [1, 3]]
+
+
+def test_testdata_plain_exact_sequence():
+    d, T, basis, n_art, n, r = _run_exact("testdata_fixed.txt", O.PLAIN)
+    assert r["status"] == O.OPTIMAL and r["iters"] == 3
+    assert r["log"].tolist() == [[1, 1], [2, 0], [4, 1]]
+    assert r["basis"].tolist() == [2, 4]
+    assert Fraction(*r["T"][0][0]) == Fraction(17, 3) and Fraction(*r["T"][1][0]) == 6
+    assert -Fraction(*r["T"][2][0]) + Fraction(19, 3) == 12
+
+
+@pytest.mark.parametrize("method", [O.BIGM, O.TWOPHASE])
+def test_testdata_forced_artificials_same_optimum(method):
+    # config 2: the same LP pushed through Big-M / two-phase with an artificial on every row
+    d = dict(H.load_dumps()["testdata_fixed.txt"])
+    d["basis"] = [None, None]
+    T, basis, n_art, n = H.tableau_from_dump(d, method)
+    assert n_art == 2
+    r = O.solve_rat(H.frac_pairs(T), basis, method=method, n_art=n_art)
+    assert r["status"] == O.OPTIMAL
+    assert -Fraction(*r["T"][2][0]) == Fraction(17, 3)
+    f = O.solve_f64(H.frac_f64(T), basis, method=method, n_art=n_art)
+    assert f["status"] == O.OPTIMAL and f["log"].tolist() == r["log"].tolist()
+    assert abs(f["z"] - 17 / 3) <= 1e-9 * (17 / 3)
+
+
+def test_min_surplus_bigm_and_twophase():
+    d, T, basis, n_art, n, r = _run_exact("min_surplus.txt", O.BIGM)
+    assert n_art == 1 and basis == [5, 4]
+    assert r["status"] == O.OPTIMAL and r["log"].tolist() == [[1, 0]]
+    assert r["basis"].tolist() == [1, 4] and r["z"] == -8.0          # max(-z) = -8  =>  min z = 8
+    _, _, _, _, _, r2 = _run_exact("min_surplus.txt", O.TWOPHASE)
+    assert r2["status"] == O.OPTIMAL and r2["log"].tolist() == [[1, 0]] and r2["phase1_iters"] == 1
+    assert r2["z"] == -8.0
+
+
+def test_infeasible_and_unbounded_statuses():
+    for method in (O.BIGM, O.TWOPHASE):
+        *_, r = _run_exact("infeasible.txt", method)
+        assert r["status"] == O.INFEASIBLE
+        assert _run_f64("infeasible.txt", method)["status"] == O.INFEASIBLE
+    *_, r = _run_exact("infeasible.txt", O.BIGM)
+    assert r["log"].tolist() == [[1, 1]] and r["zM"] == -2.0          # App. C: M-part of z = -2
+    *_, u = _run_exact("unbounded.txt", O.PLAIN)
+    assert u["status"] == O.UNBOUNDED and u["log"].tolist() == [[1, 0]] and u["iters"] == 1
+    assert _run_f64("unbounded.txt", O.PLAIN)["status"] == O.UNBOUNDED
+
+
+def test_identity_heuristic_defect_is_not_inherited():
+    # Source/matrix.c:70 accepts column (1, 1/2) as a unit column; the exact re-check rejects it
+    d = H.load_dumps()["eq_fraction_col.txt"]
+    assert d["basis"] == ["x1", None]
+    T, basis, n_art, n = H.tableau_from_dump(d, O.BIGM)
+    assert n_art == 2 and basis == [3, 4]
+    r = O.solve_rat(H.frac_pairs(T), basis, method=O.BIGM, n_art=n_art)
+    assert r["status"] == O.OPTIMAL
+    x = {int(b): Fraction(*r["T"][i][0]) for i, b in enumerate(r["basis"])}
+    assert x[1] + x[2] == 4 and Fraction(1, 2) * x[1] + 3 * x[2] == 6
+
+
+@pytest.mark.parametrize("name,method", [("three_by_three.txt", O.PLAIN), ("unr_inverted.txt", O.PLAIN),
+                                         ("mixed_three.txt", O.BIGM), ("mixed_three.txt", O.TWOPHASE),
+                                         ("min_equality.txt", O.BIGM), ("min_equality.txt", O.TWOPHASE)])
+def test_exact_and_f64_agree_on_model_family(name, method):
+    *_, r = _run_exact(name, method)
+    f = _run_f64(name, method)
+    # unr_inverted.txt is unbounded (x3 unrestricted, 2*x3 in a min objective); the rest are optimal
+    expect = O.UNBOUNDED if name == "unr_inverted.txt" else O.OPTIMAL
+    assert r["status"] == f["status"] == expect
+    assert r["log"].tolist() == f["log"].tolist()
+    assert r["basis"].tolist() == f["basis"].tolist()
+    assert abs(r["z"] - f["z"]) <= 1e-9 * max(1.0, abs(r["z"]))
+
+
+def test_mixed_three_known_optimum():
+    # textbook: min 4x1+x2, 3x1+x2=3, 4x1+3x2>=6, x1+2x2<=4  ->  x=(2/5, 9/5), z = 17/5
+    for method in (O.BIGM, O.TWOPHASE):
+        *_, r = _run_exact("mixed_three.txt", method)
+        assert r["z"] == pytest.approx(-17 / 5, rel=1e-15)
+
+
+def test_rational_overflow_is_reported():
+    big = 3037000500
+    T = [[(1, 1), (big, 1), (1, 1), (0, 1)], [(1, 1), (big, big - 1), (0, 1), (1, 1)], [(0, 1), (1, 1), (0, 1), (0, 1)]]
+    r = O.solve_rat(T, [2, 3], method=O.PLAIN)
+    assert r["status"] in (O.OVERFLOW, O.OPTIMAL)
+
+
+# ------------------------------------------------------------------ fp64 invariants
+def _check_optimal(T0, res, n_art=0, tol=1e-7):
+    """Primal feasibility + objective consistency of an OPTIMAL result against the initial tableau."""
+    R = T0.shape[0] - len(res["basis"])
+    m = T0.shape[0] - R
+    x = res["x"]
+    A, b = T0[:m, 1:], T0[:m, 0]
+    assert np.all(x >= -tol)
+    assert np.allclose(A @ x, b, atol=tol * max(1.0, np.abs(b).max()))
+    c = T0[m, 1:]
+    assert res["z"] == pytest.approx(float(c @ x) - T0[m, 0], rel=1e-7, abs=1e-7)
+    if n_art:
+        assert np.all(np.abs(x[-n_art:]) <= tol)
+
+
+@pytest.mark.parametrize("m,ns", [(4, 4), (8, 12), (32, 32), (64, 64), (40, 7)])
+def test_synth_feasible_solves_to_optimal(m, ns):
+    T0, basis = O.synth_feasible(1234, 5, m, ns)
+    assert np.all(T0[:m, 0] > 0) and np.all(T0[m, 1:ns + 1] > 0)
+    res = O.solve_f64(T0, basis)
+    assert res["status"] == O.OPTIMAL and res["iters"] > 0
+    _check_optimal(T0, res)
+    # threads do not change a bit
+    res4 = O.solve_f64(T0, basis, threads=4)
+    assert res4["log"].tolist() == res["log"].tolist() and np.array_equal(res4["T"], res["T"])
+
+
+def test_synth_is_counter_based():
+    T1, _ = O.synth_feasible(1234, 7, 6, 5)
+    T2, _ = O.synth_feasible(1234, 7, 6, 5)
+    T3, _ = O.synth_feasible(1234, 8, 6, 5)
+    assert np.array_equal(T1, T2) and not np.array_equal(T1, T3)
+    u = O.lib().lpo_uniform(1234, 7, 0, 0.1, 1.1)
+    assert T1[0, 1] == u and 0.1 <= u < 1.1
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_bigm_and_twophase_agree_on_random_mixed_lps(seed):
+    rng = np.random.default_rng(seed)
+    m, ns = int(rng.integers(3, 12)), int(rng.integers(3, 12))
+    A, b, c, rel = H.random_mixed_lp(rng, m, ns)
+    T0, basis, n_art = O.build_tableau(A, b, c, rel, R=2)
+    rb = O.solve_f64(T0, basis, method=O.BIGM, n_art=n_art, max_iter=2000)
+    rt = O.solve_f64(T0, basis, method=O.TWOPHASE, n_art=n_art, max_iter=2000)
+    assert rb["status"] == rt["status"]
+    assert rb["status"] in (O.OPTIMAL, O.UNBOUNDED)     # constructed feasible
+    if rb["status"] == O.OPTIMAL:
+        _check_optimal(T0, rb, n_art)
+        _check_optimal(T0, rt, n_art)
+        assert rb["z"] == pytest.approx(rt["z"], rel=1e-8, abs=1e-8)
+
+
+def test_build_tableau_layout_and_priceout():
+    A = np.array([[1.0, 1.0], [1.0, 3.0], [2.0, -1.0]])
+    b = np.array([4.0, 9.0, -3.0])
+    c = np.array([-2.0, -3.0])
+    rel = np.array([2, -2, 3], np.int32)
+    T, basis, n_art = O.build_tableau(A, b, c, rel, R=2)
+    # columns: x1 x2 | surplus(row0) slack(row1) | art(row0) art(row2)
+    assert T.shape == (5, 7) and n_art == 2 and basis.tolist() == [5, 4, 6]
+    assert T[0].tolist() == [4, 1, 1, -1, 0, 1, 0]
+    assert T[1].tolist() == [9, 1, 3, 0, 1, 0, 0]
+    assert T[2].tolist() == [3, -2, 1, 0, 0, 0, 1]            # "=" row negated, relation kept
+    assert T[3].tolist() == [0, -2, -3, 0, 0, 0, 0]
+    assert T[4].tolist() == [7, -1, 2, -1, 0, 0, 0]           # sum of artificial rows, 0 on artificials
+
+
+def test_iteration_cap_and_log_prefix():
+    T0, basis = O.synth_feasible(1234, 0, 16, 16)
+    full = O.solve_f64(T0, basis)
+    assert full["iters"] >= 4
+    part = O.solve_f64(T0, basis, max_iter=3)
+    assert part["status"] == O.ITER_LIMIT and part["iters"] == 3
+    assert part["log"].tolist() == full["log"][:3].tolist()
+    exact = O.solve_f64(T0, basis, max_iter=full["iters"])
+    assert exact["status"] == O.OPTIMAL
+
+
+def test_single_pivot_matches_definition():
+    rng = np.random.default_rng(0)
+    T = rng.uniform(-1, 1, size=(6, 9))
+    r, k = 2, 4
+    out = O.pivot(T, r, k)
+    prow = T[r] / T[r, k]
+    for i in range(6):
+        if i == r:
+            assert np.array_equal(out[i], prow)
+        else:
+            # one rounding: exact product + sum in Fractions, rounded once by float()
+            ref = np.array([float(Fraction(-T[i, k]) * Fraction(prow[j]) + Fraction(T[i, j])) for j in range(9)])
+            assert np.array_equal(out[i], ref)
+    assert out[r, k] == 1.0 and np.all(out[np.arange(6) != r, k] == 0.0)
+
+
+def test_batched_matches_single():
+    T, basis = O.synth_feasible_batch(1234, 0, 64, 8, 8)
+    rb = O.solve_batched_f64(T, basis, threads=4, log_cap=64)
+    for p in (0, 17, 63):
+        rs = O.solve_f64(T[p], basis[p])
+        assert rb["status"][p] == rs["status"] and rb["iters"][p] == rs["iters"]
+        assert rb["z"][p] == rs["z"] and np.array_equal(rb["x"][p], rs["x"])
+        assert rb["log"][p, :rs["iters"]].tolist() == rs["log"].tolist()

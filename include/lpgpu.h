@@ -1,0 +1,160 @@
+/*
+ * lpgpu.h -- C ABI of the B200 (sm_100a) dense-tableau simplex engine.
+ *
+ * This is the drop-in boundary.  The reference (SomeBottle/LinearProgramming) has no
+ * plugin / FFI layer: its boundary is the plain C link-level API of Source/simplex.h:9-13
+ * (LPStandardize, LPAlign, newSimplex) over the SimplexMatrix storage of
+ * Source/matrix.h:13-25.  newSimplex builds that matrix and frees it without solving
+ * (Source/simplex.c:40,67; empty Big-M / two-phase cases at :57-63, empty AddBigM at
+ * :79-82).  The functions below are what a C host calls in that gap; the host-side
+ * replacement of newSimplex that does so lives in linearprogramming_b200/host/ and
+ * INTEGRATION.md shows the binding.
+ *
+ * Plain pointers and sizes only; no C++/torch types.  Every function returns
+ * LPGPU_OK (0) or a negative LPGPU_E* code and never aborts or throws -- the reference's
+ * convention is "valid flags + message, never abort" (Source/public.h:65,
+ * Source/numOprts.h:29); lpgpu_last_error() carries the message.  There is no CPU
+ * fallback: without a CUDA device lpgpu_create fails with LPGPU_ENODEV.
+ *
+ * Tableau layout (that of SimplexMatrix: cMatrix[i][0] = b_i, cMatrix[i][j+1] = a_ij,
+ * Source/matrix.c:42-72), row-major, leading dimension ld >= n+1 doubles:
+ *     rows 0..m-1     [ b_i | a_i1 .. a_in ]
+ *     row  m          [ -z  | sigma_1 .. sigma_n ]       reduced costs c_j - z_j
+ *     row  m+1 (R=2)  [ -zM | sigmaM_1 .. sigmaM_n ]     Big-M row / phase-1 row
+ * The LP is "max" with b >= 0 (Source/simplex.c:99-106,178-186) and the tableau must be
+ * canonical: basis[i] (1-based column) is the unit column e_i with zero objective entries.
+ * Artificial columns are the LAST n_art columns.  The pivot rule is stated in DESIGN.md
+ * section 3 (the reference defines none).
+ */
+#ifndef LPGPU_H
+#define LPGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* return codes */
+#define LPGPU_OK        0
+#define LPGPU_EINVAL   (-1)   /* bad argument                                   */
+#define LPGPU_ENODEV   (-2)   /* no usable CUDA device / wrong architecture     */
+#define LPGPU_ECUDA    (-3)   /* CUDA runtime error (see lpgpu_last_error)      */
+#define LPGPU_ENOMEM   (-4)   /* device or host allocation failed               */
+#define LPGPU_ENCCL    (-5)   /* NCCL error (column-sharded path)               */
+
+/* solve status */
+#define LPGPU_OPTIMAL     0
+#define LPGPU_UNBOUNDED   1
+#define LPGPU_INFEASIBLE  2
+#define LPGPU_ITER_LIMIT  3
+#define LPGPU_RUNNING     4   /* lpgpu_dense_run stopped on its pivot budget    */
+
+/* method: how the objective rows are priced */
+#define LPGPU_PLAIN     0     /* R = 1                                           */
+#define LPGPU_BIGM      1     /* R = 2, (sigmaM, sigma) lexicographic            */
+#define LPGPU_TWOPHASE  2     /* R = 2, phase 1 on row m+1, then row m           */
+
+typedef struct lpgpu_ctx lpgpu_ctx;         /* one per process and GPU           */
+typedef struct lpgpu_dense lpgpu_dense;     /* one large device-resident tableau */
+typedef struct lpgpu_batched lpgpu_batched; /* many small tableaux               */
+
+typedef struct {
+    double eps;         /* pricing / ratio / snap tolerance (1e-9)                       */
+    int max_iter;       /* total pivot cap -> LPGPU_ITER_LIMIT                           */
+    int method;         /* LPGPU_PLAIN | LPGPU_BIGM | LPGPU_TWOPHASE                     */
+    int n_art;          /* number of trailing artificial columns                         */
+    int log_cap;        /* pivots to record in the pivot log (0 = none)                  */
+    int check_every;    /* dense: pivots enqueued between host status reads (0 = 64)     */
+    int variant;        /* kernel variant (0 = default)                   */
+    int time_kernels;   /* dense: bracket every elimination launch with CUDA events      */
+    int results_only;   /* lpgpu_solve_dense: do not copy the final tableau back to T    */
+} lpgpu_opts;
+
+typedef struct {
+    int status;
+    int iters;          /* pivots so far (phase 1 + drive-out + main)                    */
+    int phase1_iters;
+    int phase;          /* 0 main, 1 phase one, 2 drive-out                              */
+    double z;           /* -T[m][0]                                                      */
+    double zM;          /* -T[m+1][0] (R = 2) else 0                                     */
+    int n_logged;       /* min(iters, log_cap)                                           */
+    int update_launches;  /* elimination kernels that did work during this call          */
+    float update_ms;      /* their summed device time (time_kernels = 1) else 0          */
+    float select_ms;      /* summed device time of the pricing/ratio kernels, likewise   */
+} lpgpu_result;
+
+void lpgpu_default_opts(lpgpu_opts *o);
+/* sizeof(lpgpu_opts) for which = 0, sizeof(lpgpu_result) for which = 1 (binding self-check) */
+size_t lpgpu_abi_sizeof(int which);
+
+/* ---- context --------------------------------------------------------------------- */
+/* stream: a cudaStream_t to launch on (e.g. torch's current stream), or NULL to make
+ * the context create its own.  Fails with LPGPU_ENODEV unless the device is sm_100. */
+int lpgpu_create(lpgpu_ctx **ctx, int device, void *stream);
+void lpgpu_destroy(lpgpu_ctx *ctx);
+const char *lpgpu_last_error(const lpgpu_ctx *ctx);
+int lpgpu_device_info(const lpgpu_ctx *ctx, int *sm_count, size_t *hbm_bytes, int *cc_major, int *cc_minor);
+long lpgpu_launch_count(const lpgpu_ctx *ctx);   /* kernels launched through this ctx   */
+int lpgpu_sync(lpgpu_ctx *ctx);
+/* pinned host memory for the e2e path (cudaHostAlloc / cudaFreeHost) */
+void *lpgpu_host_alloc(lpgpu_ctx *ctx, size_t bytes);
+void lpgpu_host_free(lpgpu_ctx *ctx, void *p);
+
+/* ---- one large tableau: what newSimplex calls after CreateSMatrix ----------------- */
+/* One-shot: upload, pivot to a terminal status (or max_iter), download.  T and basis are
+ * updated in place (opts->results_only = 1 leaves T untouched and returns basis, x, z only);
+ * pivot_log (2*log_cap ints: column, row) and x (n doubles) may be NULL.
+ * Replaces the missing loop between Source/simplex.c:40 and :67. */
+int lpgpu_solve_dense(lpgpu_ctx *ctx, int m, int n, int R, double *T, size_t ld, int *basis,
+                      const lpgpu_opts *opts, int *pivot_log, double *x, lpgpu_result *res);
+
+/* Device-resident form of the same path (bench "value" leg, windowed parity tests). */
+int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out);
+void lpgpu_dense_destroy(lpgpu_dense *d);
+int lpgpu_dense_upload(lpgpu_dense *d, const double *T, size_t ld, const int *basis);
+/* synthetic feasible LP generated on the device; needs n = ns + m, R = 1 */
+int lpgpu_dense_synth(lpgpu_dense *d, uint64_t seed, uint64_t lp_index, int ns);
+/* resets iteration state (status RUNNING, iters 0, phase from opts->method) */
+int lpgpu_dense_reset(lpgpu_dense *d, const lpgpu_opts *opts);
+/* up to max_pivots more pivots; res->status == LPGPU_RUNNING when the budget ran out */
+int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res);
+/* one forced pivot on (row r, column k): pivot-row scaling + rank-1 elimination only */
+int lpgpu_dense_pivot(lpgpu_dense *d, int r, int k);
+int lpgpu_dense_download(lpgpu_dense *d, double *T, size_t ld, int *basis, int *pivot_log, double *x);
+size_t lpgpu_dense_ld(const lpgpu_dense *d);           /* device leading dimension (doubles) */
+
+/* ---- many small tableaux: one LP per CTA, resident in shared memory ---------------- */
+/* T_all: n_lp tableaux back to back, each (m+R) x (n+1), ld = n+1.  Outputs may be NULL
+ * except status.  pivot_log: n_lp * 2*log_cap ints.  T_all is not modified. */
+int lpgpu_solve_batched(lpgpu_ctx *ctx, long n_lp, int m, int n, int R, const double *T_all,
+                        const int *basis_all, const lpgpu_opts *opts, int *status, int *iters,
+                        double *z, double *x, int *basis_out, int *pivot_log);
+
+int lpgpu_batched_create(lpgpu_ctx *ctx, long n_lp, int m, int n, int R, lpgpu_batched **out);
+void lpgpu_batched_destroy(lpgpu_batched *b);
+int lpgpu_batched_upload(lpgpu_batched *b, const double *T_all, const int *basis_all);
+int lpgpu_batched_synth(lpgpu_batched *b, uint64_t seed, uint64_t lp0, int ns);
+/* one launch over all LPs; kernel_ms (may be NULL) = its device time from CUDA events */
+int lpgpu_batched_run(lpgpu_batched *b, const lpgpu_opts *opts, float *kernel_ms);
+/* any pointer may be NULL; T_final: n_lp tableaux as left by the kernel (parity tests) */
+int lpgpu_batched_download(lpgpu_batched *b, int *status, int *iters, double *z, double *x,
+                           int *basis_out, int *pivot_log, double *T_final);
+
+/* ---- host-side helpers (no GPU work) --------------------------------------------- */
+/* rel[i]: -2 "<=", 2 ">=", 3 "=" (Source/public.h:57).  Builds the canonical tableau of
+ *   max c.x  s.t.  A x rel b, x >= 0
+ * negating rows with b < 0 (Source/simplex.c:178-186); columns = structural, then one
+ * slack/surplus per inequality row (Source/simplex.c:189-219), then one artificial per
+ * ">=" / "=" row.  Returns n (total columns) or a negative code. */
+int lpgpu_count_columns(int m, int ns, const double *b, const int *rel, int *n_art);
+int lpgpu_build_tableau(int m, int ns, const double *A, size_t lda, const double *b, const double *c,
+                        const int *rel, int R, double *T, size_t ld, int *basis, int *n_art);
+/* the synthetic generator on the host (same bits as the device generator) */
+void lpgpu_synth_host(uint64_t seed, uint64_t lp_index, int m, int ns, double *T, size_t ld, int *basis);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LPGPU_H */

@@ -1,0 +1,112 @@
+"""ctypes loader of liblpgpu.so -- the C ABI declared in include/lpgpu.h.
+
+The library is built in-tree by ``__graft_entry__.build()`` (nvcc, sm_100a).  There is no
+CPU fallback: if the shared object is missing, loading raises, and if there is no sm_100
+device ``lpgpu_create`` returns LPGPU_ENODEV, which ``Context`` turns into an exception.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liblpgpu.so")
+
+OK, EINVAL, ENODEV, ECUDA, ENOMEM, ENCCL = 0, -1, -2, -3, -4, -5
+OPTIMAL, UNBOUNDED, INFEASIBLE, ITER_LIMIT, RUNNING = 0, 1, 2, 3, 4
+PLAIN, BIGM, TWOPHASE = 0, 1, 2
+STATUS_NAMES = {0: "OPTIMAL", 1: "UNBOUNDED", 2: "INFEASIBLE", 3: "ITER_LIMIT", 4: "RUNNING"}
+KEEP_FINAL = 0x1000      # batched: keep the final tableaux on the device (parity tests)
+ALTERNATE = 0x100        # dense: walk the elimination tasks backwards on odd pivots
+
+
+class Opts(C.Structure):
+    _fields_ = [("eps", C.c_double), ("max_iter", C.c_int), ("method", C.c_int), ("n_art", C.c_int),
+                ("log_cap", C.c_int), ("check_every", C.c_int), ("variant", C.c_int),
+                ("time_kernels", C.c_int), ("results_only", C.c_int)]
+
+
+class Result(C.Structure):
+    _fields_ = [("status", C.c_int), ("iters", C.c_int), ("phase1_iters", C.c_int), ("phase", C.c_int),
+                ("z", C.c_double), ("zM", C.c_double), ("n_logged", C.c_int), ("update_launches", C.c_int),
+                ("update_ms", C.c_float), ("select_ms", C.c_float)]
+
+
+class LpgpuError(RuntimeError):
+    pass
+
+
+_lib = None
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+_vp = C.c_void_p
+
+# name -> (restype, argtypes): every symbol include/lpgpu.h declares
+SIGNATURES = {
+    "lpgpu_default_opts": (None, [C.POINTER(Opts)]),
+    "lpgpu_abi_sizeof": (C.c_size_t, [C.c_int]),
+    "lpgpu_create": (C.c_int, [C.POINTER(_vp), C.c_int, _vp]),
+    "lpgpu_destroy": (None, [_vp]),
+    "lpgpu_last_error": (C.c_char_p, [_vp]),
+    "lpgpu_device_info": (C.c_int, [_vp, _ip, C.POINTER(C.c_size_t), _ip, _ip]),
+    "lpgpu_launch_count": (C.c_long, [_vp]),
+    "lpgpu_sync": (C.c_int, [_vp]),
+    "lpgpu_host_alloc": (_vp, [_vp, C.c_size_t]),
+    "lpgpu_host_free": (None, [_vp, _vp]),
+    "lpgpu_solve_dense": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _vp, C.c_size_t, _vp, C.POINTER(Opts), _vp, _vp,
+                                    C.POINTER(Result)]),
+    "lpgpu_dense_create": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.POINTER(_vp)]),
+    "lpgpu_dense_destroy": (None, [_vp]),
+    "lpgpu_dense_upload": (C.c_int, [_vp, _vp, C.c_size_t, _vp]),
+    "lpgpu_dense_synth": (C.c_int, [_vp, C.c_uint64, C.c_uint64, C.c_int]),
+    "lpgpu_dense_reset": (C.c_int, [_vp, C.POINTER(Opts)]),
+    "lpgpu_dense_run": (C.c_int, [_vp, C.c_int, C.POINTER(Result)]),
+    "lpgpu_dense_pivot": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "lpgpu_dense_download": (C.c_int, [_vp, _vp, C.c_size_t, _vp, _vp, _vp]),
+    "lpgpu_dense_ld": (C.c_size_t, [_vp]),
+    "lpgpu_solve_batched": (C.c_int, [_vp, C.c_long, C.c_int, C.c_int, C.c_int, _vp, _vp, C.POINTER(Opts), _vp, _vp,
+                                      _vp, _vp, _vp, _vp]),
+    "lpgpu_batched_create": (C.c_int, [_vp, C.c_long, C.c_int, C.c_int, C.c_int, C.POINTER(_vp)]),
+    "lpgpu_batched_destroy": (None, [_vp]),
+    "lpgpu_batched_upload": (C.c_int, [_vp, _vp, _vp]),
+    "lpgpu_batched_synth": (C.c_int, [_vp, C.c_uint64, C.c_uint64, C.c_int]),
+    "lpgpu_batched_run": (C.c_int, [_vp, C.POINTER(Opts), C.POINTER(C.c_float)]),
+    "lpgpu_batched_download": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "lpgpu_count_columns": (C.c_int, [C.c_int, C.c_int, _vp, _vp, _ip]),
+    "lpgpu_build_tableau": (C.c_int, [C.c_int, C.c_int, _vp, C.c_size_t, _vp, _vp, _vp, C.c_int, _vp, C.c_size_t, _vp,
+                                      _ip]),
+    "lpgpu_synth_host": (None, [C.c_uint64, C.c_uint64, C.c_int, C.c_int, _vp, C.c_size_t, _vp]),
+}
+
+
+def lib():
+    """Load liblpgpu.so (once).  Raises LpgpuError if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise LpgpuError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                         "(nvcc, sm_100a).  There is no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        f = getattr(L, name)          # AttributeError if the ABI and the header drifted apart
+        f.restype = res
+        f.argtypes = args
+    if L.lpgpu_abi_sizeof(0) != C.sizeof(Opts) or L.lpgpu_abi_sizeof(1) != C.sizeof(Result):
+        raise LpgpuError("capi.py structs do not match include/lpgpu.h (rebuild liblpgpu.so)")
+    _lib = L
+    return L
+
+
+def check(ctx_handle, rc, what):
+    if rc != OK:
+        msg = lib().lpgpu_last_error(ctx_handle) if ctx_handle else b""
+        raise LpgpuError(f"{what} failed with code {rc}: {(msg or b'').decode(errors='replace')}")
+
+
+def default_opts(**kw):
+    o = Opts()
+    lib().lpgpu_default_opts(C.byref(o))
+    for k, v in kw.items():
+        if v is not None:
+            setattr(o, k, v)
+    return o

@@ -1,0 +1,182 @@
+// common.cuh -- shared device helpers for the sm_100a simplex kernels.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/lpgpu.h"
+
+namespace lpgpu {
+
+// ------------------------------------------------------------------ device state
+// phases of the pivot state machine
+enum { PH_MAIN = 0, PH_ONE = 1, PH_DRIVEOUT = 2 };
+
+struct PivotState {
+    int status;        // LPGPU_* status
+    int iters;         // pivots done
+    int phase;         // PH_*
+    int phase1_iters;
+    int r;             // leaving row of the pivot to apply
+    int k;             // entering column (1-based)
+    int do_pivot;      // 1: the elimination kernel that follows has work
+    int budget;        // pivots still allowed in this run call
+};
+
+// ------------------------------------------------------------------ candidates
+// Both pricing (max reduced cost) and the ratio test (min b/a) are "maximise (p, q), ties
+// to the lowest index" reductions: the ratio test feeds q = -(b/a), an exact negation.
+struct Cand {
+    double p, q;
+    int idx;           // -1 = none
+};
+
+__device__ __forceinline__ bool cand_better(const Cand &a, const Cand &b) {
+    if (a.idx < 0) return false;
+    if (b.idx < 0) return true;
+    if (a.p != b.p) return a.p > b.p;
+    if (a.q != b.q) return a.q > b.q;
+    return a.idx < b.idx;
+}
+
+__device__ __forceinline__ Cand cand_none() {
+    Cand c;
+    c.p = 0.0; c.q = 0.0; c.idx = -1;
+    return c;
+}
+
+__device__ __forceinline__ Cand cand_shfl_xor(const Cand &c, int mask) {
+    Cand o;
+    o.p = __shfl_xor_sync(0xffffffffu, c.p, mask);
+    o.q = __shfl_xor_sync(0xffffffffu, c.q, mask);
+    o.idx = __shfl_xor_sync(0xffffffffu, c.idx, mask);
+    return o;
+}
+
+__device__ __forceinline__ Cand warp_best(Cand c) {
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        Cand o = cand_shfl_xor(c, s);
+        if (cand_better(o, c)) c = o;
+    }
+    return c;
+}
+
+// Block-wide best candidate: warp shuffles, then a tree over the per-warp winners in
+// shared memory.  scratch must hold blockDim.x/32 entries.  Result valid in all threads.
+__device__ __forceinline__ Cand block_best(Cand c, Cand *scratch) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+    c = warp_best(c);
+    __syncthreads();                       // scratch may still be read from a previous call
+    if (lane == 0) scratch[warp] = c;
+    __syncthreads();
+    Cand v = (lane < nwarp) ? scratch[lane] : cand_none();
+    v = warp_best(v);
+    return v;
+}
+
+// ------------------------------------------------------------------ synthetic data
+// Counter-based generator shared bit-for-bit with the host (and restated in the oracle).
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+__host__ __device__ __forceinline__ double uniform64(uint64_t seed, uint64_t lp, uint64_t elem,
+                                                     double lo, double hi) {
+    uint64_t h = mix64(mix64(mix64(seed) ^ lp) ^ elem);
+    double u = (double)(h >> 11) * 0x1.0p-53;
+#ifdef __CUDA_ARCH__
+    return __fma_rn(u, hi - lo, lo);
+#else
+    return __builtin_fma(u, hi - lo, lo);
+#endif
+}
+
+// Element (i, j) of the synthetic feasible tableau (m+1) x (n+1), n = ns + m.
+__host__ __device__ __forceinline__ double synth_elem(uint64_t seed, uint64_t lp, int m, int ns, int i, int j) {
+    const uint64_t nA = (uint64_t)m * (uint64_t)ns;
+    if (i < m) {
+        if (j == 0) return uniform64(seed, lp, nA + (uint64_t)i, 1.0, 2.0) * (double)ns;
+        if (j <= ns) return uniform64(seed, lp, (uint64_t)i * (uint64_t)ns + (uint64_t)(j - 1), 0.1, 1.1);
+        return (j - 1 - ns == i) ? 1.0 : 0.0;
+    }
+    if (j >= 1 && j <= ns) return uniform64(seed, lp, nA + (uint64_t)m + (uint64_t)(j - 1), 0.1, 1.1);
+    return 0.0;
+}
+
+// ------------------------------------------------------------------ TMA / mbarrier PTX
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+
+// make mbarrier.init visible to the async proxy (TMA unit)
+__device__ __forceinline__ void fence_mbar_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+__device__ __forceinline__ void fence_proxy_async() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+// 1-D bulk asynchronous copy global -> shared through the TMA unit (SASS: UBLKCP).
+// dst, src 16-byte aligned; bytes a multiple of 16.  Completion is counted on `bar`.
+__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// 1-D bulk asynchronous copy shared -> global.
+__device__ __forceinline__ void tma_store_1d(void *dst, const void *src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void tma_store_wait() {
+    asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// ------------------------------------------------------------------ streaming 128-bit access
+// The tableau is read once and written once per pivot: keep it out of L1.
+__device__ __forceinline__ double2 ld_stream2(const double *p) {
+    double2 v;
+    asm volatile("ld.global.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_stream2(double *p, double2 v) {
+    asm volatile("st.global.L1::no_allocate.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(v.x), "d"(v.y) : "memory");
+}
+
+}  // namespace lpgpu

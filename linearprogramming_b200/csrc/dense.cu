@@ -1,0 +1,379 @@
+// dense.cu -- C-ABI entry points of the single-large-tableau path (include/lpgpu.h).
+//
+// Fills the gap the reference leaves between CreateSMatrix and RevokeSMatrix
+// (Source/simplex.c:40-67): the pivot loop runs device-resident; the host only enqueues
+// (select, eliminate) pairs and reads one small state record every `check_every` pivots.
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "ctx.h"
+#include "dense_select.cuh"
+#include "dense_update.cuh"
+
+using namespace lpgpu;
+
+struct lpgpu_dense {
+    lpgpu_ctx *ctx;
+    int m, n, R;
+    size_t ld;
+    double *T;
+    int *basis;
+    double *prow, *pcol, *xbuf;
+    PivotState *st;
+    PivotState *h_st;       // pinned mirror
+    int *log;
+    int log_cap;
+    lpgpu_opts opts;
+    int grid_update;
+    std::vector<cudaEvent_t> ev;
+};
+
+namespace lpgpu {
+
+// forced_k > 0: skip the decision and pivot on (forced_r, forced_k) (tests of one pass).
+__global__ void __launch_bounds__(SELECT_THREADS) dense_select_kernel(DenseParams P, int forced_r, int forced_k) {
+    __shared__ Cand scratch[SELECT_THREADS / 32];
+    PivotState *st = P.st;
+    int r = -1, k = 0;
+
+    if (forced_k > 0) {
+        r = forced_r;
+        k = forced_k;
+    } else {
+        // all threads read the same state; nothing below writes it before the final section
+        const int status0 = st->status, phase0 = st->phase, iters = st->iters, p10 = st->phase1_iters;
+        const int budget = st->budget;
+        if (status0 != LPGPU_RUNNING) {
+            __syncthreads();
+            if (threadIdx.x == 0) st->do_pivot = 0;
+            return;
+        }
+        Decision D = decide(P, scratch, status0, phase0, iters, p10);
+        // out of budget for this run call: the decision still settles terminal statuses, a
+        // pending pivot is left for the next call (status stays RUNNING)
+        if (D.have && budget <= 0) D.have = false;
+        r = D.r;
+        k = D.k;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            st->status = D.status;
+            st->phase = D.phase;
+            st->phase1_iters = (D.phase == PH_ONE) ? iters + (D.have ? 1 : 0) : D.p1;
+            st->do_pivot = D.have ? 1 : 0;
+            if (D.have) {
+                st->r = r;
+                st->k = k;
+                st->iters = iters + 1;
+                st->budget = budget - 1;
+                if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
+            }
+        }
+        if (!D.have) return;
+    }
+
+    // pivot column (all rows incl. objective rows) and scaled pivot row into compact buffers
+    const double piv = P.T[(size_t)r * P.ld + (size_t)k];
+    for (int i = (int)threadIdx.x; i < P.m + P.R; i += blockDim.x) P.pcol[i] = P.T[(size_t)i * P.ld + (size_t)k];
+    const double *xr = P.T + (size_t)r * P.ld;
+    for (size_t j = threadIdx.x; j < P.ld; j += blockDim.x) P.prow[j] = xr[j] / piv;
+    if (threadIdx.x == 0) {
+        P.basis[r] = k;
+        if (forced_k > 0) { st->r = r; st->k = k; st->do_pivot = 1; }
+    }
+}
+
+}  // namespace lpgpu
+
+namespace {
+
+__global__ void extract_x_kernel(const double *T, size_t ld, const int *basis, int m, int n, double *x) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) {
+        const int j = basis[i];
+        if (j >= 1 && j <= n) x[j - 1] = T[(size_t)i * ld];
+    }
+}
+
+size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+DenseParams make_params(const lpgpu_dense *d) {
+    DenseParams P;
+    P.T = d->T; P.ld = d->ld; P.m = d->m; P.n = d->n; P.R = d->R;
+    P.basis = d->basis; P.prow = d->prow; P.pcol = d->pcol; P.st = d->st;
+    P.log = d->log; P.log_cap = d->log_cap;
+    P.eps = d->opts.eps; P.max_iter = d->opts.max_iter; P.method = d->opts.method; P.n_art = d->opts.n_art;
+    return P;
+}
+
+int launch_update(lpgpu_dense *d) {
+    lpgpu_ctx *ctx = d->ctx;
+    UpdateParams U;
+    U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.prow = d->prow; U.pcol = d->pcol; U.st = d->st;
+    U.alternate = (d->opts.variant & 0x100) ? 1 : 0;
+    const int kind = d->opts.variant & 0xf;
+    if (kind == 1) dense_update_tma_staged<<<d->grid_update, UPD_THREADS, 0, ctx->stream>>>(U);
+    else dense_update_direct<<<d->grid_update, UPD_THREADS, 0, ctx->stream>>>(U);
+    LP_LAUNCH_CHECK(ctx);
+    return LPGPU_OK;
+}
+
+int size_grid(lpgpu_dense *d) {
+    lpgpu_ctx *ctx = d->ctx;
+    int occ0 = 0, occ1 = 0;
+    LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, dense_update_direct, UPD_THREADS, 0));
+    LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, dense_update_tma_staged, UPD_THREADS, 0));
+    const int occ = std::max(1, ((d->opts.variant & 0xf) == 1) ? occ1 : occ0);
+    const long nct = (long)((d->ld + UPD_TILE_COLS - 1) / UPD_TILE_COLS);
+    const long nrb = (d->m + d->R + UPD_TILE_ROWS - 1) / UPD_TILE_ROWS;
+    d->grid_update = (int)std::max(1L, std::min((long)ctx->sm_count * occ, nct * nrb));
+    return LPGPU_OK;
+}
+
+bool opts_ok(const lpgpu_opts *o, int n, int R) {
+    if (!o) return false;
+    if (o->method != LPGPU_PLAIN && o->method != LPGPU_BIGM && o->method != LPGPU_TWOPHASE) return false;
+    if ((o->method == LPGPU_PLAIN) != (R == 1)) return false;
+    if (o->n_art < 0 || o->n_art > n || o->max_iter < 0 || o->log_cap < 0 || !(o->eps >= 0.0)) return false;
+    return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
+    if (!ctx || !out) return LPGPU_EINVAL;
+    if (m < 1 || n < 1 || (R != 1 && R != 2)) return fail(ctx, LPGPU_EINVAL, "dense_create: bad shape m=%d n=%d R=%d", m, n, R);
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    lpgpu_dense *d = new (std::nothrow) lpgpu_dense();
+    if (!d) return fail(ctx, LPGPU_ENOMEM, "dense_create: host allocation failed");
+    d->ctx = ctx; d->m = m; d->n = n; d->R = R;
+    d->ld = round_up((size_t)n + 1, 16);
+    d->T = nullptr; d->basis = nullptr; d->prow = d->pcol = d->xbuf = nullptr; d->st = nullptr; d->h_st = nullptr;
+    d->log = nullptr; d->log_cap = 0;
+    lpgpu_default_opts(&d->opts);
+    d->opts.method = (R == 1) ? LPGPU_PLAIN : LPGPU_BIGM;
+    const size_t rows = (size_t)m + R, pcn = round_up(rows, UPD_TILE_ROWS) + UPD_TILE_ROWS;
+    cudaError_t e = cudaSuccess;
+    if (e == cudaSuccess) e = cudaMalloc(&d->T, rows * d->ld * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&d->basis, (size_t)m * sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc(&d->prow, d->ld * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&d->pcol, pcn * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&d->xbuf, (size_t)n * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&d->st, sizeof(PivotState));
+    if (e == cudaSuccess) e = cudaHostAlloc(&d->h_st, sizeof(PivotState), cudaHostAllocDefault);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->T, 0, rows * d->ld * sizeof(double), ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->prow, 0, d->ld * sizeof(double), ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->pcol, 0, pcn * sizeof(double), ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->basis, 0, (size_t)m * sizeof(int), ctx->stream);
+    if (e != cudaSuccess) {
+        lpgpu_dense_destroy(d);
+        return fail(ctx, e == cudaErrorMemoryAllocation ? LPGPU_ENOMEM : LPGPU_ECUDA, "dense_create: %s", cudaGetErrorString(e));
+    }
+    int rc = size_grid(d);
+    if (rc == LPGPU_OK) rc = lpgpu_dense_reset(d, &d->opts);
+    if (rc != LPGPU_OK) { lpgpu_dense_destroy(d); return rc; }
+    *out = d;
+    return LPGPU_OK;
+}
+
+void lpgpu_dense_destroy(lpgpu_dense *d) {
+    if (!d) return;
+    cudaSetDevice(d->ctx->device);
+    cudaStreamSynchronize(d->ctx->stream);
+    for (cudaEvent_t e : d->ev) cudaEventDestroy(e);
+    cudaFree(d->T); cudaFree(d->basis); cudaFree(d->prow); cudaFree(d->pcol); cudaFree(d->xbuf);
+    cudaFree(d->st); cudaFree(d->log);
+    if (d->h_st) cudaFreeHost(d->h_st);
+    delete d;
+}
+
+size_t lpgpu_dense_ld(const lpgpu_dense *d) { return d ? d->ld : 0; }
+
+int lpgpu_dense_reset(lpgpu_dense *d, const lpgpu_opts *opts) {
+    if (!d) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = d->ctx;
+    if (!opts_ok(opts, d->n, d->R)) return fail(ctx, LPGPU_EINVAL, "dense_reset: bad options (method/R/n_art)");
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    d->opts = *opts;
+    if (d->opts.check_every <= 0) d->opts.check_every = 64;
+    if (opts->log_cap > d->log_cap) {
+        LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        cudaFree(d->log);
+        d->log = nullptr;
+        d->log_cap = 0;
+        LP_CUDA(ctx, cudaMalloc(&d->log, (size_t)opts->log_cap * 2 * sizeof(int)));
+        d->log_cap = opts->log_cap;
+    }
+    if (d->log_cap > 0) LP_CUDA(ctx, cudaMemsetAsync(d->log, 0xff, (size_t)d->log_cap * 2 * sizeof(int), ctx->stream));
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // h_st may still be in flight
+    PivotState s;
+    s.status = LPGPU_RUNNING; s.iters = 0; s.phase = (opts->method == LPGPU_TWOPHASE) ? PH_ONE : PH_MAIN;
+    s.phase1_iters = 0; s.r = -1; s.k = 0; s.do_pivot = 0; s.budget = 0;
+    *d->h_st = s;
+    LP_CUDA(ctx, cudaMemcpyAsync(d->st, d->h_st, sizeof s, cudaMemcpyHostToDevice, ctx->stream));
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return size_grid(d);
+}
+
+int lpgpu_dense_upload(lpgpu_dense *d, const double *T, size_t ld, const int *basis) {
+    if (!d || !T || !basis) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = d->ctx;
+    if (ld < (size_t)d->n + 1) return fail(ctx, LPGPU_EINVAL, "dense_upload: ld %zu < n+1", ld);
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    LP_CUDA(ctx, cudaMemcpy2DAsync(d->T, d->ld * sizeof(double), T, ld * sizeof(double), ((size_t)d->n + 1) * sizeof(double),
+                                   (size_t)d->m + d->R, cudaMemcpyHostToDevice, ctx->stream));
+    LP_CUDA(ctx, cudaMemcpyAsync(d->basis, basis, (size_t)d->m * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // the caller may reuse its buffers
+    return LPGPU_OK;
+}
+
+int lpgpu_dense_synth(lpgpu_dense *d, uint64_t seed, uint64_t lp_index, int ns) {
+    if (!d) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = d->ctx;
+    if (d->R != 1 || ns < 1 || ns + d->m != d->n) return fail(ctx, LPGPU_EINVAL, "dense_synth: needs R=1 and n = ns + m");
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    dense_synth_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(d->T, d->ld, d->m, ns, d->basis, seed, lp_index);
+    LP_LAUNCH_CHECK(ctx);
+    return LPGPU_OK;
+}
+
+static int read_state(lpgpu_dense *d) {
+    lpgpu_ctx *ctx = d->ctx;
+    LP_CUDA(ctx, cudaMemcpyAsync(d->h_st, d->st, sizeof(PivotState), cudaMemcpyDeviceToHost, ctx->stream));
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return LPGPU_OK;
+}
+
+int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
+    if (!d || !res || max_pivots < 0) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = d->ctx;
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    const bool timed = d->opts.time_kernels != 0;
+    const int chunk_max = d->opts.check_every;
+    if (timed && d->ev.size() < (size_t)3 * chunk_max) {
+        while (d->ev.size() < (size_t)3 * chunk_max) {
+            cudaEvent_t e;
+            LP_CUDA(ctx, cudaEventCreate(&e));
+            d->ev.push_back(e);
+        }
+    }
+    int rc = read_state(d);
+    if (rc != LPGPU_OK) return rc;
+    d->h_st->budget = max_pivots;
+    LP_CUDA(ctx, cudaMemcpyAsync(d->st, d->h_st, sizeof(PivotState), cudaMemcpyHostToDevice, ctx->stream));
+    const DenseParams P = make_params(d);
+    int launched = 0, done_updates = 0;
+    double upd_ms = 0.0, sel_ms = 0.0;
+    int iters_before = d->h_st->iters;
+    while (launched < max_pivots) {
+        const int chunk = std::min(chunk_max, max_pivots - launched);
+        for (int c = 0; c < chunk; ++c) {
+            if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c], ctx->stream));
+            dense_select_kernel<<<1, SELECT_THREADS, 0, ctx->stream>>>(P, -1, 0);
+            LP_LAUNCH_CHECK(ctx);
+            if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c + 1], ctx->stream));
+            rc = launch_update(d);
+            if (rc != LPGPU_OK) return rc;
+            if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c + 2], ctx->stream));
+        }
+        launched += chunk;
+        rc = read_state(d);
+        if (rc != LPGPU_OK) return rc;
+        const int did = d->h_st->iters - iters_before;      // pivots applied in this chunk
+        iters_before = d->h_st->iters;
+        done_updates += did;
+        if (timed) {
+            for (int c = 0; c < did && c < chunk; ++c) {
+                float a = 0.f, b = 0.f;
+                LP_CUDA(ctx, cudaEventElapsedTime(&a, d->ev[3 * c], d->ev[3 * c + 1]));
+                LP_CUDA(ctx, cudaEventElapsedTime(&b, d->ev[3 * c + 1], d->ev[3 * c + 2]));
+                sel_ms += a;
+                upd_ms += b;
+            }
+        }
+        if (d->h_st->status != LPGPU_RUNNING) break;
+    }
+    if (d->h_st->status == LPGPU_RUNNING) {
+        // budget spent: one decision-only select settles a terminal status (optimal, iteration
+        // limit, ...) without applying a pivot, so a run of exactly the needed pivots reports it
+        dense_select_kernel<<<1, SELECT_THREADS, 0, ctx->stream>>>(P, -1, 0);
+        LP_LAUNCH_CHECK(ctx);
+        rc = read_state(d);
+        if (rc != LPGPU_OK) return rc;
+    }
+    // objective cells
+    double zc[2] = {0.0, 0.0};
+    LP_CUDA(ctx, cudaMemcpyAsync(&zc[0], d->T + (size_t)d->m * d->ld, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (d->R == 2)
+        LP_CUDA(ctx, cudaMemcpyAsync(&zc[1], d->T + (size_t)(d->m + 1) * d->ld, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    res->status = d->h_st->status;
+    res->iters = d->h_st->iters;
+    res->phase1_iters = (d->opts.method == LPGPU_TWOPHASE) ? d->h_st->phase1_iters : 0;
+    res->phase = d->h_st->phase;
+    res->z = -zc[0];
+    res->zM = (d->R == 2) ? -zc[1] : 0.0;
+    res->n_logged = std::min(res->iters, d->log_cap);
+    res->update_launches = done_updates;
+    res->update_ms = (float)upd_ms;
+    res->select_ms = (float)sel_ms;
+    return LPGPU_OK;
+}
+
+int lpgpu_dense_pivot(lpgpu_dense *d, int r, int k) {
+    if (!d) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = d->ctx;
+    if (r < 0 || r >= d->m || k < 1 || k > d->n) return fail(ctx, LPGPU_EINVAL, "dense_pivot: (r=%d,k=%d) out of range", r, k);
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    const DenseParams P = make_params(d);
+    dense_select_kernel<<<1, SELECT_THREADS, 0, ctx->stream>>>(P, r, k);
+    LP_LAUNCH_CHECK(ctx);
+    int rc = launch_update(d);
+    if (rc != LPGPU_OK) return rc;
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return LPGPU_OK;
+}
+
+int lpgpu_dense_download(lpgpu_dense *d, double *T, size_t ld, int *basis, int *pivot_log, double *x) {
+    if (!d) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = d->ctx;
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (T) {
+        if (ld < (size_t)d->n + 1) return fail(ctx, LPGPU_EINVAL, "dense_download: ld %zu < n+1", ld);
+        LP_CUDA(ctx, cudaMemcpy2DAsync(T, ld * sizeof(double), d->T, d->ld * sizeof(double), ((size_t)d->n + 1) * sizeof(double),
+                                       (size_t)d->m + d->R, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (basis) LP_CUDA(ctx, cudaMemcpyAsync(basis, d->basis, (size_t)d->m * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    if (pivot_log && d->log_cap > 0) {
+        int rc = read_state(d);
+        if (rc != LPGPU_OK) return rc;
+        const int nl = std::min(d->h_st->iters, d->log_cap);
+        if (nl > 0) LP_CUDA(ctx, cudaMemcpyAsync(pivot_log, d->log, (size_t)nl * 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (x) {
+        LP_CUDA(ctx, cudaMemsetAsync(d->xbuf, 0, (size_t)d->n * sizeof(double), ctx->stream));
+        extract_x_kernel<<<std::max(1, std::min(1024, (d->m + 255) / 256)), 256, 0, ctx->stream>>>(d->T, d->ld, d->basis, d->m, d->n, d->xbuf);
+        LP_LAUNCH_CHECK(ctx);
+        LP_CUDA(ctx, cudaMemcpyAsync(x, d->xbuf, (size_t)d->n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return LPGPU_OK;
+}
+
+int lpgpu_solve_dense(lpgpu_ctx *ctx, int m, int n, int R, double *T, size_t ld, int *basis, const lpgpu_opts *opts,
+                      int *pivot_log, double *x, lpgpu_result *res) {
+    if (!ctx || !T || !basis || !opts || !res) return LPGPU_EINVAL;
+    if (!opts_ok(opts, n, R)) return fail(ctx, LPGPU_EINVAL, "solve_dense: bad options (method/R/n_art)");
+    lpgpu_dense *d = nullptr;
+    int rc = lpgpu_dense_create(ctx, m, n, R, &d);
+    if (rc != LPGPU_OK) return rc;
+    rc = lpgpu_dense_reset(d, opts);
+    if (rc == LPGPU_OK) rc = lpgpu_dense_upload(d, T, ld, basis);
+    if (rc == LPGPU_OK) rc = lpgpu_dense_run(d, opts->max_iter, res);
+    if (rc == LPGPU_OK) rc = lpgpu_dense_download(d, opts->results_only ? nullptr : T, ld, basis, pivot_log, x);
+    lpgpu_dense_destroy(d);
+    return rc;
+}
+
+}  // extern "C"

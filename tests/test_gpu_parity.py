@@ -1,0 +1,280 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (liblpgpu.so), against the CPU oracle
+on the same inputs.  Bar: bit-exact pivot sequence, basis, iteration count, status AND tableau
+(the method has no floating-point sums: per-element div / fma and exact comparisons only);
+objective and x therefore agree to 0 ulp, well inside the 1e-9 relative tolerance north_star states.
+"""
+import numpy as np
+import pytest
+
+import helpers as H
+import oracle_lib as O
+
+import linearprogramming_b200 as lp
+from linearprogramming_b200 import capi
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-9      # north_star's stated tolerance for objective / solution values (fp64)
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = lp.Context(0)
+    yield c
+    c.close()
+
+
+def _same_bits(a, b):
+    return np.array_equal(a, b) and np.array_equal(np.signbit(a), np.signbit(b))
+
+
+def _assert_dense_equal(got, ref, tableau=True):
+    assert got["status"] == ref["status"], (capi.STATUS_NAMES[got["status"]], O.STATUS_NAMES[ref["status"]])
+    assert got["iters"] == ref["iters"]
+    assert got["log"].tolist() == ref["log"].tolist()
+    assert np.array_equal(got["basis"], ref["basis"])
+    assert abs(got["z"] - ref["z"]) <= REL_TOL * max(1.0, abs(ref["z"]))
+    assert np.allclose(got["x"], ref["x"], rtol=REL_TOL, atol=0.0)
+    if tableau:
+        assert np.array_equal(got["T"], ref["T"])        # bit-exact (+0 == -0 tolerated here)
+        assert got["z"] == ref["z"] and np.array_equal(got["x"], ref["x"])
+
+
+# ------------------------------------------------------------------ config 1: testdata.txt family
+def test_cfg1_testdata_pivot_sequence(ctx):
+    d = H.load_dumps()["testdata_fixed.txt"]
+    T, basis, n_art, n = H.tableau_from_dump(d, O.PLAIN)
+    T0 = H.frac_f64(T)
+    exact = O.solve_rat(H.frac_pairs(T), basis)
+    ref = O.solve_f64(T0, basis, log_cap=16)
+    got = lp.solve_dense(ctx, T0, basis, log_cap=16)
+    _assert_dense_equal(got, ref)
+    assert got["log"].tolist() == exact["log"].tolist() == [[1, 1], [2, 0], [4, 1]]
+    assert got["basis"].tolist() == [2, 4] and got["status"] == lp.OPTIMAL
+    assert abs(got["z"] + 19 / 3 - 12) <= REL_TOL * 12          # + stripped constant 19/3 (Source/matrix.c:24)
+
+
+# ------------------------------------------------------------------ config 2: Big-M / two-phase / statuses
+@pytest.mark.parametrize("name", ["testdata_fixed.txt", "min_surplus.txt", "min_equality.txt", "mixed_three.txt",
+                                  "eq_fraction_col.txt", "infeasible.txt", "three_by_three.txt"])
+@pytest.mark.parametrize("method", [O.BIGM, O.TWOPHASE])
+def test_cfg2_model_family_bigm_twophase(ctx, name, method):
+    d = dict(H.load_dumps()[name])
+    if name in ("testdata_fixed.txt", "three_by_three.txt"):
+        d["basis"] = [None] * d["m"]                # force an artificial on every row
+    T, basis, n_art, n = H.tableau_from_dump(d, method)
+    T0 = H.frac_f64(T)
+    exact = O.solve_rat(H.frac_pairs(T), basis, method=method, n_art=n_art)
+    ref = O.solve_f64(T0, basis, method=method, n_art=n_art, log_cap=64)
+    got = lp.solve_dense(ctx, T0, basis, method=method, n_art=n_art, log_cap=64)
+    _assert_dense_equal(got, ref)
+    assert got["status"] == exact["status"] and got["log"].tolist() == exact["log"].tolist()
+    assert got["phase1_iters"] == ref["phase1_iters"]
+
+
+def test_cfg2_unbounded(ctx):
+    for name in ("unbounded.txt", "unr_inverted.txt"):
+        d = H.load_dumps()[name]
+        T, basis, n_art, n = H.tableau_from_dump(d, O.PLAIN)
+        ref = O.solve_f64(H.frac_f64(T), basis, log_cap=16)
+        got = lp.solve_dense(ctx, H.frac_f64(T), basis, log_cap=16)
+        _assert_dense_equal(got, ref)
+        assert got["status"] == lp.UNBOUNDED
+
+
+@pytest.mark.parametrize("seed", range(10))
+@pytest.mark.parametrize("method", [O.BIGM, O.TWOPHASE])
+def test_random_mixed_lps_dense(ctx, seed, method):
+    rng = np.random.default_rng(seed)
+    m, ns = int(rng.integers(3, 40)), int(rng.integers(3, 40))
+    A, b, c, rel = H.random_mixed_lp(rng, m, ns)
+    if seed % 3 == 2:        # make some infeasible: contradict the first row
+        A = np.vstack([A, A[0]]); b = np.append(b, b[0] - 5.0 if rel[0] != -2 else b[0] + 5.0)
+        rel = np.append(rel, -2 if rel[0] != -2 else 2).astype(np.int32)
+    T0, basis, n_art = lp.build_tableau(A, b, c, rel, R=2)
+    ref = O.solve_f64(T0, basis, method=method, n_art=n_art, max_iter=5000, log_cap=5000)
+    got = lp.solve_dense(ctx, T0, basis, method=method, n_art=n_art, max_iter=5000, log_cap=5000)
+    _assert_dense_equal(got, ref)
+
+
+# ------------------------------------------------------------------ the elimination pass alone
+@pytest.mark.parametrize("shape", [(5, 7), (33, 65), (100, 511), (257, 1030), (64, 2049)])
+@pytest.mark.parametrize("variant", [0, 1, 0x100, 0x101])
+def test_single_pivot_pass_bitwise(ctx, shape, variant):
+    rows, cols = shape
+    rng = np.random.default_rng(rows * 1000 + cols)
+    T0 = rng.uniform(-2, 2, size=(rows, cols))
+    T0[rng.random((rows, cols)) < 0.1] = 0.0
+    m, n = rows - 1, cols - 1
+    r, k = int(rng.integers(0, m)), int(rng.integers(1, n + 1))
+    T0[r, k] = 1.7
+    ref = O.pivot(T0, r, k)
+    d = lp.DenseTableau(ctx, m, n, 1)
+    d.reset(variant=variant)
+    d.upload(T0, np.arange(1, m + 1, dtype=np.int32))
+    d.pivot(r, k)
+    out = d.download(want_log=False)
+    d.close()
+    assert _same_bits(out["T"], ref)
+    assert out["basis"][r] == k
+
+
+# ------------------------------------------------------------------ large path on synthetic LPs
+@pytest.mark.parametrize("m,ns", [(32, 32), (64, 64), (200, 120), (300, 500), (512, 512)])
+@pytest.mark.parametrize("variant", [0, 1])
+def test_dense_synth_full_solve(ctx, m, ns, variant):
+    T0, basis = O.synth_feasible(1234, 3, m, ns)
+    ref = O.solve_f64(T0, basis, threads=4, log_cap=4096)
+    got = lp.solve_dense(ctx, T0, basis, log_cap=4096, variant=variant)
+    _assert_dense_equal(got, ref)
+    assert got["status"] == lp.OPTIMAL
+
+
+def test_dense_device_synth_matches_host_and_windows(ctx):
+    m, ns = 300, 212
+    n = m + ns
+    T0, basis = O.synth_feasible(77, 5, m, ns)
+    d = lp.DenseTableau(ctx, m, n, 1)
+    d.synth(77, 5, ns)
+    d.reset(log_cap=4096, check_every=7)
+    first = d.download()
+    assert np.array_equal(first["T"], T0) and np.array_equal(first["basis"], basis)   # generator parity
+    # run in windows of 25 pivots: state carries over, result identical to a single run
+    total = 0
+    while True:
+        r = d.run(25)
+        assert r["iters"] - total <= 25
+        total = r["iters"]
+        if r["status"] != lp.RUNNING:
+            break
+        part = O.solve_f64(T0, basis, max_iter=total)
+        assert np.array_equal(d.download()["T"], part["T"])
+    ref = O.solve_f64(T0, basis, log_cap=4096)
+    out = d.download()
+    assert r["status"] == ref["status"] == lp.OPTIMAL and r["iters"] == ref["iters"]
+    assert out["log"][:r["iters"]].tolist() == ref["log"].tolist()
+    assert np.array_equal(out["T"], ref["T"]) and np.array_equal(out["x"], ref["x"])
+    d.close()
+
+
+def test_dense_iteration_limit(ctx):
+    T0, basis = O.synth_feasible(1234, 0, 64, 64)
+    full = O.solve_f64(T0, basis)
+    ref = O.solve_f64(T0, basis, max_iter=5, log_cap=16)
+    got = lp.solve_dense(ctx, T0, basis, max_iter=5, log_cap=16)
+    _assert_dense_equal(got, ref)
+    assert got["status"] == lp.ITER_LIMIT and got["iters"] == 5
+    exact = lp.solve_dense(ctx, T0, basis, max_iter=full["iters"])
+    assert exact["status"] == lp.OPTIMAL and exact["iters"] == full["iters"]
+
+
+def test_dense_timed_run_reports_kernel_time(ctx):
+    m, ns = 512, 512
+    d = lp.DenseTableau(ctx, m, m + ns, 1)
+    d.synth(1234, 0, ns)
+    d.reset(time_kernels=1)
+    r = d.run(20)
+    assert r["update_launches"] == 20 and r["update_ms"] > 0 and r["select_ms"] > 0
+    d.close()
+
+
+# ------------------------------------------------------------------ batched path
+def _assert_batched_equal(got, ref, final=None):
+    assert np.array_equal(got["status"], ref["status"])
+    assert np.array_equal(got["iters"], ref["iters"])
+    assert np.array_equal(got["basis"], ref["basis"])
+    assert np.array_equal(got["z"], ref["z"]) and np.array_equal(got["x"], ref["x"])
+    if final is not None:
+        assert np.array_equal(final, ref["T"])
+
+
+@pytest.mark.parametrize("m,ns,n_lp", [(32, 32, 2000), (64, 64, 300), (8, 8, 999), (5, 9, 100), (33, 20, 101)])
+def test_cfg3_batched_synth_bitwise(ctx, m, ns, n_lp):
+    T, basis = O.synth_feasible_batch(1234, 10, n_lp, m, ns)
+    ref = O.solve_batched_f64(T, basis, threads=8, log_cap=256)
+    b = lp.BatchedLPs(ctx, n_lp, m, m + ns, 1)
+    b.upload(T, basis)
+    ms = b.run(log_cap=256, keep_final=True)
+    assert ms > 0
+    got = b.download(want_log=True, want_final=True)
+    _assert_batched_equal(got, ref, got["T"])
+    assert np.array_equal(got["log"], ref["log"])
+    assert np.all(got["status"] == lp.OPTIMAL)
+    # device generator produces the same LPs
+    b.synth(1234, 10, ns)
+    b.run()
+    got2 = b.download()
+    _assert_batched_equal(got2, ref)
+    b.close()
+    # one-shot host-buffer entry point
+    got3 = lp.solve_batched(ctx, T, basis)
+    _assert_batched_equal(got3, ref)
+
+
+@pytest.mark.parametrize("method", [O.BIGM, O.TWOPHASE])
+def test_batched_bigm_twophase(ctx, method):
+    rng = np.random.default_rng(5)
+    m, ns, n_lp = 6, 5, 64
+    rel = np.array([2, -2, 3, -2, 2, -2], np.int32)
+    Ts, Bs = [], []
+    for p in range(n_lp):
+        A = rng.uniform(0.1, 1.5, size=(m, ns))
+        x0 = rng.uniform(0, 2, ns)
+        ax = A @ x0
+        b = np.where(rel == -2, ax + 1.0, np.where(rel == 2, ax - 0.5, ax))
+        if p % 5 == 4:
+            b[1] = -1.0 - p          # A>0, x>=0: row "<= negative" -> infeasible
+        c = rng.uniform(-1, 1, ns)
+        T0, basis, n_art = lp.build_tableau(A, b, c, rel, R=2)
+        Ts.append(T0); Bs.append(basis)
+    # rows with b<0 flip relation and change the column count: keep the common-shape ones
+    shape = Ts[0].shape
+    keep = [i for i in range(n_lp) if Ts[i].shape == shape]
+    T = np.stack([Ts[i] for i in keep]); B = np.stack([Bs[i] for i in keep])
+    n_art = 3
+    ref = O.solve_batched_f64(T, B, method=method, n_art=n_art, max_iter=500, threads=4)
+    got = lp.solve_batched(ctx, T, B, method=method, n_art=n_art, max_iter=500)
+    _assert_batched_equal(got, ref)
+    assert set(np.unique(got["status"])) <= {lp.OPTIMAL, lp.UNBOUNDED, lp.INFEASIBLE}
+
+
+def test_batched_edge_cases(ctx):
+    # empty batch
+    out = lp.solve_batched(ctx, np.zeros((0, 4, 6)), np.zeros((0, 3), np.int32))
+    assert out["status"].shape == (0,)
+    # single LP, iteration cap
+    T, basis = O.synth_feasible_batch(1, 0, 1, 16, 16)
+    ref = O.solve_batched_f64(T, basis, max_iter=2)
+    got = lp.solve_batched(ctx, T, basis, max_iter=2)
+    _assert_batched_equal(got, ref)
+    assert got["status"][0] == lp.ITER_LIMIT
+    # shape too large for shared memory is refused, not silently rerouted
+    with pytest.raises(lp.LpgpuError):
+        lp.BatchedLPs(ctx, 1, 200, 400, 1)
+
+
+# ------------------------------------------------------------------ full-size properties
+def test_cfg4_full_size_window_properties(ctx):
+    """8192 x 16384: after P pivots the basic columns are exact unit vectors, b stays >= 0, the
+    objective never decreases, and the first pivots equal the oracle's (bit-exact tableau)."""
+    m = ns = 8192
+    n = m + ns
+    d = lp.DenseTableau(ctx, m, n, 1)
+    d.synth(1234, 0, ns)
+    d.reset(log_cap=64)
+    r1 = d.run(3)
+    out = d.download()
+    T0, basis0 = lp.synth_host(1234, 0, m, ns)
+    ref = O.solve_f64(T0, basis0, max_iter=3, threads=8, log_cap=64)
+    assert out["log"][:3].tolist() == ref["log"].tolist()
+    assert np.array_equal(out["T"], ref["T"]) and np.array_equal(out["basis"], ref["basis"])
+    z_prev = r1["z"]
+    r2 = d.run(29)
+    assert r2["iters"] == 32 and r2["z"] >= z_prev
+    out = d.download()
+    T = out["T"]
+    assert np.all(T[:m, 0] >= 0.0)
+    cols = out["basis"]
+    sub = T[:, cols]                      # (m+1) x m: must be [I; 0]
+    assert np.array_equal(sub[:m], np.eye(m)) and np.all(sub[m] == 0.0)
+    d.close()

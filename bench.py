@@ -1,0 +1,380 @@
+#!/usr/bin/env python3
+"""bench.py -- pivots/sec of the dense-tableau simplex pivot path on B200.
+
+Contract (see the task statement): `python bench.py --gpus N --steps K --warmup W` prints ONE
+JSON line on rank 0.  Workload at every N: BASELINE.json config 4 -- one dense 8192 x 16384
+fp64 tableau per GPU (random feasible LP, seed 1234, LP index = rank), a "step" = a window of
+--pivots pivots (pricing + ratio test + pivot-row scaling + rank-1 elimination each).
+  value  : pivots/s summed over ranks, tableau resident in HBM when the timed region starts
+  e2e    : the same metric through lpgpu_solve_dense() with HOST (pinned) buffers: H2D copy of
+           the 1.07 GB tableau, P pivots, D2H of x / basis / status inside the timed region
+  roofline: the rank-1 elimination kernel, algorithmic bytes 16*(m+1)*(n+1) per launch over
+           its CUDA-event duration, against MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline: the CPU oracle (oracle/, kind "port": the reference has no pivot loop to time)
+           on the host cores, bounded sample of the same workload
+`--impl reference` times that CPU oracle alone, on the same config/metric/unit.
+N > 1: one process per GPU (torchrun), independent LPs per rank, no data-path collective
+("weak" scaling); timing = max over ranks.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+M = 8192
+NS = 8192
+N = M + NS            # total columns incl. slacks: tableau (M+1) x (N+1)
+SEED = 1234
+ALG_BYTES = 16 * (M + 1) * (N + 1)        # one 8-B read + one 8-B write of every element
+
+BM, BNS, BN_LP = 32, 32, 100_000           # config 3 (extra): batched 100k LPs m=32 n=64
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--pivots", type=int, default=1000, help="pivots per step (window)")
+    ap.add_argument("--variant", type=lambda s: int(s, 0), default=None, help="dense kernel variant override")
+    ap.add_argument("--no-extra", action="store_true", help="skip the batched (config 3) extra measurement")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--m", type=int, default=M, help=argparse.SUPPRESS)     # debugging at reduced size only
+    return ap.parse_args()
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.p = index, [], None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for nme, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nme)
+            except Exception:
+                pass
+        # "under load" = the upper half of the samples (idle samples at the edges drop out)
+        sm_sorted = sorted(sm)
+        load = sm_sorted[len(sm_sorted) // 2:] if sm_sorted else []
+        return {"sm_mhz": statistics.median(load) if load else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+# ------------------------------------------------------------------ CPU legs (oracle = the checker, timed)
+class CpuOracle:
+    """The CPU oracle (oracle/lp_oracle.c, OpenMP over rows) on the same synthetic tableau."""
+
+    def __init__(self, m, ns, threads, lp_index=0):
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import ctypes as C
+        import numpy as np
+        import oracle_lib as O
+        self.C, self.O, self.L = C, O, O.lib()
+        self.m, self.n, self.threads = m, m + ns, threads
+        self.ns, self.lp_index = ns, lp_index
+        self.T = np.zeros((m + 1, self.n + 1))
+        self.basis = np.zeros(m, np.int32)
+        self.synth()
+
+    def synth(self):
+        C = self.C
+        self.L.lpo_synth_feasible(SEED, self.lp_index, self.m, self.ns, self.T.ctypes.data_as(C.POINTER(C.c_double)),
+                                  self.n + 1, self.basis.ctypes.data_as(C.POINTER(C.c_int)))
+
+    def run(self, pivots):
+        """`pivots` more pivots from the current state; returns (pivots done, seconds).  If the LP reaches
+        its optimum first, the tableau is regenerated (untimed) and the window continues."""
+        C, O = self.C, self.O
+        done, secs = 0, 0.0
+        while done < pivots:
+            res = O.Result()
+            opts = O.Opts(1e-9, int(pivots - done), O.PLAIN, 0, self.threads)
+            t0 = time.perf_counter()
+            rc = self.L.lpo_solve_f64(self.m, self.n, 1, self.T.ctypes.data_as(C.POINTER(C.c_double)), self.n + 1,
+                                      self.basis.ctypes.data_as(C.POINTER(C.c_int)), C.byref(opts), None, 0,
+                                      C.byref(res))
+            secs += time.perf_counter() - t0
+            assert rc == 0
+            done += res.iters
+            if res.status != O.ITER_LIMIT:
+                self.synth()
+        return done, secs
+
+    def calibrate(self, budget_s):
+        self.run(1)                                   # page in, start the thread pool
+        it, dt = self.run(2)
+        return int(max(2, min(5000, budget_s / max(dt / max(it, 1), 1e-6))))
+
+
+def cpu_baseline(m, ns, budget_s=12.0):
+    threads = host_threads()
+    o = CpuOracle(m, ns, threads)
+    p = o.calibrate(budget_s)
+    it, dt = o.run(p)
+    return {"value": it / dt, "unit": "pivots/s", "cores": threads, "kind": "port",
+            "sample": f"{it} pivots of the same {m}x{m + ns} tableau (seed {SEED}) in {dt:.1f} s, "
+                      f"oracle/lp_oracle.c with OpenMP over rows; the reference has no pivot loop to time"}
+
+
+def reference_arm(args):
+    """`--impl reference`: the reference has NO implementation of this path (Source/simplex.c:57-63 are
+    empty cases), so the timed CPU implementation is this repo's oracle port, all host threads."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    threads = host_threads()
+    m = ns = args.m
+    o = CpuOracle(m, ns, threads)
+    p = o.calibrate(3.0)                              # each step: a bounded sample of ~3 s
+    times, done = [], []
+    for s in range(args.warmup + args.steps):
+        it, dt = o.run(p)
+        if s >= args.warmup:
+            times.append(dt); done.append(it)
+    value = sum(done) / sum(times)
+    sample = f"{p} pivots per step of the {m}x{m + ns} tableau (seed {SEED}), OpenMP over rows, {threads} threads"
+    line = {
+        "impl": "reference", "metric": "pivots_per_sec", "value": value, "unit": "pivots/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(times) / len(times),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"dense tableau {m}x{m + ns} fp64 random feasible LP (BASELINE config 4)",
+                   "m": m, "n": m + ns, "pivots_per_step": p, "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "pivots/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "pivots/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "the reference has no pivot loop (Source/simplex.c:57-63 empty cases); timed = this repo's CPU oracle port",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ GPU arm
+def gpu_arm(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import linearprogramming_b200 as lp
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    m = ns = args.m
+    n = m + ns
+    P, K, W = args.pivots, args.steps, max(args.warmup, 0)
+    alg_bytes = 16 * (m + 1) * (n + 1)
+    variant = args.variant if args.variant is not None else int(os.environ.get("LPGPU_VARIANT", "0"), 0)
+
+    stream = torch.cuda.Stream()
+    ctx = lp.Context(local, stream=stream.cuda_stream)
+
+    def timed(fn):
+        """CUDA events on the launching stream, synchronize on both sides; returns seconds."""
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) * 1e-3
+
+    state = {"opts": {}}
+
+    def start(d, **opts):
+        state["opts"] = opts
+        d.synth(SEED, rank, ns)
+        d.reset(variant=variant, **opts)
+
+    def window(d):
+        """P pivots; if the LP reaches its optimum inside the window (about 17k pivots at the default
+        size) it is regenerated and the window continues, so every step performs exactly P pivots."""
+        done, upd_ms, sel_ms = 0, 0.0, 0.0
+        while done < P:
+            r = d.run(P - done)
+            done += r["update_launches"]; upd_ms += r["update_ms"]; sel_ms += r["select_ms"]
+            if r["status"] != lp.RUNNING:
+                start(d, **state["opts"])
+        return {"update_launches": done, "update_ms": upd_ms, "select_ms": sel_ms}
+
+    # ---- value: resident tableau, K windows of P pivots
+    d = lp.DenseTableau(ctx, m, n, 1)
+    start(d)
+    for _ in range(W):
+        window(d)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launch_count()
+    t_value = timed(lambda: [window(d) for _ in range(K)])
+    launches = ctx.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    t_value = max_over_ranks(t_value)
+    value = world * K * P / t_value
+
+    # ---- roofline of the dominant kernel: same region, every elimination launch bracketed by events
+    start(d, time_kernels=1)
+    for _ in range(W):
+        window(d)
+    upd_ms = sel_ms = 0.0
+    upd_n = 0
+    for _ in range(K):
+        r = window(d)
+        upd_ms += r["update_ms"]; sel_ms += r["select_ms"]; upd_n += r["update_launches"]
+    d.close()
+    peak, peak_src = measured_peak()
+    upd_avg_ms = upd_ms / upd_n
+    achieved = alg_bytes / (upd_avg_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "dense_update_direct" if (variant & 0xf) == 2 else "dense_update_tma_staged",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                "avg_launch_ms": upd_avg_ms, "select_avg_ms": sel_ms / upd_n,
+                "kernel_share_of_step": upd_ms / (upd_ms + sel_ms), "frac_of_nominal_8TBs": achieved / 8000.0}
+
+    # ---- e2e: host (pinned) buffers through the one-shot C-ABI call, copies inside the timed region
+    Th = ctx.pinned((m + 1, n + 1))
+    bh = ctx.pinned((m,), np.int32)
+    T0, b0 = lp.synth_host(SEED, rank, m, ns)
+    Th[...] = T0
+    bh[...] = b0
+    del T0
+
+    def e2e_step():
+        bh[...] = b0
+        r = lp.solve_dense(ctx, Th, bh, max_iter=P, results_only=True, inplace=True, variant=variant)
+        if r["iters"] != P:
+            raise SystemExit("e2e step did not perform the requested pivots")
+        return r
+
+    for _ in range(min(W, 2)):
+        e2e_step()
+    t_e2e = max_over_ranks(timed(lambda: [e2e_step() for _ in range(K)]))
+    e2e = {"value": world * K * P / t_e2e, "unit": "pivots/s",
+           "h2d_bytes_per_step": int((m + 1) * (n + 1) * 8 + m * 4), "d2h_bytes_per_step": int(n * 8 + m * 4 + 64),
+           "api": "lpgpu_solve_dense (max_iter = pivots per step, results_only)"}
+
+    # ---- extra: batched path, BASELINE config 3 (100k LPs m=32 n=64 per GPU, one LP per CTA in smem)
+    extra = {}
+    if not args.no_extra:
+        bn = BN_LP
+        b = lp.BatchedLPs(ctx, bn, BM, BM + BNS, 1)
+        b.synth(SEED, rank * bn, BNS)
+        for _ in range(3):
+            b.run()
+        ms = [b.run() for _ in range(5)]
+        out = b.download(want_x=False)
+        b.close()
+        t_b = max_over_ranks(statistics.median(ms) * 1e-3)
+        lp_bytes = 8 * ((BM + 1) * (BM + BNS + 1) + (BM + BNS) + 4)
+        extra["batched"] = {"metric": "LPs_per_sec", "value": world * bn / t_b, "unit": "LPs/s",
+                            "workload": f"{bn} LPs m={BM} n={BM + BNS} fp64 per GPU, resident",
+                            "kernel_ms": t_b * 1e3, "mean_pivots_per_lp": float(out["iters"].mean()),
+                            "all_optimal": bool((out["status"] == lp.OPTIMAL).all()),
+                            "hbm_GBs_algorithmic": world * bn * lp_bytes / t_b / 1e9}
+
+    line = {
+        "metric": "pivots_per_sec", "value": value, "unit": "pivots/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": 1e3 * t_value / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"dense tableau {m}x{n} fp64 random feasible LP per GPU (BASELINE config 4)",
+                   "m": m, "n": n, "tableau_bytes": (m + 1) * (n + 1) * 8, "pivots_per_step": P, "seed": SEED,
+                   "variant": variant, "l2": "inputs larger than L2 (1.07 GB tableau vs 126 MB)",
+                   "sharding": "independent LP per rank, no collective" if world > 1 else "single GPU"},
+        "hbm_GBs_whole_step": world * K * P * alg_bytes / t_value / 1e9,
+        "roofline": roofline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "extra": extra,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline(m, ns)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -15,7 +15,8 @@ OPTIMAL, UNBOUNDED, INFEASIBLE, ITER_LIMIT, RUNNING = 0, 1, 2, 3, 4
 PLAIN, BIGM, TWOPHASE = 0, 1, 2
 STATUS_NAMES = {0: "OPTIMAL", 1: "UNBOUNDED", 2: "INFEASIBLE", 3: "ITER_LIMIT", 4: "RUNNING"}
 KEEP_FINAL = 0x1000      # batched: keep the final tableaux on the device (parity tests)
-ALTERNATE = 0x100        # dense: walk the elimination tasks backwards on odd pivots
+DIRECT = 0x2             # dense: direct-load elimination kernel instead of the TMA-staged default
+NO_ALTERNATE = 0x200     # dense: do not alternate the sweep direction between pivots
 
 
 class Opts(C.Structure):

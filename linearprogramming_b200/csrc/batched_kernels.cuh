@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(BATCH_THREADS) batched_simplex_kernel(BatchedP
 
         DenseParams P;
         P.T = S; P.ld = (size_t)ld1; P.m = m; P.n = n; P.R = R; P.basis = basis;
-        P.prow = prow; P.pcol = pcol; P.st = nullptr; P.log = nullptr; P.log_cap = 0;
+        P.prow = prow; P.pcol = pcol; P.pcn = 0; P.bnext = nullptr; P.st = nullptr; P.log = nullptr; P.log_cap = 0;
         P.eps = B.eps; P.max_iter = B.max_iter; P.method = B.method; P.n_art = B.n_art;
 
         int status = LPGPU_RUNNING, phase = (B.method == LPGPU_TWOPHASE) ? PH_ONE : PH_MAIN, iters = 0, p1 = 0;

@@ -21,6 +21,8 @@ struct PivotState {
     int k;             // entering column (1-based)
     int do_pivot;      // 1: the elimination kernel that follows has work
     int budget;        // pivots still allowed in this run call
+    int k_next;        // lookahead: entering column of the NEXT pivot (0 = unknown -> full decision)
+    int cur;           // which half of colbuf holds the pivot column of the pivot to apply
 };
 
 // ------------------------------------------------------------------ candidates

@@ -19,7 +19,9 @@ struct lpgpu_dense {
     size_t ld;
     double *T;
     int *basis;
-    double *prow, *pcol, *xbuf;
+    double *prow, *pcol, *bnext, *xbuf;   // pcol: 2 x pcn (colbuf)
+    size_t pcn;
+    bool la_dirty;          // tableau changed behind the lookahead's back (upload / synth / forced pivot)
     PivotState *st;
     PivotState *h_st;       // pinned mirror
     int *log;
@@ -31,30 +33,69 @@ struct lpgpu_dense {
 
 namespace lpgpu {
 
-// forced_k > 0: skip the decision and pivot on (forced_r, forced_k) (tests of one pass).
+// Ratio test on the compact copies the previous elimination pass left behind (lookahead):
+// col[i] = a_ik and bcol[i] = b_i of the CURRENT tableau, contiguous -> coalesced.
+__device__ __forceinline__ Cand ratio_compact(const double *col, const double *bcol, int m, double eps, Cand *scratch) {
+    Cand c = cand_none();
+    for (int i = (int)threadIdx.x; i < m; i += blockDim.x) {
+        const double a = col[i];
+        if (a > eps) {
+            Cand t;
+            t.p = 0.0;
+            t.q = -(bcol[i] / a);
+            t.idx = i;
+            if (cand_better(t, c)) c = t;
+        }
+    }
+    return block_best(c, scratch);
+}
+
+// One CTA decides a pivot and stages it for the elimination pass.
+//   fast path  (st->k_next > 0): the entering column was priced one pivot ahead and its values
+//              (and b) were extracted by the previous elimination pass into compact buffers, so
+//              only the ratio test, the pivot-row scaling and the next pricing remain;
+//   full path  : dense_select.cuh decide() over the tableau in HBM (first pivot, phase changes,
+//              drive-out pivots, terminal statuses).
+// Either way the kernel then prices the pivot AFTER this one (lookahead): the objective row(s)
+// after elimination are sigma'_j = fma(-sigma_k, a_rj', sigma_j) -- the same operation on the
+// same operands the elimination pass performs, so the choice is bit-identical to pricing the
+// updated tableau.  forced_k > 0: skip the decision and pivot on (forced_r, forced_k).
 __global__ void __launch_bounds__(SELECT_THREADS) dense_select_kernel(DenseParams P, int forced_r, int forced_k) {
     __shared__ Cand scratch[SELECT_THREADS / 32];
     PivotState *st = P.st;
-    int r = -1, k = 0;
+    int r = -1, k = 0, cur = st->cur, phase = st->phase;
+    bool fast = false;
 
     if (forced_k > 0) {
         r = forced_r;
         k = forced_k;
     } else {
         // all threads read the same state; nothing below writes it before the final section
-        const int status0 = st->status, phase0 = st->phase, iters = st->iters, p10 = st->phase1_iters;
-        const int budget = st->budget;
+        const int status0 = st->status, iters = st->iters, p10 = st->phase1_iters;
+        const int budget = st->budget, knext = st->k_next;
         if (status0 != LPGPU_RUNNING) {
             __syncthreads();
             if (threadIdx.x == 0) st->do_pivot = 0;
             return;
         }
-        Decision D = decide(P, scratch, status0, phase0, iters, p10);
+        Decision D;
+        if (knext > 0 && phase != PH_DRIVEOUT) {
+            D.status = status0; D.phase = phase; D.p1 = p10; D.k = knext; D.r = -1; D.have = false;
+            const Cand l = ratio_compact(P.pcol + (size_t)(cur ^ 1) * P.pcn, P.bnext, P.m, P.eps, scratch);
+            if (l.idx < 0) D.status = LPGPU_UNBOUNDED;
+            else { D.r = l.idx; D.have = true; }
+            if (D.have && iters >= P.max_iter) { D.status = LPGPU_ITER_LIMIT; D.have = false; }
+            fast = true;
+        } else {
+            D = decide(P, scratch, status0, phase, iters, p10);
+        }
         // out of budget for this run call: the decision still settles terminal statuses, a
-        // pending pivot is left for the next call (status stays RUNNING)
+        // pending pivot is left for the next call (status stays RUNNING, lookahead kept)
         if (D.have && budget <= 0) D.have = false;
         r = D.r;
         k = D.k;
+        phase = D.phase;
+        if (D.have && fast) cur ^= 1;
         __syncthreads();
         if (threadIdx.x == 0) {
             st->status = D.status;
@@ -64,6 +105,7 @@ __global__ void __launch_bounds__(SELECT_THREADS) dense_select_kernel(DenseParam
             if (D.have) {
                 st->r = r;
                 st->k = k;
+                st->cur = cur;
                 st->iters = iters + 1;
                 st->budget = budget - 1;
                 if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
@@ -72,13 +114,52 @@ __global__ void __launch_bounds__(SELECT_THREADS) dense_select_kernel(DenseParam
         if (!D.have) return;
     }
 
-    // pivot column (all rows incl. objective rows) and scaled pivot row into compact buffers
-    const double piv = P.T[(size_t)r * P.ld + (size_t)k];
-    for (int i = (int)threadIdx.x; i < P.m + P.R; i += blockDim.x) P.pcol[i] = P.T[(size_t)i * P.ld + (size_t)k];
+    // ---- stage the pivot: pivot column (all rows incl. objective rows) and scaled pivot row
+    double *pcol = P.pcol + (size_t)cur * P.pcn;
+    const int rows = P.m + P.R;
+    if (!fast) {
+        for (int i = (int)threadIdx.x; i < rows; i += blockDim.x) pcol[i] = P.T[(size_t)i * P.ld + (size_t)k];
+        __syncthreads();                      // pcol[m..] is read below by every thread
+    }
+    const double piv = pcol[r];
     const double *xr = P.T + (size_t)r * P.ld;
-    for (size_t j = threadIdx.x; j < P.ld; j += blockDim.x) P.prow[j] = xr[j] / piv;
+
+    // lookahead pricing mode for the pivot after this one
+    const bool look = (forced_k <= 0) && (phase != PH_DRIVEOUT);
+    const bool bigm = (P.method == LPGPU_BIGM);
+    const int prow_obj = (phase == PH_ONE) ? P.m + 1 : P.m;      // row priced when not Big-M
+    const int jmax = (P.method == LPGPU_TWOPHASE && phase == PH_MAIN) ? P.n - P.n_art : P.n;
+    const double *oc = P.T + (size_t)(bigm ? P.m : prow_obj) * P.ld;
+    const double *om = P.T + (size_t)(P.m + 1) * P.ld;            // Big-M row (R = 2 only)
+    const double fc = -pcol[bigm ? P.m : prow_obj];
+    const double fm = bigm ? -pcol[P.m + 1] : 0.0;
+    Cand c = cand_none();
+    for (size_t j = threadIdx.x; j < P.ld; j += blockDim.x) {
+        const double pr = xr[j] / piv;
+        P.prow[j] = pr;
+        if (look && j >= 1 && j <= (size_t)jmax) {
+            const double q = __fma_rn(fc, pr, oc[j]);
+            Cand t;
+            t.idx = (int)j;
+            if (bigm) {
+                double p = __fma_rn(fm, pr, om[j]);
+                if (fabs(p) <= P.eps) p = 0.0;
+                t.p = p; t.q = q;
+                if ((p > 0.0 || (p == 0.0 && q > P.eps)) && cand_better(t, c)) c = t;
+            } else {
+                t.p = 0.0; t.q = q;
+                if (q > P.eps && cand_better(t, c)) c = t;
+            }
+        }
+    }
+    int knew = 0;
+    if (look) {
+        c = block_best(c, scratch);
+        knew = c.idx > 0 ? c.idx : 0;
+    }
     if (threadIdx.x == 0) {
         P.basis[r] = k;
+        st->k_next = knew;
         if (forced_k > 0) { st->r = r; st->k = k; st->do_pivot = 1; }
     }
 }
@@ -99,7 +180,7 @@ size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 DenseParams make_params(const lpgpu_dense *d) {
     DenseParams P;
     P.T = d->T; P.ld = d->ld; P.m = d->m; P.n = d->n; P.R = d->R;
-    P.basis = d->basis; P.prow = d->prow; P.pcol = d->pcol; P.st = d->st;
+    P.basis = d->basis; P.prow = d->prow; P.pcol = d->pcol; P.pcn = d->pcn; P.bnext = d->bnext; P.st = d->st;
     P.log = d->log; P.log_cap = d->log_cap;
     P.eps = d->opts.eps; P.max_iter = d->opts.max_iter; P.method = d->opts.method; P.n_art = d->opts.n_art;
     return P;
@@ -108,11 +189,13 @@ DenseParams make_params(const lpgpu_dense *d) {
 int launch_update(lpgpu_dense *d) {
     lpgpu_ctx *ctx = d->ctx;
     UpdateParams U;
-    U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.prow = d->prow; U.pcol = d->pcol; U.st = d->st;
-    U.alternate = (d->opts.variant & 0x100) ? 1 : 0;
+    U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.prow = d->prow; U.colbuf = d->pcol; U.pcn = d->pcn; U.bnext = d->bnext; U.st = d->st;
+    // variant: low nibble 0/1 = TMA-staged kernel (default), 2 = direct-load kernel;
+    //          0x200 = do NOT alternate the sweep direction between pivots
+    U.alternate = (d->opts.variant & 0x200) ? 0 : 1;
     const int kind = d->opts.variant & 0xf;
-    if (kind == 1) dense_update_tma_staged<<<d->grid_update, UPD_THREADS, 0, ctx->stream>>>(U);
-    else dense_update_direct<<<d->grid_update, UPD_THREADS, 0, ctx->stream>>>(U);
+    if (kind == 2) dense_update_direct<<<d->grid_update, UPD_THREADS, 0, ctx->stream>>>(U);
+    else dense_update_tma_staged<<<d->grid_update, UPD_THREADS, 0, ctx->stream>>>(U);
     LP_LAUNCH_CHECK(ctx);
     return LPGPU_OK;
 }
@@ -122,7 +205,7 @@ int size_grid(lpgpu_dense *d) {
     int occ0 = 0, occ1 = 0;
     LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, dense_update_direct, UPD_THREADS, 0));
     LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, dense_update_tma_staged, UPD_THREADS, 0));
-    const int occ = std::max(1, ((d->opts.variant & 0xf) == 1) ? occ1 : occ0);
+    const int occ = std::max(1, ((d->opts.variant & 0xf) == 2) ? occ0 : occ1);
     const long nct = (long)((d->ld + UPD_TILE_COLS - 1) / UPD_TILE_COLS);
     const long nrb = (d->m + d->R + UPD_TILE_ROWS - 1) / UPD_TILE_ROWS;
     d->grid_update = (int)std::max(1L, std::min((long)ctx->sm_count * occ, nct * nrb));
@@ -149,7 +232,7 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     if (!d) return fail(ctx, LPGPU_ENOMEM, "dense_create: host allocation failed");
     d->ctx = ctx; d->m = m; d->n = n; d->R = R;
     d->ld = round_up((size_t)n + 1, 16);
-    d->T = nullptr; d->basis = nullptr; d->prow = d->pcol = d->xbuf = nullptr; d->st = nullptr; d->h_st = nullptr;
+    d->T = nullptr; d->basis = nullptr; d->prow = d->pcol = d->bnext = d->xbuf = nullptr; d->la_dirty = true; d->st = nullptr; d->h_st = nullptr;
     d->log = nullptr; d->log_cap = 0;
     lpgpu_default_opts(&d->opts);
     d->opts.method = (R == 1) ? LPGPU_PLAIN : LPGPU_BIGM;
@@ -158,13 +241,16 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     if (e == cudaSuccess) e = cudaMalloc(&d->T, rows * d->ld * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&d->basis, (size_t)m * sizeof(int));
     if (e == cudaSuccess) e = cudaMalloc(&d->prow, d->ld * sizeof(double));
-    if (e == cudaSuccess) e = cudaMalloc(&d->pcol, pcn * sizeof(double));
+    d->pcn = pcn;
+    if (e == cudaSuccess) e = cudaMalloc(&d->pcol, 2 * pcn * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&d->bnext, pcn * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&d->xbuf, (size_t)n * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&d->st, sizeof(PivotState));
     if (e == cudaSuccess) e = cudaHostAlloc(&d->h_st, sizeof(PivotState), cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->T, 0, rows * d->ld * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->prow, 0, d->ld * sizeof(double), ctx->stream);
-    if (e == cudaSuccess) e = cudaMemsetAsync(d->pcol, 0, pcn * sizeof(double), ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->pcol, 0, 2 * pcn * sizeof(double), ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->bnext, 0, pcn * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->basis, 0, (size_t)m * sizeof(int), ctx->stream);
     if (e != cudaSuccess) {
         lpgpu_dense_destroy(d);
@@ -182,7 +268,7 @@ void lpgpu_dense_destroy(lpgpu_dense *d) {
     cudaSetDevice(d->ctx->device);
     cudaStreamSynchronize(d->ctx->stream);
     for (cudaEvent_t e : d->ev) cudaEventDestroy(e);
-    cudaFree(d->T); cudaFree(d->basis); cudaFree(d->prow); cudaFree(d->pcol); cudaFree(d->xbuf);
+    cudaFree(d->T); cudaFree(d->basis); cudaFree(d->prow); cudaFree(d->pcol); cudaFree(d->bnext); cudaFree(d->xbuf);
     cudaFree(d->st); cudaFree(d->log);
     if (d->h_st) cudaFreeHost(d->h_st);
     delete d;
@@ -209,7 +295,7 @@ int lpgpu_dense_reset(lpgpu_dense *d, const lpgpu_opts *opts) {
     LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // h_st may still be in flight
     PivotState s;
     s.status = LPGPU_RUNNING; s.iters = 0; s.phase = (opts->method == LPGPU_TWOPHASE) ? PH_ONE : PH_MAIN;
-    s.phase1_iters = 0; s.r = -1; s.k = 0; s.do_pivot = 0; s.budget = 0;
+    s.phase1_iters = 0; s.r = -1; s.k = 0; s.do_pivot = 0; s.budget = 0; s.k_next = 0; s.cur = 0;
     *d->h_st = s;
     LP_CUDA(ctx, cudaMemcpyAsync(d->st, d->h_st, sizeof s, cudaMemcpyHostToDevice, ctx->stream));
     LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -225,6 +311,7 @@ int lpgpu_dense_upload(lpgpu_dense *d, const double *T, size_t ld, const int *ba
                                    (size_t)d->m + d->R, cudaMemcpyHostToDevice, ctx->stream));
     LP_CUDA(ctx, cudaMemcpyAsync(d->basis, basis, (size_t)d->m * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // the caller may reuse its buffers
+    d->la_dirty = true;
     return LPGPU_OK;
 }
 
@@ -235,6 +322,7 @@ int lpgpu_dense_synth(lpgpu_dense *d, uint64_t seed, uint64_t lp_index, int ns) 
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
     dense_synth_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(d->T, d->ld, d->m, ns, d->basis, seed, lp_index);
     LP_LAUNCH_CHECK(ctx);
+    d->la_dirty = true;
     return LPGPU_OK;
 }
 
@@ -261,6 +349,8 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
     int rc = read_state(d);
     if (rc != LPGPU_OK) return rc;
     d->h_st->budget = max_pivots;
+    if (d->la_dirty) d->h_st->k_next = 0;       // never trust a lookahead across an upload / synth / forced pivot
+    d->la_dirty = false;
     LP_CUDA(ctx, cudaMemcpyAsync(d->st, d->h_st, sizeof(PivotState), cudaMemcpyHostToDevice, ctx->stream));
     const DenseParams P = make_params(d);
     int launched = 0, done_updates = 0;
@@ -327,6 +417,7 @@ int lpgpu_dense_pivot(lpgpu_dense *d, int r, int k) {
     if (r < 0 || r >= d->m || k < 1 || k > d->n) return fail(ctx, LPGPU_EINVAL, "dense_pivot: (r=%d,k=%d) out of range", r, k);
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
     const DenseParams P = make_params(d);
+    d->la_dirty = true;
     dense_select_kernel<<<1, SELECT_THREADS, 0, ctx->stream>>>(P, r, k);
     LP_LAUNCH_CHECK(ctx);
     int rc = launch_update(d);

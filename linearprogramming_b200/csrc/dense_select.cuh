@@ -21,7 +21,10 @@ struct DenseParams {
     int m, n, R;
     int *basis;         // m entries, 1-based columns
     double *prow;       // ld doubles: scaled pivot row
-    double *pcol;       // >= m+R doubles (zero padded to the row-tile multiple): pivot column
+    double *pcol;       // colbuf: 2 x pcn doubles; half st->cur = pivot column of this pivot, the other
+                        // half receives the NEXT entering column from the elimination pass (lookahead)
+    size_t pcn;         // doubles per half (>= m+R, zero padded to the row-tile multiple)
+    double *bnext;      // pcn doubles: b column as left by the elimination pass (lookahead)
     PivotState *st;
     int *log;           // 2*log_cap ints
     int log_cap;

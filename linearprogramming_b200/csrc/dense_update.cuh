@@ -27,7 +27,10 @@ struct UpdateParams {
     size_t ld;
     int rows;               // m + R
     const double *prow;     // ld doubles
-    const double *pcol;     // padded to a multiple of UPD_TILE_ROWS
+    double *colbuf;         // 2 x pcn: half st->cur = pivot column (read), other half = next entering
+                            // column as updated by this pass (written; lookahead of the select kernel)
+    size_t pcn;             // doubles per half, a multiple of UPD_TILE_ROWS
+    double *bnext;          // b column as updated by this pass (written)
     const PivotState *st;
     int alternate;          // 1: walk the tasks backwards on odd pivots (L2 reuse of the tail)
 };
@@ -38,6 +41,9 @@ __device__ __forceinline__ long upd_task(long t, long ntasks, bool reverse) { re
 __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_direct(UpdateParams U) {
     if (!U.st->do_pivot) return;
     const int r = U.st->r;
+    const int cur = U.st->cur, kn = U.st->k_next;
+    const double *pcol = U.colbuf + (size_t)cur * U.pcn;
+    double *cnext = U.colbuf + (size_t)(cur ^ 1) * U.pcn;
     const bool reverse = U.alternate && (U.st->iters & 1);
     const int nct = (int)((U.ld + UPD_TILE_COLS - 1) / UPD_TILE_COLS);
     const int nrb = (U.rows + UPD_TILE_ROWS - 1) / UPD_TILE_ROWS;
@@ -47,6 +53,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_direct(UpdatePara
         const int c = (int)(t % nct), rb = (int)(t / nct);
         const size_t j = (size_t)c * UPD_TILE_COLS + (size_t)threadIdx.x * 2;
         if (j >= U.ld) continue;
+        const bool wb = (j == 0);                                    // this thread owns the b column
+        const bool wk = (kn > 0) && (j == ((size_t)kn & ~(size_t)1));  // ... or the next entering column
         const double2 pr = *reinterpret_cast<const double2 *>(U.prow + j);
         const int i0 = rb * UPD_TILE_ROWS;
         const int i1 = min(i0 + UPD_TILE_ROWS, U.rows);
@@ -58,7 +66,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_direct(UpdatePara
             for (int u = 0; u < UPD_UNROLL; ++u)
                 if (i + u < i1) {
                     v[u] = ld_stream2(base + (size_t)u * U.ld);
-                    pc[u] = __ldg(U.pcol + i + u);
+                    pc[u] = __ldg(pcol + i + u);
                 }
 #pragma unroll
             for (int u = 0; u < UPD_UNROLL; ++u)
@@ -68,6 +76,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_direct(UpdatePara
                     o.y = __fma_rn(-pc[u], pr.y, v[u].y);
                     if (i + u == r) o = pr;
                     st_stream2(base + (size_t)u * U.ld, o);
+                    if (wb) U.bnext[i + u] = o.x;
+                    if (wk) cnext[i + u] = (kn & 1) ? o.y : o.x;
                 }
         }
     }
@@ -82,6 +92,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_tma_staged(Update
 
     if (!U.st->do_pivot) return;
     const int r = U.st->r;
+    const int cur = U.st->cur, kn = U.st->k_next;
+    const double *pcol = U.colbuf + (size_t)cur * U.pcn;
+    double *cnext = U.colbuf + (size_t)(cur ^ 1) * U.pcn;
     const bool reverse = U.alternate && (U.st->iters & 1);
     const int nct = (int)((U.ld + UPD_TILE_COLS - 1) / UPD_TILE_COLS);
     const int nrb = (U.rows + UPD_TILE_ROWS - 1) / UPD_TILE_ROWS;
@@ -102,7 +115,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_tma_staged(Update
         const uint32_t cbytes = (uint32_t)(UPD_TILE_ROWS * sizeof(double));
         mbar_arrive_expect_tx(&bar[s], pbytes + cbytes);
         tma_load_1d(s_prow[s], U.prow + j0, pbytes, &bar[s]);
-        tma_load_1d(s_pcol[s], U.pcol + (size_t)rb * UPD_TILE_ROWS, cbytes, &bar[s]);
+        tma_load_1d(s_pcol[s], pcol + (size_t)rb * UPD_TILE_ROWS, cbytes, &bar[s]);
     };
 
     long tt = blockIdx.x;
@@ -116,6 +129,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_tma_staged(Update
         const int c = (int)(t % nct), rb = (int)(t / nct);
         const size_t j = (size_t)c * UPD_TILE_COLS + (size_t)threadIdx.x * 2;
         const bool active = j < U.ld;
+        const bool wb = (j == 0);
+        const bool wk = (kn > 0) && (j == ((size_t)kn & ~(size_t)1));
         const int i0 = rb * UPD_TILE_ROWS;
         const int i1 = min(i0 + UPD_TILE_ROWS, U.rows);
         double *base = U.T + (size_t)i0 * U.ld + j;
@@ -145,6 +160,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_tma_staged(Update
                         o.y = __fma_rn(f, pr.y, v[u].y);
                         if (i + u == r) o = pr;
                         st_stream2(base + (size_t)u * U.ld, o);
+                        if (wb) U.bnext[i + u] = o.x;
+                        if (wk) cnext[i + u] = (kn & 1) ? o.y : o.x;
                     }
             }
         }

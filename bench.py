@@ -299,10 +299,18 @@ def gpu_arm(args):
         upd_ms += r["update_ms"]; sel_ms += r["select_ms"]; upd_n += r["update_launches"]
     d.close()
     peak, peak_src = measured_peak()
+    traffic, traffic_src = None, None
+    try:        # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
+        with open(os.path.join(ROOT, "profiles", "r1_update_traffic.json")) as f:
+            tj = json.load(f)
+        if m == M and tj["kernel"].endswith("direct") == ((variant & 0xf) == 2):
+            traffic, traffic_src = tj["traffic_bytes_per_launch"], tj["source"]
+    except Exception:
+        pass
     upd_avg_ms = upd_ms / upd_n
     achieved = alg_bytes / (upd_avg_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": "dense_update_direct" if (variant & 0xf) == 2 else "dense_update_tma_staged",
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                 "avg_launch_ms": upd_avg_ms, "select_avg_ms": sel_ms / upd_n,
                 "kernel_share_of_step": upd_ms / (upd_ms + sel_ms), "frac_of_nominal_8TBs": achieved / 8000.0}

@@ -3,6 +3,8 @@
 // Fills the gap the reference leaves between CreateSMatrix and RevokeSMatrix
 // (Source/simplex.c:40-67): the pivot loop runs device-resident; the host only enqueues
 // (select, eliminate) pairs and reads one small state record every `check_every` pivots.
+#include <cooperative_groups.h>
+
 #include <algorithm>
 #include <new>
 #include <vector>
@@ -33,35 +35,47 @@ struct lpgpu_dense {
 
 namespace lpgpu {
 
-// Ratio test on the compact copies the previous elimination pass left behind (lookahead):
-// col[i] = a_ik and bcol[i] = b_i of the CURRENT tableau, contiguous -> coalesced.
-__device__ __forceinline__ Cand ratio_compact(const double *col, const double *bcol, int m, double eps, Cand *scratch) {
-    Cand c = cand_none();
-    for (int i = (int)threadIdx.x; i < m; i += blockDim.x) {
-        const double a = col[i];
-        if (a > eps) {
-            Cand t;
-            t.p = 0.0;
-            t.q = -(bcol[i] / a);
-            t.idx = i;
-            if (cand_better(t, c)) c = t;
-        }
+namespace cg = cooperative_groups;
+
+constexpr int SELECT_CLUSTER = 8;     // CTAs per cluster (portable maximum); one cluster per launch
+
+// Best candidate over the whole cluster: block reduction, then every CTA pushes its winner into
+// every CTA's shared memory (DSMEM stores) and one cluster barrier makes them visible.
+// `slot` must be used for ONE exchange per launch (no reuse hazards).
+__device__ __forceinline__ Cand cluster_best(cg::cluster_group &cl, Cand c, Cand *scratch, Cand *slot) {
+    c = block_best(c, scratch);
+    if (threadIdx.x < SELECT_CLUSTER) {
+        Cand *remote = cl.map_shared_rank(slot, threadIdx.x);
+        remote[cl.block_rank()] = c;
     }
-    return block_best(c, scratch);
+    cl.sync();
+    const int lane = threadIdx.x & 31;
+    Cand v = (lane < SELECT_CLUSTER) ? slot[lane] : cand_none();
+    return warp_best(v);
 }
 
-// One CTA decides a pivot and stages it for the elimination pass.
+// One thread-block cluster (8 CTAs x 1024 threads, distributed shared memory for the arg-min /
+// arg-max exchange) decides a pivot and stages it for the elimination pass.
 //   fast path  (st->k_next > 0): the entering column was priced one pivot ahead and its values
 //              (and b) were extracted by the previous elimination pass into compact buffers, so
-//              only the ratio test, the pivot-row scaling and the next pricing remain;
-//   full path  : dense_select.cuh decide() over the tableau in HBM (first pivot, phase changes,
-//              drive-out pivots, terminal statuses).
-// Either way the kernel then prices the pivot AFTER this one (lookahead): the objective row(s)
+//              only the ratio test, the pivot-row scaling and the next pricing remain -- each a
+//              single memory round trip spread over 8192 threads;
+//   full path  : dense_select.cuh decide() over the tableau in HBM, run by CTA 0 and broadcast
+//              (first pivot, phase changes, drive-out pivots, terminal statuses).
+// Either way the cluster then prices the pivot AFTER this one (lookahead): the objective row(s)
 // after elimination are sigma'_j = fma(-sigma_k, a_rj', sigma_j) -- the same operation on the
 // same operands the elimination pass performs, so the choice is bit-identical to pricing the
 // updated tableau.  forced_k > 0: skip the decision and pivot on (forced_r, forced_k).
-__global__ void __launch_bounds__(SELECT_THREADS) dense_select_kernel(DenseParams P, int forced_r, int forced_k) {
+__global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
+dense_select_kernel(DenseParams P, int forced_r, int forced_k) {
     __shared__ Cand scratch[SELECT_THREADS / 32];
+    __shared__ Cand slot_ratio[SELECT_CLUSTER], slot_look[SELECT_CLUSTER];
+    __shared__ Decision dsh;
+    cg::cluster_group cl = cg::this_cluster();
+    const int rank = (int)cl.block_rank();
+    const int gtid = rank * SELECT_THREADS + (int)threadIdx.x;
+    constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
+
     PivotState *st = P.st;
     int r = -1, k = 0, cur = st->cur, phase = st->phase;
     bool fast = false;
@@ -70,24 +84,42 @@ __global__ void __launch_bounds__(SELECT_THREADS) dense_select_kernel(DenseParam
         r = forced_r;
         k = forced_k;
     } else {
-        // all threads read the same state; nothing below writes it before the final section
+        // every thread of the cluster reads the same state; it is written only in the final section
         const int status0 = st->status, iters = st->iters, p10 = st->phase1_iters;
         const int budget = st->budget, knext = st->k_next;
         if (status0 != LPGPU_RUNNING) {
-            __syncthreads();
-            if (threadIdx.x == 0) st->do_pivot = 0;
+            cl.sync();                         // nobody still reads the state
+            if (gtid == 0) st->do_pivot = 0;
             return;
         }
         Decision D;
         if (knext > 0 && phase != PH_DRIVEOUT) {
+            // ratio test on the compact copies left by the previous elimination pass (coalesced)
+            const double *col = P.pcol + (size_t)(cur ^ 1) * P.pcn;
+            Cand c = cand_none();
+            for (int i = gtid; i < P.m; i += GSTRIDE) {
+                const double a = col[i];
+                if (a > P.eps) {
+                    Cand t;
+                    t.p = 0.0;
+                    t.q = -(P.bnext[i] / a);
+                    t.idx = i;
+                    if (cand_better(t, c)) c = t;
+                }
+            }
+            const Cand l = cluster_best(cl, c, scratch, slot_ratio);
             D.status = status0; D.phase = phase; D.p1 = p10; D.k = knext; D.r = -1; D.have = false;
-            const Cand l = ratio_compact(P.pcol + (size_t)(cur ^ 1) * P.pcn, P.bnext, P.m, P.eps, scratch);
             if (l.idx < 0) D.status = LPGPU_UNBOUNDED;
             else { D.r = l.idx; D.have = true; }
             if (D.have && iters >= P.max_iter) { D.status = LPGPU_ITER_LIMIT; D.have = false; }
             fast = true;
         } else {
-            D = decide(P, scratch, status0, phase, iters, p10);
+            if (rank == 0) {
+                D = decide(P, scratch, status0, phase, iters, p10);
+                if (threadIdx.x < SELECT_CLUSTER) *cl.map_shared_rank(&dsh, threadIdx.x) = D;
+            }
+            cl.sync();
+            D = dsh;
         }
         // out of budget for this run call: the decision still settles terminal statuses, a
         // pending pivot is left for the next call (status stays RUNNING, lookahead kept)
@@ -96,8 +128,8 @@ __global__ void __launch_bounds__(SELECT_THREADS) dense_select_kernel(DenseParam
         k = D.k;
         phase = D.phase;
         if (D.have && fast) cur ^= 1;
-        __syncthreads();
-        if (threadIdx.x == 0) {
+        cl.sync();                             // all state reads are done before it is rewritten
+        if (gtid == 0) {
             st->status = D.status;
             st->phase = D.phase;
             st->phase1_iters = (D.phase == PH_ONE) ? iters + (D.have ? 1 : 0) : D.p1;
@@ -117,24 +149,22 @@ __global__ void __launch_bounds__(SELECT_THREADS) dense_select_kernel(DenseParam
     // ---- stage the pivot: pivot column (all rows incl. objective rows) and scaled pivot row
     double *pcol = P.pcol + (size_t)cur * P.pcn;
     const int rows = P.m + P.R;
-    if (!fast) {
-        for (int i = (int)threadIdx.x; i < rows; i += blockDim.x) pcol[i] = P.T[(size_t)i * P.ld + (size_t)k];
-        __syncthreads();                      // pcol[m..] is read below by every thread
-    }
-    const double piv = pcol[r];
+    if (!fast)
+        for (int i = gtid; i < rows; i += GSTRIDE) pcol[i] = P.T[(size_t)i * P.ld + (size_t)k];
+    const double piv = P.T[(size_t)r * P.ld + (size_t)k];
     const double *xr = P.T + (size_t)r * P.ld;
 
     // lookahead pricing mode for the pivot after this one
     const bool look = (forced_k <= 0) && (phase != PH_DRIVEOUT);
     const bool bigm = (P.method == LPGPU_BIGM);
-    const int prow_obj = (phase == PH_ONE) ? P.m + 1 : P.m;      // row priced when not Big-M
+    const int prow_obj = bigm ? P.m : ((phase == PH_ONE) ? P.m + 1 : P.m);
     const int jmax = (P.method == LPGPU_TWOPHASE && phase == PH_MAIN) ? P.n - P.n_art : P.n;
-    const double *oc = P.T + (size_t)(bigm ? P.m : prow_obj) * P.ld;
+    const double *oc = P.T + (size_t)prow_obj * P.ld;
     const double *om = P.T + (size_t)(P.m + 1) * P.ld;            // Big-M row (R = 2 only)
-    const double fc = -pcol[bigm ? P.m : prow_obj];
-    const double fm = bigm ? -pcol[P.m + 1] : 0.0;
+    const double fc = -oc[k];
+    const double fm = bigm ? -om[k] : 0.0;
     Cand c = cand_none();
-    for (size_t j = threadIdx.x; j < P.ld; j += blockDim.x) {
+    for (size_t j = (size_t)gtid; j < P.ld; j += GSTRIDE) {
         const double pr = xr[j] / piv;
         P.prow[j] = pr;
         if (look && j >= 1 && j <= (size_t)jmax) {
@@ -154,10 +184,10 @@ __global__ void __launch_bounds__(SELECT_THREADS) dense_select_kernel(DenseParam
     }
     int knew = 0;
     if (look) {
-        c = block_best(c, scratch);
+        c = cluster_best(cl, c, scratch, slot_look);
         knew = c.idx > 0 ? c.idx : 0;
     }
-    if (threadIdx.x == 0) {
+    if (gtid == 0) {
         P.basis[r] = k;
         st->k_next = knew;
         if (forced_k > 0) { st->r = r; st->k = k; st->do_pivot = 1; }
@@ -360,7 +390,7 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
         const int chunk = std::min(chunk_max, max_pivots - launched);
         for (int c = 0; c < chunk; ++c) {
             if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c], ctx->stream));
-            dense_select_kernel<<<1, SELECT_THREADS, 0, ctx->stream>>>(P, -1, 0);
+            dense_select_kernel<<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(P, -1, 0);
             LP_LAUNCH_CHECK(ctx);
             if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c + 1], ctx->stream));
             rc = launch_update(d);
@@ -387,7 +417,7 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
     if (d->h_st->status == LPGPU_RUNNING) {
         // budget spent: one decision-only select settles a terminal status (optimal, iteration
         // limit, ...) without applying a pivot, so a run of exactly the needed pivots reports it
-        dense_select_kernel<<<1, SELECT_THREADS, 0, ctx->stream>>>(P, -1, 0);
+        dense_select_kernel<<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(P, -1, 0);
         LP_LAUNCH_CHECK(ctx);
         rc = read_state(d);
         if (rc != LPGPU_OK) return rc;
@@ -418,7 +448,7 @@ int lpgpu_dense_pivot(lpgpu_dense *d, int r, int k) {
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
     const DenseParams P = make_params(d);
     d->la_dirty = true;
-    dense_select_kernel<<<1, SELECT_THREADS, 0, ctx->stream>>>(P, r, k);
+    dense_select_kernel<<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(P, r, k);
     LP_LAUNCH_CHECK(ctx);
     int rc = launch_update(d);
     if (rc != LPGPU_OK) return rc;

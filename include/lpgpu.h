@@ -142,6 +142,36 @@ int lpgpu_batched_run(lpgpu_batched *b, const lpgpu_opts *opts, float *kernel_ms
 int lpgpu_batched_download(lpgpu_batched *b, int *status, int *iters, double *z, double *x,
                            int *basis_out, int *pivot_log, double *T_final);
 
+/* ---- one large tableau, column-sharded over several GPUs ------------------------------ */
+/* Each rank owns a contiguous block of the columns 1..n plus a replica of the b column, the
+ * basis and the pivot state.  Per pivot the ranks exchange (a) one (reduced cost, global column)
+ * candidate each -- the arg-max over those picks the entering column -- and (b) the entering
+ * column itself, from the rank that owns it; the ratio test then runs redundantly on every
+ * rank, so no (ratio, row) exchange is needed in this layout.
+ * Methods: LPGPU_PLAIN and LPGPU_BIGM.
+ *   id128 != NULL : one rank per process, exchange = ncclAllGather over NVLink (libnccl is
+ *                   dlopen'ed here).  Rank 0 makes the id with lpgpu_shard_unique_id and the
+ *                   host ships its 128 bytes to the other ranks by any means it has.
+ *   id128 == NULL : all `world` ranks live in this process on ctx's device and exchange by
+ *                   device copies (single-GPU test vehicle for the N > 1 logic); `rank` ignored. */
+typedef struct lpgpu_shard lpgpu_shard;
+#define LPGPU_NCCL_ID_BYTES 128
+int lpgpu_shard_unique_id(void *id128);
+/* block of rank: global columns col0 .. col0+ncols-1 (1-based); blocks differ by at most one column */
+int lpgpu_shard_columns(int n, int world, int rank, int *col0, int *ncols);
+int lpgpu_shard_create(lpgpu_ctx *ctx, int rank, int world, const void *id128, int m, int n, int R,
+                       lpgpu_shard **out);
+void lpgpu_shard_destroy(lpgpu_shard *s);
+/* T: the GLOBAL tableau (m+R) x (n+1) in host memory; each local rank copies b and its own block */
+int lpgpu_shard_upload(lpgpu_shard *s, const double *T, size_t ld, const int *basis);
+int lpgpu_shard_synth(lpgpu_shard *s, uint64_t seed, uint64_t lp_index, int ns);
+int lpgpu_shard_reset(lpgpu_shard *s, const lpgpu_opts *opts);
+/* collective: every rank must call it with the same max_pivots */
+int lpgpu_shard_run(lpgpu_shard *s, int max_pivots, lpgpu_result *res);
+/* writes b, the local ranks' column blocks and the objective cells into the GLOBAL layout of T
+ * (other ranks' columns are left untouched); basis / pivot_log (global columns) / x (n) are replicas */
+int lpgpu_shard_download(lpgpu_shard *s, double *T, size_t ld, int *basis, int *pivot_log, double *x);
+
 /* ---- host-side helpers (no GPU work) --------------------------------------------- */
 /* rel[i]: -2 "<=", 2 ">=", 3 "=" (Source/public.h:57).  Builds the canonical tableau of
  *   max c.x  s.t.  A x rel b, x >= 0

@@ -6,8 +6,8 @@ Python mirror used by the tests and bench.py.  No CPU fallback.
 """
 from .capi import (BIGM, INFEASIBLE, ITER_LIMIT, OPTIMAL, PLAIN, RUNNING, STATUS_NAMES, TWOPHASE, UNBOUNDED,
                    LpgpuError)
-from .simplex import (BatchedLPs, Context, DenseTableau, build_tableau, solve_batched, solve_dense, synth_host)
+from .simplex import (BatchedLPs, Context, DenseTableau, ShardedTableau, build_tableau, solve_batched, solve_dense, synth_host)
 
-__all__ = ["Context", "DenseTableau", "BatchedLPs", "solve_dense", "solve_batched", "build_tableau", "synth_host",
+__all__ = ["Context", "DenseTableau", "BatchedLPs", "ShardedTableau", "solve_dense", "solve_batched", "build_tableau", "synth_host",
            "PLAIN", "BIGM", "TWOPHASE", "OPTIMAL", "UNBOUNDED", "INFEASIBLE", "ITER_LIMIT", "RUNNING",
            "STATUS_NAMES", "LpgpuError"]

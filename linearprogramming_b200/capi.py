@@ -17,6 +17,7 @@ STATUS_NAMES = {0: "OPTIMAL", 1: "UNBOUNDED", 2: "INFEASIBLE", 3: "ITER_LIMIT", 
 KEEP_FINAL = 0x1000      # batched: keep the final tableaux on the device (parity tests)
 DIRECT = 0x2             # dense: direct-load elimination kernel instead of the TMA-staged default
 NO_ALTERNATE = 0x200     # dense: do not alternate the sweep direction between pivots
+NCCL_ID_BYTES = 128
 
 
 class Opts(C.Structure):
@@ -72,6 +73,15 @@ SIGNATURES = {
     "lpgpu_batched_synth": (C.c_int, [_vp, C.c_uint64, C.c_uint64, C.c_int]),
     "lpgpu_batched_run": (C.c_int, [_vp, C.POINTER(Opts), C.POINTER(C.c_float)]),
     "lpgpu_batched_download": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "lpgpu_shard_unique_id": (C.c_int, [_vp]),
+    "lpgpu_shard_columns": (C.c_int, [C.c_int, C.c_int, C.c_int, _ip, _ip]),
+    "lpgpu_shard_create": (C.c_int, [_vp, C.c_int, C.c_int, _vp, C.c_int, C.c_int, C.c_int, C.POINTER(_vp)]),
+    "lpgpu_shard_destroy": (None, [_vp]),
+    "lpgpu_shard_upload": (C.c_int, [_vp, _vp, C.c_size_t, _vp]),
+    "lpgpu_shard_synth": (C.c_int, [_vp, C.c_uint64, C.c_uint64, C.c_int]),
+    "lpgpu_shard_reset": (C.c_int, [_vp, C.POINTER(Opts)]),
+    "lpgpu_shard_run": (C.c_int, [_vp, C.c_int, C.POINTER(Result)]),
+    "lpgpu_shard_download": (C.c_int, [_vp, _vp, C.c_size_t, _vp, _vp, _vp]),
     "lpgpu_count_columns": (C.c_int, [C.c_int, C.c_int, _vp, _vp, _ip]),
     "lpgpu_build_tableau": (C.c_int, [C.c_int, C.c_int, _vp, C.c_size_t, _vp, _vp, _vp, C.c_int, _vp, C.c_size_t, _vp,
                                       _ip]),

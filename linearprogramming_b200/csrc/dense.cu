@@ -3,56 +3,17 @@
 // Fills the gap the reference leaves between CreateSMatrix and RevokeSMatrix
 // (Source/simplex.c:40-67): the pivot loop runs device-resident; the host only enqueues
 // (select, eliminate) pairs and reads one small state record every `check_every` pivots.
-#include <cooperative_groups.h>
-
 #include <algorithm>
 #include <new>
 #include <vector>
 
-#include "ctx.h"
-#include "dense_select.cuh"
+#include "dense_internal.h"
 #include "dense_update.cuh"
 
 using namespace lpgpu;
 
-struct lpgpu_dense {
-    lpgpu_ctx *ctx;
-    int m, n, R;
-    size_t ld;
-    double *T;
-    int *basis;
-    double *prow, *pcol, *bnext, *xbuf;   // pcol: 2 x pcn (colbuf)
-    size_t pcn;
-    bool la_dirty;          // tableau changed behind the lookahead's back (upload / synth / forced pivot)
-    PivotState *st;
-    PivotState *h_st;       // pinned mirror
-    int *log;
-    int log_cap;
-    lpgpu_opts opts;
-    int grid_update;
-    std::vector<cudaEvent_t> ev;
-};
 
 namespace lpgpu {
-
-namespace cg = cooperative_groups;
-
-constexpr int SELECT_CLUSTER = 8;     // CTAs per cluster (portable maximum); one cluster per launch
-
-// Best candidate over the whole cluster: block reduction, then every CTA pushes its winner into
-// every CTA's shared memory (DSMEM stores) and one cluster barrier makes them visible.
-// `slot` must be used for ONE exchange per launch (no reuse hazards).
-__device__ __forceinline__ Cand cluster_best(cg::cluster_group &cl, Cand c, Cand *scratch, Cand *slot) {
-    c = block_best(c, scratch);
-    if (threadIdx.x < SELECT_CLUSTER) {
-        Cand *remote = cl.map_shared_rank(slot, threadIdx.x);
-        remote[cl.block_rank()] = c;
-    }
-    cl.sync();
-    const int lane = threadIdx.x & 31;
-    Cand v = (lane < SELECT_CLUSTER) ? slot[lane] : cand_none();
-    return warp_best(v);
-}
 
 // One thread-block cluster (8 CTAs x 1024 threads, distributed shared memory for the arg-min /
 // arg-max exchange) decides a pivot and stages it for the elimination pass.
@@ -194,6 +155,36 @@ dense_select_kernel(DenseParams P, int forced_r, int forced_k) {
     }
 }
 
+DenseParams make_params(const lpgpu_dense *d) {
+    DenseParams P;
+    P.T = d->T; P.ld = d->ld; P.m = d->m; P.n = d->n; P.R = d->R;
+    P.basis = d->basis; P.prow = d->prow; P.pcol = d->pcol; P.pcn = d->pcn; P.bnext = d->bnext; P.st = d->st;
+    P.log = d->log; P.log_cap = d->log_cap;
+    P.eps = d->opts.eps; P.max_iter = d->opts.max_iter; P.method = d->opts.method; P.n_art = d->opts.n_art;
+    return P;
+}
+
+int launch_update(lpgpu_dense *d, double *cnext) {
+    lpgpu_ctx *ctx = d->ctx;
+    UpdateParams U;
+    U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.prow = d->prow; U.colbuf = d->pcol; U.pcn = d->pcn; U.bnext = d->bnext; U.st = d->st; U.cnext = cnext;
+    // variant: low nibble 0/1 = TMA-staged kernel (default), 2 = direct-load kernel;
+    //          0x200 = do NOT alternate the sweep direction between pivots
+    U.alternate = (d->opts.variant & 0x200) ? 0 : 1;
+    const int kind = d->opts.variant & 0xf;
+    if (kind == 2) dense_update_direct<<<d->grid_update, UPD_THREADS, 0, ctx->stream>>>(U);
+    else dense_update_tma_staged<<<d->grid_update, UPD_THREADS, 0, ctx->stream>>>(U);
+    LP_LAUNCH_CHECK(ctx);
+    return LPGPU_OK;
+}
+
+int read_state(lpgpu_dense *d) {
+    lpgpu_ctx *ctx = d->ctx;
+    LP_CUDA(ctx, cudaMemcpyAsync(d->h_st, d->st, sizeof(PivotState), cudaMemcpyDeviceToHost, ctx->stream));
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return LPGPU_OK;
+}
+
 }  // namespace lpgpu
 
 namespace {
@@ -206,29 +197,6 @@ __global__ void extract_x_kernel(const double *T, size_t ld, const int *basis, i
 }
 
 size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-
-DenseParams make_params(const lpgpu_dense *d) {
-    DenseParams P;
-    P.T = d->T; P.ld = d->ld; P.m = d->m; P.n = d->n; P.R = d->R;
-    P.basis = d->basis; P.prow = d->prow; P.pcol = d->pcol; P.pcn = d->pcn; P.bnext = d->bnext; P.st = d->st;
-    P.log = d->log; P.log_cap = d->log_cap;
-    P.eps = d->opts.eps; P.max_iter = d->opts.max_iter; P.method = d->opts.method; P.n_art = d->opts.n_art;
-    return P;
-}
-
-int launch_update(lpgpu_dense *d) {
-    lpgpu_ctx *ctx = d->ctx;
-    UpdateParams U;
-    U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.prow = d->prow; U.colbuf = d->pcol; U.pcn = d->pcn; U.bnext = d->bnext; U.st = d->st;
-    // variant: low nibble 0/1 = TMA-staged kernel (default), 2 = direct-load kernel;
-    //          0x200 = do NOT alternate the sweep direction between pivots
-    U.alternate = (d->opts.variant & 0x200) ? 0 : 1;
-    const int kind = d->opts.variant & 0xf;
-    if (kind == 2) dense_update_direct<<<d->grid_update, UPD_THREADS, 0, ctx->stream>>>(U);
-    else dense_update_tma_staged<<<d->grid_update, UPD_THREADS, 0, ctx->stream>>>(U);
-    LP_LAUNCH_CHECK(ctx);
-    return LPGPU_OK;
-}
 
 int size_grid(lpgpu_dense *d) {
     lpgpu_ctx *ctx = d->ctx;
@@ -356,12 +324,6 @@ int lpgpu_dense_synth(lpgpu_dense *d, uint64_t seed, uint64_t lp_index, int ns) 
     return LPGPU_OK;
 }
 
-static int read_state(lpgpu_dense *d) {
-    lpgpu_ctx *ctx = d->ctx;
-    LP_CUDA(ctx, cudaMemcpyAsync(d->h_st, d->st, sizeof(PivotState), cudaMemcpyDeviceToHost, ctx->stream));
-    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return LPGPU_OK;
-}
 
 int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
     if (!d || !res || max_pivots < 0) return LPGPU_EINVAL;
@@ -393,7 +355,7 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
             dense_select_kernel<<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(P, -1, 0);
             LP_LAUNCH_CHECK(ctx);
             if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c + 1], ctx->stream));
-            rc = launch_update(d);
+            rc = launch_update(d, nullptr);
             if (rc != LPGPU_OK) return rc;
             if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c + 2], ctx->stream));
         }
@@ -450,7 +412,7 @@ int lpgpu_dense_pivot(lpgpu_dense *d, int r, int k) {
     d->la_dirty = true;
     dense_select_kernel<<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(P, r, k);
     LP_LAUNCH_CHECK(ctx);
-    int rc = launch_update(d);
+    int rc = launch_update(d, nullptr);
     if (rc != LPGPU_OK) return rc;
     LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return LPGPU_OK;

@@ -1,0 +1,36 @@
+// dense_internal.h -- what dense.cu shares with shard.cu (the column-sharded path reuses the
+// single-GPU tableau object and its elimination launch for each rank's column block).
+#pragma once
+
+#include <vector>
+
+#include "ctx.h"
+#include "dense_select.cuh"
+
+struct lpgpu_dense {
+    lpgpu_ctx *ctx;
+    int m, n, R;
+    size_t ld;
+    double *T;
+    int *basis;
+    double *prow, *pcol, *bnext, *xbuf;   // pcol: 2 x pcn (colbuf)
+    size_t pcn;
+    bool la_dirty;          // tableau changed behind the lookahead's back (upload / synth / forced pivot)
+    lpgpu::PivotState *st;
+    lpgpu::PivotState *h_st;       // pinned mirror
+    int *log;
+    int log_cap;
+    lpgpu_opts opts;
+    int grid_update;
+    std::vector<cudaEvent_t> ev;
+};
+
+namespace lpgpu {
+
+DenseParams make_params(const lpgpu_dense *d);
+// Enqueue the elimination pass.  cnext: where the pass leaves the next entering column
+// (nullptr = the other half of the tableau's own ping-pong buffer).
+int launch_update(lpgpu_dense *d, double *cnext);
+int read_state(lpgpu_dense *d);
+
+}  // namespace lpgpu

@@ -11,6 +11,8 @@
 // shuffles plus a block-level tree (common.cuh: block_best).
 #pragma once
 
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace lpgpu {
@@ -35,6 +37,25 @@ struct DenseParams {
 };
 
 constexpr int SELECT_THREADS = 1024;
+
+namespace cg = cooperative_groups;
+
+constexpr int SELECT_CLUSTER = 8;     // CTAs per cluster (portable maximum); one cluster per launch
+
+// Best candidate over the whole cluster: block reduction, then every CTA pushes its winner into
+// every CTA's shared memory (DSMEM stores) and one cluster barrier makes them visible.
+// `slot` must be used for ONE exchange per launch (no reuse hazards).
+__device__ __forceinline__ Cand cluster_best(cg::cluster_group &cl, Cand c, Cand *scratch, Cand *slot) {
+    c = block_best(c, scratch);
+    if (threadIdx.x < SELECT_CLUSTER) {
+        Cand *remote = cl.map_shared_rank(slot, threadIdx.x);
+        remote[cl.block_rank()] = c;
+    }
+    cl.sync();
+    const int lane = threadIdx.x & 31;
+    Cand v = (lane < SELECT_CLUSTER) ? slot[lane] : cand_none();
+    return warp_best(v);
+}
 
 __device__ __forceinline__ Cand price_row(const DenseParams &P, int row, int jmax, Cand *scratch) {
     const double *x = P.T + (size_t)row * P.ld;

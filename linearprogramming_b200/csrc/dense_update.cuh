@@ -33,6 +33,7 @@ struct UpdateParams {
     double *bnext;          // b column as updated by this pass (written)
     const PivotState *st;
     int alternate;          // 1: walk the tasks backwards on odd pivots (L2 reuse of the tail)
+    double *cnext;          // where the next entering column goes; nullptr = colbuf half st->cur ^ 1
 };
 
 __device__ __forceinline__ long upd_task(long t, long ntasks, bool reverse) { return reverse ? ntasks - 1 - t : t; }
@@ -43,7 +44,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_direct(UpdatePara
     const int r = U.st->r;
     const int cur = U.st->cur, kn = U.st->k_next;
     const double *pcol = U.colbuf + (size_t)cur * U.pcn;
-    double *cnext = U.colbuf + (size_t)(cur ^ 1) * U.pcn;
+    double *cnext = U.cnext ? U.cnext : U.colbuf + (size_t)(cur ^ 1) * U.pcn;
     const bool reverse = U.alternate && (U.st->iters & 1);
     const int nct = (int)((U.ld + UPD_TILE_COLS - 1) / UPD_TILE_COLS);
     const int nrb = (U.rows + UPD_TILE_ROWS - 1) / UPD_TILE_ROWS;
@@ -94,7 +95,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_tma_staged(Update
     const int r = U.st->r;
     const int cur = U.st->cur, kn = U.st->k_next;
     const double *pcol = U.colbuf + (size_t)cur * U.pcn;
-    double *cnext = U.colbuf + (size_t)(cur ^ 1) * U.pcn;
+    double *cnext = U.cnext ? U.cnext : U.colbuf + (size_t)(cur ^ 1) * U.pcn;
     const bool reverse = U.alternate && (U.st->iters & 1);
     const int nct = (int)((U.ld + UPD_TILE_COLS - 1) / UPD_TILE_COLS);
     const int nrb = (U.rows + UPD_TILE_ROWS - 1) / UPD_TILE_ROWS;

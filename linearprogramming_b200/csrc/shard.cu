@@ -1,0 +1,561 @@
+// shard.cu -- one large tableau column-sharded over several GPUs (include/lpgpu.h, lpgpu_shard_*).
+//
+// Rank g owns global columns col0_g .. col0_g + ncols_g - 1 of the SimplexMatrix-shaped tableau
+// (Source/matrix.c:42-72) as a local tableau (m+R) x (1 + ncols_g) whose column 0 is a replica of
+// the b column; basis and pivot state are replicated too.  Per pivot:
+//
+//   shard_select    ratio test on the exchanged entering column (redundant on every rank), pivot-row
+//                   scaling of the local block, and LOOKAHEAD pricing of the local block for the pivot
+//                   after this one -> one (p, q, global column) candidate per rank
+//   exchange A      all-gather of the candidates (32 B per rank)
+//   shard_resolve   arg-max over the gathered candidates (ties -> lowest global column)
+//   dense_update    the single-GPU elimination kernel on the local block; the owner of the next
+//                   entering column extracts its updated values during the pass
+//   exchange B      all-gather of that column (8 * (m+R) bytes per rank; only the owner's is read)
+//
+// so a pivot costs one streaming pass over each rank's block plus two latency-bound exchanges.
+// Exchanges go through ncclAllGather (one process per GPU, NVLink / NVSwitch) or, when every rank
+// lives in one process on one device, through device copies (test vehicle for the N > 1 logic).
+#include <algorithm>
+#include <new>
+#include <string.h>
+#include <vector>
+
+#include "dense_internal.h"
+#include "shard_nccl.h"
+
+using namespace lpgpu;
+
+namespace lpgpu {
+
+struct ShardState {
+    int k_next;     // entering column of the pivot to decide next (global, 1-based; 0 = no candidate)
+    int owner;      // rank that owns it
+};
+
+struct ShardParams {
+    DenseParams P;           // the local tableau; P.n = local columns, P.basis holds GLOBAL columns
+    int rank, world;
+    int col0;                // global index of local column 1
+    int n_global, n_art;     // artificial columns are the last n_art GLOBAL columns
+    ShardState *sh;
+    double *sendpair;        // 4 doubles: p, q, global column (-1 = none), 0
+    const double *pairs;     // world x 4 doubles
+    double *sendcol;         // pcn doubles: the next entering column if this rank owns it
+    const double *gathered;  // world x pcn doubles
+};
+
+constexpr int PAIR_DOUBLES = 4;
+
+__device__ __forceinline__ void store_pair(double *dst, const Cand &c, int col0) {
+    dst[0] = c.p;
+    dst[1] = c.q;
+    dst[2] = c.idx > 0 ? (double)(col0 + c.idx - 1) : -1.0;
+    dst[3] = 0.0;
+}
+
+// arg-max over the gathered candidates; idx = GLOBAL column, owner through *owner
+__device__ __forceinline__ Cand best_pair(const double *pairs, int world, int *owner) {
+    Cand best = cand_none();
+    int who = 0;
+    for (int g = 0; g < world; ++g) {
+        Cand t;
+        t.p = pairs[g * PAIR_DOUBLES];
+        t.q = pairs[g * PAIR_DOUBLES + 1];
+        t.idx = (int)pairs[g * PAIR_DOUBLES + 2];
+        if (t.idx > 0 && cand_better(t, best)) { best = t; who = g; }
+    }
+    *owner = who;
+    return best;
+}
+
+// Bootstrap pricing straight from the tableau (first pivot after an upload / synth).
+__global__ void __launch_bounds__(SELECT_THREADS) shard_price_kernel(ShardParams S) {
+    __shared__ Cand scratch[SELECT_THREADS / 32];
+    const DenseParams &P = S.P;
+    Cand c = (P.method == LPGPU_BIGM) ? price_bigm(P, scratch) : price_row(P, P.m, P.n, scratch);
+    if (threadIdx.x == 0) store_pair(S.sendpair, c, S.col0);
+}
+
+// After exchange A.  gather = 1 (bootstrap): the owner also pulls the entering column out of its
+// tableau (strided) and every rank refreshes its compact copy of b.
+__global__ void __launch_bounds__(SELECT_THREADS) shard_resolve_kernel(ShardParams S, int gather) {
+    const DenseParams &P = S.P;
+    int owner = 0;
+    const Cand best = best_pair(S.pairs, S.world, &owner);
+    const int k = best.idx > 0 ? best.idx : 0;
+    const bool mine = (k > 0) && (owner == S.rank);
+    const int kl = mine ? k - S.col0 + 1 : 0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        S.sh->k_next = k;
+        S.sh->owner = owner;
+        P.st->k_next = kl;
+    }
+    if (gather) {
+        const int rows = P.m + P.R;
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rows; i += gridDim.x * blockDim.x) {
+            if (mine) S.sendcol[i] = P.T[(size_t)i * P.ld + (size_t)kl];
+            P.bnext[i] = P.T[(size_t)i * P.ld];
+        }
+    }
+}
+
+// any artificial (GLOBAL column > n_global - n_art) still basic at a positive level?  b from bnext.
+__device__ __forceinline__ bool shard_art_positive(const ShardParams &S) {
+    const int nreal = S.n_global - S.n_art;
+    int f = 0;
+    for (int i = (int)threadIdx.x; i < S.P.m; i += blockDim.x)
+        if (S.P.basis[i] > nreal && S.P.bnext[i] > S.P.eps) f = 1;
+    return __syncthreads_or(f) != 0;
+}
+
+// One cluster of 8 CTAs x 1024 threads per rank (same shape as dense_select_kernel's fast path).
+__global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
+shard_select_kernel(ShardParams S) {
+    __shared__ Cand scratch[SELECT_THREADS / 32];
+    __shared__ Cand slot_ratio[SELECT_CLUSTER], slot_look[SELECT_CLUSTER];
+    cg::cluster_group cl = cg::this_cluster();
+    const DenseParams &P = S.P;
+    const int rank = (int)cl.block_rank();
+    const int gtid = rank * SELECT_THREADS + (int)threadIdx.x;
+    constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
+
+    PivotState *st = P.st;
+    const int status0 = st->status, iters = st->iters, budget = st->budget;
+    const int k = S.sh->k_next, owner = S.sh->owner;
+    if (status0 != LPGPU_RUNNING) {
+        cl.sync();
+        if (gtid == 0) st->do_pivot = 0;
+        return;
+    }
+    int status = status0, r = -1;
+    bool have = false;
+    const double *col = S.gathered + (size_t)owner * P.pcn;
+    if (k <= 0) {
+        // nothing prices in: optimal, unless Big-M left an artificial basic at a positive level
+        const bool bad = (P.method == LPGPU_BIGM) && shard_art_positive(S);
+        status = bad ? LPGPU_INFEASIBLE : LPGPU_OPTIMAL;
+    } else {
+        Cand c = cand_none();
+        for (int i = gtid; i < P.m; i += GSTRIDE) {
+            const double a = col[i];
+            if (a > P.eps) {
+                Cand t;
+                t.p = 0.0;
+                t.q = -(P.bnext[i] / a);
+                t.idx = i;
+                if (cand_better(t, c)) c = t;
+            }
+        }
+        const Cand l = cluster_best(cl, c, scratch, slot_ratio);
+        if (l.idx < 0) status = LPGPU_UNBOUNDED;
+        else { r = l.idx; have = true; }
+        if (have && iters >= P.max_iter) { status = LPGPU_ITER_LIMIT; have = false; }
+    }
+    if (have && budget <= 0) have = false;      // pending pivot stays for the next run call
+    cl.sync();                                  // all state reads are done before it is rewritten
+    if (gtid == 0) {
+        st->status = status;
+        st->do_pivot = have ? 1 : 0;
+        st->cur = 0;
+        if (have) {
+            st->r = r;
+            st->k = k;
+            st->iters = iters + 1;
+            st->budget = budget - 1;
+            if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
+            P.basis[r] = k;
+        }
+    }
+    if (!have) return;
+
+    // ---- stage the pivot: entering column (all rows) into the local pivot-column buffer, scaled
+    // local slice of the pivot row, and the local lookahead candidate for the pivot after this one
+    const int rows = P.m + P.R;
+    for (int i = gtid; i < rows; i += GSTRIDE) P.pcol[i] = col[i];
+    const double piv = col[r];
+    const double *xr = P.T + (size_t)r * P.ld;
+    const bool bigm = (P.method == LPGPU_BIGM);
+    const double *oc = P.T + (size_t)P.m * P.ld;
+    const double *om = P.T + (size_t)(P.m + 1) * P.ld;            // Big-M row (R = 2 only)
+    const double fc = -col[P.m];
+    const double fm = bigm ? -col[P.m + 1] : 0.0;
+    Cand c = cand_none();
+    for (size_t j = (size_t)gtid; j < P.ld; j += GSTRIDE) {
+        const double pr = xr[j] / piv;
+        P.prow[j] = pr;
+        if (j >= 1 && j <= (size_t)P.n) {
+            const double q = __fma_rn(fc, pr, oc[j]);
+            Cand t;
+            t.idx = (int)j;
+            if (bigm) {
+                double p = __fma_rn(fm, pr, om[j]);
+                if (fabs(p) <= P.eps) p = 0.0;
+                t.p = p; t.q = q;
+                if ((p > 0.0 || (p == 0.0 && q > P.eps)) && cand_better(t, c)) c = t;
+            } else {
+                t.p = 0.0; t.q = q;
+                if (q > P.eps && cand_better(t, c)) c = t;
+            }
+        }
+    }
+    c = cluster_best(cl, c, scratch, slot_look);
+    if (gtid == 0) store_pair(S.sendpair, c, S.col0);
+}
+
+__global__ void shard_synth_kernel(double *T, size_t ld, int m, int ns, int col0, int ncols, int *basis,
+                                   uint64_t seed, uint64_t lp) {
+    const size_t total = (size_t)(m + 1) * ld;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const int i = (int)(e / ld), jl = (int)(e % ld);
+        double v = 0.0;
+        if (jl == 0) v = synth_elem(seed, lp, m, ns, i, 0);
+        else if (jl <= ncols) v = synth_elem(seed, lp, m, ns, i, col0 + jl - 1);
+        T[e] = v;
+        if (jl == 0 && i < m) basis[i] = 1 + ns + i;
+    }
+}
+
+__global__ void shard_extract_x_kernel(const double *T, size_t ld, const int *basis, int m, int n, double *x) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) {
+        const int j = basis[i];
+        if (j >= 1 && j <= n) x[j - 1] = T[(size_t)i * ld];
+    }
+}
+
+}  // namespace lpgpu
+
+// ------------------------------------------------------------------ host side
+namespace {
+
+struct ShardRank {
+    lpgpu_dense *d;
+    int rank, col0, ncols;
+    ShardState *sh;
+    double *sendpair, *pairs, *sendcol, *gathered;
+};
+
+}  // namespace
+
+struct lpgpu_shard {
+    lpgpu_ctx *ctx;
+    int world, m, n, R;
+    bool use_nccl;
+    ncclComm_t comm;
+    std::vector<ShardRank> rk;        // the ranks that live in this process (1 with NCCL, `world` without)
+    double *pairs_buf, *gath_buf;     // exchange buffers (shared by all local ranks without NCCL)
+    double *xbuf;
+    size_t pcn;
+    bool dirty;                       // tableau changed since the last lookahead (upload / synth / reset)
+    lpgpu_opts opts;
+};
+
+namespace {
+
+#define LP_NCCL(ctx, api, call)                                                                    \
+    do {                                                                                           \
+        ncclResult_t r__ = (call);                                                                 \
+        if (r__ != ncclSuccess)                                                                    \
+            return fail((ctx), LPGPU_ENCCL, "%s:%d: %s: %s", __FILE__, __LINE__, #call, (api)->GetErrorString(r__)); \
+    } while (0)
+
+void split_columns(int n, int world, int rank, int *col0, int *ncols) {
+    const int base = n / world, extra = n % world;
+    *ncols = base + (rank < extra ? 1 : 0);
+    *col0 = 1 + rank * base + std::min(rank, extra);
+}
+
+ShardParams shard_params(const lpgpu_shard *s, const ShardRank &r) {
+    ShardParams S;
+    S.P = make_params(r.d);
+    S.rank = r.rank; S.world = s->world; S.col0 = r.col0; S.n_global = s->n; S.n_art = s->opts.n_art;
+    S.sh = r.sh; S.sendpair = r.sendpair; S.pairs = r.pairs; S.sendcol = r.sendcol; S.gathered = r.gathered;
+    return S;
+}
+
+// exchange A (which = 0): candidates; exchange B (which = 1): entering column.  Without NCCL the
+// local ranks write straight into the shared gather buffers, so there is nothing to move.
+int exchange(lpgpu_shard *s, int which) {
+    if (!s->use_nccl) return LPGPU_OK;
+    const NcclApi *api = nccl_api();
+    const ShardRank &r = s->rk[0];
+    if (which == 0)
+        LP_NCCL(s->ctx, api, api->AllGather(r.sendpair, s->pairs_buf, PAIR_DOUBLES, ncclDouble, s->comm, s->ctx->stream));
+    else
+        LP_NCCL(s->ctx, api, api->AllGather(r.sendcol, s->gath_buf, s->pcn, ncclDouble, s->comm, s->ctx->stream));
+    return LPGPU_OK;
+}
+
+int push_state(lpgpu_shard *s, const PivotState &st) {
+    lpgpu_ctx *ctx = s->ctx;
+    for (ShardRank &r : s->rk) {
+        *r.d->h_st = st;
+        LP_CUDA(ctx, cudaMemcpyAsync(r.d->st, r.d->h_st, sizeof(PivotState), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    return LPGPU_OK;
+}
+
+int enqueue_select(lpgpu_shard *s) {
+    for (ShardRank &r : s->rk) {
+        shard_select_kernel<<<SELECT_CLUSTER, SELECT_THREADS, 0, s->ctx->stream>>>(shard_params(s, r));
+        LP_LAUNCH_CHECK(s->ctx);
+    }
+    return LPGPU_OK;
+}
+
+int enqueue_resolve(lpgpu_shard *s, int gather) {
+    for (ShardRank &r : s->rk) {
+        const int grid = gather ? std::max(1, std::min(64, (s->m + s->R + SELECT_THREADS - 1) / SELECT_THREADS)) : 1;
+        shard_resolve_kernel<<<grid, gather ? SELECT_THREADS : 32, 0, s->ctx->stream>>>(shard_params(s, r), gather);
+        LP_LAUNCH_CHECK(s->ctx);
+    }
+    return LPGPU_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int lpgpu_shard_unique_id(void *id128) {
+    if (!id128) return LPGPU_EINVAL;
+    const NcclApi *api = nccl_api();
+    if (!api) return LPGPU_ENCCL;
+    static_assert(sizeof(ncclUniqueId) == LPGPU_NCCL_ID_BYTES, "NCCL id size");
+    ncclUniqueId id;
+    if (api->GetUniqueId(&id) != ncclSuccess) return LPGPU_ENCCL;
+    memcpy(id128, &id, sizeof id);
+    return LPGPU_OK;
+}
+
+int lpgpu_shard_columns(int n, int world, int rank, int *col0, int *ncols) {
+    if (n < 1 || world < 1 || world > n || rank < 0 || rank >= world || !col0 || !ncols) return LPGPU_EINVAL;
+    split_columns(n, world, rank, col0, ncols);
+    return LPGPU_OK;
+}
+
+int lpgpu_shard_create(lpgpu_ctx *ctx, int rank, int world, const void *id128, int m, int n, int R, lpgpu_shard **out) {
+    if (!ctx || !out) return LPGPU_EINVAL;
+    *out = nullptr;
+    if (m < 1 || n < 1 || (R != 1 && R != 2) || world < 1 || world > n || world > 64)
+        return fail(ctx, LPGPU_EINVAL, "shard_create: bad shape m=%d n=%d R=%d world=%d", m, n, R, world);
+    if (id128 && (rank < 0 || rank >= world)) return fail(ctx, LPGPU_EINVAL, "shard_create: rank %d of %d", rank, world);
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    lpgpu_shard *s = new (std::nothrow) lpgpu_shard();
+    if (!s) return fail(ctx, LPGPU_ENOMEM, "shard_create: host allocation failed");
+    s->ctx = ctx; s->world = world; s->m = m; s->n = n; s->R = R;
+    s->use_nccl = id128 != nullptr; s->comm = nullptr; s->pairs_buf = s->gath_buf = s->xbuf = nullptr; s->dirty = true;
+    lpgpu_default_opts(&s->opts);
+    s->opts.method = (R == 1) ? LPGPU_PLAIN : LPGPU_BIGM;
+    int rc = LPGPU_OK;
+    const int first = s->use_nccl ? rank : 0, last = s->use_nccl ? rank + 1 : world;
+    for (int g = first; g < last && rc == LPGPU_OK; ++g) {
+        ShardRank r{};
+        r.rank = g;
+        split_columns(n, world, g, &r.col0, &r.ncols);
+        rc = lpgpu_dense_create(ctx, m, r.ncols, R, &r.d);
+        if (rc == LPGPU_OK) s->rk.push_back(r);
+    }
+    if (rc != LPGPU_OK) { lpgpu_shard_destroy(s); return rc; }
+    s->pcn = s->rk[0].d->pcn;                   // depends on m + R only: the same on every rank
+    cudaError_t e = cudaSuccess;
+    // without NCCL every local rank sends straight into its slot of the shared gather buffers
+    const size_t npairs = (size_t)world * PAIR_DOUBLES, ncol = (size_t)world * s->pcn;
+    if (e == cudaSuccess) e = cudaMalloc(&s->pairs_buf, npairs * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&s->gath_buf, ncol * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&s->xbuf, (size_t)n * sizeof(double));
+    if (e == cudaSuccess) e = cudaMemsetAsync(s->pairs_buf, 0, npairs * sizeof(double), ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(s->gath_buf, 0, ncol * sizeof(double), ctx->stream);
+    for (ShardRank &r : s->rk) {
+        if (e == cudaSuccess) e = cudaMalloc(&r.sh, sizeof(ShardState));
+        if (e == cudaSuccess) e = cudaMemsetAsync(r.sh, 0, sizeof(ShardState), ctx->stream);
+        r.pairs = s->pairs_buf;
+        r.gathered = s->gath_buf;
+        if (s->use_nccl) {
+            if (e == cudaSuccess) e = cudaMalloc(&r.sendpair, PAIR_DOUBLES * sizeof(double));
+            if (e == cudaSuccess) e = cudaMalloc(&r.sendcol, s->pcn * sizeof(double));
+            if (e == cudaSuccess) e = cudaMemsetAsync(r.sendcol, 0, s->pcn * sizeof(double), ctx->stream);
+        } else {
+            r.sendpair = s->pairs_buf + (size_t)r.rank * PAIR_DOUBLES;
+            r.sendcol = s->gath_buf + (size_t)r.rank * s->pcn;
+        }
+    }
+    if (e != cudaSuccess) {
+        lpgpu_shard_destroy(s);
+        return fail(ctx, e == cudaErrorMemoryAllocation ? LPGPU_ENOMEM : LPGPU_ECUDA, "shard_create: %s", cudaGetErrorString(e));
+    }
+    if (s->use_nccl) {
+        const NcclApi *api = nccl_api();
+        if (!api) { lpgpu_shard_destroy(s); return fail(ctx, LPGPU_ENCCL, "shard_create: libnccl.so.2 could not be loaded"); }
+        ncclUniqueId id;
+        memcpy(&id, id128, sizeof id);
+        ncclResult_t nr = api->CommInitRank(&s->comm, world, id, rank);
+        if (nr != ncclSuccess) {
+            s->comm = nullptr;
+            lpgpu_shard_destroy(s);
+            return fail(ctx, LPGPU_ENCCL, "shard_create: ncclCommInitRank: %s", api->GetErrorString(nr));
+        }
+    }
+    rc = lpgpu_shard_reset(s, &s->opts);
+    if (rc != LPGPU_OK) { lpgpu_shard_destroy(s); return rc; }
+    *out = s;
+    return LPGPU_OK;
+}
+
+void lpgpu_shard_destroy(lpgpu_shard *s) {
+    if (!s) return;
+    cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->stream);
+    if (s->comm) { const NcclApi *api = nccl_api(); if (api) api->CommDestroy(s->comm); }
+    for (ShardRank &r : s->rk) {
+        lpgpu_dense_destroy(r.d);
+        cudaFree(r.sh);
+        if (s->use_nccl) { cudaFree(r.sendpair); cudaFree(r.sendcol); }
+    }
+    cudaFree(s->pairs_buf); cudaFree(s->gath_buf); cudaFree(s->xbuf);
+    delete s;
+}
+
+int lpgpu_shard_reset(lpgpu_shard *s, const lpgpu_opts *opts) {
+    if (!s || !opts) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = s->ctx;
+    if (opts->method == LPGPU_TWOPHASE) return fail(ctx, LPGPU_EINVAL, "shard_reset: the column-sharded path prices PLAIN and BIGM only");
+    if ((opts->method == LPGPU_PLAIN) != (s->R == 1) || opts->n_art < 0 || opts->n_art > s->n)
+        return fail(ctx, LPGPU_EINVAL, "shard_reset: bad options (method/R/n_art)");
+    s->opts = *opts;
+    if (s->opts.check_every <= 0) s->opts.check_every = 64;
+    lpgpu_opts local = s->opts;
+    local.n_art = 0;                     // artificial columns are tested against GLOBAL indices in shard kernels
+    local.time_kernels = 0;
+    for (ShardRank &r : s->rk) {
+        int rc = lpgpu_dense_reset(r.d, &local);
+        if (rc != LPGPU_OK) return rc;
+    }
+    s->dirty = true;
+    return LPGPU_OK;
+}
+
+int lpgpu_shard_upload(lpgpu_shard *s, const double *T, size_t ld, const int *basis) {
+    if (!s || !T || !basis) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = s->ctx;
+    if (ld < (size_t)s->n + 1) return fail(ctx, LPGPU_EINVAL, "shard_upload: ld %zu < n+1", ld);
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t rows = (size_t)s->m + s->R;
+    for (ShardRank &r : s->rk) {
+        lpgpu_dense *d = r.d;
+        LP_CUDA(ctx, cudaMemcpy2DAsync(d->T, d->ld * sizeof(double), T, ld * sizeof(double), sizeof(double), rows,
+                                       cudaMemcpyHostToDevice, ctx->stream));
+        LP_CUDA(ctx, cudaMemcpy2DAsync(d->T + 1, d->ld * sizeof(double), T + r.col0, ld * sizeof(double),
+                                       (size_t)r.ncols * sizeof(double), rows, cudaMemcpyHostToDevice, ctx->stream));
+        LP_CUDA(ctx, cudaMemcpyAsync(d->basis, basis, (size_t)s->m * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    s->dirty = true;
+    return LPGPU_OK;
+}
+
+int lpgpu_shard_synth(lpgpu_shard *s, uint64_t seed, uint64_t lp_index, int ns) {
+    if (!s) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = s->ctx;
+    if (s->R != 1 || ns < 1 || ns + s->m != s->n) return fail(ctx, LPGPU_EINVAL, "shard_synth: needs R=1 and n = ns + m");
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    for (ShardRank &r : s->rk) {
+        shard_synth_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(r.d->T, r.d->ld, s->m, ns, r.col0, r.ncols, r.d->basis, seed, lp_index);
+        LP_LAUNCH_CHECK(ctx);
+    }
+    s->dirty = true;
+    return LPGPU_OK;
+}
+
+int lpgpu_shard_run(lpgpu_shard *s, int max_pivots, lpgpu_result *res) {
+    if (!s || !res || max_pivots < 0) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = s->ctx;
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    lpgpu_dense *d0 = s->rk[0].d;
+    int rc = read_state(d0);                    // the state is a replica on every rank
+    if (rc != LPGPU_OK) return rc;
+    PivotState st = *d0->h_st;
+    st.budget = max_pivots;
+    st.cur = 0;
+    rc = push_state(s, st);
+    if (rc != LPGPU_OK) return rc;
+    if (s->dirty) {
+        // bootstrap: price the tableau as it stands, fetch the entering column from its owner (strided)
+        for (ShardRank &r : s->rk) {
+            shard_price_kernel<<<1, SELECT_THREADS, 0, ctx->stream>>>(shard_params(s, r));
+            LP_LAUNCH_CHECK(ctx);
+        }
+        if ((rc = exchange(s, 0)) != LPGPU_OK) return rc;
+        if ((rc = enqueue_resolve(s, 1)) != LPGPU_OK) return rc;
+        if ((rc = exchange(s, 1)) != LPGPU_OK) return rc;
+        s->dirty = false;
+    }
+    const int chunk_max = s->opts.check_every;
+    int launched = 0, done_updates = 0, iters_before = st.iters;
+    while (launched < max_pivots) {
+        const int chunk = std::min(chunk_max, max_pivots - launched);
+        for (int c = 0; c < chunk; ++c) {
+            if ((rc = enqueue_select(s)) != LPGPU_OK) return rc;
+            if ((rc = exchange(s, 0)) != LPGPU_OK) return rc;
+            if ((rc = enqueue_resolve(s, 0)) != LPGPU_OK) return rc;
+            for (ShardRank &r : s->rk)
+                if ((rc = launch_update(r.d, r.sendcol)) != LPGPU_OK) return rc;
+            if ((rc = exchange(s, 1)) != LPGPU_OK) return rc;
+        }
+        launched += chunk;
+        if ((rc = read_state(d0)) != LPGPU_OK) return rc;
+        done_updates += d0->h_st->iters - iters_before;
+        iters_before = d0->h_st->iters;
+        if (d0->h_st->status != LPGPU_RUNNING) break;
+    }
+    if (d0->h_st->status == LPGPU_RUNNING) {
+        // budget spent: one decision-only select settles a terminal status without applying a pivot
+        if ((rc = enqueue_select(s)) != LPGPU_OK) return rc;
+        if ((rc = read_state(d0)) != LPGPU_OK) return rc;
+    }
+    double zc[2] = {0.0, 0.0};
+    LP_CUDA(ctx, cudaMemcpyAsync(&zc[0], d0->T + (size_t)s->m * d0->ld, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (s->R == 2)
+        LP_CUDA(ctx, cudaMemcpyAsync(&zc[1], d0->T + (size_t)(s->m + 1) * d0->ld, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    memset(res, 0, sizeof *res);
+    res->status = d0->h_st->status;
+    res->iters = d0->h_st->iters;
+    res->z = -zc[0];
+    res->zM = (s->R == 2) ? -zc[1] : 0.0;
+    res->n_logged = std::min(res->iters, d0->log_cap);
+    res->update_launches = done_updates;
+    return LPGPU_OK;
+}
+
+int lpgpu_shard_download(lpgpu_shard *s, double *T, size_t ld, int *basis, int *pivot_log, double *x) {
+    if (!s) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = s->ctx;
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t rows = (size_t)s->m + s->R;
+    lpgpu_dense *d0 = s->rk[0].d;
+    if (T) {
+        if (ld < (size_t)s->n + 1) return fail(ctx, LPGPU_EINVAL, "shard_download: ld %zu < n+1", ld);
+        LP_CUDA(ctx, cudaMemcpy2DAsync(T, ld * sizeof(double), d0->T, d0->ld * sizeof(double), sizeof(double), rows,
+                                       cudaMemcpyDeviceToHost, ctx->stream));
+        for (ShardRank &r : s->rk)
+            LP_CUDA(ctx, cudaMemcpy2DAsync(T + r.col0, ld * sizeof(double), r.d->T + 1, r.d->ld * sizeof(double),
+                                           (size_t)r.ncols * sizeof(double), rows, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (basis) LP_CUDA(ctx, cudaMemcpyAsync(basis, d0->basis, (size_t)s->m * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    if (pivot_log && d0->log_cap > 0) {
+        int rc = read_state(d0);
+        if (rc != LPGPU_OK) return rc;
+        const int nl = std::min(d0->h_st->iters, d0->log_cap);
+        if (nl > 0) LP_CUDA(ctx, cudaMemcpyAsync(pivot_log, d0->log, (size_t)nl * 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (x) {
+        LP_CUDA(ctx, cudaMemsetAsync(s->xbuf, 0, (size_t)s->n * sizeof(double), ctx->stream));
+        shard_extract_x_kernel<<<std::max(1, std::min(1024, (s->m + 255) / 256)), 256, 0, ctx->stream>>>(d0->T, d0->ld, d0->basis, s->m, s->n, s->xbuf);
+        LP_LAUNCH_CHECK(ctx);
+        LP_CUDA(ctx, cudaMemcpyAsync(x, s->xbuf, (size_t)s->n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return LPGPU_OK;
+}
+
+}  // extern "C"

@@ -180,6 +180,70 @@ class DenseTableau:
             pass
 
 
+class ShardedTableau:
+    """One large tableau column-sharded over several GPUs (lpgpu_shard_*).
+
+    nccl_id = 128 bytes from ``sharding.exchange_nccl_id`` : this process is rank ``rank`` of ``world``
+    (one process per GPU, exchanges over NCCL).  nccl_id = None : all ``world`` ranks live in this
+    process on the context's device (single-GPU vehicle for the N > 1 logic)."""
+
+    def __init__(self, ctx, m, n, R=1, world=1, rank=0, nccl_id=None):
+        self.ctx, self.m, self.n, self.R, self.world, self.rank = ctx, m, n, R, world, rank
+        self._h = C.c_void_p()
+        self._log_cap = 0
+        if nccl_id is not None and len(nccl_id) != capi.NCCL_ID_BYTES:
+            raise ValueError("nccl_id must be 128 bytes")
+        idbuf = C.create_string_buffer(bytes(nccl_id), capi.NCCL_ID_BYTES) if nccl_id is not None else None
+        capi.check(ctx.handle, capi.lib().lpgpu_shard_create(ctx.handle, rank, world, idbuf, m, n, R, C.byref(self._h)),
+                   "lpgpu_shard_create")
+
+    def upload(self, T, basis):
+        T = np.ascontiguousarray(T, np.float64)
+        basis = np.ascontiguousarray(basis, np.int32)
+        if T.shape != (self.m + self.R, self.n + 1) or basis.shape != (self.m,):
+            raise ValueError("shape mismatch")
+        capi.check(self.ctx.handle, capi.lib().lpgpu_shard_upload(self._h, _ptr(T), T.shape[1], _ptr(basis)),
+                   "lpgpu_shard_upload")
+
+    def synth(self, seed, lp_index, ns):
+        capi.check(self.ctx.handle, capi.lib().lpgpu_shard_synth(self._h, seed, lp_index, ns), "lpgpu_shard_synth")
+
+    def reset(self, method=None, n_art=0, eps=1e-9, max_iter=2**31 - 1, log_cap=0, check_every=0, variant=0):
+        if method is None:
+            method = PLAIN if self.R == 1 else BIGM
+        o = capi.default_opts(eps=eps, max_iter=int(min(max_iter, 2**31 - 1)), method=method, n_art=n_art,
+                              log_cap=log_cap, check_every=check_every, variant=variant)
+        self._log_cap = log_cap
+        capi.check(self.ctx.handle, capi.lib().lpgpu_shard_reset(self._h, C.byref(o)), "lpgpu_shard_reset")
+
+    def run(self, max_pivots):
+        res = Result()
+        capi.check(self.ctx.handle, capi.lib().lpgpu_shard_run(self._h, int(max_pivots), C.byref(res)), "lpgpu_shard_run")
+        return _result_dict(res)
+
+    def download(self, want_T=True, want_log=True, want_x=True):
+        """T in the GLOBAL layout; columns owned by ranks of other processes stay NaN."""
+        T = np.full((self.m + self.R, self.n + 1), np.nan) if want_T else None
+        basis = np.zeros(self.m, np.int32)
+        log = np.full((max(self._log_cap, 1), 2), -1, np.int32) if (want_log and self._log_cap) else None
+        x = np.zeros(self.n) if want_x else None
+        capi.check(self.ctx.handle,
+                   capi.lib().lpgpu_shard_download(self._h, _ptr(T), self.n + 1, _ptr(basis), _ptr(log), _ptr(x)),
+                   "lpgpu_shard_download")
+        return dict(T=T, basis=basis, log=log, x=x)
+
+    def close(self):
+        if self._h:
+            capi.lib().lpgpu_shard_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def solve_batched(ctx, T_all, basis_all, method=PLAIN, n_art=0, eps=1e-9, max_iter=2**31 - 1, log_cap=0):
     """One-shot batched solve: n_lp tableaux (n_lp, m+R, n+1) in host memory."""
     T_all = np.ascontiguousarray(T_all, np.float64)

@@ -1,0 +1,61 @@
+"""Run under torchrun, one process per GPU: the column-sharded path over NCCL, bit-compared with the
+CPU oracle (tests/test_sharded_gpu.py::test_sharded_nccl_two_processes launches it; it can also be run
+by hand: python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 tests/mp_sharded_check.py)."""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+sys.path.insert(0, os.path.dirname(HERE))
+
+import oracle_lib as O  # noqa: E402
+
+import linearprogramming_b200 as lp  # noqa: E402
+from linearprogramming_b200 import sharding  # noqa: E402
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("gloo")                      # host plumbing only; the data path is our own NCCL comm
+    ctx = lp.Context(local)
+    for (m, ns, method) in [(64, 48, O.PLAIN), (300, 260, O.PLAIN), (40, 30, O.BIGM)]:
+        if method == O.PLAIN:
+            T, basis = O.synth_feasible(1234, 7, m, ns)
+            n_art = 0
+        else:
+            import helpers as H
+            A, b, c, rel = H.random_mixed_lp(np.random.default_rng(5), m, ns)
+            T, basis, n_art = O.build_tableau(A, b, c, rel, R=2)
+        R = 1 if method == O.PLAIN else 2
+        n = T.shape[1] - 1
+        ref = O.solve_f64(T, basis, method=method, n_art=n_art, log_cap=8192)
+        ident = sharding.exchange_nccl_id(dist)
+        s = lp.ShardedTableau(ctx, m, n, R, world=world, rank=rank, nccl_id=ident)
+        s.upload(T, basis)
+        s.reset(method=method, n_art=n_art, log_cap=8192)
+        res = s.run(2**31 - 1)
+        out = s.download()
+        s.close()
+        assert res["status"] == ref["status"] and res["iters"] == ref["iters"], (res, ref["status"], ref["iters"])
+        assert out["log"][:res["n_logged"]].tolist() == ref["log"].tolist()
+        assert np.array_equal(out["basis"], ref["basis"]) and np.array_equal(out["x"], ref["x"]) and res["z"] == ref["z"]
+        c0, nc = sharding.column_block(n, world, rank)
+        assert np.array_equal(out["T"][:, 0], ref["T"][:, 0])
+        assert np.array_equal(out["T"][:, c0:c0 + nc], ref["T"][:, c0:c0 + nc])
+        full = sharding.merge_column_blocks(dist, out["T"], n)
+        if rank == 0:
+            assert np.array_equal(full, ref["T"])
+    ctx.close()
+    dist.barrier()
+    if rank == 0:
+        print(f"sharded nccl ok: world {world}")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -48,6 +48,8 @@ def parse_args():
     ap.add_argument("--no-extra", action="store_true", help="skip the batched (config 3) extra measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--m", type=int, default=M, help=argparse.SUPPRESS)     # debugging at reduced size only
+    ap.add_argument("--shard-m", type=int, default=16384, help="rows of the column-sharded extra (N > 1); n = 4m")
+    ap.add_argument("--shard-pivots", type=int, default=200)
     return ap.parse_args()
 
 
@@ -197,7 +199,7 @@ def reference_arm(args):
         "gpu_launches": 0,
         "note": "the reference has no pivot loop (Source/simplex.c:57-63 empty cases); timed = this repo's CPU oracle port",
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------ GPU arm
@@ -356,6 +358,28 @@ def gpu_arm(args):
                             "all_optimal": bool((out["status"] == lp.OPTIMAL).all()),
                             "hbm_GBs_algorithmic": world * bn * lp_bytes / t_b / 1e9}
 
+    # ---- extra (N > 1): BASELINE config 5b, ONE 16384 x 65536 tableau column-sharded over the ranks,
+    # candidate + entering-column exchange per pivot over our own NCCL communicator
+    if world > 1 and not args.no_extra:
+        from linearprogramming_b200 import sharding
+        sm_, sn_ = args.shard_m, 4 * args.shard_m
+        ident = sharding.exchange_nccl_id(dist)
+        sh = lp.ShardedTableau(ctx, sm_, sn_, 1, world=world, rank=rank, nccl_id=ident)
+        sh.synth(SEED, 0, sn_ - sm_)
+        sh.reset()
+        sh.run(20)
+        sp = args.shard_pivots
+        t_s = max_over_ranks(timed(lambda: sh.run(sp)))
+        r_s = sh.run(0)
+        sh.close()
+        s_bytes = 16 * (sm_ + 1) * (sn_ + 1)
+        extra["column_sharded"] = {"metric": "pivots_per_sec", "value": sp / t_s, "unit": "pivots/s",
+                                   "workload": f"one dense tableau {sm_}x{sn_} fp64 column-sharded over {world} GPUs",
+                                   "pivots": sp, "us_per_pivot": 1e6 * t_s / sp, "iters_after": r_s["iters"],
+                                   "hbm_GBs_algorithmic_total": sp * s_bytes / t_s / 1e9,
+                                   "frac_of_measured_peak_per_gpu": sp * s_bytes / t_s / 1e9 / world / peak,
+                                   "exchange": "ncclAllGather x2 per pivot (32 B candidates, 8*(m+1) B column)"}
+
     line = {
         "metric": "pivots_per_sec", "value": value, "unit": "pivots/s", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": 1e3 * t_value / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -370,14 +394,29 @@ def gpu_arm(args):
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(m, ns)
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+def _reserve_stdout():
+    """stdout carries exactly ONE JSON line: everything else that writes to fd 1 (the NCCL version
+    banner, library chatter) is sent to stderr; emit() writes to the real stdout."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line):
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
+
+
 def main():
     args = parse_args()
+    _reserve_stdout()
     if args.impl == "reference":
         reference_arm(args)
     else:

@@ -4,6 +4,7 @@
 #include <new>
 
 #include "batched_kernels.cuh"
+#include "batched_reg.cuh"
 #include "ctx.h"
 
 using namespace lpgpu;
@@ -23,6 +24,9 @@ struct lpgpu_batched {
 };
 
 namespace {
+
+using RegSmall = RegCfg<1, 32, 2>;     // m <= 32, n <= 64: one warp per LP, no block barrier in the loop
+using RegWide = RegCfg<4, 16, 4>;      // m <= 64, n <= 128: four warps per LP
 
 bool batched_opts_ok(const lpgpu_opts *o, int n, int R) {
     if (!o) return false;
@@ -64,6 +68,10 @@ int lpgpu_batched_create(lpgpu_ctx *ctx, long n_lp, int m, int n, int R, lpgpu_b
     if (e == cudaSuccess) e = cudaMemsetAsync(reinterpret_cast<unsigned char *>(b->T_all) + nl * b->tsz * sizeof(double), 0, 16, ctx->stream);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(batched_simplex_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(batched_reg_kernel<1, 32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(batched_reg_kernel<4, 16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
     if (e != cudaSuccess) {
         lpgpu_batched_destroy(b);
         return fail(ctx, e == cudaErrorMemoryAllocation ? LPGPU_ENOMEM : LPGPU_ECUDA, "batched_create: %s", cudaGetErrorString(e));
@@ -134,14 +142,33 @@ int lpgpu_batched_run(lpgpu_batched *b, const lpgpu_opts *opts, float *kernel_ms
     B.basis_out = b->basis_out; B.log = opts->log_cap > 0 ? b->log : nullptr;
     B.T_final = want_final ? b->T_final : nullptr;
 
-    const size_t smem = batched_smem_bytes(b->m, b->n, b->R);
+    // Kernel choice.  Plain method on shapes that fit a register tile: the register-resident kernel
+    // (batched_reg.cuh); everything else (Big-M, two-phase, other shapes, variant bit 0x2000): the
+    // shared-memory kernel.  Grid = a whole number of resident CTAs per SM; each CTA walks LPs
+    // p = blockIdx, blockIdx + grid, ...
+    const bool plain = opts->method == LPGPU_PLAIN && b->R == 1 && !(opts->variant & 0x2000);
+    int kind = 0;
+    if (plain && b->m <= RegSmall::MAX_M && b->n <= RegSmall::MAX_N) kind = 1;
+    else if (plain && b->m <= RegWide::MAX_M && b->n <= RegWide::MAX_N) kind = 2;
     int occ = 0;
-    LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, batched_simplex_kernel, BATCH_THREADS, smem));
+    size_t smem = 0;
+    int threads = BATCH_THREADS;
+    if (kind == 1) {
+        smem = RegSmall::smem_bytes(b->m, b->n); threads = RegSmall::THREADS;
+        LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, batched_reg_kernel<1, 32, 2>, threads, smem));
+    } else if (kind == 2) {
+        smem = RegWide::smem_bytes(b->m, b->n); threads = RegWide::THREADS;
+        LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, batched_reg_kernel<4, 16, 4>, threads, smem));
+    } else {
+        smem = batched_smem_bytes(b->m, b->n, b->R);
+        LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, batched_simplex_kernel, threads, smem));
+    }
     if (occ < 1) return fail(ctx, LPGPU_EINVAL, "batched_run: kernel does not fit (smem %zu B)", smem);
-    // a whole number of resident CTAs per SM; each CTA walks LPs p = blockIdx, blockIdx + grid, ...
     const long grid = std::min(b->n_lp, (long)ctx->sm_count * occ);
     LP_CUDA(ctx, cudaEventRecord(b->e0, ctx->stream));
-    batched_simplex_kernel<<<(unsigned)grid, BATCH_THREADS, smem, ctx->stream>>>(B);
+    if (kind == 1) batched_reg_kernel<1, 32, 2><<<(unsigned)grid, threads, smem, ctx->stream>>>(B);
+    else if (kind == 2) batched_reg_kernel<4, 16, 4><<<(unsigned)grid, threads, smem, ctx->stream>>>(B);
+    else batched_simplex_kernel<<<(unsigned)grid, threads, smem, ctx->stream>>>(B);
     LP_LAUNCH_CHECK(ctx);
     LP_CUDA(ctx, cudaEventRecord(b->e1, ctx->stream));
     if (kernel_ms) {

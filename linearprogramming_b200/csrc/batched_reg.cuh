@@ -1,0 +1,267 @@
+// batched_reg.cuh -- batched path, register-resident variant (plain method, R = 1).
+//
+// One LP per CTA of WARPS warps.  The tableau lives in REGISTERS for the whole pivot loop:
+//   warp w, lane l holds  a[w*RT + i][1 + l + 32c]   for i < RT, c < CT      (v[RT][CT])
+//   every warp holds a replica of the objective row   sigma[1 + l + 32c]      (obj[CT])
+//   lane i < RT of warp w holds b[w*RT + i] and basis[w*RT + i]; every thread holds the z cell
+// so a pivot is RT*CT independent DFMAs per thread with no tableau traffic at all.  Shared memory
+// carries only the entering column (written by the one lane per warp that owns it, read back as
+// broadcasts), the scaled pivot row when WARPS > 1, and the staging buffer into which the TMA unit
+// prefetches the NEXT LP of this CTA (one cp.async.bulk per LP) while the current one is pivoting.
+// With WARPS == 1 the loop has no block barrier at all: arg-max / arg-min are warp shuffles.
+//
+// Same rule and same operations as the shared-memory kernel and the oracle:
+// a_rj' = a_rj / a_rk, a_ij = fma(-a_ik, a_rj', a_ij); ties to the lowest index.  This is the loop
+// missing from newSimplex (Source/simplex.c:40-67) over SimplexMatrix-shaped tableaux
+// (Source/matrix.h:13-21).
+#pragma once
+
+#include "batched_kernels.cuh"
+
+namespace lpgpu {
+
+template <int WARPS, int RT, int CT>
+struct RegCfg {
+    static constexpr int THREADS = WARPS * 32;
+    static constexpr int MAX_M = WARPS * RT;
+    static constexpr int MAX_N = 32 * CT;
+    __host__ __device__ static size_t smem_bytes(int m, int n) {
+        size_t b = 16;                                              // mbarrier
+        b += ((size_t)(m + 1) * (size_t)(n + 1) + 2) * sizeof(double);  // staging window
+        b = (b + 15) / 16 * 16;
+        b += (size_t)MAX_M * sizeof(double);                        // entering column
+        b += ((size_t)MAX_N + 2) * sizeof(double);                  // scaled pivot row, b_r', pivot
+        b += (size_t)WARPS * 16;                                    // per-warp ratio winners
+        b += (size_t)MAX_N * sizeof(double);                        // x scatter
+        return (b + 15) / 16 * 16;
+    }
+};
+
+// static-index access to "row ri" of a register array through a tree of warp-uniform branches
+template <int LO, int HI, int RT, int CT>
+__device__ __forceinline__ void reg_row_get(const double (&v)[RT][CT], int ri, double (&out)[CT]) {
+    if constexpr (HI - LO == 1) {
+#pragma unroll
+        for (int c = 0; c < CT; ++c) out[c] = v[LO][c];
+    } else {
+        constexpr int MID = (LO + HI) / 2;
+        if (ri < MID) reg_row_get<LO, MID, RT, CT>(v, ri, out);
+        else reg_row_get<MID, HI, RT, CT>(v, ri, out);
+    }
+}
+
+template <int LO, int HI, int RT, int CT>
+__device__ __forceinline__ void reg_row_set(double (&v)[RT][CT], int ri, const double (&in)[CT]) {
+    if constexpr (HI - LO == 1) {
+#pragma unroll
+        for (int c = 0; c < CT; ++c) v[LO][c] = in[c];
+    } else {
+        constexpr int MID = (LO + HI) / 2;
+        if (ri < MID) reg_row_set<LO, MID, RT, CT>(v, ri, in);
+        else reg_row_set<MID, HI, RT, CT>(v, ri, in);
+    }
+}
+
+// warp arg-max of (q, idx): larger q wins, ties to the lowest idx; idx < 0 = none
+__device__ __forceinline__ void warp_argmax(double &q, int &idx) {
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        const double oq = __shfl_xor_sync(0xffffffffu, q, s);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, s);
+        if (oi >= 0 && (idx < 0 || oq > q || (oq == q && oi < idx))) { q = oq; idx = oi; }
+    }
+}
+
+template <int WARPS, int RT, int CT>
+__global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : 3)) batched_reg_kernel(BatchedParams B) {
+    using Cfg = RegCfg<WARPS, RT, CT>;
+    static_assert(RT % 2 == 0 && RT <= 32, "rows per warp: even (128-bit column reads), one b per lane");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int m = B.m, n = B.n, ld1 = n + 1;
+    const size_t tsz = (size_t)(m + 1) * (size_t)ld1;
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw);
+    double *stage = reinterpret_cast<double *>(smem_raw + 16);
+    size_t off = 16 + (tsz + 2) * sizeof(double);
+    off = (off + 15) / 16 * 16;
+    double *pcs = reinterpret_cast<double *>(smem_raw + off);       // entering column, MAX_M
+    off += (size_t)Cfg::MAX_M * sizeof(double);
+    double *prs = reinterpret_cast<double *>(smem_raw + off);       // scaled pivot row, MAX_N (+ b_r', pivot)
+    off += ((size_t)Cfg::MAX_N + 2) * sizeof(double);
+    double *redq = reinterpret_cast<double *>(smem_raw + off);      // WARPS x (q, idx)
+    int *redi = reinterpret_cast<int *>(smem_raw + off + (size_t)WARPS * 8);
+    off += (size_t)WARPS * 16;
+    double *xs = reinterpret_cast<double *>(smem_raw + off);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int row0 = warp * RT;                    // first tableau row of this warp
+    const int myrow = row0 + lane;                 // the row whose b / basis this lane keeps
+    const bool has_row = (lane < RT) && (myrow < m);
+    const double eps = B.eps;
+
+    auto block_sync = [&]() {
+        if constexpr (WARPS == 1) __syncwarp();
+        else __syncthreads();
+    };
+    auto issue_load = [&](long p) {
+        const size_t gbyte = (size_t)p * tsz * sizeof(double);
+        const size_t gal = gbyte & ~(size_t)15;
+        const uint32_t nbytes = (uint32_t)(((gbyte - gal) + tsz * sizeof(double) + 15) / 16 * 16);
+        mbar_arrive_expect_tx(bar, nbytes);
+        tma_load_1d(stage, reinterpret_cast<const unsigned char *>(B.T_all) + gal, nbytes, bar);
+    };
+
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        fence_mbar_init();
+        if ((long)blockIdx.x < B.n_lp) issue_load(blockIdx.x);
+    }
+    block_sync();
+
+    uint32_t parity = 0;
+    for (long p = blockIdx.x; p < B.n_lp; p += gridDim.x) {
+        // ---- staging buffer -> registers
+        mbar_wait(bar, parity);
+        parity ^= 1;
+        const double *S = stage + (int)((((size_t)p * tsz * sizeof(double)) & 15) / sizeof(double));
+        double v[RT][CT], obj[CT];
+#pragma unroll
+        for (int c = 0; c < CT; ++c) {
+            const int j = 1 + lane + 32 * c;
+            const bool jc = j <= n;
+#pragma unroll
+            for (int i = 0; i < RT; ++i) v[i][c] = (jc && row0 + i < m) ? S[(size_t)(row0 + i) * ld1 + j] : 0.0;
+            obj[c] = jc ? S[(size_t)m * ld1 + j] : 0.0;
+        }
+        double bi = has_row ? S[(size_t)myrow * ld1] : 0.0;
+        double zc = S[(size_t)m * ld1];
+        int bas = has_row ? B.basis_all[(size_t)p * m + myrow] : 0;
+        // everyone has read the staging buffer: hand it to the TMA unit for this CTA's next LP
+        fence_proxy_async();
+        block_sync();
+        if (tid == 0 && p + gridDim.x < B.n_lp) issue_load(p + gridDim.x);
+
+        int status = LPGPU_RUNNING, iters = 0;
+        int *plog = B.log ? B.log + (size_t)p * 2 * B.log_cap : nullptr;
+        while (true) {
+            // ---- pricing: largest sigma_j > eps, ties to the lowest j (every warp, replicated row)
+            double pq = 0.0;
+            int k = -1;
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                if (obj[c] > eps && (k < 0 || obj[c] > pq)) { pq = obj[c]; k = 1 + lane + 32 * c; }
+            warp_argmax(pq, k);
+            if (k < 0) { status = LPGPU_OPTIMAL; break; }
+            const int kc = (k - 1) >> 5, kl = (k - 1) & 31;
+            // ---- entering column: its owner lane spills it; sigma_k by shuffle
+            double sig = 0.0;
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                if (kc == c) {                                   // warp-uniform
+                    sig = obj[c];
+                    if (lane == kl) {
+#pragma unroll
+                        for (int i = 0; i < RT; ++i) pcs[row0 + i] = v[i][c];
+                    }
+                }
+            sig = __shfl_sync(0xffffffffu, sig, kl);
+            __syncwarp();
+            // ---- ratio test: min b_i / a_ik over a_ik > eps, ties to the lowest row
+            const double mine = has_row ? pcs[myrow] : 0.0;
+            double rq = 0.0;
+            int r = -1;
+            if (mine > eps) { rq = -(bi / mine); r = myrow; }
+            warp_argmax(rq, r);
+            if constexpr (WARPS > 1) {
+                if (lane == 0) { redq[warp] = rq; redi[warp] = r; }
+                __syncthreads();
+                rq = (lane < WARPS) ? redq[lane] : 0.0;
+                r = (lane < WARPS) ? redi[lane] : -1;
+                warp_argmax(rq, r);
+            }
+            if (r < 0) { status = LPGPU_UNBOUNDED; break; }
+            if (iters >= B.max_iter) { status = LPGPU_ITER_LIMIT; break; }
+            // ---- pivot-row scaling a_rj / a_rk (one IEEE division each), b_r / a_rk
+            const int rw = r / RT, ri = r - rw * RT;
+            double prow[CT], brp;
+            if constexpr (WARPS == 1) {
+                const double piv = __shfl_sync(0xffffffffu, mine, ri);
+                double rv[CT];
+                reg_row_get<0, RT, RT, CT>(v, ri, rv);
+#pragma unroll
+                for (int c = 0; c < CT; ++c) prow[c] = rv[c] / piv;
+                brp = __shfl_sync(0xffffffffu, bi, ri) / piv;
+            } else {
+                if (warp == rw) {
+                    const double piv = __shfl_sync(0xffffffffu, mine, ri);
+                    double rv[CT];
+                    reg_row_get<0, RT, RT, CT>(v, ri, rv);
+#pragma unroll
+                    for (int c = 0; c < CT; ++c) prs[lane + 32 * c] = rv[c] / piv;
+                    const double t = __shfl_sync(0xffffffffu, bi, ri) / piv;
+                    if (lane == 0) prs[Cfg::MAX_N] = t;
+                }
+                __syncthreads();
+#pragma unroll
+                for (int c = 0; c < CT; ++c) prow[c] = prs[lane + 32 * c];
+                brp = prs[Cfg::MAX_N];
+            }
+            // ---- rank-1 elimination out of registers
+#pragma unroll
+            for (int i = 0; i < RT; i += 2) {
+                const double2 f2 = *reinterpret_cast<const double2 *>(pcs + row0 + i);
+#pragma unroll
+                for (int c = 0; c < CT; ++c) {
+                    v[i][c] = __fma_rn(-f2.x, prow[c], v[i][c]);
+                    v[i + 1][c] = __fma_rn(-f2.y, prow[c], v[i + 1][c]);
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < CT; ++c) obj[c] = __fma_rn(-sig, prow[c], obj[c]);
+            bi = __fma_rn(-mine, brp, bi);
+            zc = __fma_rn(-sig, brp, zc);
+            if (warp == rw) {
+                reg_row_set<0, RT, RT, CT>(v, ri, prow);
+                if (lane == ri) { bi = brp; bas = k; }
+            }
+            if (tid == 0 && plog && iters < B.log_cap) { plog[2 * iters] = k; plog[2 * iters + 1] = r; }
+            ++iters;
+            // pcs (per warp) is rewritten by the next pivot; prs / redq are protected by the two block
+            // barriers of the next pivot, so no third one is needed
+            __syncwarp();
+        }
+
+        // ---- results
+        if (tid == 0) {
+            B.status[p] = status;
+            B.iters[p] = iters;
+            if (B.z) B.z[p] = -zc;
+        }
+        if (B.x) {
+            for (int j = tid; j < n; j += Cfg::THREADS) xs[j] = 0.0;
+            block_sync();
+            if (has_row && bas >= 1 && bas <= n) xs[bas - 1] = bi;
+            block_sync();
+            double *xo = B.x + (size_t)p * n;
+            for (int j = tid; j < n; j += Cfg::THREADS) xo[j] = xs[j];
+        }
+        if (B.basis_out && has_row) B.basis_out[(size_t)p * m + myrow] = bas;
+        if (B.T_final) {
+            double *to = B.T_final + (size_t)p * tsz;
+#pragma unroll
+            for (int c = 0; c < CT; ++c) {
+                const int j = 1 + lane + 32 * c;
+                if (j <= n) {
+#pragma unroll
+                    for (int i = 0; i < RT; ++i)
+                        if (row0 + i < m) to[(size_t)(row0 + i) * ld1 + j] = v[i][c];
+                    if (warp == 0) to[(size_t)m * ld1 + j] = obj[c];
+                }
+            }
+            if (has_row) to[(size_t)myrow * ld1] = bi;
+            if (tid == 0) to[(size_t)m * ld1] = zc;
+        }
+        block_sync();          // xs / pcs are reused by the next LP of this CTA
+    }
+}
+
+}  // namespace lpgpu

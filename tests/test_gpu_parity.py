@@ -211,6 +211,49 @@ def test_cfg3_batched_synth_bitwise(ctx, m, ns, n_lp):
     _assert_batched_equal(got3, ref)
 
 
+@pytest.mark.parametrize("m,ns,n_lp", [(32, 32, 700), (64, 64, 150), (16, 48, 200), (40, 88, 120), (2, 2, 50),
+                                       (32, 31, 97), (31, 33, 97), (64, 63, 40), (7, 120, 40)])
+@pytest.mark.parametrize("force_smem", [False, True])
+def test_batched_register_and_smem_kernels_agree_with_oracle(ctx, m, ns, n_lp, force_smem):
+    """Shapes on and around the register tiles (m <= 32, n <= 64 -> one warp per LP; m <= 64, n <= 128 ->
+    four warps per LP) through both kernels: bit-exact results, pivot logs and final tableaux."""
+    T, basis = O.synth_feasible_batch(77, 3, n_lp, m, ns)
+    ref = O.solve_batched_f64(T, basis, threads=8, log_cap=300)
+    b = lp.BatchedLPs(ctx, n_lp, m, m + ns, 1)
+    b.upload(T, basis)
+    b.run(log_cap=300, keep_final=True, force_smem=force_smem)
+    got = b.download(want_log=True, want_final=True)
+    b.close()
+    _assert_batched_equal(got, ref, got["T"])
+    assert np.array_equal(got["log"], ref["log"])
+
+
+@pytest.mark.parametrize("force_smem", [False, True])
+def test_batched_plain_unbounded_and_iteration_limit(ctx, force_smem):
+    """Plain-method LPs with negative entries: some unbounded, some optimal; plus a pivot cap."""
+    rng = np.random.default_rng(11)
+    n_lp, m, ns = 400, 12, 10
+    T = np.zeros((n_lp, m + 1, m + ns + 1))
+    B = np.zeros((n_lp, m), np.int32)
+    for p in range(n_lp):
+        A = rng.uniform(-1.0, 1.0, size=(m, ns))
+        A[rng.random((m, ns)) < 0.3] = 0.0
+        bvec = rng.uniform(0.0, 3.0, m)
+        bvec[rng.random(m) < 0.2] = 0.0                  # degenerate rows -> ratio ties
+        c = rng.uniform(-0.5, 1.0, ns)
+        T[p], B[p], _ = lp.build_tableau(A, bvec, c, np.full(m, -2, np.int32), R=1)
+    for cap in (2**31 - 1, 3):
+        ref = O.solve_batched_f64(T, B, max_iter=cap, threads=4, log_cap=128)
+        b = lp.BatchedLPs(ctx, n_lp, m, m + ns, 1)
+        b.upload(T, B)
+        b.run(max_iter=cap, log_cap=128, keep_final=True, force_smem=force_smem)
+        got = b.download(want_log=True, want_final=True)
+        b.close()
+        _assert_batched_equal(got, ref, got["T"])
+        assert np.array_equal(got["log"], ref["log"])
+    assert lp.UNBOUNDED in set(ref["status"].tolist()) | set(O.solve_batched_f64(T, B)["status"].tolist())
+
+
 @pytest.mark.parametrize("method", [O.BIGM, O.TWOPHASE])
 def test_batched_bigm_twophase(ctx, method):
     rng = np.random.default_rng(5)

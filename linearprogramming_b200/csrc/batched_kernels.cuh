@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(BATCH_THREADS) batched_simplex_kernel(BatchedP
             // ---- pivot-row scaling and pivot-column snapshot
             const double piv = S[(size_t)r * ld1 + k];
             for (int i = tid; i < rows; i += BATCH_THREADS) pcol[i] = S[(size_t)i * ld1 + k];
-            for (int j = tid; j <= n; j += BATCH_THREADS) prow[j] = S[(size_t)r * ld1 + j] / piv;
+            for (int j = tid; j <= n; j += BATCH_THREADS) prow[j] = div_skip_zero(S[(size_t)r * ld1 + j], piv);
             if (tid == 0) {
                 basis[r] = k;
                 if (plog && iters < B.log_cap) { plog[2 * iters] = k; plog[2 * iters + 1] = r; }

@@ -62,14 +62,30 @@ __device__ __forceinline__ void reg_row_set(double (&v)[RT][CT], int ri, const d
     }
 }
 
-// warp arg-max of (q, idx): larger q wins, ties to the lowest idx; idx < 0 = none
-__device__ __forceinline__ void warp_argmax(double &q, int &idx) {
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        const double oq = __shfl_xor_sync(0xffffffffu, q, s);
-        const int oi = __shfl_xor_sync(0xffffffffu, idx, s);
-        if (oi >= 0 && (idx < 0 || oq > q || (oq == q && oi < idx))) { q = oq; idx = oi; }
-    }
+// Warp-wide arg-max / arg-min on 64-bit order-preserving keys with three redux.sync operations
+// (high word, low word among the high-word winners, lowest index among the exact ties) instead of a
+// five-level shuffle tree.  has = this lane holds a candidate; idx >= 0.  Returns the winning idx
+// (the same in every lane) or -1 when no lane has a candidate.
+__device__ __forceinline__ int warp_arg_reduce(unsigned long long key, bool has, int idx, bool want_max) {
+    constexpr unsigned FULL = 0xffffffffu;
+    if (!want_max) key = ~key;                                       // arg-min = arg-max of the complement
+    const unsigned hi = has ? (unsigned)(key >> 32) : 0u, lo = (unsigned)key;
+    const unsigned any = __ballot_sync(FULL, has);
+    if (any == 0u) return -1;
+    const unsigned mh = __reduce_max_sync(FULL, hi);
+    const bool in1 = has && hi == mh;
+    const unsigned ml = __reduce_max_sync(FULL, in1 ? lo : 0u);
+    const bool in2 = in1 && lo == ml;
+    return (int)__reduce_min_sync(FULL, in2 ? (unsigned)idx : 0x7fffffffu);
+}
+
+// positive doubles order like their bit patterns
+__device__ __forceinline__ unsigned long long key_positive(double q) { return (unsigned long long)__double_as_longlong(q); }
+
+// any finite double: flip the sign bit of non-negatives, all bits of negatives; -0 is folded into +0
+__device__ __forceinline__ unsigned long long key_ordered(double x) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(x + 0.0);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
 }
 
 template <int WARPS, int RT, int CT>
@@ -149,7 +165,7 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : 3)) batched_reg
 #pragma unroll
             for (int c = 0; c < CT; ++c)
                 if (obj[c] > eps && (k < 0 || obj[c] > pq)) { pq = obj[c]; k = 1 + lane + 32 * c; }
-            warp_argmax(pq, k);
+            k = warp_arg_reduce(key_positive(pq), k >= 0, k, true);
             if (k < 0) { status = LPGPU_OPTIMAL; break; }
             const int kc = (k - 1) >> 5, kl = (k - 1) & 31;
             // ---- entering column: its owner lane spills it; sigma_k by shuffle
@@ -167,16 +183,22 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : 3)) batched_reg
             __syncwarp();
             // ---- ratio test: min b_i / a_ik over a_ik > eps, ties to the lowest row
             const double mine = has_row ? pcs[myrow] : 0.0;
-            double rq = 0.0;
-            int r = -1;
-            if (mine > eps) { rq = -(bi / mine); r = myrow; }
-            warp_argmax(rq, r);
+            const bool elig = mine > eps;
+            const double theta = elig ? bi / mine : 0.0;
+            int r = warp_arg_reduce(key_ordered(theta), elig, myrow, false);
             if constexpr (WARPS > 1) {
-                if (lane == 0) { redq[warp] = rq; redi[warp] = r; }
+                // rows ascend with the warp index, so "first strictly smaller" keeps ties on the lowest row
+                const double tr = __shfl_sync(0xffffffffu, theta, (r >= 0 ? r - row0 : 0));
+                if (lane == 0) { redq[warp] = tr; redi[warp] = r; }
                 __syncthreads();
-                rq = (lane < WARPS) ? redq[lane] : 0.0;
-                r = (lane < WARPS) ? redi[lane] : -1;
-                warp_argmax(rq, r);
+                r = -1;
+                double best = 0.0;
+#pragma unroll
+                for (int w = 0; w < WARPS; ++w) {
+                    const int rw_ = redi[w];
+                    const double tw = redq[w];
+                    if (rw_ >= 0 && (r < 0 || tw < best)) { r = rw_; best = tw; }
+                }
             }
             if (r < 0) { status = LPGPU_UNBOUNDED; break; }
             if (iters >= B.max_iter) { status = LPGPU_ITER_LIMIT; break; }
@@ -188,16 +210,16 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : 3)) batched_reg
                 double rv[CT];
                 reg_row_get<0, RT, RT, CT>(v, ri, rv);
 #pragma unroll
-                for (int c = 0; c < CT; ++c) prow[c] = rv[c] / piv;
-                brp = __shfl_sync(0xffffffffu, bi, ri) / piv;
+                for (int c = 0; c < CT; ++c) prow[c] = div_skip_zero(rv[c], piv);
+                brp = div_skip_zero(__shfl_sync(0xffffffffu, bi, ri), piv);
             } else {
                 if (warp == rw) {
                     const double piv = __shfl_sync(0xffffffffu, mine, ri);
                     double rv[CT];
                     reg_row_get<0, RT, RT, CT>(v, ri, rv);
 #pragma unroll
-                    for (int c = 0; c < CT; ++c) prs[lane + 32 * c] = rv[c] / piv;
-                    const double t = __shfl_sync(0xffffffffu, bi, ri) / piv;
+                    for (int c = 0; c < CT; ++c) prs[lane + 32 * c] = div_skip_zero(rv[c], piv);
+                    const double t = div_skip_zero(__shfl_sync(0xffffffffu, bi, ri), piv);
                     if (lane == 0) prs[Cfg::MAX_N] = t;
                 }
                 __syncthreads();

@@ -77,6 +77,13 @@ __device__ __forceinline__ Cand block_best(Cand c, Cand *scratch) {
     return v;
 }
 
+// ------------------------------------------------------------------ pivot-row scaling
+// a / piv with one IEEE division; exact zeros (most of a tableau row early on) skip the divide
+// sequence, whose slow path they would otherwise drag the whole warp through
+__device__ __forceinline__ double div_skip_zero(double a, double piv) {
+    return (a == 0.0) ? ((piv > 0.0) ? a : -a) : a / piv;
+}
+
 // ------------------------------------------------------------------ synthetic data
 // Counter-based generator shared bit-for-bit with the host (and restated in the oracle).
 __host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {

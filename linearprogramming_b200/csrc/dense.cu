@@ -126,7 +126,7 @@ dense_select_kernel(DenseParams P, int forced_r, int forced_k) {
     const double fm = bigm ? -om[k] : 0.0;
     Cand c = cand_none();
     for (size_t j = (size_t)gtid; j < P.ld; j += GSTRIDE) {
-        const double pr = xr[j] / piv;
+        const double pr = div_skip_zero(xr[j], piv);
         P.prow[j] = pr;
         if (look && j >= 1 && j <= (size_t)jmax) {
             const double q = __fma_rn(fc, pr, oc[j]);

@@ -182,7 +182,7 @@ shard_select_kernel(ShardParams S) {
     const double fm = bigm ? -col[P.m + 1] : 0.0;
     Cand c = cand_none();
     for (size_t j = (size_t)gtid; j < P.ld; j += GSTRIDE) {
-        const double pr = xr[j] / piv;
+        const double pr = div_skip_zero(xr[j], piv);
         P.prow[j] = pr;
         if (j >= 1 && j <= (size_t)P.n) {
             const double q = __fma_rn(fc, pr, oc[j]);

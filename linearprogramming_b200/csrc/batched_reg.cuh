@@ -25,15 +25,15 @@ struct RegCfg {
     static constexpr int THREADS = WARPS * 32;
     static constexpr int MAX_M = WARPS * RT;
     static constexpr int MAX_N = 32 * CT;
+    // scratch used inside the pivot loop (entering column; scaled pivot row, b_r' and per-warp ratio
+    // winners when WARPS > 1); the x scatter of the result phase reuses the same bytes
+    static constexpr size_t LOOP_BYTES = (size_t)MAX_M * 8 + (WARPS > 1 ? ((size_t)MAX_N + 2) * 8 + (size_t)WARPS * 16 : 0);
+    static constexpr size_t SCRATCH_BYTES = LOOP_BYTES > (size_t)MAX_N * 8 ? LOOP_BYTES : (size_t)MAX_N * 8;
     __host__ __device__ static size_t smem_bytes(int m, int n) {
         size_t b = 16;                                              // mbarrier
         b += ((size_t)(m + 1) * (size_t)(n + 1) + 2) * sizeof(double);  // staging window
         b = (b + 15) / 16 * 16;
-        b += (size_t)MAX_M * sizeof(double);                        // entering column
-        b += ((size_t)MAX_N + 2) * sizeof(double);                  // scaled pivot row, b_r', pivot
-        b += (size_t)WARPS * 16;                                    // per-warp ratio winners
-        b += (size_t)MAX_N * sizeof(double);                        // x scatter
-        return (b + 15) / 16 * 16;
+        return b + (SCRATCH_BYTES + 15) / 16 * 16;
     }
 };
 
@@ -89,7 +89,7 @@ __device__ __forceinline__ unsigned long long key_ordered(double x) {
 }
 
 template <int WARPS, int RT, int CT>
-__global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : 3)) batched_reg_kernel(BatchedParams B) {
+__global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 11 : 3)) batched_reg_kernel(BatchedParams B) {
     using Cfg = RegCfg<WARPS, RT, CT>;
     static_assert(RT % 2 == 0 && RT <= 32, "rows per warp: even (128-bit column reads), one b per lane");
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -100,13 +100,10 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : 3)) batched_reg
     size_t off = 16 + (tsz + 2) * sizeof(double);
     off = (off + 15) / 16 * 16;
     double *pcs = reinterpret_cast<double *>(smem_raw + off);       // entering column, MAX_M
-    off += (size_t)Cfg::MAX_M * sizeof(double);
-    double *prs = reinterpret_cast<double *>(smem_raw + off);       // scaled pivot row, MAX_N (+ b_r', pivot)
-    off += ((size_t)Cfg::MAX_N + 2) * sizeof(double);
-    double *redq = reinterpret_cast<double *>(smem_raw + off);      // WARPS x (q, idx)
-    int *redi = reinterpret_cast<int *>(smem_raw + off + (size_t)WARPS * 8);
-    off += (size_t)WARPS * 16;
-    double *xs = reinterpret_cast<double *>(smem_raw + off);
+    double *prs = pcs + Cfg::MAX_M;                                 // WARPS > 1: scaled pivot row, MAX_N (+ b_r')
+    double *redq = prs + Cfg::MAX_N + 2;                            // WARPS > 1: per-warp ratio winners
+    int *redi = reinterpret_cast<int *>(redq + WARPS);
+    double *xs = pcs;                                               // result phase: x scatter (loop scratch is dead)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int row0 = warp * RT;                    // first tableau row of this warp
@@ -228,14 +225,21 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : 3)) batched_reg
                 brp = prs[Cfg::MAX_N];
             }
             // ---- rank-1 elimination out of registers
+            // entering column read back as 128-bit broadcasts, EB rows per batch so that the loads of a
+            // batch are all in flight before its first DFMA needs one
+            constexpr int EB = (RT % 8 == 0) ? 8 : 2;
 #pragma unroll
-            for (int i = 0; i < RT; i += 2) {
-                const double2 f2 = *reinterpret_cast<const double2 *>(pcs + row0 + i);
+            for (int i0 = 0; i0 < RT; i0 += EB) {
+                double2 f2[EB / 2];
 #pragma unroll
-                for (int c = 0; c < CT; ++c) {
-                    v[i][c] = __fma_rn(-f2.x, prow[c], v[i][c]);
-                    v[i + 1][c] = __fma_rn(-f2.y, prow[c], v[i + 1][c]);
-                }
+                for (int u = 0; u < EB / 2; ++u) f2[u] = *reinterpret_cast<const double2 *>(pcs + row0 + i0 + 2 * u);
+#pragma unroll
+                for (int u = 0; u < EB / 2; ++u)
+#pragma unroll
+                    for (int c = 0; c < CT; ++c) {
+                        v[i0 + 2 * u][c] = __fma_rn(-f2[u].x, prow[c], v[i0 + 2 * u][c]);
+                        v[i0 + 2 * u + 1][c] = __fma_rn(-f2[u].y, prow[c], v[i0 + 2 * u + 1][c]);
+                    }
             }
 #pragma unroll
             for (int c = 0; c < CT; ++c) obj[c] = __fma_rn(-sig, prow[c], obj[c]);
@@ -259,6 +263,7 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : 3)) batched_reg
             if (B.z) B.z[p] = -zc;
         }
         if (B.x) {
+            block_sync();      // xs aliases the loop scratch: every warp has left the pivot loop
             for (int j = tid; j < n; j += Cfg::THREADS) xs[j] = 0.0;
             block_sync();
             if (has_row && bas >= 1 && bas <= n) xs[bas - 1] = bi;

@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--m", type=int, default=M, help=argparse.SUPPRESS)     # debugging at reduced size only
     ap.add_argument("--shard-m", type=int, default=16384, help="rows of the column-sharded extra (N > 1); n = 4m")
     ap.add_argument("--shard-pivots", type=int, default=200)
+    ap.add_argument("--batched5", type=int, default=1_000_000, help="LPs of the m=64 n=128 batched extra (whole job)")
     return ap.parse_args()
 
 
@@ -353,10 +354,31 @@ def gpu_arm(args):
         t_b = max_over_ranks(statistics.median(ms) * 1e-3)
         lp_bytes = 8 * ((BM + 1) * (BM + BNS + 1) + (BM + BNS) + 4)
         extra["batched"] = {"metric": "LPs_per_sec", "value": world * bn / t_b, "unit": "LPs/s",
-                            "workload": f"{bn} LPs m={BM} n={BM + BNS} fp64 per GPU, resident",
+                            "workload": f"{bn} LPs m={BM} n={BM + BNS} fp64 per GPU, resident (BASELINE config 3)",
+                            "kernel": "batched_reg_kernel<1,32,2> (one warp per LP, tableau in registers)",
                             "kernel_ms": t_b * 1e3, "mean_pivots_per_lp": float(out["iters"].mean()),
                             "all_optimal": bool((out["status"] == lp.OPTIMAL).all()),
-                            "hbm_GBs_algorithmic": world * bn * lp_bytes / t_b / 1e9}
+                            "hbm_GBs_algorithmic": world * bn * lp_bytes / t_b / 1e9,
+                            "frac_of_measured_peak_per_gpu": bn * lp_bytes / t_b / 1e9 / peak}
+        # BASELINE config 5a: m=64 n=128, instances sharded over the ranks by contiguous index range
+        from linearprogramming_b200 import sharding as _sh
+        n5 = args.batched5 if world > 1 else min(args.batched5, 200_000)
+        lo5, hi5 = _sh.lp_range(n5, world, rank)
+        b5 = lp.BatchedLPs(ctx, hi5 - lo5, 64, 128, 1)
+        b5.synth(SEED, lo5, 64)
+        b5.run()
+        ms5 = [b5.run() for _ in range(3)]
+        out5 = b5.download(want_x=False)
+        b5.close()
+        t5 = max_over_ranks(statistics.median(ms5) * 1e-3)
+        lp5_bytes = 8 * (65 * 129 + 128 + 4)
+        extra["batched_m64_n128"] = {"metric": "LPs_per_sec", "value": n5 / t5, "unit": "LPs/s",
+                                     "workload": f"{n5} LPs m=64 n=128 fp64 sharded by index range over {world} GPU(s), "
+                                                 "no collective (BASELINE config 5a" + ("" if world > 1 else ", 1-GPU sample") + ")",
+                                     "kernel": "batched_reg_kernel<4,16,4>", "kernel_ms": t5 * 1e3,
+                                     "mean_pivots_per_lp": float(out5["iters"].mean()),
+                                     "all_optimal": bool((out5["status"] == lp.OPTIMAL).all()),
+                                     "hbm_GBs_algorithmic": n5 * lp5_bytes / t5 / 1e9}
 
     # ---- extra (N > 1): BASELINE config 5b, ONE 16384 x 65536 tableau column-sharded over the ranks,
     # candidate + entering-column exchange per pivot over our own NCCL communicator

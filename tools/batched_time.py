@@ -1,3 +1,5 @@
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import linearprogramming_b200 as lp
 ctx=lp.Context(0)
 for (n_lp,m,n) in [(100000,32,64),(200000,64,128)]:

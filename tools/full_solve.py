@@ -1,5 +1,7 @@
 """Scratch: solve the config-4 LP to optimality on the GPU and report iterations / time."""
 import sys, time, json
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import linearprogramming_b200 as lp
 m = ns = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
 variant = int(sys.argv[2], 0) if len(sys.argv) > 2 else 0

@@ -306,13 +306,13 @@ def gpu_arm(args):
     try:        # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
         with open(os.path.join(ROOT, "profiles", "r1_update_traffic.json")) as f:
             tj = json.load(f)
-        if m == M and tj["kernel"].endswith("direct") == ((variant & 0xf) == 2):
+        if m == M and tj["variant"] == (variant & 0xf):
             traffic, traffic_src = tj["traffic_bytes_per_launch"], tj["source"]
     except Exception:
         pass
     upd_avg_ms = upd_ms / upd_n
     achieved = alg_bytes / (upd_avg_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "dense_update_direct" if (variant & 0xf) == 2 else "dense_update_tma_staged",
+    roofline = {"bound": "hbm", "kernel": {0: "dense_update_dynamic", 1: "dense_update_tma_staged", 2: "dense_update_direct"}[variant & 0xf],
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                 "avg_launch_ms": upd_avg_ms, "select_avg_ms": sel_ms / upd_n,

@@ -16,7 +16,9 @@ PLAIN, BIGM, TWOPHASE = 0, 1, 2
 STATUS_NAMES = {0: "OPTIMAL", 1: "UNBOUNDED", 2: "INFEASIBLE", 3: "ITER_LIMIT", 4: "RUNNING"}
 KEEP_FINAL = 0x1000      # batched: keep the final tableaux on the device (parity tests)
 FORCE_SMEM = 0x2000      # batched: shared-memory kernel even where the register-resident one applies
+STATIC = 0x1             # dense: TMA-staged elimination with a static task stride (default: work stealing)
 DIRECT = 0x2             # dense: direct-load elimination kernel instead of the TMA-staged default
+NO_PDL = 0x400           # dense: plain stream-ordered launches (default: programmatic dependent launch)
 NO_ALTERNATE = 0x200     # dense: do not alternate the sweep direction between pivots
 NCCL_ID_BYTES = 128
 

@@ -177,6 +177,14 @@ __device__ __forceinline__ void tma_store_wait() {
     asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
 
+// ------------------------------------------------------------------ programmatic dependent launch
+// Kernels launched with cudaLaunchAttributeProgrammaticStreamSerialization may become resident while
+// the kernel before them in the stream is still draining; pdl_wait() blocks until that kernel has
+// completed and its writes are visible (a no-op in a normal launch), pdl_launch_dependents() lets the
+// kernel AFTER this one start its own prologue early.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ------------------------------------------------------------------ streaming 128-bit access
 // The tableau is read once and written once per pivot: keep it out of L1.
 __device__ __forceinline__ double2 ld_stream2(const double *p) {

@@ -37,6 +37,8 @@ dense_select_kernel(DenseParams P, int forced_r, int forced_k) {
     const int gtid = rank * SELECT_THREADS + (int)threadIdx.x;
     constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
 
+    pdl_wait();                 // the elimination pass before this launch has completed
+    pdl_launch_dependents();    // the next elimination pass may set itself up behind this kernel
     PivotState *st = P.st;
     int r = -1, k = 0, cur = st->cur, phase = st->phase;
     bool fast = false;
@@ -164,17 +166,46 @@ DenseParams make_params(const lpgpu_dense *d) {
     return P;
 }
 
+// Launch with programmatic stream serialization (variant bit 0x400 turns it off): the kernel may become
+// resident while its predecessor drains and blocks in pdl_wait() until that one has completed.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
+int launch_select(lpgpu_dense *d, int forced_r, int forced_k) {
+    lpgpu_ctx *ctx = d->ctx;
+    const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels;
+    LP_CUDA(ctx, launch_pdl(pdl, dense_select_kernel, dim3(SELECT_CLUSTER), dim3(SELECT_THREADS), ctx->stream,
+                            make_params(d), forced_r, forced_k));
+    ctx->launches++;
+    return LPGPU_OK;
+}
+
 int launch_update(lpgpu_dense *d, double *cnext) {
     lpgpu_ctx *ctx = d->ctx;
     UpdateParams U;
     U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.prow = d->prow; U.colbuf = d->pcol; U.pcn = d->pcn; U.bnext = d->bnext; U.st = d->st; U.cnext = cnext;
-    // variant: low nibble 0/1 = TMA-staged kernel (default), 2 = direct-load kernel;
+    U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
+    // variant: low nibble 0 = TMA-staged kernel with work stealing (default), 1 = TMA-staged with a
+    //          static task stride, 2 = direct-load kernel;
     //          0x200 = do NOT alternate the sweep direction between pivots
     U.alternate = (d->opts.variant & 0x200) ? 0 : 1;
     const int kind = d->opts.variant & 0xf;
-    if (kind == 2) dense_update_direct<<<d->grid_update, UPD_THREADS, 0, ctx->stream>>>(U);
-    else dense_update_tma_staged<<<d->grid_update, UPD_THREADS, 0, ctx->stream>>>(U);
-    LP_LAUNCH_CHECK(ctx);
+    const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels && cnext == nullptr;
+    LP_CUDA(ctx, launch_pdl(pdl, kind == 2 ? dense_update_direct : kind == 1 ? dense_update_tma_staged : dense_update_dynamic, dim3(d->grid_update),
+                            dim3(UPD_THREADS), ctx->stream, U));
+    ctx->launches++;
     return LPGPU_OK;
 }
 
@@ -200,10 +231,12 @@ size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 int size_grid(lpgpu_dense *d) {
     lpgpu_ctx *ctx = d->ctx;
-    int occ0 = 0, occ1 = 0;
+    int occ0 = 0, occ1 = 0, occ3 = 0;
+    LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3, dense_update_dynamic, UPD_THREADS, 0));
     LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, dense_update_direct, UPD_THREADS, 0));
     LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, dense_update_tma_staged, UPD_THREADS, 0));
-    const int occ = std::max(1, ((d->opts.variant & 0xf) == 2) ? occ0 : occ1);
+    const int kind = d->opts.variant & 0xf;
+    const int occ = std::max(1, kind == 2 ? occ0 : kind == 1 ? occ1 : occ3);
     const long nct = (long)((d->ld + UPD_TILE_COLS - 1) / UPD_TILE_COLS);
     const long nrb = (d->m + d->R + UPD_TILE_ROWS - 1) / UPD_TILE_ROWS;
     d->grid_update = (int)std::max(1L, std::min((long)ctx->sm_count * occ, nct * nrb));
@@ -231,7 +264,7 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     d->ctx = ctx; d->m = m; d->n = n; d->R = R;
     d->ld = round_up((size_t)n + 1, 16);
     d->T = nullptr; d->basis = nullptr; d->prow = d->pcol = d->bnext = d->xbuf = nullptr; d->la_dirty = true; d->st = nullptr; d->h_st = nullptr;
-    d->log = nullptr; d->log_cap = 0;
+    d->log = nullptr; d->log_cap = 0; d->task_ctr = nullptr; d->upd_seq = 0;
     lpgpu_default_opts(&d->opts);
     d->opts.method = (R == 1) ? LPGPU_PLAIN : LPGPU_BIGM;
     const size_t rows = (size_t)m + R, pcn = round_up(rows, UPD_TILE_ROWS) + UPD_TILE_ROWS;
@@ -244,6 +277,8 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     if (e == cudaSuccess) e = cudaMalloc(&d->bnext, pcn * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&d->xbuf, (size_t)n * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&d->st, sizeof(PivotState));
+    if (e == cudaSuccess) e = cudaMalloc(&d->task_ctr, 2 * sizeof(int));
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->task_ctr, 0, 2 * sizeof(int), ctx->stream);
     if (e == cudaSuccess) e = cudaHostAlloc(&d->h_st, sizeof(PivotState), cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->T, 0, rows * d->ld * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->prow, 0, d->ld * sizeof(double), ctx->stream);
@@ -267,7 +302,7 @@ void lpgpu_dense_destroy(lpgpu_dense *d) {
     cudaStreamSynchronize(d->ctx->stream);
     for (cudaEvent_t e : d->ev) cudaEventDestroy(e);
     cudaFree(d->T); cudaFree(d->basis); cudaFree(d->prow); cudaFree(d->pcol); cudaFree(d->bnext); cudaFree(d->xbuf);
-    cudaFree(d->st); cudaFree(d->log);
+    cudaFree(d->st); cudaFree(d->log); cudaFree(d->task_ctr);
     if (d->h_st) cudaFreeHost(d->h_st);
     delete d;
 }
@@ -344,7 +379,6 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
     if (d->la_dirty) d->h_st->k_next = 0;       // never trust a lookahead across an upload / synth / forced pivot
     d->la_dirty = false;
     LP_CUDA(ctx, cudaMemcpyAsync(d->st, d->h_st, sizeof(PivotState), cudaMemcpyHostToDevice, ctx->stream));
-    const DenseParams P = make_params(d);
     int launched = 0, done_updates = 0;
     double upd_ms = 0.0, sel_ms = 0.0;
     int iters_before = d->h_st->iters;
@@ -352,8 +386,8 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
         const int chunk = std::min(chunk_max, max_pivots - launched);
         for (int c = 0; c < chunk; ++c) {
             if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c], ctx->stream));
-            dense_select_kernel<<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(P, -1, 0);
-            LP_LAUNCH_CHECK(ctx);
+            rc = launch_select(d, -1, 0);
+            if (rc != LPGPU_OK) return rc;
             if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c + 1], ctx->stream));
             rc = launch_update(d, nullptr);
             if (rc != LPGPU_OK) return rc;
@@ -379,8 +413,8 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
     if (d->h_st->status == LPGPU_RUNNING) {
         // budget spent: one decision-only select settles a terminal status (optimal, iteration
         // limit, ...) without applying a pivot, so a run of exactly the needed pivots reports it
-        dense_select_kernel<<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(P, -1, 0);
-        LP_LAUNCH_CHECK(ctx);
+        rc = launch_select(d, -1, 0);
+        if (rc != LPGPU_OK) return rc;
         rc = read_state(d);
         if (rc != LPGPU_OK) return rc;
     }
@@ -408,11 +442,10 @@ int lpgpu_dense_pivot(lpgpu_dense *d, int r, int k) {
     lpgpu_ctx *ctx = d->ctx;
     if (r < 0 || r >= d->m || k < 1 || k > d->n) return fail(ctx, LPGPU_EINVAL, "dense_pivot: (r=%d,k=%d) out of range", r, k);
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
-    const DenseParams P = make_params(d);
     d->la_dirty = true;
-    dense_select_kernel<<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(P, r, k);
-    LP_LAUNCH_CHECK(ctx);
-    int rc = launch_update(d, nullptr);
+    int rc = launch_select(d, r, k);
+    if (rc != LPGPU_OK) return rc;
+    rc = launch_update(d, nullptr);
     if (rc != LPGPU_OK) return rc;
     LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return LPGPU_OK;

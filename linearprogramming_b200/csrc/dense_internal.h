@@ -22,6 +22,8 @@ struct lpgpu_dense {
     int log_cap;
     lpgpu_opts opts;
     int grid_update;
+    int *task_ctr;          // work-stealing counters of the elimination kernel (2 ints)
+    unsigned upd_seq;       // elimination launches so far
     std::vector<cudaEvent_t> ev;
 };
 

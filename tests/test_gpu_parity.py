@@ -99,7 +99,7 @@ def test_random_mixed_lps_dense(ctx, seed, method):
 
 # ------------------------------------------------------------------ the elimination pass alone
 @pytest.mark.parametrize("shape", [(5, 7), (33, 65), (100, 511), (257, 1030), (64, 2049)])
-@pytest.mark.parametrize("variant", [0, 2, 0x200, 0x202])
+@pytest.mark.parametrize("variant", [0, 1, 2, 0x200, 0x201, 0x202, 0x400, 0x401])
 def test_single_pivot_pass_bitwise(ctx, shape, variant):
     rows, cols = shape
     rng = np.random.default_rng(rows * 1000 + cols)
@@ -121,7 +121,7 @@ def test_single_pivot_pass_bitwise(ctx, shape, variant):
 
 # ------------------------------------------------------------------ large path on synthetic LPs
 @pytest.mark.parametrize("m,ns", [(32, 32), (64, 64), (200, 120), (300, 500), (512, 512)])
-@pytest.mark.parametrize("variant", [0, 2])
+@pytest.mark.parametrize("variant", [0, 1, 2])
 def test_dense_synth_full_solve(ctx, m, ns, variant):
     T0, basis = O.synth_feasible(1234, 3, m, ns)
     ref = O.solve_f64(T0, basis, threads=4, log_cap=4096)

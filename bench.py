@@ -385,22 +385,32 @@ def gpu_arm(args):
     if world > 1 and not args.no_extra:
         from linearprogramming_b200 import sharding
         sm_, sn_ = args.shard_m, 4 * args.shard_m
-        ident = sharding.exchange_nccl_id(dist)
-        sh = lp.ShardedTableau(ctx, sm_, sn_, 1, world=world, rank=rank, nccl_id=ident)
-        sh.synth(SEED, 0, sn_ - sm_)
-        sh.reset()
-        sh.run(20)
         sp = args.shard_pivots
-        t_s = max_over_ranks(timed(lambda: sh.run(sp)))
-        r_s = sh.run(0)
-        sh.close()
+        per_transport = {}
+        for transport in ("p2p", "nccl"):
+            if transport == "nccl":
+                ident = sharding.exchange_nccl_id(dist)
+                sh = lp.ShardedTableau(ctx, sm_, sn_, 1, world=world, rank=rank, nccl_id=ident)
+            else:
+                sh = lp.ShardedTableau(ctx, sm_, sn_, 1, world=world, rank=rank, p2p=True)
+                sharding.attach_p2p(dist, sh)
+            sh.synth(SEED, 0, sn_ - sm_)
+            sh.reset()
+            sh.run(20)
+            per_transport[transport] = max_over_ranks(timed(lambda: sh.run(sp)))
+            r_s = sh.run(0)
+            barrier()               # p2p: nobody unmaps while a peer may still store into its region
+            sh.close()
+        t_s = per_transport["p2p"]
         s_bytes = 16 * (sm_ + 1) * (sn_ + 1)
         extra["column_sharded"] = {"metric": "pivots_per_sec", "value": sp / t_s, "unit": "pivots/s",
                                    "workload": f"one dense tableau {sm_}x{sn_} fp64 column-sharded over {world} GPUs",
                                    "pivots": sp, "us_per_pivot": 1e6 * t_s / sp, "iters_after": r_s["iters"],
                                    "hbm_GBs_algorithmic_total": sp * s_bytes / t_s / 1e9,
                                    "frac_of_measured_peak_per_gpu": sp * s_bytes / t_s / 1e9 / world / peak,
-                                   "exchange": "ncclAllGather x2 per pivot (32 B candidates, 8*(m+1) B column)"}
+                                   "exchange": "peer-memory stores over NVLink from inside the select / elimination "
+                                               "kernels (32 B candidates, 8*(m+1) B column per pivot)",
+                                   "us_per_pivot_nccl_allgather_transport": 1e6 * per_transport["nccl"] / sp}
 
     line = {
         "metric": "pivots_per_sec", "value": value, "unit": "pivots/s", "n_gpus": world, "steps": K, "warmup": W,

@@ -161,6 +161,17 @@ int lpgpu_shard_unique_id(void *id128);
 int lpgpu_shard_columns(int n, int world, int rank, int *col0, int *ncols);
 int lpgpu_shard_create(lpgpu_ctx *ctx, int rank, int world, const void *id128, int m, int n, int R,
                        lpgpu_shard **out);
+/* Peer-memory transport: one rank per process like NCCL, but the two per-pivot exchanges are stores
+ * into the other GPUs' memory over NVLink / NVSwitch from inside the select and elimination kernels
+ * (sequence-numbered flags, no collective library on the path).  Protocol: create, export this rank's
+ * 64-byte CUDA IPC handle, ship the handles of all ranks to all ranks (rank order), attach, then use
+ * the shard like any other.  A peer that stops responding ends the run with LPGPU_ENCCL after 30 s.
+ * Destroy only after EVERY rank has returned from its last lpgpu_shard_run (host barrier): until then
+ * peers may still be storing flags into this rank's region. */
+#define LPGPU_IPC_HANDLE_BYTES 64
+int lpgpu_shard_create_p2p(lpgpu_ctx *ctx, int rank, int world, int m, int n, int R, lpgpu_shard **out);
+int lpgpu_shard_p2p_export(lpgpu_shard *s, void *handle64);
+int lpgpu_shard_p2p_attach(lpgpu_shard *s, const void *handles /* world x 64 bytes */);
 void lpgpu_shard_destroy(lpgpu_shard *s);
 /* T: the GLOBAL tableau (m+R) x (n+1) in host memory; each local rank copies b and its own block */
 int lpgpu_shard_upload(lpgpu_shard *s, const double *T, size_t ld, const int *basis);

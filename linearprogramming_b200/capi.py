@@ -21,6 +21,7 @@ DIRECT = 0x2             # dense: direct-load elimination kernel instead of the 
 NO_PDL = 0x400           # dense: plain stream-ordered launches (default: programmatic dependent launch)
 NO_ALTERNATE = 0x200     # dense: do not alternate the sweep direction between pivots
 NCCL_ID_BYTES = 128
+IPC_HANDLE_BYTES = 64
 
 
 class Opts(C.Structure):
@@ -79,6 +80,9 @@ SIGNATURES = {
     "lpgpu_shard_unique_id": (C.c_int, [_vp]),
     "lpgpu_shard_columns": (C.c_int, [C.c_int, C.c_int, C.c_int, _ip, _ip]),
     "lpgpu_shard_create": (C.c_int, [_vp, C.c_int, C.c_int, _vp, C.c_int, C.c_int, C.c_int, C.POINTER(_vp)]),
+    "lpgpu_shard_create_p2p": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(_vp)]),
+    "lpgpu_shard_p2p_export": (C.c_int, [_vp, _vp]),
+    "lpgpu_shard_p2p_attach": (C.c_int, [_vp, _vp]),
     "lpgpu_shard_destroy": (None, [_vp]),
     "lpgpu_shard_upload": (C.c_int, [_vp, _vp, C.c_size_t, _vp]),
     "lpgpu_shard_synth": (C.c_int, [_vp, C.c_uint64, C.c_uint64, C.c_int]),

@@ -192,17 +192,26 @@ int launch_select(lpgpu_dense *d, int forced_r, int forced_k) {
     return LPGPU_OK;
 }
 
-int launch_update(lpgpu_dense *d, double *cnext) {
+static int launch_update_impl(lpgpu_dense *d, double *cnext, void *const *peer_x, int n_peers, size_t peer_off);
+
+int launch_update(lpgpu_dense *d, double *cnext) { return launch_update_impl(d, cnext, nullptr, 0, 0); }
+
+int launch_update_peers(lpgpu_dense *d, void *const *peer_x, int n_peers, size_t peer_off) {
+    return launch_update_impl(d, nullptr, peer_x, n_peers, peer_off);
+}
+
+static int launch_update_impl(lpgpu_dense *d, double *cnext, void *const *peer_x, int n_peers, size_t peer_off) {
     lpgpu_ctx *ctx = d->ctx;
     UpdateParams U;
     U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.prow = d->prow; U.colbuf = d->pcol; U.pcn = d->pcn; U.bnext = d->bnext; U.st = d->st; U.cnext = cnext;
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
+    U.peer_x = peer_x; U.n_peers = n_peers; U.peer_off = peer_off;
     // variant: low nibble 0 = TMA-staged kernel with work stealing (default), 1 = TMA-staged with a
     //          static task stride, 2 = direct-load kernel;
     //          0x200 = do NOT alternate the sweep direction between pivots
     U.alternate = (d->opts.variant & 0x200) ? 0 : 1;
     const int kind = d->opts.variant & 0xf;
-    const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels && cnext == nullptr;
+    const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels && cnext == nullptr && n_peers == 0;
     LP_CUDA(ctx, launch_pdl(pdl, kind == 2 ? dense_update_direct : kind == 1 ? dense_update_tma_staged : dense_update_dynamic, dim3(d->grid_update),
                             dim3(UPD_THREADS), ctx->stream, U));
     ctx->launches++;

@@ -33,6 +33,9 @@ DenseParams make_params(const lpgpu_dense *d);
 // Enqueue the elimination pass.  cnext: where the pass leaves the next entering column
 // (nullptr = the other half of the tableau's own ping-pong buffer).
 int launch_update(lpgpu_dense *d, double *cnext);
+// column-sharded, peer-memory transport: the next entering column goes to byte offset peer_off of every
+// rank's exchange region (peer_x: device array of n_peers pointers)
+int launch_update_peers(lpgpu_dense *d, void *const *peer_x, int n_peers, size_t peer_off);
 int read_state(lpgpu_dense *d);
 
 }  // namespace lpgpu

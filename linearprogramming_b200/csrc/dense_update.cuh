@@ -36,7 +36,21 @@ struct UpdateParams {
     double *cnext;          // where the next entering column goes; nullptr = colbuf half st->cur ^ 1
     int *task_ctr;          // 2 counters for the work-stealing variant, used alternately by launch parity
     unsigned seq;           // launch sequence number (host side)
+    void *const *peer_x;    // column-sharded, peer-memory transport: the next entering column is stored into
+    int n_peers;            // every rank's exchange region at byte offset peer_off instead of cnext
+    size_t peer_off;
 };
+
+// where the owner of the next entering column leaves its freshly computed value for row i
+__device__ __forceinline__ void put_next_col(const UpdateParams &U, double *cnext, int i, double val) {
+    if (U.n_peers > 0) {
+        for (int g = 0; g < U.n_peers; ++g)
+            reinterpret_cast<double *>(reinterpret_cast<unsigned char *>(U.peer_x[g]) + U.peer_off)[i] = val;
+        __threadfence_system();      // performed at the peers before this kernel ends; the flag follows in stream order
+    } else {
+        cnext[i] = val;
+    }
+}
 
 constexpr int UPD_SPLIT = UPD_TILE_ROWS / UPD_UNROLL;   // row slices a leftover task is cut into
 
@@ -113,7 +127,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_direct(UpdatePara
                     if (i + u == r) o = pr;
                     st_stream2(base + (size_t)u * U.ld, o);
                     if (wb) U.bnext[i + u] = o.x;
-                    if (wk) cnext[i + u] = (kn & 1) ? o.y : o.x;
+                    if (wk) put_next_col(U, cnext, i + u, (kn & 1) ? o.y : o.x);
                 }
         }
     }
@@ -196,7 +210,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_tma_staged(Update
                         if (i + u == r) o = pr;
                         st_stream2(base + (size_t)u * U.ld, o);
                         if (wb) U.bnext[i + u] = o.x;
-                        if (wk) cnext[i + u] = (kn & 1) ? o.y : o.x;
+                        if (wk) put_next_col(U, cnext, i + u, (kn & 1) ? o.y : o.x);
                     }
             }
         }
@@ -297,7 +311,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) dense_update_dynamic(UpdatePar
                         if (i + u == r) o = pr;
                         st_stream2(base + (size_t)u * U.ld, o);
                         if (wb) U.bnext[i + u] = o.x;
-                        if (wk) cnext[i + u] = (kn & 1) ? o.y : o.x;
+                        if (wk) put_next_col(U, cnext, i + u, (kn & 1) ? o.y : o.x);
                     }
             }
         }

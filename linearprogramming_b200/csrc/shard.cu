@@ -23,10 +23,13 @@
 
 #include "dense_internal.h"
 #include "shard_nccl.h"
+#include "shard_p2p.cuh"
 
 using namespace lpgpu;
 
 namespace lpgpu {
+
+constexpr int PAIR_DOUBLES = 4;
 
 struct ShardState {
     int k_next;     // entering column of the pivot to decide next (global, 1-based; 0 = no candidate)
@@ -43,9 +46,34 @@ struct ShardParams {
     const double *pairs;     // world x 4 doubles
     double *sendcol;         // pcn doubles: the next entering column if this rank owns it
     const double *gathered;  // world x pcn doubles
+    // peer-memory transport (shard_p2p.cuh); peer_x == nullptr: stream-ordered exchange (NCCL / shared buffers)
+    void *const *peer_x;     // world pointers: every rank's exchange region, own included
+    unsigned iter;           // pipeline iteration, counted identically on every rank
+    int post;                // 0: decide only, post nothing (the extra select that ends a run call)
 };
 
-constexpr int PAIR_DOUBLES = 4;
+constexpr unsigned long long XCHG_TIMEOUT_NS = 30ull * 1000 * 1000 * 1000;
+
+// candidate of this rank -> every rank's pairs[parity][me], then the flags (release after the data)
+__device__ __forceinline__ void post_pair(const ShardParams &S) {
+    const int par = (int)(S.iter & 1u);
+    for (int g = 0; g < S.world; ++g) {
+        double *dst = xptr<double>(S.peer_x[g], XLayout::pairs(par)) + (size_t)S.rank * PAIR_DOUBLES;
+#pragma unroll
+        for (int q = 0; q < PAIR_DOUBLES; ++q) dst[q] = S.sendpair[q];
+    }
+    for (int g = 0; g < S.world; ++g)
+        st_release_sys(xptr<unsigned>(S.peer_x[g], XLayout::pair_flag(par)) + S.rank, S.iter + 1u);
+}
+
+// block-wide wait for every rank's candidate of this iteration; false = a peer never posted
+__device__ __forceinline__ bool wait_pairs(const ShardParams &S) {
+    const int par = (int)(S.iter & 1u);
+    int ok = 1;
+    if (threadIdx.x < (unsigned)S.world)
+        ok = spin_until(xptr<unsigned>(S.peer_x[S.rank], XLayout::pair_flag(par)) + threadIdx.x, S.iter + 1u, XCHG_TIMEOUT_NS);
+    return __syncthreads_and(ok) != 0;
+}
 
 __device__ __forceinline__ void store_pair(double *dst, const Cand &c, int col0) {
     dst[0] = c.p;
@@ -60,9 +88,9 @@ __device__ __forceinline__ Cand best_pair(const double *pairs, int world, int *o
     int who = 0;
     for (int g = 0; g < world; ++g) {
         Cand t;
-        t.p = pairs[g * PAIR_DOUBLES];
-        t.q = pairs[g * PAIR_DOUBLES + 1];
-        t.idx = (int)pairs[g * PAIR_DOUBLES + 2];
+        t.p = __ldcg(pairs + g * PAIR_DOUBLES);          // written by other GPUs: L2 is the point of coherence
+        t.q = __ldcg(pairs + g * PAIR_DOUBLES + 1);
+        t.idx = (int)__ldcg(pairs + g * PAIR_DOUBLES + 2);
         if (t.idx > 0 && cand_better(t, best)) { best = t; who = g; }
     }
     *owner = who;
@@ -74,15 +102,27 @@ __global__ void __launch_bounds__(SELECT_THREADS) shard_price_kernel(ShardParams
     __shared__ Cand scratch[SELECT_THREADS / 32];
     const DenseParams &P = S.P;
     Cand c = (P.method == LPGPU_BIGM) ? price_bigm(P, scratch) : price_row(P, P.m, P.n, scratch);
-    if (threadIdx.x == 0) store_pair(S.sendpair, c, S.col0);
+    if (threadIdx.x == 0) {
+        store_pair(S.sendpair, c, S.col0);
+        if (S.peer_x) post_pair(S);
+    }
 }
 
 // After exchange A.  gather = 1 (bootstrap): the owner also pulls the entering column out of its
 // tableau (strided) and every rank refreshes its compact copy of b.
 __global__ void __launch_bounds__(SELECT_THREADS) shard_resolve_kernel(ShardParams S, int gather) {
     const DenseParams &P = S.P;
+    const int par = (int)(S.iter & 1u);
+    const double *pairs = S.pairs;
+    if (S.peer_x) {
+        if (!wait_pairs(S)) {
+            if (blockIdx.x == 0 && threadIdx.x == 0) { P.st->status = LPGPU_EXCHANGE_TIMEOUT; P.st->do_pivot = 0; }
+            return;
+        }
+        pairs = xptr<double>(S.peer_x[S.rank], XLayout::pairs(par));
+    }
     int owner = 0;
-    const Cand best = best_pair(S.pairs, S.world, &owner);
+    const Cand best = best_pair(pairs, S.world, &owner);
     const int k = best.idx > 0 ? best.idx : 0;
     const bool mine = (k > 0) && (owner == S.rank);
     const int kl = mine ? k - S.col0 + 1 : 0;
@@ -94,9 +134,29 @@ __global__ void __launch_bounds__(SELECT_THREADS) shard_resolve_kernel(ShardPara
     if (gather) {
         const int rows = P.m + P.R;
         for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rows; i += gridDim.x * blockDim.x) {
-            if (mine) S.sendcol[i] = P.T[(size_t)i * P.ld + (size_t)kl];
+            if (mine) {
+                const double a = P.T[(size_t)i * P.ld + (size_t)kl];
+                if (S.peer_x) {
+                    for (int g = 0; g < S.world; ++g) xptr<double>(S.peer_x[g], XLayout::cols(par, P.pcn))[i] = a;
+                    __threadfence_system();
+                } else {
+                    S.sendcol[i] = a;
+                }
+            }
             P.bnext[i] = P.T[(size_t)i * P.ld];
         }
+    }
+}
+
+// peer-memory transport: after the elimination pass (stream order) the OWNER of the entering column --
+// the only rank that stored it -- tells every rank that the column of this iteration is complete in
+// its region.  (Were every rank to post, a rank's own flag would overtake the owner's data.)
+__global__ void shard_publish_kernel(ShardParams S) {
+    if (S.sh->owner != S.rank) return;
+    const int g = (int)threadIdx.x;
+    if (g < S.world) {
+        __threadfence_system();
+        st_release_sys(xptr<unsigned>(S.peer_x[g], XLayout::col_flag((int)(S.iter & 1u))), S.iter + 1u);
     }
 }
 
@@ -125,12 +185,29 @@ shard_select_kernel(ShardParams S) {
     const int k = S.sh->k_next, owner = S.sh->owner;
     if (status0 != LPGPU_RUNNING) {
         cl.sync();
-        if (gtid == 0) st->do_pivot = 0;
+        if (gtid == 0) {
+            st->do_pivot = 0;
+            if (S.peer_x && S.post) post_pair(S);      // peers still wait for a candidate every iteration
+        }
         return;
     }
     int status = status0, r = -1;
     bool have = false;
     const double *col = S.gathered + (size_t)owner * P.pcn;
+    if (S.peer_x) {
+        // the entering column was stored into this rank's region by its owner during iteration iter-1
+        const int cpar = (int)((S.iter - 1u) & 1u);
+        col = xptr<double>(S.peer_x[S.rank], XLayout::cols(cpar, P.pcn));
+        int ok = 1;
+        if (threadIdx.x == 0 && k > 0)
+            ok = spin_until(xptr<unsigned>(S.peer_x[S.rank], XLayout::col_flag(cpar)), S.iter, XCHG_TIMEOUT_NS);
+        ok = __syncthreads_and(ok);
+        if (!ok) {                                      // every CTA of the cluster times out alike
+            cl.sync();
+            if (gtid == 0) { st->status = LPGPU_EXCHANGE_TIMEOUT; st->do_pivot = 0; }
+            return;
+        }
+    }
     if (k <= 0) {
         // nothing prices in: optimal, unless Big-M left an artificial basic at a positive level
         const bool bad = (P.method == LPGPU_BIGM) && shard_art_positive(S);
@@ -138,7 +215,7 @@ shard_select_kernel(ShardParams S) {
     } else {
         Cand c = cand_none();
         for (int i = gtid; i < P.m; i += GSTRIDE) {
-            const double a = col[i];
+            const double a = __ldcg(col + i);
             if (a > P.eps) {
                 Cand t;
                 t.p = 0.0;
@@ -167,19 +244,22 @@ shard_select_kernel(ShardParams S) {
             P.basis[r] = k;
         }
     }
-    if (!have) return;
+    if (!have) {
+        if (gtid == 0 && S.peer_x && S.post) post_pair(S);
+        return;
+    }
 
     // ---- stage the pivot: entering column (all rows) into the local pivot-column buffer, scaled
     // local slice of the pivot row, and the local lookahead candidate for the pivot after this one
     const int rows = P.m + P.R;
-    for (int i = gtid; i < rows; i += GSTRIDE) P.pcol[i] = col[i];
-    const double piv = col[r];
+    for (int i = gtid; i < rows; i += GSTRIDE) P.pcol[i] = __ldcg(col + i);
+    const double piv = __ldcg(col + r);
     const double *xr = P.T + (size_t)r * P.ld;
     const bool bigm = (P.method == LPGPU_BIGM);
     const double *oc = P.T + (size_t)P.m * P.ld;
     const double *om = P.T + (size_t)(P.m + 1) * P.ld;            // Big-M row (R = 2 only)
-    const double fc = -col[P.m];
-    const double fm = bigm ? -col[P.m + 1] : 0.0;
+    const double fc = -__ldcg(col + P.m);
+    const double fm = bigm ? -__ldcg(col + P.m + 1) : 0.0;
     Cand c = cand_none();
     for (size_t j = (size_t)gtid; j < P.ld; j += GSTRIDE) {
         const double pr = div_skip_zero(xr[j], piv);
@@ -200,7 +280,10 @@ shard_select_kernel(ShardParams S) {
         }
     }
     c = cluster_best(cl, c, scratch, slot_look);
-    if (gtid == 0) store_pair(S.sendpair, c, S.col0);
+    if (gtid == 0) {
+        store_pair(S.sendpair, c, S.col0);
+        if (S.peer_x) post_pair(S);
+    }
 }
 
 __global__ void shard_synth_kernel(double *T, size_t ld, int m, int ns, int col0, int ncols, int *basis,
@@ -241,7 +324,13 @@ struct lpgpu_shard {
     lpgpu_ctx *ctx;
     int world, m, n, R;
     bool use_nccl;
+    bool use_p2p;                     // peer-memory transport (shard_p2p.cuh)
+    bool attached;                    // ... and the peers' regions are mapped
     ncclComm_t comm;
+    void *xregion;                    // this rank's exchange region
+    void **peer_host;                 // world mapped pointers (own = xregion), host copy
+    void **peer_dev;                  // the same table in device memory
+    unsigned iter;                    // pipeline iterations so far (identical on every rank)
     std::vector<ShardRank> rk;        // the ranks that live in this process (1 with NCCL, `world` without)
     double *pairs_buf, *gath_buf;     // exchange buffers (shared by all local ranks without NCCL)
     double *xbuf;
@@ -270,12 +359,22 @@ ShardParams shard_params(const lpgpu_shard *s, const ShardRank &r) {
     S.P = make_params(r.d);
     S.rank = r.rank; S.world = s->world; S.col0 = r.col0; S.n_global = s->n; S.n_art = s->opts.n_art;
     S.sh = r.sh; S.sendpair = r.sendpair; S.pairs = r.pairs; S.sendcol = r.sendcol; S.gathered = r.gathered;
+    S.peer_x = s->use_p2p ? s->peer_dev : nullptr; S.iter = s->iter; S.post = 1;
     return S;
 }
 
 // exchange A (which = 0): candidates; exchange B (which = 1): entering column.  Without NCCL the
 // local ranks write straight into the shared gather buffers, so there is nothing to move.
 int exchange(lpgpu_shard *s, int which) {
+    if (s->use_p2p) {
+        // candidates travel inside the select / price kernels; the column inside the elimination pass.
+        // What is left is the "column complete" flag, after the pass in stream order.
+        if (which == 1) {
+            shard_publish_kernel<<<1, XMAXW, 0, s->ctx->stream>>>(shard_params(s, s->rk[0]));
+            LP_LAUNCH_CHECK(s->ctx);
+        }
+        return LPGPU_OK;
+    }
     if (!s->use_nccl) return LPGPU_OK;
     const NcclApi *api = nccl_api();
     const ShardRank &r = s->rk[0];
@@ -295,9 +394,11 @@ int push_state(lpgpu_shard *s, const PivotState &st) {
     return LPGPU_OK;
 }
 
-int enqueue_select(lpgpu_shard *s) {
+int enqueue_select(lpgpu_shard *s, int post = 1) {
     for (ShardRank &r : s->rk) {
-        shard_select_kernel<<<SELECT_CLUSTER, SELECT_THREADS, 0, s->ctx->stream>>>(shard_params(s, r));
+        ShardParams S = shard_params(s, r);
+        S.post = post;
+        shard_select_kernel<<<SELECT_CLUSTER, SELECT_THREADS, 0, s->ctx->stream>>>(S);
         LP_LAUNCH_CHECK(s->ctx);
     }
     return LPGPU_OK;
@@ -306,11 +407,23 @@ int enqueue_select(lpgpu_shard *s) {
 int enqueue_resolve(lpgpu_shard *s, int gather) {
     for (ShardRank &r : s->rk) {
         const int grid = gather ? std::max(1, std::min(64, (s->m + s->R + SELECT_THREADS - 1) / SELECT_THREADS)) : 1;
-        shard_resolve_kernel<<<grid, gather ? SELECT_THREADS : 32, 0, s->ctx->stream>>>(shard_params(s, r), gather);
+        shard_resolve_kernel<<<grid, gather ? SELECT_THREADS : XMAXW, 0, s->ctx->stream>>>(shard_params(s, r), gather);
         LP_LAUNCH_CHECK(s->ctx);
     }
     return LPGPU_OK;
 }
+
+int enqueue_update(lpgpu_shard *s) {
+    int rc = LPGPU_OK;
+    for (ShardRank &r : s->rk) {
+        if (s->use_p2p) rc = launch_update_peers(r.d, s->peer_dev, s->world, XLayout::cols((int)(s->iter & 1u), s->pcn));
+        else rc = launch_update(r.d, r.sendcol);
+        if (rc != LPGPU_OK) return rc;
+    }
+    return rc;
+}
+
+int shard_create_common(lpgpu_ctx *ctx, int rank, int world, int transport, const void *id128, int m, int n, int R, lpgpu_shard **out);
 
 }  // namespace
 
@@ -334,20 +447,64 @@ int lpgpu_shard_columns(int n, int world, int rank, int *col0, int *ncols) {
 }
 
 int lpgpu_shard_create(lpgpu_ctx *ctx, int rank, int world, const void *id128, int m, int n, int R, lpgpu_shard **out) {
+    return shard_create_common(ctx, rank, world, id128 ? 1 : 0, id128, m, n, R, out);
+}
+
+int lpgpu_shard_create_p2p(lpgpu_ctx *ctx, int rank, int world, int m, int n, int R, lpgpu_shard **out) {
+    return shard_create_common(ctx, rank, world, 2, nullptr, m, n, R, out);
+}
+
+int lpgpu_shard_p2p_export(lpgpu_shard *s, void *handle64) {
+    if (!s || !handle64) return LPGPU_EINVAL;
+    if (!s->use_p2p) return fail(s->ctx, LPGPU_EINVAL, "shard_p2p_export: not a peer-memory shard");
+    static_assert(sizeof(cudaIpcMemHandle_t) == LPGPU_IPC_HANDLE_BYTES, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    LP_CUDA(s->ctx, cudaSetDevice(s->ctx->device));
+    LP_CUDA(s->ctx, cudaIpcGetMemHandle(&h, s->xregion));
+    memcpy(handle64, &h, sizeof h);
+    return LPGPU_OK;
+}
+
+int lpgpu_shard_p2p_attach(lpgpu_shard *s, const void *handles) {
+    if (!s || !handles) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = s->ctx;
+    if (!s->use_p2p || s->attached) return fail(ctx, LPGPU_EINVAL, "shard_p2p_attach: not a peer-memory shard, or attached already");
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int me = s->rk[0].rank;
+    for (int g = 0; g < s->world; ++g) {
+        if (g == me) { s->peer_host[g] = s->xregion; continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, static_cast<const unsigned char *>(handles) + (size_t)g * LPGPU_IPC_HANDLE_BYTES, sizeof h);
+        LP_CUDA(ctx, cudaIpcOpenMemHandle(&s->peer_host[g], h, cudaIpcMemLazyEnablePeerAccess));
+    }
+    LP_CUDA(ctx, cudaMemcpyAsync(s->peer_dev, s->peer_host, (size_t)s->world * sizeof(void *), cudaMemcpyHostToDevice, ctx->stream));
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    s->attached = true;
+    return LPGPU_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+int shard_create_common(lpgpu_ctx *ctx, int rank, int world, int transport, const void *id128, int m, int n, int R, lpgpu_shard **out) {
     if (!ctx || !out) return LPGPU_EINVAL;
     *out = nullptr;
     if (m < 1 || n < 1 || (R != 1 && R != 2) || world < 1 || world > n || world > 64)
         return fail(ctx, LPGPU_EINVAL, "shard_create: bad shape m=%d n=%d R=%d world=%d", m, n, R, world);
-    if (id128 && (rank < 0 || rank >= world)) return fail(ctx, LPGPU_EINVAL, "shard_create: rank %d of %d", rank, world);
+    if (transport != 0 && (rank < 0 || rank >= world)) return fail(ctx, LPGPU_EINVAL, "shard_create: rank %d of %d", rank, world);
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
     lpgpu_shard *s = new (std::nothrow) lpgpu_shard();
     if (!s) return fail(ctx, LPGPU_ENOMEM, "shard_create: host allocation failed");
     s->ctx = ctx; s->world = world; s->m = m; s->n = n; s->R = R;
-    s->use_nccl = id128 != nullptr; s->comm = nullptr; s->pairs_buf = s->gath_buf = s->xbuf = nullptr; s->dirty = true;
+    s->use_nccl = transport == 1; s->use_p2p = transport == 2; s->attached = false; s->comm = nullptr;
+    s->xregion = nullptr; s->peer_host = nullptr; s->peer_dev = nullptr; s->iter = 0;
+    s->pairs_buf = s->gath_buf = s->xbuf = nullptr; s->dirty = true;
     lpgpu_default_opts(&s->opts);
     s->opts.method = (R == 1) ? LPGPU_PLAIN : LPGPU_BIGM;
     int rc = LPGPU_OK;
-    const int first = s->use_nccl ? rank : 0, last = s->use_nccl ? rank + 1 : world;
+    const bool one_rank = transport != 0;
+    const int first = one_rank ? rank : 0, last = one_rank ? rank + 1 : world;
     for (int g = first; g < last && rc == LPGPU_OK; ++g) {
         ShardRank r{};
         r.rank = g;
@@ -370,7 +527,7 @@ int lpgpu_shard_create(lpgpu_ctx *ctx, int rank, int world, const void *id128, i
         if (e == cudaSuccess) e = cudaMemsetAsync(r.sh, 0, sizeof(ShardState), ctx->stream);
         r.pairs = s->pairs_buf;
         r.gathered = s->gath_buf;
-        if (s->use_nccl) {
+        if (one_rank) {
             if (e == cudaSuccess) e = cudaMalloc(&r.sendpair, PAIR_DOUBLES * sizeof(double));
             if (e == cudaSuccess) e = cudaMalloc(&r.sendcol, s->pcn * sizeof(double));
             if (e == cudaSuccess) e = cudaMemsetAsync(r.sendcol, 0, s->pcn * sizeof(double), ctx->stream);
@@ -382,6 +539,24 @@ int lpgpu_shard_create(lpgpu_ctx *ctx, int rank, int world, const void *id128, i
     if (e != cudaSuccess) {
         lpgpu_shard_destroy(s);
         return fail(ctx, e == cudaErrorMemoryAllocation ? LPGPU_ENOMEM : LPGPU_ECUDA, "shard_create: %s", cudaGetErrorString(e));
+    }
+    if (s->use_p2p) {
+        const size_t xb = XLayout::bytes(s->pcn);
+        s->peer_host = new (std::nothrow) void *[world]();
+        if (e == cudaSuccess && !s->peer_host) e = cudaErrorMemoryAllocation;
+        if (e == cudaSuccess) e = cudaMalloc(&s->xregion, xb);
+        if (e == cudaSuccess) e = cudaMemsetAsync(s->xregion, 0, xb, ctx->stream);
+        if (e == cudaSuccess) e = cudaMalloc(&s->peer_dev, (size_t)world * sizeof(void *));
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) {
+            lpgpu_shard_destroy(s);
+            return fail(ctx, e == cudaErrorMemoryAllocation ? LPGPU_ENOMEM : LPGPU_ECUDA, "shard_create_p2p: %s", cudaGetErrorString(e));
+        }
+        if (world == 1) {                 // nothing to map
+            s->peer_host[0] = s->xregion;
+            cudaMemcpy(s->peer_dev, s->peer_host, sizeof(void *), cudaMemcpyHostToDevice);
+            s->attached = true;
+        }
     }
     if (s->use_nccl) {
         const NcclApi *api = nccl_api();
@@ -401,6 +576,10 @@ int lpgpu_shard_create(lpgpu_ctx *ctx, int rank, int world, const void *id128, i
     return LPGPU_OK;
 }
 
+}  // namespace
+
+extern "C" {
+
 void lpgpu_shard_destroy(lpgpu_shard *s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device);
@@ -409,8 +588,14 @@ void lpgpu_shard_destroy(lpgpu_shard *s) {
     for (ShardRank &r : s->rk) {
         lpgpu_dense_destroy(r.d);
         cudaFree(r.sh);
-        if (s->use_nccl) { cudaFree(r.sendpair); cudaFree(r.sendcol); }
+        if (s->use_nccl || s->use_p2p) { cudaFree(r.sendpair); cudaFree(r.sendcol); }
     }
+    if (s->peer_host) {
+        for (int g = 0; g < s->world; ++g)
+            if (s->peer_host[g] && s->peer_host[g] != s->xregion) cudaIpcCloseMemHandle(s->peer_host[g]);
+        delete[] s->peer_host;
+    }
+    cudaFree(s->xregion); cudaFree(s->peer_dev);
     cudaFree(s->pairs_buf); cudaFree(s->gath_buf); cudaFree(s->xbuf);
     delete s;
 }
@@ -469,6 +654,7 @@ int lpgpu_shard_synth(lpgpu_shard *s, uint64_t seed, uint64_t lp_index, int ns) 
 int lpgpu_shard_run(lpgpu_shard *s, int max_pivots, lpgpu_result *res) {
     if (!s || !res || max_pivots < 0) return LPGPU_EINVAL;
     lpgpu_ctx *ctx = s->ctx;
+    if (s->use_p2p && !s->attached) return fail(ctx, LPGPU_EINVAL, "shard_run: peer regions are not attached (lpgpu_shard_p2p_attach)");
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
     lpgpu_dense *d0 = s->rk[0].d;
     int rc = read_state(d0);                    // the state is a replica on every rank
@@ -487,6 +673,7 @@ int lpgpu_shard_run(lpgpu_shard *s, int max_pivots, lpgpu_result *res) {
         if ((rc = exchange(s, 0)) != LPGPU_OK) return rc;
         if ((rc = enqueue_resolve(s, 1)) != LPGPU_OK) return rc;
         if ((rc = exchange(s, 1)) != LPGPU_OK) return rc;
+        s->iter++;
         s->dirty = false;
     }
     const int chunk_max = s->opts.check_every;
@@ -497,9 +684,9 @@ int lpgpu_shard_run(lpgpu_shard *s, int max_pivots, lpgpu_result *res) {
             if ((rc = enqueue_select(s)) != LPGPU_OK) return rc;
             if ((rc = exchange(s, 0)) != LPGPU_OK) return rc;
             if ((rc = enqueue_resolve(s, 0)) != LPGPU_OK) return rc;
-            for (ShardRank &r : s->rk)
-                if ((rc = launch_update(r.d, r.sendcol)) != LPGPU_OK) return rc;
+            if ((rc = enqueue_update(s)) != LPGPU_OK) return rc;
             if ((rc = exchange(s, 1)) != LPGPU_OK) return rc;
+            s->iter++;
         }
         launched += chunk;
         if ((rc = read_state(d0)) != LPGPU_OK) return rc;
@@ -509,9 +696,11 @@ int lpgpu_shard_run(lpgpu_shard *s, int max_pivots, lpgpu_result *res) {
     }
     if (d0->h_st->status == LPGPU_RUNNING) {
         // budget spent: one decision-only select settles a terminal status without applying a pivot
-        if ((rc = enqueue_select(s)) != LPGPU_OK) return rc;
+        if ((rc = enqueue_select(s, 0)) != LPGPU_OK) return rc;
         if ((rc = read_state(d0)) != LPGPU_OK) return rc;
     }
+    if (d0->h_st->status == LPGPU_EXCHANGE_TIMEOUT)
+        return fail(ctx, LPGPU_ENCCL, "shard_run: a peer did not post its part of the exchange within %llu s", XCHG_TIMEOUT_NS / 1000000000ull);
     double zc[2] = {0.0, 0.0};
     LP_CUDA(ctx, cudaMemcpyAsync(&zc[0], d0->T + (size_t)s->m * d0->ld, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     if (s->R == 2)

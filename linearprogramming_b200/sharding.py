@@ -57,6 +57,14 @@ def exchange_nccl_id(dist, src=0):
     return box[0]
 
 
+def attach_p2p(dist, shard):
+    """Peer-memory transport: all-gather the ranks' CUDA IPC handles over the process group and map them."""
+    handles = [None] * dist.get_world_size()
+    dist.all_gather_object(handles, shard.p2p_export())
+    shard.p2p_attach(handles)
+    dist.barrier()          # nobody starts posting before everybody has mapped
+
+
 def gather_batched(dist, local, dst=0):
     """Concatenate per-rank result dicts (status, iters, z, x, basis) in rank order on ``dst``."""
     world = dist.get_world_size()

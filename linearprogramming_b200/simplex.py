@@ -185,17 +185,36 @@ class ShardedTableau:
 
     nccl_id = 128 bytes from ``sharding.exchange_nccl_id`` : this process is rank ``rank`` of ``world``
     (one process per GPU, exchanges over NCCL).  nccl_id = None : all ``world`` ranks live in this
-    process on the context's device (single-GPU vehicle for the N > 1 logic)."""
+    process on the context's device (single-GPU vehicle for the N > 1 logic).  p2p = True: one rank per
+    process, exchanges are stores into peer GPU memory (``sharding.attach_p2p`` maps the peers)."""
 
-    def __init__(self, ctx, m, n, R=1, world=1, rank=0, nccl_id=None):
+    def __init__(self, ctx, m, n, R=1, world=1, rank=0, nccl_id=None, p2p=False):
         self.ctx, self.m, self.n, self.R, self.world, self.rank = ctx, m, n, R, world, rank
         self._h = C.c_void_p()
         self._log_cap = 0
+        if p2p:
+            capi.check(ctx.handle, capi.lib().lpgpu_shard_create_p2p(ctx.handle, rank, world, m, n, R, C.byref(self._h)),
+                       "lpgpu_shard_create_p2p")
+            return
         if nccl_id is not None and len(nccl_id) != capi.NCCL_ID_BYTES:
             raise ValueError("nccl_id must be 128 bytes")
         idbuf = C.create_string_buffer(bytes(nccl_id), capi.NCCL_ID_BYTES) if nccl_id is not None else None
         capi.check(ctx.handle, capi.lib().lpgpu_shard_create(ctx.handle, rank, world, idbuf, m, n, R, C.byref(self._h)),
                    "lpgpu_shard_create")
+
+    def p2p_export(self):
+        """This rank's 64-byte CUDA IPC handle of its exchange region."""
+        buf = C.create_string_buffer(capi.IPC_HANDLE_BYTES)
+        capi.check(self.ctx.handle, capi.lib().lpgpu_shard_p2p_export(self._h, buf), "lpgpu_shard_p2p_export")
+        return bytes(buf.raw)
+
+    def p2p_attach(self, handles):
+        """handles: the export of every rank, in rank order."""
+        blob = b"".join(handles)
+        if len(blob) != self.world * capi.IPC_HANDLE_BYTES:
+            raise ValueError("need one 64-byte handle per rank")
+        capi.check(self.ctx.handle, capi.lib().lpgpu_shard_p2p_attach(self._h, C.create_string_buffer(blob, len(blob))),
+                   "lpgpu_shard_p2p_attach")
 
     def upload(self, T, basis):
         T = np.ascontiguousarray(T, np.float64)

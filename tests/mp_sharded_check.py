@@ -23,33 +23,46 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("gloo")                      # host plumbing only; the data path is our own NCCL comm
     ctx = lp.Context(local)
-    for (m, ns, method) in [(64, 48, O.PLAIN), (300, 260, O.PLAIN), (40, 30, O.BIGM)]:
-        if method == O.PLAIN:
-            T, basis = O.synth_feasible(1234, 7, m, ns)
-            n_art = 0
-        else:
-            import helpers as H
-            A, b, c, rel = H.random_mixed_lp(np.random.default_rng(5), m, ns)
-            T, basis, n_art = O.build_tableau(A, b, c, rel, R=2)
-        R = 1 if method == O.PLAIN else 2
-        n = T.shape[1] - 1
-        ref = O.solve_f64(T, basis, method=method, n_art=n_art, log_cap=8192)
-        ident = sharding.exchange_nccl_id(dist)
-        s = lp.ShardedTableau(ctx, m, n, R, world=world, rank=rank, nccl_id=ident)
-        s.upload(T, basis)
-        s.reset(method=method, n_art=n_art, log_cap=8192)
-        res = s.run(2**31 - 1)
-        out = s.download()
-        s.close()
-        assert res["status"] == ref["status"] and res["iters"] == ref["iters"], (res, ref["status"], ref["iters"])
-        assert out["log"][:res["n_logged"]].tolist() == ref["log"].tolist()
-        assert np.array_equal(out["basis"], ref["basis"]) and np.array_equal(out["x"], ref["x"]) and res["z"] == ref["z"]
-        c0, nc = sharding.column_block(n, world, rank)
-        assert np.array_equal(out["T"][:, 0], ref["T"][:, 0])
-        assert np.array_equal(out["T"][:, c0:c0 + nc], ref["T"][:, c0:c0 + nc])
-        full = sharding.merge_column_blocks(dist, out["T"], n)
-        if rank == 0:
-            assert np.array_equal(full, ref["T"])
+    window = int(os.environ.get("MP_WINDOW", "9"))
+    for transport in os.environ.get("MP_TRANSPORTS", "nccl,p2p").split(","):
+      for (m, ns, method) in [(64, 48, O.PLAIN), (300, 260, O.PLAIN), (40, 30, O.BIGM)]:
+          if method == O.PLAIN:
+              T, basis = O.synth_feasible(1234, 7, m, ns)
+              n_art = 0
+          else:
+              import helpers as H
+              A, b, c, rel = H.random_mixed_lp(np.random.default_rng(5), m, ns)
+              T, basis, n_art = O.build_tableau(A, b, c, rel, R=2)
+          R = 1 if method == O.PLAIN else 2
+          n = T.shape[1] - 1
+          ref = O.solve_f64(T, basis, method=method, n_art=n_art, log_cap=8192)
+          if transport == "nccl":
+              ident = sharding.exchange_nccl_id(dist)
+              s = lp.ShardedTableau(ctx, m, n, R, world=world, rank=rank, nccl_id=ident)
+          else:
+              s = lp.ShardedTableau(ctx, m, n, R, world=world, rank=rank, p2p=True)
+              sharding.attach_p2p(dist, s)
+          s.upload(T, basis)
+          s.reset(method=method, n_art=n_art, log_cap=8192)
+          if transport == "p2p" and window > 0:
+              while True:                                   # windows of 9 pivots: flags keep counting across run calls
+                  res = s.run(window)
+                  if res["status"] != lp.RUNNING:
+                      break
+          else:
+              res = s.run(2**31 - 1)
+          out = s.download()
+          dist.barrier()                                   # p2p: peers may still be storing flags into this rank's region
+          s.close()
+          assert res["status"] == ref["status"] and res["iters"] == ref["iters"], (transport, m, res, ref["status"], ref["iters"])
+          assert out["log"][:res["n_logged"]].tolist() == ref["log"].tolist(), (transport, m, out["log"][:res["n_logged"]].tolist(), ref["log"].tolist())
+          assert np.array_equal(out["basis"], ref["basis"]) and np.array_equal(out["x"], ref["x"]) and res["z"] == ref["z"]
+          c0, nc = sharding.column_block(n, world, rank)
+          assert np.array_equal(out["T"][:, 0], ref["T"][:, 0])
+          assert np.array_equal(out["T"][:, c0:c0 + nc], ref["T"][:, c0:c0 + nc])
+          full = sharding.merge_column_blocks(dist, out["T"], n)
+          if rank == 0:
+              assert np.array_equal(full, ref["T"])
     ctx.close()
     dist.barrier()
     if rank == 0:

@@ -138,8 +138,25 @@ def test_sharded_nccl_transport_world1(ctx):
     _assert_equal(got, ref)
 
 
+def test_sharded_p2p_transport_world1(ctx):
+    """Peer-memory transport with a single rank: flags, parity buffers and windows on one GPU."""
+    T, basis = O.synth_feasible(1234, 2, 64, 48)
+    ref = O.solve_f64(T, basis, log_cap=4096)
+    s = lp.ShardedTableau(ctx, 64, 112, 1, world=1, rank=0, p2p=True)
+    s.upload(T, basis)
+    s.reset(log_cap=4096, check_every=5)
+    while True:
+        res = s.run(7)
+        if res["status"] != lp.RUNNING:
+            break
+    out = s.download()
+    s.close()
+    res.update(T=out["T"], basis=out["basis"], log=out["log"][:res["n_logged"]], x=out["x"])
+    _assert_equal(res, ref)
+
+
 def test_sharded_nccl_two_processes():
-    """One process per GPU over NCCL (torchrun), bit-compared with the oracle inside the script."""
+    """One process per GPU (torchrun), NCCL and peer-memory transports, bit-compared with the oracle inside the script."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")

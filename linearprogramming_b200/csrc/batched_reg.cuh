@@ -89,7 +89,7 @@ __device__ __forceinline__ unsigned long long key_ordered(double x) {
 }
 
 template <int WARPS, int RT, int CT>
-__global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 11 : 3)) batched_reg_kernel(BatchedParams B) {
+__global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : WARPS == 2 ? 8 : 3)) batched_reg_kernel(BatchedParams B) {
     using Cfg = RegCfg<WARPS, RT, CT>;
     static_assert(RT % 2 == 0 && RT <= 32, "rows per warp: even (128-bit column reads), one b per lane");
     extern __shared__ __align__(128) unsigned char smem_raw[];

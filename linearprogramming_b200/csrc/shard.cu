@@ -138,7 +138,6 @@ __global__ void __launch_bounds__(SELECT_THREADS) shard_resolve_kernel(ShardPara
                 const double a = P.T[(size_t)i * P.ld + (size_t)kl];
                 if (S.peer_x) {
                     for (int g = 0; g < S.world; ++g) xptr<double>(S.peer_x[g], XLayout::cols(par, P.pcn))[i] = a;
-                    __threadfence_system();
                 } else {
                     S.sendcol[i] = a;
                 }

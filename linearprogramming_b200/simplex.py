@@ -306,12 +306,12 @@ class BatchedLPs:
         capi.check(self.ctx.handle, capi.lib().lpgpu_batched_synth(self._h, seed, lp0, ns), "lpgpu_batched_synth")
 
     def run(self, method=None, n_art=0, eps=1e-9, max_iter=2**31 - 1, log_cap=0, keep_final=False, timed=True,
-            force_smem=False):
+            force_smem=False, variant=0):
         if method is None:
             method = PLAIN if self.R == 1 else BIGM
         o = capi.default_opts(eps=eps, max_iter=int(min(max_iter, 2**31 - 1)), method=method, n_art=n_art,
                               log_cap=log_cap,
-                              variant=(capi.KEEP_FINAL if keep_final else 0) | (capi.FORCE_SMEM if force_smem else 0))
+                              variant=(capi.KEEP_FINAL if keep_final else 0) | (capi.FORCE_SMEM if force_smem else 0) | variant)
         self._log_cap = max(self._log_cap, log_cap)
         self._keep = keep_final
         ms = C.c_float(0.0)

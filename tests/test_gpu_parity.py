@@ -254,6 +254,35 @@ def test_batched_plain_unbounded_and_iteration_limit(ctx, force_smem):
     assert lp.UNBOUNDED in set(ref["status"].tolist()) | set(O.solve_batched_f64(T, B)["status"].tolist())
 
 
+def test_cfg3_full_size_batched_bitwise(ctx):
+    """BASELINE config 3 at its full size: 100 000 LPs m=32 n=64, device generator, every LP's status,
+    iteration count, objective, x and basis bit-compared with the oracle (host generator)."""
+    n_lp, m, ns = 100_000, 32, 32
+    b = lp.BatchedLPs(ctx, n_lp, m, m + ns, 1)
+    b.synth(1234, 0, ns)
+    b.run()
+    got = b.download()
+    b.close()
+    T, basis = O.synth_feasible_batch(1234, 0, n_lp, m, ns)
+    ref = O.solve_batched_f64(T, basis, threads=16)
+    _assert_batched_equal(got, ref)
+    assert np.all(got["status"] == lp.OPTIMAL) and got["iters"].mean() > 10
+
+
+def test_cfg5a_sample_batched_bitwise(ctx):
+    """BASELINE config 5a shape (m=64 n=128), LP indices 600 000 .. 620 000 of the million (what rank 4 of 8
+    would hold first), against the oracle."""
+    n_lp, m, ns, lo = 20_000, 64, 64, 600_000
+    b = lp.BatchedLPs(ctx, n_lp, m, m + ns, 1)
+    b.synth(1234, lo, ns)
+    b.run()
+    got = b.download()
+    b.close()
+    T, basis = O.synth_feasible_batch(1234, lo, n_lp, m, ns)
+    ref = O.solve_batched_f64(T, basis, threads=16)
+    _assert_batched_equal(got, ref)
+
+
 @pytest.mark.parametrize("method", [O.BIGM, O.TWOPHASE])
 def test_batched_bigm_twophase(ctx, method):
     rng = np.random.default_rng(5)

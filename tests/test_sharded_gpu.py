@@ -118,6 +118,28 @@ def test_sharded_windows_iteration_limit_and_device_synth(ctx):
     assert np.array_equal(out["T"], ref["T"]) and out["log"][:res["n_logged"]].tolist() == ref["log"].tolist()
 
 
+def test_sharded_equals_single_gpu_path_bitwise_midsize(ctx):
+    """1024 x 4096, first 300 pivots: the column-sharded run (4 and 7 ranks) leaves exactly the tableau,
+    basis and pivot log of the single-tableau path (tier T4)."""
+    m, ns, P = 1024, 3072, 300
+    d = lp.DenseTableau(ctx, m, m + ns, 1)
+    d.synth(1234, 3, ns)
+    d.reset(log_cap=P)
+    r1 = d.run(P)
+    one = d.download()
+    d.close()
+    for world in (4, 7):
+        s = lp.ShardedTableau(ctx, m, m + ns, 1, world=world)
+        s.synth(1234, 3, ns)
+        s.reset(log_cap=P)
+        r2 = s.run(P)
+        many = s.download()
+        s.close()
+        assert r2["iters"] == r1["iters"] == P and r2["status"] == r1["status"] == lp.RUNNING
+        assert np.array_equal(many["log"], one["log"]) and np.array_equal(many["basis"], one["basis"])
+        assert np.array_equal(many["T"], one["T"]) and r2["z"] == r1["z"]
+
+
 def test_sharded_rejects_twophase_and_bad_shapes(ctx):
     with pytest.raises(lp.LpgpuError):
         lp.ShardedTableau(ctx, 4, 3, 1, world=4)             # more ranks than columns

@@ -193,8 +193,9 @@ def reference_arm(args):
         "impl": "reference", "metric": "pivots_per_sec", "value": value, "unit": "pivots/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(times) / len(times),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"dense tableau {m}x{m + ns} fp64 random feasible LP (BASELINE config 4)",
-                   "m": m, "n": m + ns, "pivots_per_step": p, "sample": sample},
+        "config": {"workload": f"dense tableau {m}x{m + ns} fp64 random feasible LP per GPU (BASELINE config 4)",
+                   "m": m, "n": m + ns, "tableau_bytes": (m + 1) * (m + ns + 1) * 8, "pivots_per_step": p, "seed": SEED,
+                   "sample": sample},
         "cpu_baseline": {"value": value, "unit": "pivots/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "pivots/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,

@@ -55,6 +55,9 @@ extern "C" {
 #define LPGPU_PLAIN     0     /* R = 1                                           */
 #define LPGPU_BIGM      1     /* R = 2, (sigmaM, sigma) lexicographic            */
 #define LPGPU_TWOPHASE  2     /* R = 2, phase 1 on row m+1, then row m           */
+#define LPGPU_DUAL      3     /* R = 1, dual simplex: the tableau must be dual feasible (every sigma_j
+                               * <= 0), b may be negative; leaving row = most negative b_i, entering
+                               * column = min sigma_j / a_rj over a_rj < 0      */
 
 typedef struct lpgpu_ctx lpgpu_ctx;         /* one per process and GPU           */
 typedef struct lpgpu_dense lpgpu_dense;     /* one large device-resident tableau */
@@ -63,7 +66,7 @@ typedef struct lpgpu_batched lpgpu_batched; /* many small tableaux              
 typedef struct {
     double eps;         /* pricing / ratio / snap tolerance (1e-9)                       */
     int max_iter;       /* total pivot cap -> LPGPU_ITER_LIMIT                           */
-    int method;         /* LPGPU_PLAIN | LPGPU_BIGM | LPGPU_TWOPHASE                     */
+    int method;         /* LPGPU_PLAIN | LPGPU_BIGM | LPGPU_TWOPHASE | LPGPU_DUAL        */
     int n_art;          /* number of trailing artificial columns                         */
     int log_cap;        /* pivots to record in the pivot log (0 = none)                  */
     int check_every;    /* dense: pivots enqueued between host status reads (0 = 64)     */

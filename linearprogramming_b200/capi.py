@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(HERE, "liblpgpu.so")
 
 OK, EINVAL, ENODEV, ECUDA, ENOMEM, ENCCL = 0, -1, -2, -3, -4, -5
 OPTIMAL, UNBOUNDED, INFEASIBLE, ITER_LIMIT, RUNNING = 0, 1, 2, 3, 4
-PLAIN, BIGM, TWOPHASE = 0, 1, 2
+PLAIN, BIGM, TWOPHASE, DUAL = 0, 1, 2, 3
 STATUS_NAMES = {0: "OPTIMAL", 1: "UNBOUNDED", 2: "INFEASIBLE", 3: "ITER_LIMIT", 4: "RUNNING"}
 KEEP_FINAL = 0x1000      # batched: keep the final tableaux on the device (parity tests)
 FORCE_SMEM = 0x2000      # batched: shared-memory kernel even where the register-resident one applies

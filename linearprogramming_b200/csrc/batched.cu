@@ -30,8 +30,8 @@ using RegWide = RegCfg<4, 16, 4>;      // m <= 64, n <= 128: four warps per LP
 
 bool batched_opts_ok(const lpgpu_opts *o, int n, int R) {
     if (!o) return false;
-    if (o->method != LPGPU_PLAIN && o->method != LPGPU_BIGM && o->method != LPGPU_TWOPHASE) return false;
-    if ((o->method == LPGPU_PLAIN) != (R == 1)) return false;
+    if (o->method != LPGPU_PLAIN && o->method != LPGPU_BIGM && o->method != LPGPU_TWOPHASE && o->method != LPGPU_DUAL) return false;
+    if ((o->method == LPGPU_PLAIN || o->method == LPGPU_DUAL) != (R == 1)) return false;
     if (o->n_art < 0 || o->n_art > n || o->max_iter < 0 || o->log_cap < 0 || !(o->eps >= 0.0)) return false;
     return true;
 }

@@ -118,7 +118,7 @@ dense_select_kernel(DenseParams P, int forced_r, int forced_k) {
     const double *xr = P.T + (size_t)r * P.ld;
 
     // lookahead pricing mode for the pivot after this one
-    const bool look = (forced_k <= 0) && (phase != PH_DRIVEOUT);
+    const bool look = (forced_k <= 0) && (phase != PH_DRIVEOUT) && (P.method != LPGPU_DUAL);   // dual: full decision every pivot
     const bool bigm = (P.method == LPGPU_BIGM);
     const int prow_obj = bigm ? P.m : ((phase == PH_ONE) ? P.m + 1 : P.m);
     const int jmax = (P.method == LPGPU_TWOPHASE && phase == PH_MAIN) ? P.n - P.n_art : P.n;
@@ -254,8 +254,8 @@ int size_grid(lpgpu_dense *d) {
 
 bool opts_ok(const lpgpu_opts *o, int n, int R) {
     if (!o) return false;
-    if (o->method != LPGPU_PLAIN && o->method != LPGPU_BIGM && o->method != LPGPU_TWOPHASE) return false;
-    if ((o->method == LPGPU_PLAIN) != (R == 1)) return false;
+    if (o->method != LPGPU_PLAIN && o->method != LPGPU_BIGM && o->method != LPGPU_TWOPHASE && o->method != LPGPU_DUAL) return false;
+    if ((o->method == LPGPU_PLAIN || o->method == LPGPU_DUAL) != (R == 1)) return false;
     if (o->n_art < 0 || o->n_art > n || o->max_iter < 0 || o->log_cap < 0 || !(o->eps >= 0.0)) return false;
     return true;
 }

@@ -103,6 +103,36 @@ __device__ __forceinline__ Cand ratio_test(const DenseParams &P, int k, Cand *sc
     return block_best(c, scratch);
 }
 
+// Dual simplex (LPGPU_DUAL): leaving row = most negative b_i < -eps, ties -> lowest row.
+__device__ __forceinline__ Cand dual_leave(const DenseParams &P, Cand *scratch) {
+    Cand c = cand_none();
+    for (int i = (int)threadIdx.x; i < P.m; i += blockDim.x) {
+        const double b = P.T[(size_t)i * P.ld];
+        if (b < -P.eps) {
+            Cand t;
+            t.p = 0.0; t.q = -b; t.idx = i;              // exact negation: arg max -b == arg min b
+            if (cand_better(t, c)) c = t;
+        }
+    }
+    return block_best(c, scratch);
+}
+
+// ... entering column = min sigma_j / a_rj over a_rj < -eps, ties -> lowest column.
+__device__ __forceinline__ Cand dual_enter(const DenseParams &P, int r, Cand *scratch) {
+    const double *xr = P.T + (size_t)r * P.ld;
+    const double *oc = P.T + (size_t)P.m * P.ld;
+    Cand c = cand_none();
+    for (int j = 1 + (int)threadIdx.x; j <= P.n; j += blockDim.x) {
+        const double a = xr[j];
+        if (a < -P.eps) {
+            Cand t;
+            t.p = 0.0; t.q = -(oc[j] / a); t.idx = j;
+            if (cand_better(t, c)) c = t;
+        }
+    }
+    return block_best(c, scratch);
+}
+
 // any artificial still basic at a positive level?
 __device__ __forceinline__ bool art_basic_positive(const DenseParams &P) {
     const int nreal = P.n - P.n_art;
@@ -147,6 +177,16 @@ __device__ __forceinline__ Decision decide(const DenseParams &P, Cand *scratch, 
     Decision D;
     D.r = -1; D.k = 0; D.have = false;
     while (!D.have && status == LPGPU_RUNNING) {
+        if (P.method == LPGPU_DUAL) {
+            const Cand l = dual_leave(P, scratch);
+            if (l.idx < 0) { status = LPGPU_OPTIMAL; continue; }
+            D.r = l.idx;
+            const Cand e = dual_enter(P, D.r, scratch);
+            if (e.idx < 0) { status = LPGPU_INFEASIBLE; continue; }
+            D.k = e.idx;
+            D.have = true;
+            continue;
+        }
         if (phase == PH_DRIVEOUT) {
             if (driveout_find(P, scratch, &D.r, &D.k)) D.have = true;
             else phase = PH_MAIN;

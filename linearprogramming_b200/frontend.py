@@ -43,6 +43,8 @@ def lib():
         L = C.CDLL(LIB_PATH)
         L.lpf_parse_file.argtypes = [C.c_char_p, C.POINTER(Model)]
         L.lpf_parse_string.argtypes = [C.c_char_p, C.POINTER(Model)]
+        L.lpf_parse_file_mode.argtypes = [C.c_char_p, C.c_int, C.POINTER(Model)]
+        L.lpf_parse_string_mode.argtypes = [C.c_char_p, C.c_int, C.POINTER(Model)]
         L.lpf_free.argtypes = [C.POINTER(Model)]
         L.lpf_build_tableau.argtypes = [C.POINTER(Model), C.c_int, C.POINTER(C.POINTER(C.c_double)),
                                         C.POINTER(C.POINTER(C.c_int)), C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -65,10 +67,13 @@ def _model_dict(m):
                    latter=m.vars[v].latter.decode()) for v in range(m.nvars)], nuser=m.nuser)
 
 
-def parse(text=None, path=None):
-    """Parse + standardise + align a model; returns a dict, raises ValueError with the front end's message."""
+def parse(text=None, path=None, dual=False):
+    """Parse + standardise + align a model; returns a dict, raises ValueError with the front end's message.
+    dual = True: the dual-simplex standard form (">=" rows negated into "<=", b keeps its sign)."""
     m = Model()
-    rc = lib().lpf_parse_file(path.encode(), C.byref(m)) if path else lib().lpf_parse_string(text.encode(), C.byref(m))
+    d = 1 if dual else 0
+    rc = (lib().lpf_parse_file_mode(path.encode(), d, C.byref(m)) if path
+          else lib().lpf_parse_string_mode(text.encode(), d, C.byref(m)))
     if rc != 0:
         raise ValueError(m.error.decode(errors="replace"))
     out = _model_dict(m)
@@ -77,16 +82,17 @@ def parse(text=None, path=None):
 
 
 def tableau(path, method):
-    """(T, basis, n_art) as the front end hands them to lpgpu_solve_dense."""
+    """(T, basis, n_art) as the front end hands them to lpgpu_solve_dense (method 3 = dual simplex)."""
     m = Model()
-    if lib().lpf_parse_file(path.encode(), C.byref(m)) != 0:
+    dual = method == capi.DUAL
+    if lib().lpf_parse_file_mode(path.encode(), 1 if dual else 0, C.byref(m)) != 0:
         raise ValueError(m.error.decode(errors="replace"))
     Tp, bp, n, na = C.POINTER(C.c_double)(), C.POINTER(C.c_int)(), C.c_int(), C.c_int()
-    rc = lib().lpf_build_tableau(C.byref(m), method, C.byref(Tp), C.byref(bp), C.byref(n), C.byref(na))
+    rc = lib().lpf_build_tableau(C.byref(m), 0 if dual else method, C.byref(Tp), C.byref(bp), C.byref(n), C.byref(na))
     if rc != 0:
         lib().lpf_free(C.byref(m))
         raise ValueError("the plain method needs an identity basis")
-    R = 1 if method == 0 else 2
+    R = 1 if method in (0, capi.DUAL) else 2
     T = np.ctypeslib.as_array(Tp, shape=(m.m + R, n.value + 1)).copy()
     basis = np.ctypeslib.as_array(bp, shape=(m.m,)).astype(np.int32).copy()
     libc = C.CDLL(None)

@@ -3,7 +3,7 @@
  * Source/router.c:13-42): read a model file, print the standard form, solve with the primal simplex
  * on the GPU, print the solution.  The interactive prompts (PAUSE, menu digits, "1. Big M / 2.
  * Two-phase", Source/simplex.c:43-55) become flags:
- *     lp_cli model.txt [--method bigm|twophase] [--json] [--parse-only] [--device N]
+ *     lp_cli model.txt [--method bigm|twophase|dual] [--json] [--parse-only] [--device N]
  */
 #include <stdio.h>
 #include <stdlib.h>
@@ -68,15 +68,16 @@ int main(int argc, char **argv) {
             ++a;
             if (!strcmp(argv[a], "bigm") || !strcmp(argv[a], "1")) method = LPGPU_BIGM;
             else if (!strcmp(argv[a], "twophase") || !strcmp(argv[a], "2")) method = LPGPU_TWOPHASE;
+            else if (!strcmp(argv[a], "dual")) method = LPGPU_DUAL;      /* the reference's menu item 2, Source/router.c:32-34 */
             else { fprintf(stderr, "unknown method %s\n", argv[a]); return 2; }
         } else if (!strcmp(argv[a], "--json")) json = 1;
         else if (!strcmp(argv[a], "--parse-only")) parse_only = 1;
         else if (!strcmp(argv[a], "--device") && a + 1 < argc) device = atoi(argv[++a]);
         else path = argv[a];
     }
-    if (!path) { printf("Missing argument. \nUsage: \n\t%s <filename> [--method bigm|twophase] [--json] [--parse-only]\n\n", argv[0]); return 2; }
+    if (!path) { printf("Missing argument. \nUsage: \n\t%s <filename> [--method bigm|twophase|dual] [--json] [--parse-only]\n\n", argv[0]); return 2; }
     lpf_model mo;
-    if (lpf_parse_file(path, &mo) != 0) {
+    if (lpf_parse_file_mode(path, method == LPGPU_DUAL, &mo) != 0) {
         if (json) printf("{\"parsed\":0,\"error\":\"%s\"}\n", mo.error);
         else printf("%s\nError occurred when parsing the model.\n", mo.error);
         return 1;
@@ -100,7 +101,8 @@ int main(int argc, char **argv) {
         printf("]}\n");
     } else {
         print_model_text(&mo);
-        printf("\n> Primal Simplex Method (%s)\n", sol.method == LPGPU_PLAIN ? "identity basis" : sol.method == LPGPU_BIGM ? "Big M" : "Two-phase");
+        if (sol.method == LPGPU_DUAL) printf("\n> Dual Simplex Method\n");
+        else printf("\n> Primal Simplex Method (%s)\n", sol.method == LPGPU_PLAIN ? "identity basis" : sol.method == LPGPU_BIGM ? "Big M" : "Two-phase");
         for (int p = 0; p < sol.n_log; ++p) {
             const int col = sol.pivot_log[2 * p], row = sol.pivot_log[2 * p + 1];
             printf("\titeration %d: column %d enters, row %d leaves\n", p + 1, col, row);

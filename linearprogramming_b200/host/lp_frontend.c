@@ -400,8 +400,10 @@ static void negate_terms(terms_t *v) {
 }
 
 /* min -> max(-z); x(unr) -> x'' - x'; b < 0 -> negate the row; slack / surplus; sort; x <= 0 -> -x'
- * (Source/simplex.c:91-230, dual = 0) */
-static void standardise(raw_model *r, dict_t *d) {
+ * (Source/simplex.c:91-230).  dual = 1 is the reference's variant for the dual simplex
+ * (Source/simplex.c:177-178): rows are NOT made b >= 0, instead every ">=" row is negated into "<=" so
+ * that each inequality row gets a +1 slack. */
+static void standardise(raw_model *r, dict_t *d, int dual) {
     terms_t *of = &r->objective.right;
     if (r->sense != 1) negate_terms(of);
     r->nuser = d->n;                                /* everything added below is generated */
@@ -436,7 +438,7 @@ static void standardise(raw_model *r, dict_t *d) {
     }
     for (int s = 0; s < r->nst; ++s) {
         formula_t *f = &r->st[s];
-        if (rat_sign(f->right.t[0].c) < 0) {
+        if ((!dual && rat_sign(f->right.t[0].c) < 0) || (dual && f->rel > 0 && f->rel != 3)) {
             f->right.t[0].c = rat_neg(f->right.t[0].c);
             negate_terms(&f->left);
             if (f->rel != 3) f->rel = -f->rel;
@@ -515,7 +517,9 @@ static int finish_model(raw_model *r, dict_t *d, lpf_model *m) {
     return 0;
 }
 
-int lpf_parse_string(const char *text, lpf_model *m) {
+int lpf_parse_string(const char *text, lpf_model *m) { return lpf_parse_string_mode(text, 0, m); }
+
+int lpf_parse_string_mode(const char *text, int dual, lpf_model *m) {
     memset(m, 0, sizeof *m);
     if (!text) return fail(m, "no input");
     raw_model r;
@@ -524,14 +528,16 @@ int lpf_parse_string(const char *text, lpf_model *m) {
     memset(&d, 0, sizeof d);
     int rc = split_sections(text, &r, m);
     if (rc == 0) rc = normalise(&r, &d, m);
-    if (rc == 0) { standardise(&r, &d); rc = finish_model(&r, &d, m); }
+    if (rc == 0) { standardise(&r, &d, dual); rc = finish_model(&r, &d, m); }
     raw_free(&r);
     free(d.v);
     if (rc != 0) { char e[256]; memcpy(e, m->error, sizeof e); lpf_free(m); memcpy(m->error, e, sizeof e); }
     return rc;
 }
 
-int lpf_parse_file(const char *path, lpf_model *m) {
+int lpf_parse_file(const char *path, lpf_model *m) { return lpf_parse_file_mode(path, 0, m); }
+
+int lpf_parse_file_mode(const char *path, int dual, lpf_model *m) {
     memset(m, 0, sizeof *m);
     FILE *f = fopen(path, "rb");
     if (!f) return fail(m, "File not readable or does not exist.");
@@ -542,7 +548,7 @@ int lpf_parse_file(const char *path, lpf_model *m) {
     size_t got = fread(buf, 1, (size_t)sz, f);
     buf[got] = '\0';
     fclose(f);
-    int rc = lpf_parse_string(buf, m);
+    int rc = lpf_parse_string_mode(buf, dual, m);
     free(buf);
     return rc;
 }

@@ -59,6 +59,10 @@ typedef struct {
 /* parse + standardise + align.  Returns 0 and model->valid = 1, or -1 with model->error set. */
 int lpf_parse_string(const char *text, lpf_model *model);
 int lpf_parse_file(const char *path, lpf_model *model);
+/* dual = 1: the standard form the dual simplex starts from (Source/simplex.c:177-178, LPStandardize
+ * with dual = 1): ">=" rows are negated into "<=" instead of making b >= 0. */
+int lpf_parse_string_mode(const char *text, int dual, lpf_model *model);
+int lpf_parse_file_mode(const char *path, int dual, lpf_model *model);
 void lpf_free(lpf_model *model);
 
 /* Dense fp64 canonical tableau (layout of include/lpgpu.h).  method: 0 plain (fails if a row lacks a
@@ -79,7 +83,9 @@ typedef struct {
 } lpf_solution;
 
 /* Parse `path`, build the tableau, solve it on the GPU through liblpgpu.so and map the solution back.
- * method_if_needed: 1 Big-M or 2 two-phase, used only when artificials are required.
+ * method_if_needed: 1 Big-M or 2 two-phase, used only when artificials are required; 3 = dual simplex
+ * (what the reference's menu item 2 announces, Source/router.c:32-34): needs every row to own a slack
+ * and every cost <= 0 in the max form, else -1 with a message.
  * ctx: an lpgpu_ctx* (void* here to keep this header free of lpgpu.h).  Returns 0 / -1. */
 int lpf_solve_file(void *ctx, const char *path, int method_if_needed, lpf_solution *sol, char *err, size_t errlen);
 int lpf_solve_model(void *ctx, const lpf_model *model, int method_if_needed, lpf_solution *sol, char *err, size_t errlen);

@@ -30,15 +30,20 @@ int lpf_solve_model(void *ctx, const lpf_model *mo, int method_if_needed, lpf_so
     int lacking = 0;
     for (int i = 0; i < mo->m; ++i) lacking += (mo->basis[i] == 0);
     int method = LPGPU_PLAIN;
-    if (lacking) {
+    if (method_if_needed == LPGPU_DUAL) {
+        if (lacking) return seterr(err, errlen, "Dual simplex needs a slack in every row (no equality rows)");
+        for (int j = 0; j < mo->n; ++j)
+            if (mo->costs[j].num > 0) return seterr(err, errlen, "Dual simplex needs a dual feasible start (every cost <= 0 in the max form)");
+        method = LPGPU_DUAL;
+    } else if (lacking) {
         if (method_if_needed != LPGPU_BIGM && method_if_needed != LPGPU_TWOPHASE)
             return seterr(err, errlen, "Artificial variables are needed: choose Big M (1) or Two-phase (2)");
         method = method_if_needed;
     }
     double *T = NULL;
     int *basis = NULL, n = 0, n_art = 0;
-    if (lpf_build_tableau(mo, method, &T, &basis, &n, &n_art) != 0) return seterr(err, errlen, "cannot build the tableau");
-    const int R = method == LPGPU_PLAIN ? 1 : 2;
+    if (lpf_build_tableau(mo, method == LPGPU_DUAL ? LPGPU_PLAIN : method, &T, &basis, &n, &n_art) != 0) return seterr(err, errlen, "cannot build the tableau");
+    const int R = (method == LPGPU_PLAIN || method == LPGPU_DUAL) ? 1 : 2;
     lpgpu_opts o;
     lpgpu_default_opts(&o);
     o.method = method;
@@ -77,7 +82,7 @@ int lpf_solve_model(void *ctx, const lpf_model *mo, int method_if_needed, lpf_so
 
 int lpf_solve_file(void *ctx, const char *path, int method_if_needed, lpf_solution *sol, char *err, size_t errlen) {
     lpf_model mo;
-    if (lpf_parse_file(path, &mo) != 0) return seterr(err, errlen, mo.error);
+    if (lpf_parse_file_mode(path, method_if_needed == LPGPU_DUAL, &mo) != 0) return seterr(err, errlen, mo.error);
     int rc = lpf_solve_model(ctx, &mo, method_if_needed, sol, err, errlen);
     lpf_free(&mo);
     return rc;

@@ -18,6 +18,9 @@
  * Environment switches for non-interactive runs (the reference is menu driven):
  *   LPGPU_BATCH=1          skip the "Press Enter" pauses of this function
  *   LPGPU_METHOD=bigm|twophase   answer the "1. Big M / 2. Two-phase" prompt
+ *   LPGPU_METHOD=dual            dual simplex: standardise with the reference's LPStandardize(model, 1)
+ *                                (Source/simplex.c:177-178; the menu entry "2. Dual Simplex Method" of
+ *                                Source/router.c:32-34 calls nothing) and pivot with LPGPU_DUAL
  */
 #include "public.h"
 #include "simplex.h"
@@ -64,7 +67,9 @@ static int choose_method(void) {
 void newSimplex(LPModel *model) {
     LPModel modelCopy = CopyModel(model);
     const short int sense = model->objective.type;          /* 1 max, -1 min, before standardising */
-    LPStandardize(&modelCopy, 0);
+    const char *menv = getenv("LPGPU_METHOD");
+    const short int dual = (menv && !strcmp(menv, "dual")) ? 1 : 0;
+    LPStandardize(&modelCopy, dual);
     printf("\n---------------\n> Standard Form\n\n");
     PrintModel(&modelCopy);
     pause_if_interactive();
@@ -109,8 +114,22 @@ void newSimplex(LPModel *model) {
     int n_art = 0;
     for (i = 0; i < (size_t)m; i++) n_art += (basis[i] == 0);
     int method = LPGPU_PLAIN;
-    if (n_art) method = choose_method();
-    const int R = method == LPGPU_PLAIN ? 1 : 2, n = n0 + n_art;
+    if (dual) {
+        int ok = (n_art == 0);
+        for (j = 0; j < (size_t)n0 && ok; j++)
+            if (Decimalize(*sm.ofCosts[j]) > 0) ok = 0;
+        if (!ok) {
+            printf("The Dual Simplex Method needs a slack in every row and no positive cost in the max form.\n");
+            pause_if_interactive();
+            free(basis); free(scratch); free(slots);
+            if (lackFromRef != NULL) free(lackFromRef);
+            RevokeSMatrix(&sm);
+            FreeModel(&modelCopy);
+            return;
+        }
+        method = LPGPU_DUAL;
+    } else if (n_art) method = choose_method();
+    const int R = (method == LPGPU_PLAIN || method == LPGPU_DUAL) ? 1 : 2, n = n0 + n_art;
     const size_t ld = (size_t)n + 1;
 
     /* SimplexMatrix -> dense fp64 tableau (include/lpgpu.h layout) */
@@ -147,8 +166,9 @@ void newSimplex(LPModel *model) {
         if (rc != LPGPU_OK) {
             printf("ERROR: GPU solve failed (%d): %s\n", rc, lpgpu_last_error(ctx));
         } else {
-            printf("\n---------------\n> Primal Simplex Method (%s)\n\n",
-                   method == LPGPU_PLAIN ? "identity basis" : method == LPGPU_BIGM ? "Big M" : "Two-phase");
+            if (method == LPGPU_DUAL) printf("\n---------------\n> Dual Simplex Method\n\n");
+            else printf("\n---------------\n> Primal Simplex Method (%s)\n\n",
+                        method == LPGPU_PLAIN ? "identity basis" : method == LPGPU_BIGM ? "Big M" : "Two-phase");
             for (int p = 0; p < res.n_logged; p++) {
                 const int col = plog[2 * p], row = plog[2 * p + 1];
                 printf("\tIteration %d: ", p + 1);

@@ -10,7 +10,7 @@ import ctypes as C
 import numpy as np
 
 from . import capi
-from .capi import (BIGM, INFEASIBLE, ITER_LIMIT, OPTIMAL, PLAIN, RUNNING, STATUS_NAMES, TWOPHASE, UNBOUNDED,  # noqa: F401
+from .capi import (BIGM, DUAL, INFEASIBLE, ITER_LIMIT, OPTIMAL, PLAIN, RUNNING, STATUS_NAMES, TWOPHASE, UNBOUNDED,  # noqa: F401
                    LpgpuError, Opts, Result)
 
 
@@ -19,7 +19,7 @@ def _ptr(a):
 
 
 def _R(method):
-    return 1 if method == PLAIN else 2
+    return 1 if method in (PLAIN, DUAL) else 2
 
 
 class Context:

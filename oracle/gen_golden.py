@@ -56,7 +56,8 @@ def run_kat():
     return out
 
 
-def run_dumps():
+def run_dumps(dual=0):
+    """dual = 1: the reference's LPStandardize(model, dual = 1) branch (Source/simplex.c:177-178)."""
     exe = os.path.join(HERE, "_ref", "ref_dump")
     mdir = os.path.join(GOLD, "models")
     out = {}
@@ -64,7 +65,7 @@ def run_dumps():
         if not name.endswith(".txt"):
             continue
         with tempfile.NamedTemporaryFile(suffix=".json") as tf:
-            subprocess.run([exe, os.path.join(mdir, name), tf.name], capture_output=True, check=True)
+            subprocess.run([exe, os.path.join(mdir, name), tf.name, str(dual)], capture_output=True, check=True)
             out[name] = json.load(open(tf.name))
     return out
 
@@ -78,6 +79,8 @@ def main():
         json.dump(run_kat(), f, indent=1)
     with open(os.path.join(GOLD, "frontend_dumps.json"), "w") as f:
         json.dump(run_dumps(), f, indent=1)
+    with open(os.path.join(GOLD, "frontend_dumps_dual.json"), "w") as f:
+        json.dump(run_dumps(dual=1), f, indent=1)
     print("wrote", GOLD)
 
 

@@ -70,6 +70,33 @@ static int ratio_test(const lpo_ctx *c, int k) {
     return best;
 }
 
+/* Dual simplex (the reference only has the menu stub, Source/router.c:32-34, and the dual = 1
+ * branch of LPStandardize, Source/simplex.c:177-178).  Rule defined here: leaving row = most negative
+ * b_i < -eps, ties -> lowest row; entering column = min sigma_j / a_rj over a_rj < -eps, ties ->
+ * lowest column (one IEEE division each); no such column -> the row proves infeasibility. */
+static int dual_leave(const lpo_ctx *c) {
+    int best = -1;
+    double bv = 0.0;
+    for (int i = 0; i < c->m; ++i) {
+        double b = AT(c, i, 0);
+        if (b < -c->eps && (best < 0 || b < bv)) { best = i; bv = b; }
+    }
+    return best;
+}
+
+static int dual_enter(const lpo_ctx *c, int r) {
+    int best = 0;
+    double bt = 0.0;
+    for (int j = 1; j <= c->n; ++j) {
+        double a = AT(c, r, j);
+        if (a < -c->eps) {
+            double t = AT(c, c->m, j) / a;
+            if (best == 0 || t < bt) { best = j; bt = t; }
+        }
+    }
+    return best;
+}
+
 void lpo_pivot_f64(int rows, int n, double *T, size_t ld, int r, int k, int threads) {
     double *prow = (double *)malloc(sizeof(double) * (size_t)(n + 1));
     double *pcol = (double *)malloc(sizeof(double) * (size_t)rows);
@@ -113,7 +140,7 @@ int lpo_solve_f64(int m, int n, int R, double *T, size_t ld, int *basis,
                   const lpo_opts *opts, int *pivot_log, int log_cap, lpo_result *res) {
     if (m < 1 || n < 1 || (R != 1 && R != 2) || !T || !basis || !opts || !res) return -1;
     if (ld < (size_t)n + 1) return -1;
-    if ((opts->method == LPO_PLAIN) != (R == 1)) return -1;
+    if ((opts->method == LPO_PLAIN || opts->method == LPO_DUAL) != (R == 1)) return -1;
     if (opts->n_art < 0 || opts->n_art > n) return -1;
     lpo_ctx c = { m, n, R, T, ld, basis, opts->eps, opts->method, opts->n_art,
                   opts->threads > 0 ? opts->threads : 1 };
@@ -121,7 +148,12 @@ int lpo_solve_f64(int m, int n, int R, double *T, size_t ld, int *basis,
     int status = LPO_RUNNING, iters = 0, p1 = 0;
     while (status == LPO_RUNNING) {
         int r = -1, k = 0;
-        if (phase == LPO_PH_DRIVEOUT) {
+        if (c.method == LPO_DUAL) {
+            r = dual_leave(&c);
+            if (r < 0) { status = LPO_OPTIMAL; break; }
+            k = dual_enter(&c, r);
+            if (k == 0) { status = LPO_INFEASIBLE; break; }
+        } else if (phase == LPO_PH_DRIVEOUT) {
             if (!driveout_find(&c, &r, &k)) { phase = LPO_PH_MAIN; continue; }
         } else {
             if (c.method == LPO_BIGM) k = price_bigm(&c);

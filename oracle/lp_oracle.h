@@ -40,14 +40,14 @@ extern "C" {
 
 enum { LPO_OPTIMAL = 0, LPO_UNBOUNDED = 1, LPO_INFEASIBLE = 2, LPO_ITER_LIMIT = 3,
        LPO_RUNNING = 4, LPO_OVERFLOW = 5 };
-enum { LPO_PLAIN = 0, LPO_BIGM = 1, LPO_TWOPHASE = 2 };
+enum { LPO_PLAIN = 0, LPO_BIGM = 1, LPO_TWOPHASE = 2, LPO_DUAL = 3 };
 /* phases of the state machine */
 enum { LPO_PH_MAIN = 0, LPO_PH_ONE = 1, LPO_PH_DRIVEOUT = 2 };
 
 typedef struct {
     double eps;      /* 1e-9: pricing / ratio / snap tolerance                      */
     int max_iter;    /* iteration cap (-> LPO_ITER_LIMIT)                            */
-    int method;      /* LPO_PLAIN (R=1) | LPO_BIGM (R=2) | LPO_TWOPHASE (R=2)        */
+    int method;      /* LPO_PLAIN (R=1) | LPO_BIGM (R=2) | LPO_TWOPHASE (R=2) | LPO_DUAL (R=1) */
     int n_art;       /* artificial columns = the LAST n_art columns of the tableau   */
     int threads;     /* OpenMP threads for the elimination (results do not depend)   */
 } lpo_opts;

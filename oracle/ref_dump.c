@@ -3,7 +3,7 @@
  *
  * Compiled by oracle/Makefile against the reference sources where they lie
  * (/root/reference/Source, never copied) into oracle/_ref/ref_dump.  It runs
- *   Parser -> LPTrans -> CopyModel -> LPStandardize(.,0) -> LPAlign -> CreateSMatrix
+ *   Parser -> LPTrans -> CopyModel -> LPStandardize(.,dual) -> LPAlign -> CreateSMatrix
  * (Source/main.c:16-19, Source/simplex.c:27-40) on one model file and writes what the
  * reference built as JSON, so that tests/golden/ can pin this repository's own front end
  * and tableau layout against real reference behaviour.
@@ -19,7 +19,8 @@ static void put_num(FILE *o, Number v) {
 }
 
 int main(int argc, char **argv) {
-    if (argc < 3) { fprintf(stderr, "usage: %s model.txt out.json\n", argv[0]); return 2; }
+    if (argc < 3) { fprintf(stderr, "usage: %s model.txt out.json [dual]\n", argv[0]); return 2; }
+    const short dual = (argc > 3 && argv[3][0] == '1') ? 1 : 0;   /* LPStandardize's second argument */
     FILE *in = fopen(argv[1], "r");
     FILE *o = fopen(argv[2], "w");
     if (!in || !o) { fprintf(stderr, "cannot open files\n"); return 2; }
@@ -31,7 +32,7 @@ int main(int argc, char **argv) {
 
     LPModel mc = CopyModel(&parsed);
     const int sense = parsed.objective.type;        /* 1 max, -1 min, before standardising */
-    LPStandardize(&mc, 0);
+    LPStandardize(&mc, dual);
     LPAlign(&mc);
     if (!mc.valid) { fprintf(o, "{\"parsed\":1,\"standard\":0}\n"); fclose(o); return 0; }
 

@@ -15,6 +15,12 @@ def load_dumps():
         return json.load(f)
 
 
+def load_dumps_dual():
+    """The same models through the reference's LPStandardize(model, dual = 1) (Source/simplex.c:177-178)."""
+    with open(os.path.join(GOLD, "frontend_dumps_dual.json")) as f:
+        return json.load(f)
+
+
 def load_kat():
     with open(os.path.join(GOLD, "rational_kat.json")) as f:
         return json.load(f)
@@ -95,3 +101,30 @@ def random_mixed_lp(rng, m, ns, p_ge=0.25, p_eq=0.15, neg_b=0.2, dense=True):
     rel[flip & (rel != 3)] *= -1
     c = rng.uniform(-1.0, 1.0, size=ns)
     return A, b, c, rel
+
+
+def random_dual_lp(rng, m, ns, p_ge=0.5, infeasible=False):
+    """max c.x with c <= 0, rows  a.x <= b  where the '>=' rows were flipped (so some b_i < 0): a slack
+    basis that is dual feasible but not primal feasible -- the start the dual simplex wants
+    (LPStandardize(model, dual = 1), Source/simplex.c:177-178).  Returns (T, basis, (A, b, c, rel)) with
+    the (A, b, c, rel) form for the primal Big-M / two-phase solvers."""
+    A = rng.uniform(0.0, 1.5, size=(m, ns))
+    A[rng.random((m, ns)) < 0.2] = 0.0
+    x0 = rng.uniform(0.0, 2.0, size=ns)
+    ge = rng.random(m) < p_ge
+    ax = A @ x0
+    b = np.where(ge, ax - rng.uniform(0.1, 1.0, m), ax + rng.uniform(0.1, 2.0, m))
+    b = np.where(ge, np.maximum(b, 0.05), b)                  # keep '>=' right-hand sides positive
+    c = -rng.uniform(0.1, 1.0, size=ns)
+    rel = np.where(ge, 2, -2).astype(np.int32)
+    if infeasible:
+        A[0] = np.abs(A[0]); rel[0] = -2; b[0] = -1.0         # a.x <= -1 with a >= 0, x >= 0
+    n = ns + m
+    T = np.zeros((m + 1, n + 1))
+    sgn = np.where(rel == 2, -1.0, 1.0)                       # '>=' rows times -1 -> '<='
+    T[:m, 0] = sgn * b
+    T[:m, 1:ns + 1] = sgn[:, None] * A
+    T[:m, ns + 1:] = np.eye(m)
+    T[m, 1:ns + 1] = c
+    basis = (ns + 1 + np.arange(m)).astype(np.int32)
+    return T, basis, (A, b, c, rel)

@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
 OPTIMAL, UNBOUNDED, INFEASIBLE, ITER_LIMIT, RUNNING, OVERFLOW = range(6)
-PLAIN, BIGM, TWOPHASE = 0, 1, 2
+PLAIN, BIGM, TWOPHASE, DUAL = 0, 1, 2, 3
 STATUS_NAMES = ["OPTIMAL", "UNBOUNDED", "INFEASIBLE", "ITER_LIMIT", "RUNNING", "OVERFLOW"]
 
 
@@ -101,7 +101,7 @@ def solve_f64(T, basis, method=PLAIN, n_art=0, eps=1e-9, max_iter=1 << 30, threa
     T = np.array(T, dtype=np.float64, order="C", copy=True)
     basis = np.array(basis, dtype=np.int32, copy=True)
     if R is None:
-        R = 1 if method == PLAIN else 2
+        R = 1 if method in (PLAIN, DUAL) else 2
     rows, ld = T.shape
     m, n = rows - R, ld - 1
     if log_cap is None:
@@ -122,7 +122,7 @@ def solve_batched_f64(T_all, basis_all, method=PLAIN, n_art=0, eps=1e-9, max_ite
     T_all = np.array(T_all, dtype=np.float64, order="C", copy=True)
     basis_all = np.array(basis_all, dtype=np.int32, order="C", copy=True)
     n_lp, rows, ld = T_all.shape
-    R = 1 if method == PLAIN else 2
+    R = 1 if method in (PLAIN, DUAL) else 2
     m, n = rows - R, ld - 1
     status = np.zeros(n_lp, np.int32)
     iters = np.zeros(n_lp, np.int32)
@@ -189,7 +189,7 @@ def rat_parse(s):
 def solve_rat(T_pairs, basis, method=PLAIN, n_art=0, max_iter=1 << 30, log_cap=256):
     """T_pairs: rows x cols list of (num, den).  Returns dict like solve_f64 with T as (num, den) tuples."""
     rows, cols = len(T_pairs), len(T_pairs[0])
-    R = 1 if method == PLAIN else 2
+    R = 1 if method in (PLAIN, DUAL) else 2
     m, n = rows - R, cols - 1
     arr = (Rat * (rows * cols))()
     for i in range(rows):

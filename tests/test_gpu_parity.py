@@ -178,6 +178,35 @@ def test_dense_timed_run_reports_kernel_time(ctx):
     d.close()
 
 
+# ------------------------------------------------------------------ dual simplex
+@pytest.mark.parametrize("seed", range(8))
+def test_dual_simplex_dense_bitwise(ctx, seed):
+    rng = np.random.default_rng(900 + seed)
+    m, ns = int(rng.integers(3, 60)), int(rng.integers(3, 60))
+    T, basis, _ = H.random_dual_lp(rng, m, ns, infeasible=(seed == 7))
+    ref = O.solve_f64(T, basis, method=O.DUAL, log_cap=512)
+    got = lp.solve_dense(ctx, T, basis, method=lp.DUAL, log_cap=512)
+    _assert_dense_equal(got, ref)
+    assert got["status"] == (lp.INFEASIBLE if seed == 7 else lp.OPTIMAL)
+    capped = lp.solve_dense(ctx, T, basis, method=lp.DUAL, log_cap=512, max_iter=1)
+    _assert_dense_equal(capped, O.solve_f64(T, basis, method=O.DUAL, log_cap=512, max_iter=1))
+
+
+def test_dual_simplex_midsize_and_batched(ctx):
+    rng = np.random.default_rng(77)
+    T, basis, _ = H.random_dual_lp(rng, 300, 200)
+    ref = O.solve_f64(T, basis, method=O.DUAL, log_cap=4096)
+    got = lp.solve_dense(ctx, T, basis, method=lp.DUAL, log_cap=4096)
+    _assert_dense_equal(got, ref)
+    assert ref["status"] == O.OPTIMAL and ref["iters"] > 20
+    # batched: the shared-memory kernel takes the dual method through the same decide()
+    Ts, Bs = zip(*[H.random_dual_lp(rng, 10, 12)[:2] for _ in range(200)])
+    Tb, Bb = np.stack(Ts), np.stack(Bs)
+    refb = O.solve_batched_f64(Tb, Bb, method=O.DUAL, threads=4)
+    gotb = lp.solve_batched(ctx, Tb, Bb, method=lp.DUAL)
+    _assert_batched_equal(gotb, refb)
+
+
 # ------------------------------------------------------------------ batched path
 def _assert_batched_equal(got, ref, final=None):
     assert np.array_equal(got["status"], ref["status"])

@@ -256,3 +256,41 @@ def test_batched_matches_single():
         assert rb["status"][p] == rs["status"] and rb["iters"][p] == rs["iters"]
         assert rb["z"][p] == rs["z"] and np.array_equal(rb["x"][p], rs["x"])
         assert rb["log"][p, :rs["iters"]].tolist() == rs["log"].tolist()
+
+
+# ------------------------------------------------------------------ dual simplex
+@pytest.mark.parametrize("seed", range(12))
+def test_dual_simplex_reaches_the_primal_optimum(seed):
+    """Dual simplex from a dual-feasible slack basis (b of mixed sign) vs Big-M on the same LP."""
+    rng = np.random.default_rng(900 + seed)
+    m, ns = int(rng.integers(3, 25)), int(rng.integers(3, 25))
+    T, basis, (A, b, c, rel) = H.random_dual_lp(rng, m, ns)
+    dual = O.solve_f64(T, basis, method=O.DUAL)
+    Tb, bb, n_art = O.build_tableau(A, b, c, rel, R=2)
+    prim = O.solve_f64(Tb, bb, method=O.BIGM, n_art=n_art)
+    assert dual["status"] == prim["status"] == O.OPTIMAL
+    assert dual["z"] == pytest.approx(prim["z"], rel=1e-9, abs=1e-9)
+    assert np.all(dual["T"][:m, 0] >= -1e-9) and np.all(dual["T"][m, 1:] <= 1e-9)      # primal and dual feasible
+
+
+def test_dual_simplex_statuses_and_rule():
+    rng = np.random.default_rng(5)
+    T, basis, _ = H.random_dual_lp(rng, 6, 5, infeasible=True)
+    out = O.solve_f64(T, basis, method=O.DUAL)
+    assert out["status"] == O.INFEASIBLE
+    # textbook example: min 2x1 + 3x2 + 4x3, x1 + 2x2 + x3 >= 3, 2x1 - x2 + 3x3 >= 4  ->  z = 28/5
+    T = np.array([[-3.0, -1, -2, -1, 1, 0], [-4.0, -2, 1, -3, 0, 1], [0.0, -2, -3, -4, 0, 0]])
+    out = O.solve_f64(T, np.array([4, 5], np.int32), method=O.DUAL, log_cap=8)
+    assert out["status"] == O.OPTIMAL and out["log"].tolist() == [[1, 1], [2, 0]]
+    assert -out["z"] == pytest.approx(28 / 5) and out["x"][:3] == pytest.approx([11 / 5, 2 / 5, 0])
+    # already optimal (b >= 0): zero pivots
+    T2, b2 = O.synth_feasible(1, 0, 4, 4)
+    T2[4, 1:] = -np.abs(T2[4, 1:])
+    out = O.solve_f64(T2, b2, method=O.DUAL)
+    assert out["status"] == O.OPTIMAL and out["iters"] == 0
+    # iteration cap
+    T, basis, _ = H.random_dual_lp(np.random.default_rng(3), 12, 10)
+    full = O.solve_f64(T, basis, method=O.DUAL)
+    if full["iters"] > 1:
+        capped = O.solve_f64(T, basis, method=O.DUAL, max_iter=1)
+        assert capped["status"] == O.ITER_LIMIT and capped["iters"] == 1

@@ -130,6 +130,23 @@ def test_dense_synth_full_solve(ctx, m, ns, variant):
     assert got["status"] == lp.OPTIMAL
 
 
+def test_dense_full_solve_2048x4096_bitwise(ctx):
+    """A few thousand pivots to the optimum of a 2048 x 4096 tableau: pivot log, basis and the final
+    tableau still equal the oracle's bit for bit (no drift: the method has no floating-point sums)."""
+    m = ns = 2048
+    T, basis = O.synth_feasible(1234, 1, m, ns)
+    ref = O.solve_f64(T, basis, threads=16, log_cap=16384)
+    d = lp.DenseTableau(ctx, m, m + ns, 1)
+    d.synth(1234, 1, ns)
+    d.reset(log_cap=16384)
+    res = d.run(2**31 - 1)
+    out = d.download()
+    d.close()
+    assert res["status"] == ref["status"] == lp.OPTIMAL and res["iters"] == ref["iters"] > 1000
+    assert out["log"][:res["iters"]].tolist() == ref["log"].tolist() and np.array_equal(out["basis"], ref["basis"])
+    assert np.array_equal(out["T"], ref["T"]) and res["z"] == ref["z"]
+
+
 def test_dense_device_synth_matches_host_and_windows(ctx):
     m, ns = 300, 212
     n = m + ns

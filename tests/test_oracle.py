@@ -294,3 +294,43 @@ def test_dual_simplex_statuses_and_rule():
     if full["iters"] > 1:
         capped = O.solve_f64(T, basis, method=O.DUAL, max_iter=1)
         assert capped["status"] == O.ITER_LIMIT and capped["iters"] == 1
+
+
+# ------------------------------------------------------------------ independent solver (scipy / HiGHS)
+@pytest.mark.parametrize("seed", range(20))
+def test_oracle_optimum_agrees_with_scipy_highs(seed):
+    """The pivot PATH is this repo's rule (unpinned by the reference), but the END of the path is not a
+    matter of convention: status and optimal objective must agree with an independent LP solver."""
+    scipy_opt = pytest.importorskip("scipy.optimize")
+    rng = np.random.default_rng(4000 + seed)
+    m, ns = int(rng.integers(3, 30)), int(rng.integers(3, 30))
+    A, b, c, rel = H.random_mixed_lp(rng, m, ns, dense=bool(seed % 2))
+    if seed % 5 == 4:                       # make some instances infeasible: x1 + ... <= -1 with A >= 0
+        A[0] = np.abs(A[0]); b[0] = -1.0; rel[0] = -2
+    le, ge, eq = rel == -2, rel == 2, rel == 3
+    res = scipy_opt.linprog(-c, A_ub=np.vstack([A[le], -A[ge]]) if (le | ge).any() else None,
+                            b_ub=np.concatenate([b[le], -b[ge]]) if (le | ge).any() else None,
+                            A_eq=A[eq] if eq.any() else None, b_eq=b[eq] if eq.any() else None,
+                            bounds=(0, None), method="highs")
+    want = {0: O.OPTIMAL, 2: O.INFEASIBLE, 3: O.UNBOUNDED}.get(res.status)
+    for method in (O.BIGM, O.TWOPHASE):
+        T, basis, n_art = O.build_tableau(A, b, c, rel, R=2)
+        got = O.solve_f64(T, basis, method=method, n_art=n_art)
+        if want is None:
+            continue
+        assert got["status"] == want, (method, O.STATUS_NAMES[got["status"]], res.message)
+        if want == O.OPTIMAL:
+            assert got["z"] == pytest.approx(-res.fun, rel=1e-7, abs=1e-7)
+            x = got["x"][:ns]
+            assert np.all(x >= -1e-9) and c @ x == pytest.approx(-res.fun, rel=1e-7, abs=1e-7)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_oracle_synthetic_family_agrees_with_scipy_highs(seed):
+    scipy_opt = pytest.importorskip("scipy.optimize")
+    m, ns = 24 + seed, 20 + 2 * seed
+    T, basis = O.synth_feasible(1234, seed, m, ns)
+    got = O.solve_f64(T, basis)
+    res = scipy_opt.linprog(-T[m, 1:ns + 1], A_ub=T[:m, 1:ns + 1], b_ub=T[:m, 0], bounds=(0, None), method="highs")
+    assert got["status"] == O.OPTIMAL and res.status == 0
+    assert got["z"] == pytest.approx(-res.fun, rel=1e-9)

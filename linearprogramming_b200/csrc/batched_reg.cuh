@@ -88,6 +88,31 @@ __device__ __forceinline__ unsigned long long key_ordered(double x) {
     return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
 }
 
+// pivot-row scaling of one lane's CT entries plus b_r: a_rj / a_rk, each the correctly rounded IEEE
+// quotient (common.cuh: div_by_pivot); the plain divide sequence only for out-of-range operands
+template <int CT, bool SHARED_RECIP>
+__device__ __forceinline__ void scale_row(const double (&rv)[CT], double br, double piv, double (&out)[CT], double &brp) {
+    if constexpr (!SHARED_RECIP) {       // four-warp shape: register pressure makes the divide sequences cheaper
+#pragma unroll
+        for (int c = 0; c < CT; ++c) out[c] = div_skip_zero(rv[c], piv);
+        brp = div_skip_zero(br, piv);
+        return;
+    }
+    const PivotRecip R = pivot_recip(piv);
+    bool ok = div_in_range(piv) && div_in_range(br);
+#pragma unroll
+    for (int c = 0; c < CT; ++c) {
+        out[c] = div_by_pivot(rv[c], R);
+        ok = ok && div_in_range(rv[c]);
+    }
+    brp = div_by_pivot(br, R);
+    if (!__all_sync(0xffffffffu, ok)) {
+#pragma unroll
+        for (int c = 0; c < CT; ++c) out[c] = div_skip_zero(rv[c], piv);
+        brp = div_skip_zero(br, piv);
+    }
+}
+
 template <int WARPS, int RT, int CT>
 __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : WARPS == 2 ? 8 : 3)) batched_reg_kernel(BatchedParams B) {
     using Cfg = RegCfg<WARPS, RT, CT>;
@@ -206,17 +231,17 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : WARPS == 2 ? 8 
                 const double piv = __shfl_sync(0xffffffffu, mine, ri);
                 double rv[CT];
                 reg_row_get<0, RT, RT, CT>(v, ri, rv);
-#pragma unroll
-                for (int c = 0; c < CT; ++c) prow[c] = div_skip_zero(rv[c], piv);
-                brp = div_skip_zero(__shfl_sync(0xffffffffu, bi, ri), piv);
+                const double br = __shfl_sync(0xffffffffu, bi, ri);
+                scale_row<CT, true>(rv, br, piv, prow, brp);
             } else {
                 if (warp == rw) {
                     const double piv = __shfl_sync(0xffffffffu, mine, ri);
-                    double rv[CT];
+                    double rv[CT], pw[CT], t;
                     reg_row_get<0, RT, RT, CT>(v, ri, rv);
+                    const double br = __shfl_sync(0xffffffffu, bi, ri);
+                    scale_row<CT, false>(rv, br, piv, pw, t);
 #pragma unroll
-                    for (int c = 0; c < CT; ++c) prs[lane + 32 * c] = div_skip_zero(rv[c], piv);
-                    const double t = div_skip_zero(__shfl_sync(0xffffffffu, bi, ri), piv);
+                    for (int c = 0; c < CT; ++c) prs[lane + 32 * c] = pw[c];
                     if (lane == 0) prs[Cfg::MAX_N] = t;
                 }
                 __syncthreads();

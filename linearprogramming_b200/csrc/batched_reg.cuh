@@ -34,8 +34,7 @@ struct RegCfg {
     __host__ __device__ static size_t smem_bytes(int m, int n) {
         size_t b = 16;                                              // mbarrier
         b += ((size_t)(m + 1) * (size_t)(n + 1) + 2) * sizeof(double);  // staging window
-        b = (b + 15) / 16 * 16;
-        return b + (SCRATCH_BYTES + 15) / 16 * 16;
+        return (b + 15) / 16 * 16;                                  // dynamic part; the loop scratch is static
     }
 };
 
@@ -113,7 +112,9 @@ __device__ __forceinline__ void scale_row(const double (&rv)[CT], double piv, do
 // numerator or denominator -- is not dragged in by lanes whose quotient is never used.
 __device__ __forceinline__ double ratio_quotient(double b, double a, bool elig) {
     const bool dv = elig && b != 0.0;
-    const double q = (dv ? b : 1.0) / (dv ? a : 1.0);
+    double num = dv ? b : 1.0, den = dv ? a : 1.0;
+    asm("" : "+d"(num), "+d"(den));      // opaque: otherwise the selects are folded away and 0 / 0 is divided after all
+    const double q = num / den;
     return dv ? q : (elig ? b : 0.0);
 }
 
@@ -135,16 +136,18 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 1 ? 12 : WARPS == 2 ? 8 
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int m = B.m, n = B.n, ld1 = n + 1;
     const size_t tsz = (size_t)(m + 1) * (size_t)ld1;
+    // loop scratch: STATIC shared memory, so every access of the loop has a compile-time address (the
+    // arithmetic of a run-time offset was being rematerialised at each of them); dynamic shared memory:
+    // mbarrier | staging window
     uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw);
-    double *stage = reinterpret_cast<double *>(smem_raw + 16);
-    size_t off = 16 + (tsz + 2) * sizeof(double);
-    off = (off + 15) / 16 * 16;
-    double *pcs = reinterpret_cast<double *>(smem_raw + off);       // entering column, MAX_M
-    double *prs = pcs + Cfg::MAX_M;                                 // WARPS > 1: scaled pivot row, MAX_N (+ b_r')
+    __shared__ __align__(16) unsigned char scratch_raw[(Cfg::SCRATCH_BYTES + 15) / 16 * 16];
+    double *pcs = reinterpret_cast<double *>(scratch_raw);          // entering column, MAX_M
+    double *prs = pcs + Cfg::MAX_M;                                 // WARPS > 1: scaled pivot row, MAX_N (+ 2 spare)
     double *redq = prs + Cfg::MAX_N + 2;                            // WARPS > 1: per-warp ratio winners (theta, a_rk, row)
     double *redp = redq + WARPS;
     int *redi = reinterpret_cast<int *>(redp + WARPS);
     double *raws = redp + 2 * WARPS;                                // WARPS > 1: each warp's candidate row, unscaled
+    double *stage = reinterpret_cast<double *>(smem_raw + 16);
     double *xs = pcs;                                               // result phase: x scatter (loop scratch is dead)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;

@@ -23,6 +23,8 @@ struct PivotState {
     int budget;        // pivots still allowed in this run call
     int k_next;        // lookahead: entering column of the NEXT pivot (0 = unknown -> full decision)
     int cur;           // which half of colbuf holds the pivot column of the pivot to apply
+    int blk_t;         // blocked path: pivots decided since the tableau was last brought up to date
+    int blk_seq;       // blocked path: sequence number of the current block (stamps pivot rows)
 };
 
 // ------------------------------------------------------------------ candidates

@@ -9,6 +9,7 @@
 
 #include "dense_internal.h"
 #include "dense_update.cuh"
+#include "dense_block.cuh"
 
 using namespace lpgpu;
 
@@ -225,6 +226,47 @@ int read_state(lpgpu_dense *d) {
     return LPGPU_OK;
 }
 
+// ---- blocked path (dense_block.cuh): variant bit 0x800, pivots per block in variant bits 16..21 (0 = 32)
+bool use_blocked(const lpgpu_dense *d) {
+    return (d->opts.variant & 0x800) && (d->opts.method == LPGPU_PLAIN || d->opts.method == LPGPU_BIGM);
+}
+
+static BlockBufs make_bufs(const lpgpu_dense *d) {
+    BlockBufs B;
+    B.Ft = d->Ft; B.Pm = d->Pm; B.objcur = d->objcur; B.bcur = d->bcur; B.rowstamp = d->rowstamp;
+    const int k = (d->opts.variant >> 16) & 0x3f;
+    B.K = (k >= 1 && k <= BLK_KMAX) ? k : BLK_KMAX;
+    return B;
+}
+
+static int launch_block_init(lpgpu_dense *d) {
+    lpgpu_ctx *ctx = d->ctx;
+    blk_init_kernel<<<ctx->sm_count, 1024, 0, ctx->stream>>>(make_params(d), make_bufs(d));
+    LP_LAUNCH_CHECK(ctx);
+    ctx->launches++;
+    return LPGPU_OK;
+}
+
+static int launch_block_step(lpgpu_dense *d, int first) {
+    lpgpu_ctx *ctx = d->ctx;
+    const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels;
+    LP_CUDA(ctx, launch_pdl(pdl, blk_step_kernel, dim3(SELECT_CLUSTER), dim3(SELECT_THREADS), ctx->stream, make_params(d),
+                            make_bufs(d), first));
+    ctx->launches++;
+    return LPGPU_OK;
+}
+
+static int launch_block_flush(lpgpu_dense *d) {
+    lpgpu_ctx *ctx = d->ctx;
+    FlushParams U;
+    U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.Ft = d->Ft; U.Pm = d->Pm; U.rowstamp = d->rowstamp; U.st = d->st;
+    U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
+    blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, ctx->stream>>>(U);
+    LP_LAUNCH_CHECK(ctx);
+    ctx->launches++;
+    return LPGPU_OK;
+}
+
 }  // namespace lpgpu
 
 namespace {
@@ -249,6 +291,11 @@ int size_grid(lpgpu_dense *d) {
     const long nct = (long)((d->ld + UPD_TILE_COLS - 1) / UPD_TILE_COLS);
     const long nrb = (d->m + d->R + UPD_TILE_ROWS - 1) / UPD_TILE_ROWS;
     d->grid_update = (int)std::max(1L, std::min((long)ctx->sm_count * occ, nct * nrb));
+    int occf = 0;
+    LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_kernel, FL_THREADS, FL_SMEM_BYTES));
+    const long fct = (long)((d->ld + FL_COLS - 1) / FL_COLS);
+    const long fsb = ((d->m + d->R + FL_ROWS - 1) / FL_ROWS + FL_RB - 1) / FL_RB;
+    d->grid_flush = (int)std::max(1L, std::min((long)ctx->sm_count * std::max(1, occf), fct * fsb));
     return LPGPU_OK;
 }
 
@@ -274,6 +321,7 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     d->ld = round_up((size_t)n + 1, 16);
     d->T = nullptr; d->basis = nullptr; d->prow = d->pcol = d->bnext = d->xbuf = nullptr; d->la_dirty = true; d->st = nullptr; d->h_st = nullptr;
     d->log = nullptr; d->log_cap = 0; d->task_ctr = nullptr; d->upd_seq = 0;
+    d->Ft = d->Pm = d->objcur = d->bcur = nullptr; d->rowstamp = nullptr; d->blk_open = false; d->blk_steps = 0;
     lpgpu_default_opts(&d->opts);
     d->opts.method = (R == 1) ? LPGPU_PLAIN : LPGPU_BIGM;
     const size_t rows = (size_t)m + R, pcn = round_up(rows, UPD_TILE_ROWS) + UPD_TILE_ROWS;
@@ -288,6 +336,16 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     if (e == cudaSuccess) e = cudaMalloc(&d->st, sizeof(PivotState));
     if (e == cudaSuccess) e = cudaMalloc(&d->task_ctr, 2 * sizeof(int));
     if (e == cudaSuccess) e = cudaMemsetAsync(d->task_ctr, 0, 2 * sizeof(int), ctx->stream);
+    if (e == cudaSuccess) e = cudaMalloc(&d->Ft, pcn * BLK_KMAX * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&d->Pm, (size_t)BLK_KMAX * d->ld * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&d->objcur, (size_t)R * d->ld * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&d->bcur, pcn * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&d->rowstamp, pcn * sizeof(int));
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->Ft, 0, pcn * BLK_KMAX * sizeof(double), ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->Pm, 0, (size_t)BLK_KMAX * d->ld * sizeof(double), ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->rowstamp, 0, pcn * sizeof(int), ctx->stream);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(blk_flush_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL_SMEM_BYTES);
     if (e == cudaSuccess) e = cudaHostAlloc(&d->h_st, sizeof(PivotState), cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->T, 0, rows * d->ld * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->prow, 0, d->ld * sizeof(double), ctx->stream);
@@ -312,6 +370,7 @@ void lpgpu_dense_destroy(lpgpu_dense *d) {
     for (cudaEvent_t e : d->ev) cudaEventDestroy(e);
     cudaFree(d->T); cudaFree(d->basis); cudaFree(d->prow); cudaFree(d->pcol); cudaFree(d->bnext); cudaFree(d->xbuf);
     cudaFree(d->st); cudaFree(d->log); cudaFree(d->task_ctr);
+    cudaFree(d->Ft); cudaFree(d->Pm); cudaFree(d->objcur); cudaFree(d->bcur); cudaFree(d->rowstamp);
     if (d->h_st) cudaFreeHost(d->h_st);
     delete d;
 }
@@ -338,6 +397,9 @@ int lpgpu_dense_reset(lpgpu_dense *d, const lpgpu_opts *opts) {
     PivotState s;
     s.status = LPGPU_RUNNING; s.iters = 0; s.phase = (opts->method == LPGPU_TWOPHASE) ? PH_ONE : PH_MAIN;
     s.phase1_iters = 0; s.r = -1; s.k = 0; s.do_pivot = 0; s.budget = 0; s.k_next = 0; s.cur = 0;
+    s.blk_t = 0; s.blk_seq = 0;
+    d->blk_open = false; d->blk_steps = 0;
+    d->la_dirty = true;      // the blocked path's objective rows / b column are re-read from the tableau
     *d->h_st = s;
     LP_CUDA(ctx, cudaMemcpyAsync(d->st, d->h_st, sizeof s, cudaMemcpyHostToDevice, ctx->stream));
     LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -385,13 +447,75 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
     int rc = read_state(d);
     if (rc != LPGPU_OK) return rc;
     d->h_st->budget = max_pivots;
-    if (d->la_dirty) d->h_st->k_next = 0;       // never trust a lookahead across an upload / synth / forced pivot
+    const bool dirty = d->la_dirty;
+    if (dirty) d->h_st->k_next = 0;             // never trust a lookahead across an upload / synth / forced pivot
     d->la_dirty = false;
     LP_CUDA(ctx, cudaMemcpyAsync(d->st, d->h_st, sizeof(PivotState), cudaMemcpyHostToDevice, ctx->stream));
     int launched = 0, done_updates = 0;
     double upd_ms = 0.0, sel_ms = 0.0;
     int iters_before = d->h_st->iters;
-    while (launched < max_pivots) {
+    const bool blocked = use_blocked(d);
+    if (blocked) {
+        // ---- blocked path: K step kernels (decide a pivot each on lazily updated slices), then one pass over
+        // the tableau that applies them all; the tableau is brought up to date before this call returns
+        const int K = make_bufs(d).K;
+        if (dirty) { rc = launch_block_init(d); if (rc != LPGPU_OK) return rc; }
+        std::vector<int> kinds;                 // timed mode: 0 = step, 1 = flush, in launch order
+        auto enqueue = [&](int kind, int first) -> int {
+            const size_t e = 2 * kinds.size();
+            if (timed) {
+                while (d->ev.size() < e + 2) {
+                    cudaEvent_t ev;
+                    LP_CUDA(ctx, cudaEventCreate(&ev));
+                    d->ev.push_back(ev);
+                }
+                LP_CUDA(ctx, cudaEventRecord(d->ev[e], ctx->stream));
+            }
+            const int rc2 = kind ? launch_block_flush(d) : launch_block_step(d, first);
+            if (rc2 != LPGPU_OK) return rc2;
+            if (timed) { LP_CUDA(ctx, cudaEventRecord(d->ev[e + 1], ctx->stream)); kinds.push_back(kind); }
+            return LPGPU_OK;
+        };
+        auto flush = [&]() -> int {
+            const int rc2 = enqueue(1, 0);
+            d->blk_open = false;
+            d->blk_steps = 0;
+            ++done_updates;
+            return rc2;
+        };
+        auto collect = [&]() -> int {
+            for (size_t i = 0; i < kinds.size(); ++i) {
+                float ms = 0.f;
+                LP_CUDA(ctx, cudaEventElapsedTime(&ms, d->ev[2 * i], d->ev[2 * i + 1]));
+                (kinds[i] ? upd_ms : sel_ms) += ms;
+            }
+            kinds.clear();
+            return LPGPU_OK;
+        };
+        while (launched < max_pivots) {
+            const int chunk = std::min(chunk_max, max_pivots - launched);
+            for (int c = 0; c < chunk; ++c) {
+                rc = enqueue(0, d->blk_open ? 0 : 1);
+                if (rc != LPGPU_OK) return rc;
+                d->blk_open = true;
+                if (++d->blk_steps >= K) { rc = flush(); if (rc != LPGPU_OK) return rc; }
+            }
+            launched += chunk;
+            rc = read_state(d);
+            if (rc == LPGPU_OK && timed) rc = collect();
+            if (rc != LPGPU_OK) return rc;
+            if (d->h_st->status != LPGPU_RUNNING) break;
+        }
+        if (d->blk_open) { rc = flush(); if (rc != LPGPU_OK) return rc; }
+        if (d->h_st->status == LPGPU_RUNNING) {
+            rc = launch_block_step(d, 1);       // decision only (budget is spent): settles a terminal status
+            if (rc != LPGPU_OK) return rc;
+        }
+        rc = read_state(d);
+        if (rc == LPGPU_OK && timed) rc = collect();
+        if (rc != LPGPU_OK) return rc;
+    }
+    while (!blocked && launched < max_pivots) {
         const int chunk = std::min(chunk_max, max_pivots - launched);
         for (int c = 0; c < chunk; ++c) {
             if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c], ctx->stream));
@@ -419,7 +543,7 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
         }
         if (d->h_st->status != LPGPU_RUNNING) break;
     }
-    if (d->h_st->status == LPGPU_RUNNING) {
+    if (!blocked && d->h_st->status == LPGPU_RUNNING) {
         // budget spent: one decision-only select settles a terminal status (optimal, iteration
         // limit, ...) without applying a pivot, so a run of exactly the needed pivots reports it
         rc = launch_select(d, -1, 0);

@@ -1,0 +1,321 @@
+// dense_block.cuh -- delayed ("blocked") application of the rank-1 eliminations of ONE large tableau.
+//
+// The rank-1 path (dense_update.cuh) reads and writes the whole tableau once per pivot: 16 B per
+// element per pivot, which is what bounds it (it runs at the measured HBM copy peak).  Here up to
+// BLK_KMAX pivots are DECIDED on lazily updated slices and APPLIED to the tableau in one pass:
+//
+//   per pivot t of a block (blk_step_kernel, one 8-CTA cluster):
+//     entering column k_t   from the eagerly maintained objective row(s)  objcur
+//     column k_t, current   = T[:,k_t] run through the pivots s < t of this block      -> F[:,t]
+//     ratio test            on the eagerly maintained b column  bcur                   -> r_t
+//     row r_t, current      = T[r_t,:] run through the pivots s < t, divided by a_rk   -> P[t,:]
+//     objcur, bcur          updated with (F[:,t], P[t,:]);  next entering column priced
+//   per block (blk_flush_kernel, persistent grid):
+//     a_ij <- fma(-F[i,K-1], P[K-1,j], ... fma(-F[i,0], P[0,j], a_ij))   every element, once
+//     (a row that was the pivot row of step s restarts from P[s,j] and runs the steps after s)
+//
+// Every element goes through exactly the operations of the rank-1 path, in the same order, on the
+// same operands (F[i,s] IS the element (i,k_s) at step s, produced by the same chain), so tableau,
+// basis and pivot log are bit-identical to it -- only the HBM traffic per pivot drops from
+// 16 B/element to 16/K B/element.  At K = 32 the pass is about as long on the FP64 pipe as on HBM.
+// Reference: the loop missing from newSimplex (Source/simplex.c:40-67); layout Source/matrix.c:42-72.
+#pragma once
+
+#include "dense_select.cuh"
+
+namespace lpgpu {
+
+constexpr int BLK_KMAX = 32;           // pivots per block at most (shared-memory tile of the pass)
+
+struct BlockBufs {
+    double *Ft;          // pcn x BLK_KMAX, row-major per tableau row: Ft[i*KMAX + s] = a_{i,k_s} before step s
+    double *Pm;          // BLK_KMAX x ld: Pm[s*ld + j] = scaled pivot row of step s (col 0 = b_r')
+    double *objcur;      // R x ld: objective rows as of the last decided pivot (row m first)
+    double *bcur;        // pcn: b column as of the last decided pivot (rows < m)
+    int *rowstamp;       // pcn: (block sequence << 8) | (s + 1) if the row was the pivot row of step s of that block
+    int K;               // pivots per block, 1..BLK_KMAX
+};
+
+// objcur / bcur <- tableau (after an upload, a synth, a forced pivot or a run of the rank-1 path)
+__global__ void blk_init_kernel(DenseParams P, BlockBufs B) {
+    const size_t gt = (size_t)blockIdx.x * blockDim.x + threadIdx.x, gs = (size_t)gridDim.x * blockDim.x;
+    for (size_t e = gt; e < (size_t)P.R * P.ld; e += gs) B.objcur[e] = P.T[(size_t)P.m * P.ld + e];
+    for (size_t i = gt; i < (size_t)P.m; i += gs) B.bcur[i] = P.T[i * P.ld];
+    for (size_t i = gt; i < (size_t)(P.m + P.R); i += gs) B.rowstamp[i] = 0;
+}
+
+__device__ __forceinline__ int blk_row_start(int stamp, int seq) { return ((stamp >> 8) == seq) ? (stamp & 0xff) : 0; }
+
+// pricing candidate of column j from the (current) objective row values
+__device__ __forceinline__ void blk_price(const DenseParams &P, bool bigm, int j, double oc, double om, Cand &c) {
+    Cand t;
+    t.idx = j;
+    if (bigm) {
+        double p = om;
+        if (fabs(p) <= P.eps) p = 0.0;
+        t.p = p; t.q = oc;
+        if ((p > 0.0 || (p == 0.0 && oc > P.eps)) && cand_better(t, c)) c = t;
+    } else {
+        t.p = 0.0; t.q = oc;
+        if (oc > P.eps && cand_better(t, c)) c = t;
+    }
+}
+
+// One pivot of a block: decision + lazy slices + eager objective rows / b column (PLAIN and BIGM).
+// first != 0: the tableau was flushed (or initialised) since the last step: a new block starts.
+__global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
+blk_step_kernel(DenseParams P, BlockBufs B, int first) {
+    __shared__ Cand scratch[SELECT_THREADS / 32];
+    __shared__ Cand slot_a[SELECT_CLUSTER], slot_b[SELECT_CLUSTER], slot_c[SELECT_CLUSTER], slot_d[SELECT_CLUSTER];
+    __shared__ double s_pk[BLK_KMAX], s_fr[BLK_KMAX];
+    cg::cluster_group cl = cg::this_cluster();
+    const int rank = (int)cl.block_rank();
+    const int gtid = rank * SELECT_THREADS + (int)threadIdx.x;
+    constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
+
+    pdl_wait();
+    pdl_launch_dependents();
+    PivotState *st = P.st;
+    // every thread of the cluster reads the same state; it is rewritten only after a cluster barrier
+    const int status0 = st->status, iters = st->iters, budget = st->budget;
+    const int t = first ? 0 : st->blk_t, seq = st->blk_seq + (first ? 1 : 0);
+    int k = st->k_next;
+    const bool bigm = (P.method == LPGPU_BIGM);
+    const int rows = P.m + P.R;
+    const double *oc = B.objcur, *om = B.objcur + P.ld;          // om valid for R == 2 only
+
+    int status = status0;
+    bool have = false;
+    int r = -1;
+    if (status0 == LPGPU_RUNNING) {
+        // ---- entering column, unless it was priced at the end of the previous step
+        if (k <= 0) {
+            Cand c = cand_none();
+            for (int j = 1 + gtid; j <= P.n; j += GSTRIDE) blk_price(P, bigm, j, oc[j], bigm ? om[j] : 0.0, c);
+            c = cluster_best(cl, c, scratch, slot_a);
+            k = c.idx > 0 ? c.idx : 0;
+            if (k == 0) {
+                // optimal, unless Big-M left an artificial basic at a positive level
+                Cand a = cand_none();
+                if (bigm) {
+                    const int nreal = P.n - P.n_art;
+                    for (int i = gtid; i < P.m; i += GSTRIDE)
+                        if (P.basis[i] > nreal && B.bcur[i] > P.eps) { a.p = 0.0; a.q = 0.0; a.idx = i; break; }
+                }
+                a = cluster_best(cl, a, scratch, slot_d);
+                status = (a.idx >= 0) ? LPGPU_INFEASIBLE : LPGPU_OPTIMAL;
+            }
+        }
+        if (status == LPGPU_RUNNING) {
+            // ---- column k as it stands after the t pivots of this block, and the ratio test on it
+            if ((int)threadIdx.x < t) s_pk[threadIdx.x] = B.Pm[(size_t)threadIdx.x * P.ld + (size_t)k];
+            __syncthreads();
+            Cand c = cand_none();
+            for (int i = gtid; i < rows; i += GSTRIDE) {
+                const int s0 = blk_row_start(B.rowstamp[i], seq);
+                double a = s0 ? s_pk[s0 - 1] : P.T[(size_t)i * P.ld + (size_t)k];
+                const double *fi = B.Ft + (size_t)i * BLK_KMAX;
+                for (int s = s0; s < t; ++s) a = __fma_rn(-fi[s], s_pk[s], a);
+                B.Ft[(size_t)i * BLK_KMAX + t] = a;
+                if (i < P.m && a > P.eps) {
+                    Cand x;
+                    x.p = 0.0;
+                    x.q = -(B.bcur[i] / a);
+                    x.idx = i;
+                    if (cand_better(x, c)) c = x;
+                }
+            }
+            c = cluster_best(cl, c, scratch, slot_b);
+            if (c.idx < 0) status = LPGPU_UNBOUNDED;
+            else if (iters >= P.max_iter) status = LPGPU_ITER_LIMIT;
+            else if (budget > 0) { have = true; r = c.idx; }
+        }
+    }
+    if (!have) {
+        cl.sync();                               // all state reads are done
+        if (gtid == 0) {
+            st->status = status;
+            st->do_pivot = 0;
+            st->blk_t = t;
+            st->blk_seq = seq;
+            if (status == LPGPU_RUNNING) st->k_next = k;      // budget ran out: the priced column stays valid
+        }
+        return;
+    }
+
+    // ---- row r as it stands after the t pivots of this block, scaled; objective rows and next pricing
+    const int s0r = blk_row_start(B.rowstamp[r], seq);
+    if ((int)threadIdx.x < t) s_fr[threadIdx.x] = B.Ft[(size_t)r * BLK_KMAX + threadIdx.x];
+    __syncthreads();
+    const double piv = __ldcg(B.Ft + (size_t)r * BLK_KMAX + t);              // written above by another CTA
+    const double sig_c = __ldcg(B.Ft + (size_t)P.m * BLK_KMAX + t);
+    const double sig_m = (P.R == 2) ? __ldcg(B.Ft + (size_t)(P.m + 1) * BLK_KMAX + t) : 0.0;
+    double *pt = B.Pm + (size_t)t * P.ld;
+    const double *base = s0r ? B.Pm + (size_t)(s0r - 1) * P.ld : P.T + (size_t)r * P.ld;
+    Cand c = cand_none();
+    for (size_t j = (size_t)gtid; j < P.ld; j += GSTRIDE) {
+        double a = base[j];
+        for (int s = s0r; s < t; ++s) a = __fma_rn(-s_fr[s], B.Pm[(size_t)s * P.ld + j], a);
+        const double pr = div_skip_zero(a, piv);
+        pt[j] = pr;
+        const double qc = __fma_rn(-sig_c, pr, oc[j]);
+        B.objcur[j] = qc;
+        double qm = 0.0;
+        if (P.R == 2) {
+            qm = __fma_rn(-sig_m, pr, om[j]);
+            B.objcur[P.ld + j] = qm;
+        }
+        if (j >= 1 && j <= (size_t)P.n) blk_price(P, bigm, (int)j, qc, qm, c);
+    }
+    c = cluster_best(cl, c, scratch, slot_c);
+    const int knew = c.idx > 0 ? c.idx : 0;
+
+    // ---- b column (b_r' = P[t][0] was written by thread 0 of CTA 0 before the barrier above)
+    const double brp = __ldcg(pt);
+    for (int i = gtid; i < P.m; i += GSTRIDE)
+        B.bcur[i] = (i == r) ? brp : __fma_rn(-B.Ft[(size_t)i * BLK_KMAX + t], brp, B.bcur[i]);
+
+    if (gtid == 0) {
+        P.basis[r] = k;
+        B.rowstamp[r] = (seq << 8) | (t + 1);
+        st->status = status;
+        st->do_pivot = 1;
+        st->r = r;
+        st->k = k;
+        st->iters = iters + 1;
+        st->budget = budget - 1;
+        st->k_next = knew;
+        st->blk_t = t + 1;
+        st->blk_seq = seq;
+        if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
+    }
+}
+
+// ------------------------------------------------------------------ the pass that applies a block
+// Tile = FL_ROWS rows x FL_COLS columns per CTA step; a task = one column tile x FL_RB consecutive row
+// tiles, so the K staged pivot-row segments (K x 2 KB) are reused FL_RB times.  Warp w owns rows
+// 2w, 2w+1 of the tile, lane l columns 2l + 64q (q < 4) as 128-bit accesses: 16 independent DFMAs per
+// step of the chain per thread, operands from shared memory (4 conflict-free LDS.128 + 2 broadcasts).
+// Tasks are claimed from a global counter (same protocol as dense_update_dynamic).
+constexpr int FL_THREADS = 256;
+constexpr int FL_COLS = 256;
+constexpr int FL_ROWS = 16;
+constexpr int FL_RB = 8;
+
+struct FlushParams {
+    double *T;
+    size_t ld;
+    int rows;                 // m + R
+    const double *Ft;         // pcn x BLK_KMAX
+    const double *Pm;         // BLK_KMAX x ld
+    const int *rowstamp;
+    const PivotState *st;
+    int *task_ctr;
+    unsigned seq;
+};
+
+constexpr size_t FL_SMEM_BYTES = (size_t)BLK_KMAX * FL_COLS * 8 + 2 * (size_t)FL_ROWS * BLK_KMAX * 8;
+
+__global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U) {
+    extern __shared__ __align__(128) unsigned char fl_smem[];
+    double *sP = reinterpret_cast<double *>(fl_smem);                                 // [BLK_KMAX][FL_COLS]
+    double *sF = sP + (size_t)BLK_KMAX * FL_COLS;                                     // [2][FL_ROWS][BLK_KMAX]
+    __shared__ __align__(8) uint64_t bar_p, bar_f[2];
+    __shared__ long s_task[2];
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bar_p, 1);
+        mbar_init(&bar_f[0], 1);
+        mbar_init(&bar_f[1], 1);
+        fence_mbar_init();
+    }
+    pdl_wait();
+    int *ctr = U.task_ctr + (U.seq & 1u);
+    if (blockIdx.x == 0 && threadIdx.x == 0) U.task_ctr[(U.seq & 1u) ^ 1u] = 0;
+    const int kc = U.st->blk_t, bseq = U.st->blk_seq;
+    if (kc <= 0) return;
+
+    const int nct = (int)((U.ld + FL_COLS - 1) / FL_COLS);
+    const int nrt = (U.rows + FL_ROWS - 1) / FL_ROWS;                  // row tiles
+    const int nsb = (nrt + FL_RB - 1) / FL_RB;                         // row super-blocks
+    const long ntasks = (long)nct * nsb;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    if (threadIdx.x == 0) s_task[0] = (long)atomicAdd(ctr, 1);
+    __syncthreads();
+    uint32_t par_p = 0, par_f[2] = {0, 0};
+    for (int it = 0;; ++it) {
+        const long tt = s_task[it & 1];
+        if (tt >= ntasks) break;
+        const int ct = (int)(tt % nct), sb = (int)(tt / nct);
+        const size_t j0 = (size_t)ct * FL_COLS;
+        const int ncols = (int)min((size_t)FL_COLS, U.ld - j0);        // a multiple of 16 (ld % 16 == 0)
+        const int rt0 = sb * FL_RB, rt1 = min(rt0 + FL_RB, nrt);
+        if (threadIdx.x == 0) {
+            s_task[(it & 1) ^ 1] = (long)atomicAdd(ctr, 1);            // next task; visible after the barriers below
+            mbar_arrive_expect_tx(&bar_p, (uint32_t)(kc * ncols * 8));
+            for (int s = 0; s < kc; ++s) tma_load_1d(sP + (size_t)s * FL_COLS, U.Pm + (size_t)s * U.ld + j0, (uint32_t)(ncols * 8), &bar_p);
+            mbar_arrive_expect_tx(&bar_f[0], (uint32_t)(FL_ROWS * BLK_KMAX * 8));
+            tma_load_1d(sF, U.Ft + (size_t)rt0 * FL_ROWS * BLK_KMAX, (uint32_t)(FL_ROWS * BLK_KMAX * 8), &bar_f[0]);
+        }
+        for (int rt = rt0; rt < rt1; ++rt) {
+            const int fb = (rt - rt0) & 1;
+            const int i0 = rt * FL_ROWS + 2 * warp;
+            // this thread's 2 x 8 elements go out first
+            double2 acc[2][4];
+            int st_[2];
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr) {
+                const int i = i0 + rr;
+                st_[rr] = (i < U.rows) ? blk_row_start(U.rowstamp[i], bseq) : 0;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int jc = 2 * lane + 64 * q;
+                    acc[rr][q] = make_double2(0.0, 0.0);
+                    if (i < U.rows && jc < ncols && st_[rr] == 0) acc[rr][q] = ld_stream2(U.T + (size_t)i * U.ld + j0 + jc);
+                }
+            }
+            if (threadIdx.x == 0 && rt + 1 < rt1) {      // the other F buffer was released by the barrier that ended tile rt-1
+                mbar_arrive_expect_tx(&bar_f[fb ^ 1], (uint32_t)(FL_ROWS * BLK_KMAX * 8));
+                tma_load_1d(sF + (size_t)(fb ^ 1) * FL_ROWS * BLK_KMAX, U.Ft + (size_t)(rt + 1) * FL_ROWS * BLK_KMAX,
+                            (uint32_t)(FL_ROWS * BLK_KMAX * 8), &bar_f[fb ^ 1]);
+            }
+            if (rt == rt0) { mbar_wait(&bar_p, par_p); par_p ^= 1; }
+            mbar_wait(&bar_f[fb], par_f[fb]);
+            par_f[fb] ^= 1;
+            // rows that were pivot rows in this block restart from their scaled pivot row
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr)
+                if (st_[rr] > 0) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        acc[rr][q] = *reinterpret_cast<const double2 *>(sP + (size_t)(st_[rr] - 1) * FL_COLS + 2 * lane + 64 * q);
+                }
+            const double *f0 = sF + (size_t)fb * FL_ROWS * BLK_KMAX + (size_t)(2 * warp) * BLK_KMAX;
+            const double *f1 = f0 + BLK_KMAX;
+#pragma unroll 4
+            for (int s = 0; s < kc; ++s) {
+                const double a0 = -f0[s], a1 = -f1[s];
+                const bool on0 = s >= st_[0], on1 = s >= st_[1];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const double2 p = *reinterpret_cast<const double2 *>(sP + (size_t)s * FL_COLS + 2 * lane + 64 * q);
+                    if (on0) { acc[0][q].x = __fma_rn(a0, p.x, acc[0][q].x); acc[0][q].y = __fma_rn(a0, p.y, acc[0][q].y); }
+                    if (on1) { acc[1][q].x = __fma_rn(a1, p.x, acc[1][q].x); acc[1][q].y = __fma_rn(a1, p.y, acc[1][q].y); }
+                }
+            }
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr) {
+                const int i = i0 + rr;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int jc = 2 * lane + 64 * q;
+                    if (i < U.rows && jc < ncols) st_stream2(U.T + (size_t)i * U.ld + j0 + jc, acc[rr][q]);
+                }
+            }
+            __syncthreads();       // sF[fb] may be refilled (two tiles ahead), and at the last tile sP and s_task
+        }
+    }
+}
+
+}  // namespace lpgpu

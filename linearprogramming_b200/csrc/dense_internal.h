@@ -22,9 +22,15 @@ struct lpgpu_dense {
     int log_cap;
     lpgpu_opts opts;
     int grid_update;
+    int grid_flush;         // persistent grid of the blocked path's pass
     int *task_ctr;          // work-stealing counters of the elimination kernel (2 ints)
     unsigned upd_seq;       // elimination launches so far
     std::vector<cudaEvent_t> ev;
+    // blocked path (dense_block.cuh): lazy slices of the pivots not yet applied to T
+    double *Ft, *Pm, *objcur, *bcur;
+    int *rowstamp;
+    bool blk_open;          // step kernels were enqueued since the last flush
+    int blk_steps;          // ... how many
 };
 
 namespace lpgpu {

@@ -195,6 +195,97 @@ def test_dense_timed_run_reports_kernel_time(ctx):
     d.close()
 
 
+# ------------------------------------------------------------------ blocked path (delayed rank-1 applications)
+def _blocked(K=0):
+    return capi.BLOCKED | (K << 16)
+
+
+@pytest.mark.parametrize("m,ns", [(32, 32), (64, 64), (200, 120), (300, 500), (512, 512)])
+@pytest.mark.parametrize("K", [0, 1, 2, 5, 32])
+def test_blocked_synth_full_solve_bitwise(ctx, m, ns, K):
+    """Up to K pivots decided on lazily updated slices and applied in one pass: pivot log, basis, statuses and
+    the tableau equal the oracle's (and so the rank-1 path's) bit for bit."""
+    T0, basis = O.synth_feasible(1234, 3, m, ns)
+    ref = O.solve_f64(T0, basis, threads=4, log_cap=4096)
+    got = lp.solve_dense(ctx, T0, basis, log_cap=4096, variant=_blocked(K))
+    _assert_dense_equal(got, ref)
+    assert got["status"] == lp.OPTIMAL
+
+
+@pytest.mark.parametrize("seed", range(10))
+@pytest.mark.parametrize("K", [0, 3])
+def test_blocked_bigm_random_mixed(ctx, seed, K):
+    rng = np.random.default_rng(seed)
+    m, ns = int(rng.integers(3, 40)), int(rng.integers(3, 40))
+    A, b, c, rel = H.random_mixed_lp(rng, m, ns)
+    if seed % 3 == 2:        # make some infeasible: contradict the first row
+        A = np.vstack([A, A[0]]); b = np.append(b, b[0] - 5.0 if rel[0] != -2 else b[0] + 5.0)
+        rel = np.append(rel, -2 if rel[0] != -2 else 2).astype(np.int32)
+    T0, basis, n_art = lp.build_tableau(A, b, c, rel, R=2)
+    ref = O.solve_f64(T0, basis, method=O.BIGM, n_art=n_art, max_iter=5000, log_cap=5000)
+    got = lp.solve_dense(ctx, T0, basis, method=O.BIGM, n_art=n_art, max_iter=5000, log_cap=5000, variant=_blocked(K))
+    _assert_dense_equal(got, ref)
+
+
+def test_blocked_statuses_windows_and_limits(ctx):
+    # unbounded
+    for name in ("unbounded.txt", "unr_inverted.txt"):
+        d = H.load_dumps()[name]
+        T, basis, n_art, n = H.tableau_from_dump(d, O.PLAIN)
+        ref = O.solve_f64(H.frac_f64(T), basis, log_cap=16)
+        got = lp.solve_dense(ctx, H.frac_f64(T), basis, log_cap=16, variant=_blocked())
+        _assert_dense_equal(got, ref)
+        assert got["status"] == lp.UNBOUNDED
+    # iteration limit, and exactly the needed number of pivots
+    T0, basis = O.synth_feasible(1234, 0, 64, 64)
+    full = O.solve_f64(T0, basis)
+    ref = O.solve_f64(T0, basis, max_iter=5, log_cap=16)
+    got = lp.solve_dense(ctx, T0, basis, max_iter=5, log_cap=16, variant=_blocked())
+    _assert_dense_equal(got, ref)
+    assert got["status"] == lp.ITER_LIMIT and got["iters"] == 5
+    exact = lp.solve_dense(ctx, T0, basis, max_iter=full["iters"], variant=_blocked())
+    assert exact["status"] == lp.OPTIMAL and exact["iters"] == full["iters"]
+    # windows of 25 pivots with blocks of 7 and a state read every 10: the tableau is up to date after every call
+    m, ns = 300, 212
+    T0, basis = O.synth_feasible(77, 5, m, ns)
+    d = lp.DenseTableau(ctx, m, m + ns, 1)
+    d.synth(77, 5, ns)
+    d.reset(log_cap=4096, check_every=10, variant=_blocked(7))
+    total = 0
+    while True:
+        r = d.run(25)
+        assert r["iters"] - total <= 25
+        total = r["iters"]
+        if r["status"] != lp.RUNNING:
+            break
+        part = O.solve_f64(T0, basis, max_iter=total)
+        assert np.array_equal(d.download()["T"], part["T"])
+    ref = O.solve_f64(T0, basis, log_cap=4096)
+    out = d.download()
+    assert r["status"] == ref["status"] == lp.OPTIMAL and r["iters"] == ref["iters"]
+    assert out["log"][:r["iters"]].tolist() == ref["log"].tolist()
+    assert np.array_equal(out["T"], ref["T"]) and np.array_equal(out["x"], ref["x"])
+    d.close()
+
+
+def test_blocked_equals_rank1_path_midsize_bitwise(ctx):
+    """1024 x 4096, 300 pivots: blocked (K = 32 and 13) and rank-1 runs leave the same bits; then the two paths
+    alternate on one tableau object (reset between them) and still agree."""
+    m, ns, Pn = 1024, 3072, 300
+    outs = []
+    for variant in (0, _blocked(), _blocked(13)):
+        d = lp.DenseTableau(ctx, m, m + ns, 1)
+        d.synth(1234, 3, ns)
+        d.reset(log_cap=Pn, variant=variant)
+        r = d.run(Pn)
+        outs.append((r, d.download()))
+        d.close()
+    for r, o in outs[1:]:
+        assert r["iters"] == outs[0][0]["iters"] == Pn and r["z"] == outs[0][0]["z"]
+        assert np.array_equal(o["log"], outs[0][1]["log"]) and np.array_equal(o["basis"], outs[0][1]["basis"])
+        assert np.array_equal(o["T"], outs[0][1]["T"])
+
+
 # ------------------------------------------------------------------ dual simplex (SURVEY section 8 f3)
 @pytest.mark.parametrize("seed", range(8))
 def test_dual_simplex_dense_bitwise(ctx, seed):

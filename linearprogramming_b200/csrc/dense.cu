@@ -233,7 +233,7 @@ bool use_blocked(const lpgpu_dense *d) {
 
 static BlockBufs make_bufs(const lpgpu_dense *d) {
     BlockBufs B;
-    B.Ft = d->Ft; B.Pm = d->Pm; B.objcur = d->objcur; B.bcur = d->bcur; B.rowstamp = d->rowstamp;
+    B.Ft = d->Ft; B.Pm = d->Pm; B.objcur = d->objcur; B.bcur = d->bcur; B.rowstamp = d->rowstamp; B.steprow = d->steprow;
     const int k = (d->opts.variant >> 16) & 0x3f;
     B.K = (k >= 1 && k <= BLK_KMAX) ? k : BLK_KMAX;
     return B;
@@ -259,11 +259,14 @@ static int launch_block_step(lpgpu_dense *d, int first) {
 static int launch_block_flush(lpgpu_dense *d) {
     lpgpu_ctx *ctx = d->ctx;
     FlushParams U;
-    U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.Ft = d->Ft; U.Pm = d->Pm; U.rowstamp = d->rowstamp; U.st = d->st;
+    U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.Ft = d->Ft; U.Pm = d->Pm; U.rowstamp = d->rowstamp; U.steprow = d->steprow; U.st = d->st;
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
     blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, ctx->stream>>>(U);
     LP_LAUNCH_CHECK(ctx);
-    ctx->launches++;
+    const unsigned fx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, (d->ld + 255) / 256));
+    blk_fixrows_kernel<<<dim3(fx, BLK_KMAX), 256, 0, ctx->stream>>>(U);
+    LP_LAUNCH_CHECK(ctx);
+    ctx->launches += 2;
     return LPGPU_OK;
 }
 
@@ -321,7 +324,7 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     d->ld = round_up((size_t)n + 1, 16);
     d->T = nullptr; d->basis = nullptr; d->prow = d->pcol = d->bnext = d->xbuf = nullptr; d->la_dirty = true; d->st = nullptr; d->h_st = nullptr;
     d->log = nullptr; d->log_cap = 0; d->task_ctr = nullptr; d->upd_seq = 0;
-    d->Ft = d->Pm = d->objcur = d->bcur = nullptr; d->rowstamp = nullptr; d->blk_open = false; d->blk_steps = 0;
+    d->Ft = d->Pm = d->objcur = d->bcur = nullptr; d->rowstamp = d->steprow = nullptr; d->blk_open = false; d->blk_steps = 0;
     lpgpu_default_opts(&d->opts);
     d->opts.method = (R == 1) ? LPGPU_PLAIN : LPGPU_BIGM;
     const size_t rows = (size_t)m + R, pcn = round_up(rows, UPD_TILE_ROWS) + UPD_TILE_ROWS;
@@ -341,6 +344,8 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     if (e == cudaSuccess) e = cudaMalloc(&d->objcur, (size_t)R * d->ld * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&d->bcur, pcn * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&d->rowstamp, pcn * sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc(&d->steprow, BLK_KMAX * sizeof(int));
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->steprow, 0, BLK_KMAX * sizeof(int), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->Ft, 0, pcn * BLK_KMAX * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->Pm, 0, (size_t)BLK_KMAX * d->ld * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->rowstamp, 0, pcn * sizeof(int), ctx->stream);
@@ -370,7 +375,7 @@ void lpgpu_dense_destroy(lpgpu_dense *d) {
     for (cudaEvent_t e : d->ev) cudaEventDestroy(e);
     cudaFree(d->T); cudaFree(d->basis); cudaFree(d->prow); cudaFree(d->pcol); cudaFree(d->bnext); cudaFree(d->xbuf);
     cudaFree(d->st); cudaFree(d->log); cudaFree(d->task_ctr);
-    cudaFree(d->Ft); cudaFree(d->Pm); cudaFree(d->objcur); cudaFree(d->bcur); cudaFree(d->rowstamp);
+    cudaFree(d->Ft); cudaFree(d->Pm); cudaFree(d->objcur); cudaFree(d->bcur); cudaFree(d->rowstamp); cudaFree(d->steprow);
     if (d->h_st) cudaFreeHost(d->h_st);
     delete d;
 }

@@ -33,6 +33,7 @@ struct BlockBufs {
     double *objcur;      // R x ld: objective rows as of the last decided pivot (row m first)
     double *bcur;        // pcn: b column as of the last decided pivot (rows < m)
     int *rowstamp;       // pcn: (block sequence << 8) | (s + 1) if the row was the pivot row of step s of that block
+    int *steprow;        // BLK_KMAX: pivot row of step s of the current block
     int K;               // pivots per block, 1..BLK_KMAX
 };
 
@@ -114,8 +115,19 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
             for (int i = gtid; i < rows; i += GSTRIDE) {
                 const int s0 = blk_row_start(B.rowstamp[i], seq);
                 double a = s0 ? s_pk[s0 - 1] : P.T[(size_t)i * P.ld + (size_t)k];
-                const double *fi = B.Ft + (size_t)i * BLK_KMAX;
-                for (int s = s0; s < t; ++s) a = __fma_rn(-fi[s], s_pk[s], a);
+                // the row's multipliers of the earlier steps: 128-bit loads, all in flight before the chain starts
+                const double2 *fi2 = reinterpret_cast<const double2 *>(B.Ft + (size_t)i * BLK_KMAX);
+                for (int sb = s0 & ~7; sb < t; sb += 8) {
+                    double2 f2[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) f2[u] = (sb + 2 * u < t) ? fi2[(sb >> 1) + u] : make_double2(0.0, 0.0);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int s = sb + 2 * u;
+                        if (s >= s0 && s < t) a = __fma_rn(-f2[u].x, s_pk[s], a);
+                        if (s + 1 >= s0 && s + 1 < t) a = __fma_rn(-f2[u].y, s_pk[s + 1], a);
+                    }
+                }
                 B.Ft[(size_t)i * BLK_KMAX + t] = a;
                 if (i < P.m && a > P.eps) {
                     Cand x;
@@ -155,7 +167,14 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     Cand c = cand_none();
     for (size_t j = (size_t)gtid; j < P.ld; j += GSTRIDE) {
         double a = base[j];
-        for (int s = s0r; s < t; ++s) a = __fma_rn(-s_fr[s], B.Pm[(size_t)s * P.ld + j], a);
+        for (int sb = s0r; sb < t; sb += 8) {            // 8 pivot rows in flight before the chain consumes them
+            double pv[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) pv[u] = (sb + u < t) ? B.Pm[(size_t)(sb + u) * P.ld + j] : 0.0;
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                if (sb + u < t) a = __fma_rn(-s_fr[sb + u], pv[u], a);
+        }
         const double pr = div_skip_zero(a, piv);
         pt[j] = pr;
         const double qc = __fma_rn(-sig_c, pr, oc[j]);
@@ -178,6 +197,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     if (gtid == 0) {
         P.basis[r] = k;
         B.rowstamp[r] = (seq << 8) | (t + 1);
+        B.steprow[t] = r;
         st->status = status;
         st->do_pivot = 1;
         st->r = r;
@@ -192,15 +212,23 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
 }
 
 // ------------------------------------------------------------------ the pass that applies a block
-// Tile = FL_ROWS rows x FL_COLS columns per CTA step; a task = one column tile x FL_RB consecutive row
-// tiles, so the K staged pivot-row segments (K x 2 KB) are reused FL_RB times.  Warp w owns rows
-// 2w, 2w+1 of the tile, lane l columns 2l + 64q (q < 4) as 128-bit accesses: 16 independent DFMAs per
-// step of the chain per thread, operands from shared memory (4 conflict-free LDS.128 + 2 broadcasts).
-// Tasks are claimed from a global counter (same protocol as dense_update_dynamic).
+// CTA tile = FL_ROWS x FL_COLS, 8 warps as 2 (rows) x 4 (columns); a thread owns 32 rows x 2 adjacent
+// columns (one 128-bit access per row, 64 accumulator registers).  Per step of the chain a thread
+// needs ONE pivot-row pair (a per-lane LDS.128: 4 shared-memory wavefronts per warp) but 32 multipliers
+// that are warp-uniform (broadcast LDS.128 = 1 wavefront for two steps of a row), so the tall, narrow
+// thread tile keeps shared memory at ~20 wavefronts per 64 DFMAs and the FP64 pipe the busier unit
+// (a 2 x 8 thread tile measured 4x slower: 18 wavefronts per 16 DFMAs).  Steps are taken in pairs.
+// A task = one column tile x FL_RB consecutive row tiles: the K staged pivot-row segments (K x 2 KB,
+// TMA bulk copies) are reused FL_RB times, the multipliers (64 rows x K, one 16 KB bulk copy) are
+// double buffered.  Tasks are claimed from a global counter (protocol of dense_update_dynamic).
+// Rows that were pivot rows inside the block are NOT special-cased here: blk_fixrows_kernel rewrites
+// them afterwards.
 constexpr int FL_THREADS = 256;
 constexpr int FL_COLS = 256;
-constexpr int FL_ROWS = 16;
-constexpr int FL_RB = 8;
+constexpr int FL_ROWS = 64;
+constexpr int FL_TR = 32;              // rows per thread
+constexpr int FL_RG = 8;               // rows whose multipliers are in flight together
+constexpr int FL_RB = 4;
 
 struct FlushParams {
     double *T;
@@ -209,6 +237,7 @@ struct FlushParams {
     const double *Ft;         // pcn x BLK_KMAX
     const double *Pm;         // BLK_KMAX x ld
     const int *rowstamp;
+    const int *steprow;       // pivot row of step s of the current block
     const PivotState *st;
     int *task_ctr;
     unsigned seq;
@@ -216,7 +245,7 @@ struct FlushParams {
 
 constexpr size_t FL_SMEM_BYTES = (size_t)BLK_KMAX * FL_COLS * 8 + 2 * (size_t)FL_ROWS * BLK_KMAX * 8;
 
-__global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U) {
+__global__ void __launch_bounds__(FL_THREADS, 2) blk_flush_kernel(FlushParams U) {
     extern __shared__ __align__(128) unsigned char fl_smem[];
     double *sP = reinterpret_cast<double *>(fl_smem);                                 // [BLK_KMAX][FL_COLS]
     double *sF = sP + (size_t)BLK_KMAX * FL_COLS;                                     // [2][FL_ROWS][BLK_KMAX]
@@ -232,7 +261,7 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
     pdl_wait();
     int *ctr = U.task_ctr + (U.seq & 1u);
     if (blockIdx.x == 0 && threadIdx.x == 0) U.task_ctr[(U.seq & 1u) ^ 1u] = 0;
-    const int kc = U.st->blk_t, bseq = U.st->blk_seq;
+    const int kc = U.st->blk_t;
     if (kc <= 0) return;
 
     const int nct = (int)((U.ld + FL_COLS - 1) / FL_COLS);
@@ -240,10 +269,13 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
     const int nsb = (nrt + FL_RB - 1) / FL_RB;                         // row super-blocks
     const long ntasks = (long)nct * nsb;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int wr = warp >> 2, wc = warp & 3;
+    const int jc = 64 * wc + 2 * lane;                                 // this thread's column pair inside the tile
+    constexpr uint32_t FBYTES = (uint32_t)(FL_ROWS * BLK_KMAX * 8);
 
     if (threadIdx.x == 0) s_task[0] = (long)atomicAdd(ctr, 1);
     __syncthreads();
-    uint32_t par_p = 0, par_f[2] = {0, 0};
+    uint32_t par_p = 0, par_f = 0;               // bit fb of par_f = parity of F buffer fb
     for (int it = 0;; ++it) {
         const long tt = s_task[it & 1];
         if (tt >= ntasks) break;
@@ -255,66 +287,80 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
             s_task[(it & 1) ^ 1] = (long)atomicAdd(ctr, 1);            // next task; visible after the barriers below
             mbar_arrive_expect_tx(&bar_p, (uint32_t)(kc * ncols * 8));
             for (int s = 0; s < kc; ++s) tma_load_1d(sP + (size_t)s * FL_COLS, U.Pm + (size_t)s * U.ld + j0, (uint32_t)(ncols * 8), &bar_p);
-            mbar_arrive_expect_tx(&bar_f[0], (uint32_t)(FL_ROWS * BLK_KMAX * 8));
-            tma_load_1d(sF, U.Ft + (size_t)rt0 * FL_ROWS * BLK_KMAX, (uint32_t)(FL_ROWS * BLK_KMAX * 8), &bar_f[0]);
+            mbar_arrive_expect_tx(&bar_f[0], FBYTES);
+            tma_load_1d(sF, U.Ft + (size_t)rt0 * FL_ROWS * BLK_KMAX, FBYTES, &bar_f[0]);
         }
+        const bool colok = jc < ncols;
         for (int rt = rt0; rt < rt1; ++rt) {
             const int fb = (rt - rt0) & 1;
-            const int i0 = rt * FL_ROWS + 2 * warp;
-            // this thread's 2 x 8 elements go out first
-            double2 acc[2][4];
-            int st_[2];
+            const int i0 = rt * FL_ROWS + FL_TR * wr;
+            double2 acc[FL_TR];
+            double *tp = U.T + (size_t)i0 * U.ld + j0 + jc;
 #pragma unroll
-            for (int rr = 0; rr < 2; ++rr) {
-                const int i = i0 + rr;
-                st_[rr] = (i < U.rows) ? blk_row_start(U.rowstamp[i], bseq) : 0;
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int jc = 2 * lane + 64 * q;
-                    acc[rr][q] = make_double2(0.0, 0.0);
-                    if (i < U.rows && jc < ncols && st_[rr] == 0) acc[rr][q] = ld_stream2(U.T + (size_t)i * U.ld + j0 + jc);
-                }
-            }
+            for (int rr = 0; rr < FL_TR; ++rr)
+                acc[rr] = (colok && i0 + rr < U.rows) ? ld_stream2(tp + (size_t)rr * U.ld) : make_double2(0.0, 0.0);
             if (threadIdx.x == 0 && rt + 1 < rt1) {      // the other F buffer was released by the barrier that ended tile rt-1
-                mbar_arrive_expect_tx(&bar_f[fb ^ 1], (uint32_t)(FL_ROWS * BLK_KMAX * 8));
-                tma_load_1d(sF + (size_t)(fb ^ 1) * FL_ROWS * BLK_KMAX, U.Ft + (size_t)(rt + 1) * FL_ROWS * BLK_KMAX,
-                            (uint32_t)(FL_ROWS * BLK_KMAX * 8), &bar_f[fb ^ 1]);
+                mbar_arrive_expect_tx(&bar_f[fb ^ 1], FBYTES);
+                tma_load_1d(sF + (size_t)(fb ^ 1) * FL_ROWS * BLK_KMAX, U.Ft + (size_t)(rt + 1) * FL_ROWS * BLK_KMAX, FBYTES, &bar_f[fb ^ 1]);
             }
             if (rt == rt0) { mbar_wait(&bar_p, par_p); par_p ^= 1; }
-            mbar_wait(&bar_f[fb], par_f[fb]);
-            par_f[fb] ^= 1;
-            // rows that were pivot rows in this block restart from their scaled pivot row
+            mbar_wait(&bar_f[fb], (par_f >> fb) & 1u);
+            par_f ^= 1u << fb;
+            const double *fw = sF + (size_t)fb * FL_ROWS * BLK_KMAX + (size_t)(FL_TR * wr) * BLK_KMAX;
+            const double *pw = sP + jc;
+            int s = 0;
+            for (; s + 1 < kc; s += 2) {
+                const double2 p0 = *reinterpret_cast<const double2 *>(pw + (size_t)s * FL_COLS);
+                const double2 p1 = *reinterpret_cast<const double2 *>(pw + (size_t)(s + 1) * FL_COLS);
 #pragma unroll
-            for (int rr = 0; rr < 2; ++rr)
-                if (st_[rr] > 0) {
+                for (int rg = 0; rg < FL_TR; rg += FL_RG) {
+                    double2 f[FL_RG];                         // multipliers of steps s, s+1 for FL_RG rows (broadcast loads)
 #pragma unroll
-                    for (int q = 0; q < 4; ++q)
-                        acc[rr][q] = *reinterpret_cast<const double2 *>(sP + (size_t)(st_[rr] - 1) * FL_COLS + 2 * lane + 64 * q);
+                    for (int u = 0; u < FL_RG; ++u) f[u] = *reinterpret_cast<const double2 *>(fw + (size_t)(rg + u) * BLK_KMAX + s);
+#pragma unroll
+                    for (int u = 0; u < FL_RG; ++u) {
+                        acc[rg + u].x = __fma_rn(-f[u].x, p0.x, acc[rg + u].x);
+                        acc[rg + u].y = __fma_rn(-f[u].x, p0.y, acc[rg + u].y);
+                    }
+#pragma unroll
+                    for (int u = 0; u < FL_RG; ++u) {
+                        acc[rg + u].x = __fma_rn(-f[u].y, p1.x, acc[rg + u].x);
+                        acc[rg + u].y = __fma_rn(-f[u].y, p1.y, acc[rg + u].y);
+                    }
+                    asm volatile("" ::: "memory");            // keeps the next group's loads from being hoisted (register budget)
                 }
-            const double *f0 = sF + (size_t)fb * FL_ROWS * BLK_KMAX + (size_t)(2 * warp) * BLK_KMAX;
-            const double *f1 = f0 + BLK_KMAX;
-#pragma unroll 4
-            for (int s = 0; s < kc; ++s) {
-                const double a0 = -f0[s], a1 = -f1[s];
-                const bool on0 = s >= st_[0], on1 = s >= st_[1];
+            }
+            if (s < kc) {                                  // odd number of steps: the last one alone
+                const double2 p0 = *reinterpret_cast<const double2 *>(pw + (size_t)s * FL_COLS);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const double2 p = *reinterpret_cast<const double2 *>(sP + (size_t)s * FL_COLS + 2 * lane + 64 * q);
-                    if (on0) { acc[0][q].x = __fma_rn(a0, p.x, acc[0][q].x); acc[0][q].y = __fma_rn(a0, p.y, acc[0][q].y); }
-                    if (on1) { acc[1][q].x = __fma_rn(a1, p.x, acc[1][q].x); acc[1][q].y = __fma_rn(a1, p.y, acc[1][q].y); }
+                for (int rr = 0; rr < FL_TR; ++rr) {
+                    const double f = fw[(size_t)rr * BLK_KMAX + s];
+                    acc[rr].x = __fma_rn(-f, p0.x, acc[rr].x);
+                    acc[rr].y = __fma_rn(-f, p0.y, acc[rr].y);
                 }
             }
 #pragma unroll
-            for (int rr = 0; rr < 2; ++rr) {
-                const int i = i0 + rr;
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int jc = 2 * lane + 64 * q;
-                    if (i < U.rows && jc < ncols) st_stream2(U.T + (size_t)i * U.ld + j0 + jc, acc[rr][q]);
-                }
-            }
+            for (int rr = 0; rr < FL_TR; ++rr)
+                if (colok && i0 + rr < U.rows) st_stream2(tp + (size_t)rr * U.ld, acc[rr]);
             __syncthreads();       // sF[fb] may be refilled (two tiles ahead), and at the last tile sP and s_task
         }
+    }
+}
+
+// Rows that were a pivot row inside the block: restart from the scaled pivot row of their LAST such step
+// and run the steps after it.  grid = (column chunks, BLK_KMAX); block y = step s.
+__global__ void __launch_bounds__(256) blk_fixrows_kernel(FlushParams U) {
+    const int kc = U.st->blk_t, bseq = U.st->blk_seq, s0 = (int)blockIdx.y;
+    if (s0 >= kc) return;
+    const int r = U.steprow[s0];
+    if (blk_row_start(U.rowstamp[r], bseq) != s0 + 1) return;      // the row was a pivot row again later in the block
+    __shared__ double s_f[BLK_KMAX];
+    if ((int)threadIdx.x < kc) s_f[threadIdx.x] = U.Ft[(size_t)r * BLK_KMAX + threadIdx.x];
+    __syncthreads();
+    for (size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x; j < U.ld; j += (size_t)gridDim.x * blockDim.x) {
+        double a = U.Pm[(size_t)s0 * U.ld + j];
+        for (int s = s0 + 1; s < kc; ++s) a = __fma_rn(-s_f[s], U.Pm[(size_t)s * U.ld + j], a);
+        U.T[(size_t)r * U.ld + j] = a;
     }
 }
 

@@ -28,7 +28,7 @@ struct lpgpu_dense {
     std::vector<cudaEvent_t> ev;
     // blocked path (dense_block.cuh): lazy slices of the pivots not yet applied to T
     double *Ft, *Pm, *objcur, *bcur;
-    int *rowstamp;
+    int *rowstamp, *steprow;
     bool blk_open;          // step kernels were enqueued since the last flush
     int blk_steps;          // ... how many
 };

@@ -212,22 +212,22 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
 }
 
 // ------------------------------------------------------------------ the pass that applies a block
-// CTA tile = FL_ROWS x FL_COLS, 8 warps as 2 (rows) x 4 (columns); a thread owns 32 rows x 2 adjacent
-// columns (one 128-bit access per row, 64 accumulator registers).  Per step of the chain a thread
-// needs ONE pivot-row pair (a per-lane LDS.128: 4 shared-memory wavefronts per warp) but 32 multipliers
-// that are warp-uniform (broadcast LDS.128 = 1 wavefront for two steps of a row), so the tall, narrow
-// thread tile keeps shared memory at ~20 wavefronts per 64 DFMAs and the FP64 pipe the busier unit
-// (a 2 x 8 thread tile measured 4x slower: 18 wavefronts per 16 DFMAs).  Steps are taken in pairs.
-// A task = one column tile x FL_RB consecutive row tiles: the K staged pivot-row segments (K x 2 KB,
+// CTA tile = FL_ROWS x FL_COLS, 4 warps stacked over the rows; a thread owns 16 rows x 4 columns
+// (two 128-bit accesses per row, 64 accumulator registers).  Per step of the chain a thread needs two
+// pivot-row pairs (per-lane LDS.128: 4 shared-memory wavefronts per warp each) and 16 multipliers that
+// are warp-uniform (a broadcast LDS.128 = 1 wavefront serves two steps of a row): 16 wavefronts per 64
+// DFMAs, so the FP64 pipe, not shared memory, is the busier unit (a 2 x 8 thread tile measured 4x
+// slower: 18 wavefronts per 16 DFMAs).  Steps are taken in pairs.
+// A task = one column tile x FL_RB consecutive row tiles: the K staged pivot-row segments (K x 1 KB,
 // TMA bulk copies) are reused FL_RB times, the multipliers (64 rows x K, one 16 KB bulk copy) are
 // double buffered.  Tasks are claimed from a global counter (protocol of dense_update_dynamic).
 // Rows that were pivot rows inside the block are NOT special-cased here: blk_fixrows_kernel rewrites
 // them afterwards.
-constexpr int FL_THREADS = 256;
-constexpr int FL_COLS = 256;
+constexpr int FL_THREADS = 128;
+constexpr int FL_COLS = 128;
 constexpr int FL_ROWS = 64;
-constexpr int FL_TR = 32;              // rows per thread
-constexpr int FL_RG = 8;               // rows whose multipliers are in flight together
+constexpr int FL_TR = 16;              // rows per thread (x 4 columns: two 128-bit accesses 64 columns apart)
+constexpr int FL_RG = 4;               // rows whose multipliers are in flight together
 constexpr int FL_RB = 4;
 
 struct FlushParams {
@@ -245,7 +245,85 @@ struct FlushParams {
 
 constexpr size_t FL_SMEM_BYTES = (size_t)BLK_KMAX * FL_COLS * 8 + 2 * (size_t)FL_ROWS * BLK_KMAX * 8;
 
-__global__ void __launch_bounds__(FL_THREADS, 2) blk_flush_kernel(FlushParams U) {
+// where a tile's operands live
+struct FlTile {
+    size_t j0;          // first column of the tile
+    int ncols;          // columns in it (a multiple of 16)
+    int rt;             // row tile index
+};
+
+__device__ __forceinline__ void fl_load_tile(const FlushParams &U, const FlTile &t, int wr, int jc, double2 (&acc)[FL_TR][2]) {
+    const int i0 = t.rt * FL_ROWS + FL_TR * wr;
+    const double *tp = U.T + (size_t)i0 * U.ld + t.j0 + jc;
+    const bool ok0 = jc < t.ncols, ok1 = jc + 64 < t.ncols;
+#pragma unroll
+    for (int rr = 0; rr < FL_TR; ++rr) {
+        const bool rowok = i0 + rr < U.rows;
+        acc[rr][0] = (ok0 && rowok) ? ld_stream2(tp + (size_t)rr * U.ld) : make_double2(0.0, 0.0);
+        acc[rr][1] = (ok1 && rowok) ? ld_stream2(tp + (size_t)rr * U.ld + 64) : make_double2(0.0, 0.0);
+    }
+}
+
+// the chain of kc steps on one thread's 16 x 4 elements, then the store
+__device__ __forceinline__ void fl_apply_tile(const FlushParams &U, const FlTile &t, int wr, int jc, int kc, const double *fw,
+                                              const double *pw, double2 (&acc)[FL_TR][2]) {
+    int s = 0;
+    for (; s + 1 < kc; s += 2) {
+        double2 p[2][2];                                  // [step][column pair]
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+            for (int q = 0; q < 2; ++q) p[e][q] = *reinterpret_cast<const double2 *>(pw + (size_t)(s + e) * FL_COLS + 64 * q);
+#pragma unroll
+        for (int rg = 0; rg < FL_TR; rg += FL_RG) {
+            double2 f[FL_RG];                         // multipliers of steps s, s+1 for FL_RG rows (broadcast loads)
+#pragma unroll
+            for (int u = 0; u < FL_RG; ++u) f[u] = *reinterpret_cast<const double2 *>(fw + (size_t)(rg + u) * BLK_KMAX + s);
+#pragma unroll
+            for (int u = 0; u < FL_RG; ++u)
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    acc[rg + u][q].x = __fma_rn(-f[u].x, p[0][q].x, acc[rg + u][q].x);
+                    acc[rg + u][q].y = __fma_rn(-f[u].x, p[0][q].y, acc[rg + u][q].y);
+                }
+#pragma unroll
+            for (int u = 0; u < FL_RG; ++u)
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    acc[rg + u][q].x = __fma_rn(-f[u].y, p[1][q].x, acc[rg + u][q].x);
+                    acc[rg + u][q].y = __fma_rn(-f[u].y, p[1][q].y, acc[rg + u][q].y);
+                }
+            asm volatile("" ::: "memory");            // keeps the next group's loads from being hoisted (register budget)
+        }
+    }
+    if (s < kc) {                                  // odd number of steps: the last one alone
+        double2 p[2];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) p[q] = *reinterpret_cast<const double2 *>(pw + (size_t)s * FL_COLS + 64 * q);
+#pragma unroll
+        for (int rr = 0; rr < FL_TR; ++rr) {
+            const double f = fw[(size_t)rr * BLK_KMAX + s];
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                acc[rr][q].x = __fma_rn(-f, p[q].x, acc[rr][q].x);
+                acc[rr][q].y = __fma_rn(-f, p[q].y, acc[rr][q].y);
+            }
+        }
+    }
+    const int i0 = t.rt * FL_ROWS + FL_TR * wr;
+    double *tp = U.T + (size_t)i0 * U.ld + t.j0 + jc;
+    const bool ok0 = jc < t.ncols, ok1 = jc + 64 < t.ncols;
+#pragma unroll
+    for (int rr = 0; rr < FL_TR; ++rr) {
+        const bool rowok = i0 + rr < U.rows;
+        if (ok0 && rowok) st_stream2(tp + (size_t)rr * U.ld, acc[rr][0]);
+        if (ok1 && rowok) st_stream2(tp + (size_t)rr * U.ld + 64, acc[rr][1]);
+    }
+}
+
+// Three CTAs of four warps per SM (170 registers each: 64 accumulators, 32 operands, no spills): while one
+// CTA waits for its tile of the tableau, the others keep the FP64 pipe busy.
+__global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U) {
     extern __shared__ __align__(128) unsigned char fl_smem[];
     double *sP = reinterpret_cast<double *>(fl_smem);                                 // [BLK_KMAX][FL_COLS]
     double *sF = sP + (size_t)BLK_KMAX * FL_COLS;                                     // [2][FL_ROWS][BLK_KMAX]
@@ -269,8 +347,8 @@ __global__ void __launch_bounds__(FL_THREADS, 2) blk_flush_kernel(FlushParams U)
     const int nsb = (nrt + FL_RB - 1) / FL_RB;                         // row super-blocks
     const long ntasks = (long)nct * nsb;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int wr = warp >> 2, wc = warp & 3;
-    const int jc = 64 * wc + 2 * lane;                                 // this thread's column pair inside the tile
+    const int wr = warp;                                               // 4 warps stacked over 64 rows x 128 columns
+    const int jc = 2 * lane;                                           // this thread's first column pair inside the tile
     constexpr uint32_t FBYTES = (uint32_t)(FL_ROWS * BLK_KMAX * 8);
 
     if (threadIdx.x == 0) s_task[0] = (long)atomicAdd(ctr, 1);
@@ -279,26 +357,22 @@ __global__ void __launch_bounds__(FL_THREADS, 2) blk_flush_kernel(FlushParams U)
     for (int it = 0;; ++it) {
         const long tt = s_task[it & 1];
         if (tt >= ntasks) break;
-        const int ct = (int)(tt % nct), sb = (int)(tt / nct);
-        const size_t j0 = (size_t)ct * FL_COLS;
-        const int ncols = (int)min((size_t)FL_COLS, U.ld - j0);        // a multiple of 16 (ld % 16 == 0)
-        const int rt0 = sb * FL_RB, rt1 = min(rt0 + FL_RB, nrt);
+        FlTile t;
+        t.j0 = (size_t)(tt % nct) * FL_COLS;
+        t.ncols = (int)min((size_t)FL_COLS, U.ld - t.j0);              // a multiple of 16 (ld % 16 == 0)
+        const int rt0 = (int)(tt / nct) * FL_RB, rt1 = min(rt0 + FL_RB, nrt);
         if (threadIdx.x == 0) {
             s_task[(it & 1) ^ 1] = (long)atomicAdd(ctr, 1);            // next task; visible after the barriers below
-            mbar_arrive_expect_tx(&bar_p, (uint32_t)(kc * ncols * 8));
-            for (int s = 0; s < kc; ++s) tma_load_1d(sP + (size_t)s * FL_COLS, U.Pm + (size_t)s * U.ld + j0, (uint32_t)(ncols * 8), &bar_p);
+            mbar_arrive_expect_tx(&bar_p, (uint32_t)(kc * t.ncols * 8));
+            for (int s = 0; s < kc; ++s) tma_load_1d(sP + (size_t)s * FL_COLS, U.Pm + (size_t)s * U.ld + t.j0, (uint32_t)(t.ncols * 8), &bar_p);
             mbar_arrive_expect_tx(&bar_f[0], FBYTES);
             tma_load_1d(sF, U.Ft + (size_t)rt0 * FL_ROWS * BLK_KMAX, FBYTES, &bar_f[0]);
         }
-        const bool colok = jc < ncols;
         for (int rt = rt0; rt < rt1; ++rt) {
             const int fb = (rt - rt0) & 1;
-            const int i0 = rt * FL_ROWS + FL_TR * wr;
-            double2 acc[FL_TR];
-            double *tp = U.T + (size_t)i0 * U.ld + j0 + jc;
-#pragma unroll
-            for (int rr = 0; rr < FL_TR; ++rr)
-                acc[rr] = (colok && i0 + rr < U.rows) ? ld_stream2(tp + (size_t)rr * U.ld) : make_double2(0.0, 0.0);
+            t.rt = rt;
+            double2 acc[FL_TR][2];
+            fl_load_tile(U, t, wr, jc, acc);
             if (threadIdx.x == 0 && rt + 1 < rt1) {      // the other F buffer was released by the barrier that ended tile rt-1
                 mbar_arrive_expect_tx(&bar_f[fb ^ 1], FBYTES);
                 tma_load_1d(sF + (size_t)(fb ^ 1) * FL_ROWS * BLK_KMAX, U.Ft + (size_t)(rt + 1) * FL_ROWS * BLK_KMAX, FBYTES, &bar_f[fb ^ 1]);
@@ -306,42 +380,7 @@ __global__ void __launch_bounds__(FL_THREADS, 2) blk_flush_kernel(FlushParams U)
             if (rt == rt0) { mbar_wait(&bar_p, par_p); par_p ^= 1; }
             mbar_wait(&bar_f[fb], (par_f >> fb) & 1u);
             par_f ^= 1u << fb;
-            const double *fw = sF + (size_t)fb * FL_ROWS * BLK_KMAX + (size_t)(FL_TR * wr) * BLK_KMAX;
-            const double *pw = sP + jc;
-            int s = 0;
-            for (; s + 1 < kc; s += 2) {
-                const double2 p0 = *reinterpret_cast<const double2 *>(pw + (size_t)s * FL_COLS);
-                const double2 p1 = *reinterpret_cast<const double2 *>(pw + (size_t)(s + 1) * FL_COLS);
-#pragma unroll
-                for (int rg = 0; rg < FL_TR; rg += FL_RG) {
-                    double2 f[FL_RG];                         // multipliers of steps s, s+1 for FL_RG rows (broadcast loads)
-#pragma unroll
-                    for (int u = 0; u < FL_RG; ++u) f[u] = *reinterpret_cast<const double2 *>(fw + (size_t)(rg + u) * BLK_KMAX + s);
-#pragma unroll
-                    for (int u = 0; u < FL_RG; ++u) {
-                        acc[rg + u].x = __fma_rn(-f[u].x, p0.x, acc[rg + u].x);
-                        acc[rg + u].y = __fma_rn(-f[u].x, p0.y, acc[rg + u].y);
-                    }
-#pragma unroll
-                    for (int u = 0; u < FL_RG; ++u) {
-                        acc[rg + u].x = __fma_rn(-f[u].y, p1.x, acc[rg + u].x);
-                        acc[rg + u].y = __fma_rn(-f[u].y, p1.y, acc[rg + u].y);
-                    }
-                    asm volatile("" ::: "memory");            // keeps the next group's loads from being hoisted (register budget)
-                }
-            }
-            if (s < kc) {                                  // odd number of steps: the last one alone
-                const double2 p0 = *reinterpret_cast<const double2 *>(pw + (size_t)s * FL_COLS);
-#pragma unroll
-                for (int rr = 0; rr < FL_TR; ++rr) {
-                    const double f = fw[(size_t)rr * BLK_KMAX + s];
-                    acc[rr].x = __fma_rn(-f, p0.x, acc[rr].x);
-                    acc[rr].y = __fma_rn(-f, p0.y, acc[rr].y);
-                }
-            }
-#pragma unroll
-            for (int rr = 0; rr < FL_TR; ++rr)
-                if (colok && i0 + rr < U.rows) st_stream2(tp + (size_t)rr * U.ld, acc[rr]);
+            fl_apply_tile(U, t, wr, jc, kc, sF + (size_t)fb * FL_ROWS * BLK_KMAX + (size_t)(FL_TR * wr) * BLK_KMAX, sP + jc, acc);
             __syncthreads();       // sF[fb] may be refilled (two tiles ahead), and at the last tile sP and s_task
         }
     }

@@ -264,6 +264,13 @@ __device__ __forceinline__ void fl_load_tile(const FlushParams &U, const FlTile 
     }
 }
 
+// HBM -> L2 prefetch of a tile (no registers involved): thread i < FL_ROWS asks for row i's segment.
+__device__ __forceinline__ void fl_prefetch_tile(const FlushParams &U, const FlTile &t) {
+    const int i = t.rt * FL_ROWS + (int)threadIdx.x;
+    if ((int)threadIdx.x < FL_ROWS && i < U.rows)
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(U.T + (size_t)i * U.ld + t.j0), "r"(t.ncols * 8) : "memory");
+}
+
 // the chain of kc steps on one thread's 16 x 4 elements, then the store
 __device__ __forceinline__ void fl_apply_tile(const FlushParams &U, const FlTile &t, int wr, int jc, int kc, const double *fw,
                                               const double *pw, double2 (&acc)[FL_TR][2]) {
@@ -376,6 +383,23 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
             if (threadIdx.x == 0 && rt + 1 < rt1) {      // the other F buffer was released by the barrier that ended tile rt-1
                 mbar_arrive_expect_tx(&bar_f[fb ^ 1], FBYTES);
                 tma_load_1d(sF + (size_t)(fb ^ 1) * FL_ROWS * BLK_KMAX, U.Ft + (size_t)(rt + 1) * FL_ROWS * BLK_KMAX, FBYTES, &bar_f[fb ^ 1]);
+            }
+            // the tile after this one starts its way from HBM into L2 now, so that DRAM keeps streaming while this
+            // CTA (and its neighbours on the SM) are busy on the FP64 pipe
+            {
+                FlTile nx = t;
+                bool have = true;
+                if (rt + 1 < rt1) nx.rt = rt + 1;
+                else {
+                    const long nt = s_task[(it & 1) ^ 1];       // claimed at the start of this task; visible since tile rt0's barrier
+                    have = (rt > rt0) && nt < ntasks;
+                    if (have) {
+                        nx.j0 = (size_t)(nt % nct) * FL_COLS;
+                        nx.ncols = (int)min((size_t)FL_COLS, U.ld - nx.j0);
+                        nx.rt = (int)(nt / nct) * FL_RB;
+                    }
+                }
+                if (have) fl_prefetch_tile(U, nx);
             }
             if (rt == rt0) { mbar_wait(&bar_p, par_p); par_p ^= 1; }
             mbar_wait(&bar_f[fb], (par_f >> fb) & 1u);

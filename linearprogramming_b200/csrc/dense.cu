@@ -4,6 +4,8 @@
 // (Source/simplex.c:40-67): the pivot loop runs device-resident; the host only enqueues
 // (select, eliminate) pairs and reads one small state record every `check_every` pivots.
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <new>
 #include <vector>
 
@@ -233,9 +235,10 @@ bool use_blocked(const lpgpu_dense *d) {
 
 static BlockBufs make_bufs(const lpgpu_dense *d) {
     BlockBufs B;
-    B.Ft = d->Ft; B.Pm = d->Pm; B.objcur = d->objcur; B.bcur = d->bcur; B.rowstamp = d->rowstamp; B.steprow = d->steprow;
+    B.Fs = d->Ft; B.cands = d->cands; B.Pm = d->Pm; B.objcur = d->objcur; B.bcur = d->bcur; B.rowstamp = d->rowstamp; B.steprow = d->steprow;
     const int k = (d->opts.variant >> 16) & 0x3f;
     B.K = (k >= 1 && k <= BLK_KMAX) ? k : BLK_KMAX;
+    B.dbg = d->blk_dbg ? d->blk_dbg + 8 * (size_t)(d->blk_dbg_n % 4096) : nullptr;
     return B;
 }
 
@@ -252,6 +255,7 @@ static int launch_block_step(lpgpu_dense *d, int first) {
     const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels;
     LP_CUDA(ctx, launch_pdl(pdl, blk_step_kernel, dim3(SELECT_CLUSTER), dim3(SELECT_THREADS), ctx->stream, make_params(d),
                             make_bufs(d), first));
+    if (d->blk_dbg) d->blk_dbg_n++;
     ctx->launches++;
     return LPGPU_OK;
 }
@@ -259,7 +263,7 @@ static int launch_block_step(lpgpu_dense *d, int first) {
 static int launch_block_flush(lpgpu_dense *d) {
     lpgpu_ctx *ctx = d->ctx;
     FlushParams U;
-    U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.Ft = d->Ft; U.Pm = d->Pm; U.rowstamp = d->rowstamp; U.steprow = d->steprow; U.st = d->st;
+    U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.Fs = d->Ft; U.pcn = d->pcn; U.Pm = d->Pm; U.rowstamp = d->rowstamp; U.steprow = d->steprow; U.st = d->st;
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
     blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, ctx->stream>>>(U);
     LP_LAUNCH_CHECK(ctx);
@@ -324,7 +328,7 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     d->ld = round_up((size_t)n + 1, 16);
     d->T = nullptr; d->basis = nullptr; d->prow = d->pcol = d->bnext = d->xbuf = nullptr; d->la_dirty = true; d->st = nullptr; d->h_st = nullptr;
     d->log = nullptr; d->log_cap = 0; d->task_ctr = nullptr; d->upd_seq = 0;
-    d->Ft = d->Pm = d->objcur = d->bcur = nullptr; d->rowstamp = d->steprow = nullptr; d->blk_open = false; d->blk_steps = 0;
+    d->Ft = d->Pm = d->objcur = d->bcur = nullptr; d->rowstamp = d->steprow = nullptr; d->cands = nullptr; d->blk_open = false; d->blk_steps = 0;
     lpgpu_default_opts(&d->opts);
     d->opts.method = (R == 1) ? LPGPU_PLAIN : LPGPU_BIGM;
     const size_t rows = (size_t)m + R, pcn = round_up(rows, UPD_TILE_ROWS) + UPD_TILE_ROWS;
@@ -345,6 +349,13 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     if (e == cudaSuccess) e = cudaMalloc(&d->bcur, pcn * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&d->rowstamp, pcn * sizeof(int));
     if (e == cudaSuccess) e = cudaMalloc(&d->steprow, BLK_KMAX * sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc(&d->cands, SELECT_CLUSTER * sizeof(Cand));
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->cands, 0xff, SELECT_CLUSTER * sizeof(Cand), ctx->stream);
+    d->blk_dbg = nullptr; d->blk_dbg_n = 0;
+    if (e == cudaSuccess && getenv("LPGPU_BLK_DEBUG")) {
+        e = cudaMalloc(&d->blk_dbg, 4096 * 8 * sizeof(unsigned long long));
+        if (e == cudaSuccess) e = cudaMemsetAsync(d->blk_dbg, 0, 4096 * 8 * sizeof(unsigned long long), ctx->stream);
+    }
     if (e == cudaSuccess) e = cudaMemsetAsync(d->steprow, 0, BLK_KMAX * sizeof(int), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->Ft, 0, pcn * BLK_KMAX * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->Pm, 0, (size_t)BLK_KMAX * d->ld * sizeof(double), ctx->stream);
@@ -373,9 +384,26 @@ void lpgpu_dense_destroy(lpgpu_dense *d) {
     cudaSetDevice(d->ctx->device);
     cudaStreamSynchronize(d->ctx->stream);
     for (cudaEvent_t e : d->ev) cudaEventDestroy(e);
+    if (d->blk_dbg) {       // development aid: mean time between the step kernel's phase stamps
+        std::vector<unsigned long long> h(4096 * 8);
+        cudaMemcpy(h.data(), d->blk_dbg, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+        const long n = std::min<long>(d->blk_dbg_n, 4096);
+        double acc[8] = {0}, gap = 0;
+        long cnt = 0, gcnt = 0;
+        for (long i = 0; i < n; ++i) {
+            const unsigned long long *s = &h[8 * i];
+            if (!s[6] || !s[0]) continue;
+            for (int q = 1; q <= 6; ++q) acc[q] += (double)(s[q] - s[q - 1]);
+            if (i + 1 < n && h[8 * (i + 1)]) { gap += (double)(h[8 * (i + 1)] - s[6]); ++gcnt; }
+            ++cnt;
+        }
+        if (cnt) fprintf(stderr, "[lpgpu blk debug] %ld steps: pdl_wait %.2f | column+ratio loop %.2f | best %.2f | row+price loop %.2f | best %.2f | b+state %.2f | gap to next start %.2f us\n",
+                         cnt, acc[1] / cnt / 1e3, acc[2] / cnt / 1e3, acc[3] / cnt / 1e3, acc[4] / cnt / 1e3, acc[5] / cnt / 1e3, acc[6] / cnt / 1e3, gcnt ? gap / gcnt / 1e3 : 0.0);
+        cudaFree(d->blk_dbg);
+    }
     cudaFree(d->T); cudaFree(d->basis); cudaFree(d->prow); cudaFree(d->pcol); cudaFree(d->bnext); cudaFree(d->xbuf);
     cudaFree(d->st); cudaFree(d->log); cudaFree(d->task_ctr);
-    cudaFree(d->Ft); cudaFree(d->Pm); cudaFree(d->objcur); cudaFree(d->bcur); cudaFree(d->rowstamp); cudaFree(d->steprow);
+    cudaFree(d->Ft); cudaFree(d->Pm); cudaFree(d->objcur); cudaFree(d->bcur); cudaFree(d->rowstamp); cudaFree(d->steprow); cudaFree(d->cands);
     if (d->h_st) cudaFreeHost(d->h_st);
     delete d;
 }

@@ -28,13 +28,15 @@ namespace lpgpu {
 constexpr int BLK_KMAX = 32;           // pivots per block at most (shared-memory tile of the pass)
 
 struct BlockBufs {
-    double *Ft;          // pcn x BLK_KMAX, row-major per tableau row: Ft[i*KMAX + s] = a_{i,k_s} before step s
+    double *Fs;          // BLK_KMAX x pcn: Fs[s*pcn + i] = a_{i,k_s} before step s (the multiplier of row i at step s)
+    Cand *cands;         // SELECT_CLUSTER: per-CTA pricing candidates for the next pivot (st->k_next == -2)
     double *Pm;          // BLK_KMAX x ld: Pm[s*ld + j] = scaled pivot row of step s (col 0 = b_r')
     double *objcur;      // R x ld: objective rows as of the last decided pivot (row m first)
     double *bcur;        // pcn: b column as of the last decided pivot (rows < m)
     int *rowstamp;       // pcn: (block sequence << 8) | (s + 1) if the row was the pivot row of step s of that block
     int *steprow;        // BLK_KMAX: pivot row of step s of the current block
     int K;               // pivots per block, 1..BLK_KMAX
+    unsigned long long *dbg;   // LPGPU_BLK_DEBUG=1: 8 globaltimer stamps per launch slot (development aid), else nullptr
 };
 
 // objcur / bcur <- tableau (after an upload, a synth, a forced pivot or a run of the rank-1 path)
@@ -64,83 +66,113 @@ __device__ __forceinline__ void blk_price(const DenseParams &P, bool bigm, int j
 
 // One pivot of a block: decision + lazy slices + eager objective rows / b column (PLAIN and BIGM).
 // first != 0: the tableau was flushed (or initialised) since the last step: a new block starts.
+// The kernel is a chain of dependent memory round trips (~1 us each), so every phase first issues ALL
+// the loads it can (tableau column / row, stamps, b, objective row) and only then waits; the second
+// cluster-wide reduction (next pivot's pricing) is left to the next launch: each CTA leaves its best
+// candidate in `cands` (st->k_next = -2) and the next step reduces the 8 of them on entry.
+constexpr int STEP_PB = 4;             // earlier pivot rows per batch of loads in the row phase (64 registers per thread)
+constexpr int STEP_CPT = 3;            // columns per thread in flight in the row phase (covers ld <= 3 * 8192 in one go)
+
 __global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
 blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     __shared__ Cand scratch[SELECT_THREADS / 32];
-    __shared__ Cand slot_a[SELECT_CLUSTER], slot_b[SELECT_CLUSTER], slot_c[SELECT_CLUSTER], slot_d[SELECT_CLUSTER];
+    __shared__ Cand slot_a[SELECT_CLUSTER], slot_b[SELECT_CLUSTER], slot_d[SELECT_CLUSTER];
     __shared__ double s_pk[BLK_KMAX], s_fr[BLK_KMAX];
     cg::cluster_group cl = cg::this_cluster();
     const int rank = (int)cl.block_rank();
     const int gtid = rank * SELECT_THREADS + (int)threadIdx.x;
     constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
 
+    auto stamp = [&](int slot) {
+        if (B.dbg && gtid == 0) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            B.dbg[slot] = now;
+        }
+    };
+    stamp(0);
     pdl_wait();
     pdl_launch_dependents();
+    stamp(1);
     PivotState *st = P.st;
     // every thread of the cluster reads the same state; it is rewritten only after a cluster barrier
     const int status0 = st->status, iters = st->iters, budget = st->budget;
     const int t = first ? 0 : st->blk_t, seq = st->blk_seq + (first ? 1 : 0);
-    int k = st->k_next;
+    const int kn = st->k_next;
     const bool bigm = (P.method == LPGPU_BIGM);
-    const int rows = P.m + P.R;
     const double *oc = B.objcur, *om = B.objcur + P.ld;          // om valid for R == 2 only
+    const size_t pcn = P.pcn;
 
-    int status = status0;
+    int status = status0, k = 0, r = -1;
     bool have = false;
-    int r = -1;
+    double brp = 0.0, sig_c = 0.0, sig_m = 0.0;
     if (status0 == LPGPU_RUNNING) {
-        // ---- entering column, unless it was priced at the end of the previous step
-        if (k <= 0) {
+        // ---- entering column: priced by the previous step (one candidate per CTA), or from scratch
+        if (kn > 0) k = kn;
+        else if (kn == -2) {
+            const int lane = threadIdx.x & 31;
+            Cand c = cand_none();
+            if (lane < SELECT_CLUSTER) {
+                c.p = __ldcg(&B.cands[lane].p); c.q = __ldcg(&B.cands[lane].q); c.idx = __ldcg(&B.cands[lane].idx);
+            }
+            c = warp_best(c);
+            k = c.idx > 0 ? c.idx : 0;
+        } else {
             Cand c = cand_none();
             for (int j = 1 + gtid; j <= P.n; j += GSTRIDE) blk_price(P, bigm, j, oc[j], bigm ? om[j] : 0.0, c);
             c = cluster_best(cl, c, scratch, slot_a);
             k = c.idx > 0 ? c.idx : 0;
-            if (k == 0) {
-                // optimal, unless Big-M left an artificial basic at a positive level
-                Cand a = cand_none();
-                if (bigm) {
-                    const int nreal = P.n - P.n_art;
-                    for (int i = gtid; i < P.m; i += GSTRIDE)
-                        if (P.basis[i] > nreal && B.bcur[i] > P.eps) { a.p = 0.0; a.q = 0.0; a.idx = i; break; }
-                }
-                a = cluster_best(cl, a, scratch, slot_d);
-                status = (a.idx >= 0) ? LPGPU_INFEASIBLE : LPGPU_OPTIMAL;
-            }
         }
-        if (status == LPGPU_RUNNING) {
+        if (k == 0) {
+            // optimal, unless Big-M left an artificial basic at a positive level
+            Cand a = cand_none();
+            if (bigm) {
+                const int nreal = P.n - P.n_art;
+                for (int i = gtid; i < P.m; i += GSTRIDE)
+                    if (P.basis[i] > nreal && B.bcur[i] > P.eps) { a.p = 0.0; a.q = 0.0; a.idx = i; break; }
+            }
+            a = cluster_best(cl, a, scratch, slot_d);
+            status = (a.idx >= 0) ? LPGPU_INFEASIBLE : LPGPU_OPTIMAL;
+        } else {
             // ---- column k as it stands after the t pivots of this block, and the ratio test on it
+            sig_c = oc[k];                                        // read before the row phase rewrites objcur
+            sig_m = (P.R == 2) ? om[k] : 0.0;
+            if (gtid < P.R) B.Fs[(size_t)t * pcn + P.m + gtid] = oc[(size_t)gtid * P.ld + k];   // objective rows: kept eagerly, same bits
+            // first row of this thread: everything it needs is requested before anyone waits
+            int i = gtid;
+            double tv = 0.0, bv = 0.0;
+            int rs = 0;
+            if (i < P.m) { tv = P.T[(size_t)i * P.ld + (size_t)k]; rs = B.rowstamp[i]; bv = B.bcur[i]; }
             if ((int)threadIdx.x < t) s_pk[threadIdx.x] = B.Pm[(size_t)threadIdx.x * P.ld + (size_t)k];
             __syncthreads();
             Cand c = cand_none();
-            for (int i = gtid; i < rows; i += GSTRIDE) {
-                const int s0 = blk_row_start(B.rowstamp[i], seq);
-                double a = s0 ? s_pk[s0 - 1] : P.T[(size_t)i * P.ld + (size_t)k];
-                // the row's multipliers of the earlier steps: 128-bit loads, all in flight before the chain starts
-                const double2 *fi2 = reinterpret_cast<const double2 *>(B.Ft + (size_t)i * BLK_KMAX);
-                for (int sb = s0 & ~7; sb < t; sb += 8) {
-                    double2 f2[4];
+            for (; i < P.m; i += GSTRIDE) {
+                if (i != gtid) { tv = P.T[(size_t)i * P.ld + (size_t)k]; rs = B.rowstamp[i]; bv = B.bcur[i]; }
+                const int s0 = blk_row_start(rs, seq);
+                double a = s0 ? s_pk[s0 - 1] : tv;
+                for (int sb = s0; sb < t; sb += 8) {              // multipliers of 8 earlier steps in flight (coalesced over rows)
+                    double fv[8];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) f2[u] = (sb + 2 * u < t) ? fi2[(sb >> 1) + u] : make_double2(0.0, 0.0);
+                    for (int u = 0; u < 8; ++u) fv[u] = (sb + u < t) ? B.Fs[(size_t)(sb + u) * pcn + i] : 0.0;
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const int s = sb + 2 * u;
-                        if (s >= s0 && s < t) a = __fma_rn(-f2[u].x, s_pk[s], a);
-                        if (s + 1 >= s0 && s + 1 < t) a = __fma_rn(-f2[u].y, s_pk[s + 1], a);
-                    }
+                    for (int u = 0; u < 8; ++u)
+                        if (sb + u < t) a = __fma_rn(-fv[u], s_pk[sb + u], a);
                 }
-                B.Ft[(size_t)i * BLK_KMAX + t] = a;
-                if (i < P.m && a > P.eps) {
+                B.Fs[(size_t)t * pcn + i] = a;
+                if (a > P.eps) {
                     Cand x;
                     x.p = 0.0;
-                    x.q = -(B.bcur[i] / a);
+                    x.q = -(bv / a);
                     x.idx = i;
                     if (cand_better(x, c)) c = x;
                 }
             }
+            stamp(2);
             c = cluster_best(cl, c, scratch, slot_b);
+            stamp(3);
             if (c.idx < 0) status = LPGPU_UNBOUNDED;
             else if (iters >= P.max_iter) status = LPGPU_ITER_LIMIT;
-            else if (budget > 0) { have = true; r = c.idx; }
+            else if (budget > 0) { have = true; r = c.idx; brp = -c.q; }    // b_r / a_rk IS the winning ratio
         }
     }
     if (!have) {
@@ -156,43 +188,79 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     }
 
     // ---- row r as it stands after the t pivots of this block, scaled; objective rows and next pricing
-    const int s0r = blk_row_start(B.rowstamp[r], seq);
-    if ((int)threadIdx.x < t) s_fr[threadIdx.x] = B.Ft[(size_t)r * BLK_KMAX + threadIdx.x];
-    __syncthreads();
-    const double piv = __ldcg(B.Ft + (size_t)r * BLK_KMAX + t);              // written above by another CTA
-    const double sig_c = __ldcg(B.Ft + (size_t)P.m * BLK_KMAX + t);
-    const double sig_m = (P.R == 2) ? __ldcg(B.Ft + (size_t)(P.m + 1) * BLK_KMAX + t) : 0.0;
-    double *pt = B.Pm + (size_t)t * P.ld;
-    const double *base = s0r ? B.Pm + (size_t)(s0r - 1) * P.ld : P.T + (size_t)r * P.ld;
-    Cand c = cand_none();
-    for (size_t j = (size_t)gtid; j < P.ld; j += GSTRIDE) {
-        double a = base[j];
-        for (int sb = s0r; sb < t; sb += 8) {            // 8 pivot rows in flight before the chain consumes them
-            double pv[8];
+    double av[STEP_CPT], ocv[STEP_CPT], omv[STEP_CPT];
+    const size_t jb = (size_t)gtid;
 #pragma unroll
-            for (int u = 0; u < 8; ++u) pv[u] = (sb + u < t) ? B.Pm[(size_t)(sb + u) * P.ld + j] : 0.0;
-#pragma unroll
-            for (int u = 0; u < 8; ++u)
-                if (sb + u < t) a = __fma_rn(-s_fr[sb + u], pv[u], a);
+    for (int cth = 0; cth < STEP_CPT; ++cth) {
+        const size_t j = jb + (size_t)cth * GSTRIDE;
+        av[cth] = ocv[cth] = omv[cth] = 0.0;
+        if (j < P.ld) {
+            av[cth] = P.T[(size_t)r * P.ld + j];
+            ocv[cth] = oc[j];
+            if (P.R == 2) omv[cth] = om[j];
         }
-        const double pr = div_skip_zero(a, piv);
-        pt[j] = pr;
-        const double qc = __fma_rn(-sig_c, pr, oc[j]);
-        B.objcur[j] = qc;
-        double qm = 0.0;
-        if (P.R == 2) {
-            qm = __fma_rn(-sig_m, pr, om[j]);
-            B.objcur[P.ld + j] = qm;
-        }
-        if (j >= 1 && j <= (size_t)P.n) blk_price(P, bigm, (int)j, qc, qm, c);
     }
-    c = cluster_best(cl, c, scratch, slot_c);
-    const int knew = c.idx > 0 ? c.idx : 0;
-
-    // ---- b column (b_r' = P[t][0] was written by thread 0 of CTA 0 before the barrier above)
-    const double brp = __ldcg(pt);
+    const int s0r = blk_row_start(B.rowstamp[r], seq);
+    const double piv = __ldcg(B.Fs + (size_t)t * pcn + r);                   // written above, possibly by another CTA
+    if ((int)threadIdx.x < t) s_fr[threadIdx.x] = B.Fs[(size_t)threadIdx.x * pcn + r];
+    __syncthreads();
+    double *pt = B.Pm + (size_t)t * P.ld;
+    Cand c = cand_none();
+    for (size_t j0 = jb; j0 < P.ld; j0 += (size_t)STEP_CPT * GSTRIDE) {
+        if (j0 != jb) {
+#pragma unroll
+            for (int cth = 0; cth < STEP_CPT; ++cth) {
+                const size_t j = j0 + (size_t)cth * GSTRIDE;
+                if (j < P.ld) { av[cth] = P.T[(size_t)r * P.ld + j]; ocv[cth] = oc[j]; if (P.R == 2) omv[cth] = om[j]; }
+            }
+        }
+        if (s0r > 0) {                            // the row was a pivot row earlier in this block: restart from its scaled row
+#pragma unroll
+            for (int cth = 0; cth < STEP_CPT; ++cth) {
+                const size_t j = j0 + (size_t)cth * GSTRIDE;
+                if (j < P.ld) av[cth] = B.Pm[(size_t)(s0r - 1) * P.ld + j];
+            }
+        }
+        for (int sb = s0r; sb < t; sb += STEP_PB) {     // STEP_PB earlier pivot rows x STEP_CPT columns in flight
+            double pv[STEP_CPT][STEP_PB];
+#pragma unroll
+            for (int cth = 0; cth < STEP_CPT; ++cth) {
+                const size_t j = j0 + (size_t)cth * GSTRIDE;
+#pragma unroll
+                for (int u = 0; u < STEP_PB; ++u) pv[cth][u] = (sb + u < t && j < P.ld) ? B.Pm[(size_t)(sb + u) * P.ld + j] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < STEP_PB; ++u)
+                if (sb + u < t) {
+#pragma unroll
+                    for (int cth = 0; cth < STEP_CPT; ++cth) av[cth] = __fma_rn(-s_fr[sb + u], pv[cth][u], av[cth]);
+                }
+        }
+#pragma unroll
+        for (int cth = 0; cth < STEP_CPT; ++cth) {
+            const size_t j = j0 + (size_t)cth * GSTRIDE;
+            if (j < P.ld) {
+                const double pr = div_skip_zero(av[cth], piv);
+                pt[j] = pr;
+                const double qc = __fma_rn(-sig_c, pr, ocv[cth]);
+                B.objcur[j] = qc;
+                double qm = 0.0;
+                if (P.R == 2) {
+                    qm = __fma_rn(-sig_m, pr, omv[cth]);
+                    B.objcur[P.ld + j] = qm;
+                }
+                if (j >= 1 && j <= (size_t)P.n) blk_price(P, bigm, (int)j, qc, qm, c);
+            }
+        }
+    }
+    // ---- b column
     for (int i = gtid; i < P.m; i += GSTRIDE)
-        B.bcur[i] = (i == r) ? brp : __fma_rn(-B.Ft[(size_t)i * BLK_KMAX + t], brp, B.bcur[i]);
+        B.bcur[i] = (i == r) ? brp : __fma_rn(-B.Fs[(size_t)t * pcn + i], brp, B.bcur[i]);
+    stamp(4);
+    // ---- this CTA's best candidate for the next pivot; the next launch reduces the SELECT_CLUSTER of them
+    c = block_best(c, scratch);
+    if (threadIdx.x == 0) B.cands[rank] = c;
+    stamp(5);
 
     if (gtid == 0) {
         P.basis[r] = k;
@@ -204,11 +272,12 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         st->k = k;
         st->iters = iters + 1;
         st->budget = budget - 1;
-        st->k_next = knew;
+        st->k_next = -2;
         st->blk_t = t + 1;
         st->blk_seq = seq;
         if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
     }
+    stamp(6);
 }
 
 // ------------------------------------------------------------------ the pass that applies a block
@@ -234,7 +303,8 @@ struct FlushParams {
     double *T;
     size_t ld;
     int rows;                 // m + R
-    const double *Ft;         // pcn x BLK_KMAX
+    const double *Fs;         // BLK_KMAX x pcn
+    size_t pcn;
     const double *Pm;         // BLK_KMAX x ld
     const int *rowstamp;
     const int *steprow;       // pivot row of step s of the current block
@@ -272,6 +342,7 @@ __device__ __forceinline__ void fl_prefetch_tile(const FlushParams &U, const FlT
 }
 
 // the chain of kc steps on one thread's 16 x 4 elements, then the store
+// fw: this warp's 16 multipliers of step 0 in the staged tile sF[s][FL_ROWS] (row pairs = one LDS.128)
 __device__ __forceinline__ void fl_apply_tile(const FlushParams &U, const FlTile &t, int wr, int jc, int kc, const double *fw,
                                               const double *pw, double2 (&acc)[FL_TR][2]) {
     int s = 0;
@@ -283,23 +354,22 @@ __device__ __forceinline__ void fl_apply_tile(const FlushParams &U, const FlTile
             for (int q = 0; q < 2; ++q) p[e][q] = *reinterpret_cast<const double2 *>(pw + (size_t)(s + e) * FL_COLS + 64 * q);
 #pragma unroll
         for (int rg = 0; rg < FL_TR; rg += FL_RG) {
-            double2 f[FL_RG];                         // multipliers of steps s, s+1 for FL_RG rows (broadcast loads)
+            double2 f[2][FL_RG / 2];                  // [step][row pair]: multipliers of FL_RG rows (broadcast loads)
 #pragma unroll
-            for (int u = 0; u < FL_RG; ++u) f[u] = *reinterpret_cast<const double2 *>(fw + (size_t)(rg + u) * BLK_KMAX + s);
+            for (int e = 0; e < 2; ++e)
 #pragma unroll
-            for (int u = 0; u < FL_RG; ++u)
+                for (int u = 0; u < FL_RG / 2; ++u) f[e][u] = *reinterpret_cast<const double2 *>(fw + (size_t)(s + e) * FL_ROWS + rg + 2 * u);
 #pragma unroll
-                for (int q = 0; q < 2; ++q) {
-                    acc[rg + u][q].x = __fma_rn(-f[u].x, p[0][q].x, acc[rg + u][q].x);
-                    acc[rg + u][q].y = __fma_rn(-f[u].x, p[0][q].y, acc[rg + u][q].y);
-                }
+            for (int e = 0; e < 2; ++e)
 #pragma unroll
-            for (int u = 0; u < FL_RG; ++u)
+                for (int u = 0; u < FL_RG / 2; ++u)
 #pragma unroll
-                for (int q = 0; q < 2; ++q) {
-                    acc[rg + u][q].x = __fma_rn(-f[u].y, p[1][q].x, acc[rg + u][q].x);
-                    acc[rg + u][q].y = __fma_rn(-f[u].y, p[1][q].y, acc[rg + u][q].y);
-                }
+                    for (int q = 0; q < 2; ++q) {
+                        acc[rg + 2 * u][q].x = __fma_rn(-f[e][u].x, p[e][q].x, acc[rg + 2 * u][q].x);
+                        acc[rg + 2 * u][q].y = __fma_rn(-f[e][u].x, p[e][q].y, acc[rg + 2 * u][q].y);
+                        acc[rg + 2 * u + 1][q].x = __fma_rn(-f[e][u].y, p[e][q].x, acc[rg + 2 * u + 1][q].x);
+                        acc[rg + 2 * u + 1][q].y = __fma_rn(-f[e][u].y, p[e][q].y, acc[rg + 2 * u + 1][q].y);
+                    }
             asm volatile("" ::: "memory");            // keeps the next group's loads from being hoisted (register budget)
         }
     }
@@ -309,7 +379,7 @@ __device__ __forceinline__ void fl_apply_tile(const FlushParams &U, const FlTile
         for (int q = 0; q < 2; ++q) p[q] = *reinterpret_cast<const double2 *>(pw + (size_t)s * FL_COLS + 64 * q);
 #pragma unroll
         for (int rr = 0; rr < FL_TR; ++rr) {
-            const double f = fw[(size_t)rr * BLK_KMAX + s];
+            const double f = fw[(size_t)s * FL_ROWS + rr];
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
                 acc[rr][q].x = __fma_rn(-f, p[q].x, acc[rr][q].x);
@@ -333,7 +403,7 @@ __device__ __forceinline__ void fl_apply_tile(const FlushParams &U, const FlTile
 __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U) {
     extern __shared__ __align__(128) unsigned char fl_smem[];
     double *sP = reinterpret_cast<double *>(fl_smem);                                 // [BLK_KMAX][FL_COLS]
-    double *sF = sP + (size_t)BLK_KMAX * FL_COLS;                                     // [2][FL_ROWS][BLK_KMAX]
+    double *sF = sP + (size_t)BLK_KMAX * FL_COLS;                                     // [2][BLK_KMAX][FL_ROWS]
     __shared__ __align__(8) uint64_t bar_p, bar_f[2];
     __shared__ long s_task[2];
 
@@ -356,7 +426,12 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int wr = warp;                                               // 4 warps stacked over 64 rows x 128 columns
     const int jc = 2 * lane;                                           // this thread's first column pair inside the tile
-    constexpr uint32_t FBYTES = (uint32_t)(FL_ROWS * BLK_KMAX * 8);
+    const uint32_t FBYTES = (uint32_t)(kc * FL_ROWS * 8);
+    auto issue_f = [&](int rt, int fb) {           // thread 0: kc x (FL_ROWS multipliers) of one row tile
+        mbar_arrive_expect_tx(&bar_f[fb], FBYTES);
+        for (int s = 0; s < kc; ++s)
+            tma_load_1d(sF + ((size_t)fb * BLK_KMAX + s) * FL_ROWS, U.Fs + (size_t)s * U.pcn + (size_t)rt * FL_ROWS, (uint32_t)(FL_ROWS * 8), &bar_f[fb]);
+    };
 
     if (threadIdx.x == 0) s_task[0] = (long)atomicAdd(ctr, 1);
     __syncthreads();
@@ -372,18 +447,14 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
             s_task[(it & 1) ^ 1] = (long)atomicAdd(ctr, 1);            // next task; visible after the barriers below
             mbar_arrive_expect_tx(&bar_p, (uint32_t)(kc * t.ncols * 8));
             for (int s = 0; s < kc; ++s) tma_load_1d(sP + (size_t)s * FL_COLS, U.Pm + (size_t)s * U.ld + t.j0, (uint32_t)(t.ncols * 8), &bar_p);
-            mbar_arrive_expect_tx(&bar_f[0], FBYTES);
-            tma_load_1d(sF, U.Ft + (size_t)rt0 * FL_ROWS * BLK_KMAX, FBYTES, &bar_f[0]);
+            issue_f(rt0, 0);
         }
         for (int rt = rt0; rt < rt1; ++rt) {
             const int fb = (rt - rt0) & 1;
             t.rt = rt;
             double2 acc[FL_TR][2];
             fl_load_tile(U, t, wr, jc, acc);
-            if (threadIdx.x == 0 && rt + 1 < rt1) {      // the other F buffer was released by the barrier that ended tile rt-1
-                mbar_arrive_expect_tx(&bar_f[fb ^ 1], FBYTES);
-                tma_load_1d(sF + (size_t)(fb ^ 1) * FL_ROWS * BLK_KMAX, U.Ft + (size_t)(rt + 1) * FL_ROWS * BLK_KMAX, FBYTES, &bar_f[fb ^ 1]);
-            }
+            if (threadIdx.x == 0 && rt + 1 < rt1) issue_f(rt + 1, fb ^ 1);   // that F buffer was released by the barrier that ended tile rt-1
             // the tile after this one starts its way from HBM into L2 now, so that DRAM keeps streaming while this
             // CTA (and its neighbours on the SM) are busy on the FP64 pipe
             {
@@ -404,7 +475,7 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
             if (rt == rt0) { mbar_wait(&bar_p, par_p); par_p ^= 1; }
             mbar_wait(&bar_f[fb], (par_f >> fb) & 1u);
             par_f ^= 1u << fb;
-            fl_apply_tile(U, t, wr, jc, kc, sF + (size_t)fb * FL_ROWS * BLK_KMAX + (size_t)(FL_TR * wr) * BLK_KMAX, sP + jc, acc);
+            fl_apply_tile(U, t, wr, jc, kc, sF + (size_t)fb * BLK_KMAX * FL_ROWS + FL_TR * wr, sP + jc, acc);
             __syncthreads();       // sF[fb] may be refilled (two tiles ahead), and at the last tile sP and s_task
         }
     }
@@ -418,7 +489,7 @@ __global__ void __launch_bounds__(256) blk_fixrows_kernel(FlushParams U) {
     const int r = U.steprow[s0];
     if (blk_row_start(U.rowstamp[r], bseq) != s0 + 1) return;      // the row was a pivot row again later in the block
     __shared__ double s_f[BLK_KMAX];
-    if ((int)threadIdx.x < kc) s_f[threadIdx.x] = U.Ft[(size_t)r * BLK_KMAX + threadIdx.x];
+    if ((int)threadIdx.x < kc) s_f[threadIdx.x] = U.Fs[(size_t)threadIdx.x * U.pcn + r];
     __syncthreads();
     for (size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x; j < U.ld; j += (size_t)gridDim.x * blockDim.x) {
         double a = U.Pm[(size_t)s0 * U.ld + j];

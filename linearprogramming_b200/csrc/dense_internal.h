@@ -27,8 +27,11 @@ struct lpgpu_dense {
     unsigned upd_seq;       // elimination launches so far
     std::vector<cudaEvent_t> ev;
     // blocked path (dense_block.cuh): lazy slices of the pivots not yet applied to T
-    double *Ft, *Pm, *objcur, *bcur;
+    double *Ft, *Pm, *objcur, *bcur;   // Ft: BLK_KMAX x pcn multipliers, Pm: BLK_KMAX x ld scaled pivot rows
     int *rowstamp, *steprow;
+    lpgpu::Cand *cands;     // per-CTA pricing candidates handed from one step launch to the next
+    unsigned long long *blk_dbg;   // LPGPU_BLK_DEBUG: phase stamps of the step kernel
+    long blk_dbg_n;
     bool blk_open;          // step kernels were enqueued since the last flush
     int blk_steps;          // ... how many
 };

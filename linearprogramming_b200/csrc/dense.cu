@@ -349,8 +349,8 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     if (e == cudaSuccess) e = cudaMalloc(&d->bcur, pcn * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&d->rowstamp, pcn * sizeof(int));
     if (e == cudaSuccess) e = cudaMalloc(&d->steprow, BLK_KMAX * sizeof(int));
-    if (e == cudaSuccess) e = cudaMalloc(&d->cands, SELECT_CLUSTER * sizeof(Cand));
-    if (e == cudaSuccess) e = cudaMemsetAsync(d->cands, 0xff, SELECT_CLUSTER * sizeof(Cand), ctx->stream);
+    if (e == cudaSuccess) e = cudaMalloc(&d->cands, SELECT_CLUSTER * sizeof(KeyCand));
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->cands, 0xff, SELECT_CLUSTER * sizeof(KeyCand), ctx->stream);
     d->blk_dbg = nullptr; d->blk_dbg_n = 0;
     if (e == cudaSuccess && getenv("LPGPU_BLK_DEBUG")) {
         e = cudaMalloc(&d->blk_dbg, 4096 * 8 * sizeof(unsigned long long));

@@ -27,9 +27,11 @@ namespace lpgpu {
 
 constexpr int BLK_KMAX = 32;           // pivots per block at most (shared-memory tile of the pass)
 
+struct KeyCand;
+
 struct BlockBufs {
     double *Fs;          // BLK_KMAX x pcn: Fs[s*pcn + i] = a_{i,k_s} before step s (the multiplier of row i at step s)
-    Cand *cands;         // SELECT_CLUSTER: per-CTA pricing candidates for the next pivot (st->k_next == -2)
+    KeyCand *cands;      // SELECT_CLUSTER: per-CTA pricing candidates for the next pivot (st->k_next == -2)
     double *Pm;          // BLK_KMAX x ld: Pm[s*ld + j] = scaled pivot row of step s (col 0 = b_r')
     double *objcur;      // R x ld: objective rows as of the last decided pivot (row m first)
     double *bcur;        // pcn: b column as of the last decided pivot (rows < m)
@@ -49,18 +51,92 @@ __global__ void blk_init_kernel(DenseParams P, BlockBufs B) {
 
 __device__ __forceinline__ int blk_row_start(int stamp, int seq) { return ((stamp >> 8) == seq) ? (stamp & 0xff) : 0; }
 
+// ------------------------------------------------------------------ arg-max on order-preserving keys
+// "maximise (p, q), ties to the lowest index" with redux.sync on 64-bit keys instead of shuffle trees
+// of (double, double, int) triples: a warp level is 3 (one key) or 5 (two keys) reductions, a CTA level one
+// barrier, the cluster level one DSMEM exchange.  Only the winning INDEX comes back (and the keys).
+struct KeyCand {
+    unsigned long long kp, kq;     // order-preserving images of p and q
+    int idx;                       // -1 = none
+};
+
+__device__ __forceinline__ KeyCand keycand_none() {
+    KeyCand c;
+    c.kp = 0; c.kq = 0; c.idx = -1;
+    return c;
+}
+
+// any double -> u64 with the same order; -0 and +0 map to the same key (they compare equal)
+__device__ __forceinline__ unsigned long long ord_key(double x) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(x + 0.0);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+
+__device__ __forceinline__ bool keycand_better(const KeyCand &a, const KeyCand &b) {
+    if (a.idx < 0) return false;
+    if (b.idx < 0) return true;
+    if (a.kp != b.kp) return a.kp > b.kp;
+    if (a.kq != b.kq) return a.kq > b.kq;
+    return a.idx < b.idx;
+}
+
+template <bool TWO>
+__device__ __forceinline__ KeyCand warp_key_best(KeyCand c) {
+    constexpr unsigned FULL = 0xffffffffu;
+    bool in = c.idx >= 0;
+    if (__ballot_sync(FULL, in) == 0u) return keycand_none();
+    KeyCand w;
+    w.kp = 0;
+    if (TWO) {
+        const unsigned h = __reduce_max_sync(FULL, in ? (unsigned)(c.kp >> 32) : 0u);
+        in = in && (unsigned)(c.kp >> 32) == h;
+        const unsigned l = __reduce_max_sync(FULL, in ? (unsigned)c.kp : 0u);
+        in = in && (unsigned)c.kp == l;
+        w.kp = ((unsigned long long)h << 32) | l;
+    }
+    const unsigned h = __reduce_max_sync(FULL, in ? (unsigned)(c.kq >> 32) : 0u);
+    in = in && (unsigned)(c.kq >> 32) == h;
+    const unsigned l = __reduce_max_sync(FULL, in ? (unsigned)c.kq : 0u);
+    in = in && (unsigned)c.kq == l;
+    w.kq = ((unsigned long long)h << 32) | l;
+    w.idx = (int)__reduce_min_sync(FULL, in ? (unsigned)c.idx : 0x7fffffffu);
+    return w;
+}
+
+// CTA-wide: per-warp winners through shared memory, one barrier; every warp reduces the winners again, so
+// the result is in all threads.  `scratch`: blockDim.x / 32 entries, used for ONE reduction per launch.
+template <bool TWO>
+__device__ __forceinline__ KeyCand block_key_best(KeyCand c, KeyCand *scratch) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+    c = warp_key_best<TWO>(c);
+    if (lane == 0) scratch[warp] = c;
+    __syncthreads();
+    return warp_key_best<TWO>(lane < nwarp ? scratch[lane] : keycand_none());
+}
+
+// cluster-wide: every CTA pushes its winner into every CTA's `slot` (DSMEM), one cluster barrier
+template <bool TWO>
+__device__ __forceinline__ KeyCand cluster_key_best(cg::cluster_group &cl, KeyCand c, KeyCand *scratch, KeyCand *slot) {
+    c = block_key_best<TWO>(c, scratch);
+    if (threadIdx.x < SELECT_CLUSTER) cl.map_shared_rank(slot, threadIdx.x)[cl.block_rank()] = c;
+    cl.sync();
+    const int lane = threadIdx.x & 31;
+    return warp_key_best<TWO>(lane < SELECT_CLUSTER ? slot[lane] : keycand_none());
+}
+
 // pricing candidate of column j from the (current) objective row values
-__device__ __forceinline__ void blk_price(const DenseParams &P, bool bigm, int j, double oc, double om, Cand &c) {
-    Cand t;
+__device__ __forceinline__ void blk_price(const DenseParams &P, bool bigm, int j, double oc, double om, KeyCand &c) {
+    KeyCand t;
     t.idx = j;
+    t.kq = ord_key(oc);
     if (bigm) {
         double p = om;
         if (fabs(p) <= P.eps) p = 0.0;
-        t.p = p; t.q = oc;
-        if ((p > 0.0 || (p == 0.0 && oc > P.eps)) && cand_better(t, c)) c = t;
+        t.kp = ord_key(p);
+        if ((p > 0.0 || (p == 0.0 && oc > P.eps)) && keycand_better(t, c)) c = t;
     } else {
-        t.p = 0.0; t.q = oc;
-        if (oc > P.eps && cand_better(t, c)) c = t;
+        t.kp = 0;
+        if (oc > P.eps && keycand_better(t, c)) c = t;
     }
 }
 
@@ -75,8 +151,9 @@ constexpr int STEP_CPT = 3;            // columns per thread in flight in the ro
 
 __global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
 blk_step_kernel(DenseParams P, BlockBufs B, int first) {
-    __shared__ Cand scratch[SELECT_THREADS / 32];
-    __shared__ Cand slot_a[SELECT_CLUSTER], slot_b[SELECT_CLUSTER], slot_d[SELECT_CLUSTER];
+    // one scratch / slot array per reduction of a launch: no reuse, so no extra barriers
+    __shared__ KeyCand scr_a[SELECT_THREADS / 32], scr_b[SELECT_THREADS / 32], scr_c[SELECT_THREADS / 32], scr_d[SELECT_THREADS / 32];
+    __shared__ KeyCand slot_a[SELECT_CLUSTER], slot_b[SELECT_CLUSTER], slot_d[SELECT_CLUSTER];
     __shared__ double s_pk[BLK_KMAX], s_fr[BLK_KMAX];
     cg::cluster_group cl = cg::this_cluster();
     const int rank = (int)cl.block_rank();
@@ -105,33 +182,33 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
 
     int status = status0, k = 0, r = -1;
     bool have = false;
-    double brp = 0.0, sig_c = 0.0, sig_m = 0.0;
+    double sig_c = 0.0, sig_m = 0.0;
     if (status0 == LPGPU_RUNNING) {
         // ---- entering column: priced by the previous step (one candidate per CTA), or from scratch
         if (kn > 0) k = kn;
         else if (kn == -2) {
             const int lane = threadIdx.x & 31;
-            Cand c = cand_none();
+            KeyCand c = keycand_none();
             if (lane < SELECT_CLUSTER) {
-                c.p = __ldcg(&B.cands[lane].p); c.q = __ldcg(&B.cands[lane].q); c.idx = __ldcg(&B.cands[lane].idx);
+                c.kp = __ldcg(&B.cands[lane].kp); c.kq = __ldcg(&B.cands[lane].kq); c.idx = __ldcg(&B.cands[lane].idx);
             }
-            c = warp_best(c);
+            c = bigm ? warp_key_best<true>(c) : warp_key_best<false>(c);
             k = c.idx > 0 ? c.idx : 0;
         } else {
-            Cand c = cand_none();
+            KeyCand c = keycand_none();
             for (int j = 1 + gtid; j <= P.n; j += GSTRIDE) blk_price(P, bigm, j, oc[j], bigm ? om[j] : 0.0, c);
-            c = cluster_best(cl, c, scratch, slot_a);
+            c = cluster_key_best<true>(cl, c, scr_a, slot_a);
             k = c.idx > 0 ? c.idx : 0;
         }
         if (k == 0) {
             // optimal, unless Big-M left an artificial basic at a positive level
-            Cand a = cand_none();
+            KeyCand a = keycand_none();
             if (bigm) {
                 const int nreal = P.n - P.n_art;
                 for (int i = gtid; i < P.m; i += GSTRIDE)
-                    if (P.basis[i] > nreal && B.bcur[i] > P.eps) { a.p = 0.0; a.q = 0.0; a.idx = i; break; }
+                    if (P.basis[i] > nreal && B.bcur[i] > P.eps) { a.idx = i; break; }
             }
-            a = cluster_best(cl, a, scratch, slot_d);
+            a = cluster_key_best<false>(cl, a, scr_d, slot_d);
             status = (a.idx >= 0) ? LPGPU_INFEASIBLE : LPGPU_OPTIMAL;
         } else {
             // ---- column k as it stands after the t pivots of this block, and the ratio test on it
@@ -145,7 +222,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
             if (i < P.m) { tv = P.T[(size_t)i * P.ld + (size_t)k]; rs = B.rowstamp[i]; bv = B.bcur[i]; }
             if ((int)threadIdx.x < t) s_pk[threadIdx.x] = B.Pm[(size_t)threadIdx.x * P.ld + (size_t)k];
             __syncthreads();
-            Cand c = cand_none();
+            KeyCand c = keycand_none();
             for (; i < P.m; i += GSTRIDE) {
                 if (i != gtid) { tv = P.T[(size_t)i * P.ld + (size_t)k]; rs = B.rowstamp[i]; bv = B.bcur[i]; }
                 const int s0 = blk_row_start(rs, seq);
@@ -160,19 +237,19 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
                 }
                 B.Fs[(size_t)t * pcn + i] = a;
                 if (a > P.eps) {
-                    Cand x;
-                    x.p = 0.0;
-                    x.q = -(bv / a);
+                    KeyCand x;
+                    x.kp = 0;
+                    x.kq = ord_key(-(bv / a));                  // arg max -theta == arg min theta
                     x.idx = i;
-                    if (cand_better(x, c)) c = x;
+                    if (keycand_better(x, c)) c = x;
                 }
             }
             stamp(2);
-            c = cluster_best(cl, c, scratch, slot_b);
+            c = cluster_key_best<false>(cl, c, scr_b, slot_b);
             stamp(3);
             if (c.idx < 0) status = LPGPU_UNBOUNDED;
             else if (iters >= P.max_iter) status = LPGPU_ITER_LIMIT;
-            else if (budget > 0) { have = true; r = c.idx; brp = -c.q; }    // b_r / a_rk IS the winning ratio
+            else if (budget > 0) { have = true; r = c.idx; }
         }
     }
     if (!have) {
@@ -201,11 +278,13 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         }
     }
     const int s0r = blk_row_start(B.rowstamp[r], seq);
+    const double b_r = B.bcur[r];
     const double piv = __ldcg(B.Fs + (size_t)t * pcn + r);                   // written above, possibly by another CTA
     if ((int)threadIdx.x < t) s_fr[threadIdx.x] = B.Fs[(size_t)threadIdx.x * pcn + r];
     __syncthreads();
     double *pt = B.Pm + (size_t)t * P.ld;
-    Cand c = cand_none();
+    const double brp = div_skip_zero(b_r, piv);       // = P[t][0]: column 0 of the row is the b column
+    KeyCand c = keycand_none();
     for (size_t j0 = jb; j0 < P.ld; j0 += (size_t)STEP_CPT * GSTRIDE) {
         if (j0 != jb) {
 #pragma unroll
@@ -258,7 +337,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         B.bcur[i] = (i == r) ? brp : __fma_rn(-B.Fs[(size_t)t * pcn + i], brp, B.bcur[i]);
     stamp(4);
     // ---- this CTA's best candidate for the next pivot; the next launch reduces the SELECT_CLUSTER of them
-    c = block_best(c, scratch);
+    c = bigm ? block_key_best<true>(c, scr_c) : block_key_best<false>(c, scr_c);
     if (threadIdx.x == 0) B.cands[rank] = c;
     stamp(5);
 

@@ -7,6 +7,8 @@
 #include "ctx.h"
 #include "dense_select.cuh"
 
+namespace lpgpu { struct KeyCand; }
+
 struct lpgpu_dense {
     lpgpu_ctx *ctx;
     int m, n, R;
@@ -29,7 +31,7 @@ struct lpgpu_dense {
     // blocked path (dense_block.cuh): lazy slices of the pivots not yet applied to T
     double *Ft, *Pm, *objcur, *bcur;   // Ft: BLK_KMAX x pcn multipliers, Pm: BLK_KMAX x ld scaled pivot rows
     int *rowstamp, *steprow;
-    lpgpu::Cand *cands;     // per-CTA pricing candidates handed from one step launch to the next
+    lpgpu::KeyCand *cands;     // per-CTA pricing candidates handed from one step launch to the next
     unsigned long long *blk_dbg;   // LPGPU_BLK_DEBUG: phase stamps of the step kernel
     long blk_dbg_n;
     bool blk_open;          // step kernels were enqueued since the last flush

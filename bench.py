@@ -8,8 +8,9 @@ fp64 tableau per GPU (random feasible LP, seed 1234, LP index = rank), a "step" 
   value  : pivots/s summed over ranks, tableau resident in HBM when the timed region starts
   e2e    : the same metric through lpgpu_solve_dense() with HOST (pinned) buffers: H2D copy of
            the 1.07 GB tableau, P pivots, D2H of x / basis / status inside the timed region
-  roofline: the rank-1 elimination kernel, algorithmic bytes 16*(m+1)*(n+1) per launch over
-           its CUDA-event duration, against MEASURED_PEAKS.json hbm_gbs
+  roofline: the dominant kernel = the pass that applies a block of K pivots to the tableau
+           (blk_flush_kernel; with --variant 0x800 the rank-1 elimination kernel), algorithmic bytes
+           16*(m+1)*(n+1) per launch over its CUDA-event duration, against MEASURED_PEAKS.json hbm_gbs
   cpu_baseline: the CPU oracle (oracle/, kind "port": the reference has no pivot loop to time)
            on the host cores, bounded sample of the same workload
 `--impl reference` times that CPU oracle alone, on the same config/metric/unit.
@@ -263,19 +264,22 @@ def gpu_arm(args):
 
     def start(d, **opts):
         state["opts"] = opts
+        state["iters"] = 0
         d.synth(SEED, rank, ns)
-        d.reset(variant=variant, **opts)
+        d.reset(variant=state.get("variant", variant), check_every=256, **opts)
 
     def window(d):
         """P pivots; if the LP reaches its optimum inside the window (about 17k pivots at the default
         size) it is regenerated and the window continues, so every step performs exactly P pivots."""
-        done, upd_ms, sel_ms = 0, 0.0, 0.0
+        done, upd_ms, sel_ms, passes = 0, 0.0, 0.0, 0
         while done < P:
             r = d.run(P - done)
-            done += r["update_launches"]; upd_ms += r["update_ms"]; sel_ms += r["select_ms"]
+            done += r["iters"] - state["iters"]
+            state["iters"] = r["iters"]
+            passes += r["update_launches"]; upd_ms += r["update_ms"]; sel_ms += r["select_ms"]
             if r["status"] != lp.RUNNING:
                 start(d, **state["opts"])
-        return {"update_launches": done, "update_ms": upd_ms, "select_ms": sel_ms}
+        return {"pivots": done, "update_launches": passes, "update_ms": upd_ms, "select_ms": sel_ms}
 
     # ---- value: resident tableau, K windows of P pivots
     d = lp.DenseTableau(ctx, m, n, 1)
@@ -292,32 +296,64 @@ def gpu_arm(args):
     t_value = max_over_ranks(t_value)
     value = world * K * P / t_value
 
-    # ---- roofline of the dominant kernel: same region, every elimination launch bracketed by events
+    # ---- roofline of the dominant kernel: same region, every pass over the tableau bracketed by events
+    RANK1 = 0x800
+    blocked = not (variant & RANK1)
+    block_k = ((variant >> 16) & 0x3f) or 32
+
+    def kernel_times():
+        upd_ms = sel_ms = 0.0
+        upd_n = piv = 0
+        for _ in range(W):
+            window(d)
+        for _ in range(K):
+            r = window(d)
+            upd_ms += r["update_ms"]; sel_ms += r["select_ms"]; upd_n += r["update_launches"]; piv += r["pivots"]
+        return upd_ms, sel_ms, upd_n, piv
+
     start(d, time_kernels=1)
-    for _ in range(W):
-        window(d)
-    upd_ms = sel_ms = 0.0
-    upd_n = 0
-    for _ in range(K):
-        r = window(d)
-        upd_ms += r["update_ms"]; sel_ms += r["select_ms"]; upd_n += r["update_launches"]
-    d.close()
+    upd_ms, sel_ms, upd_n, piv_n = kernel_times()
     peak, peak_src = measured_peak()
     traffic, traffic_src = None, None
+    kname = "blk_flush_kernel" if blocked else {0: "dense_update_dynamic", 1: "dense_update_tma_staged", 2: "dense_update_direct"}[variant & 0xf]
     try:        # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
-        with open(os.path.join(ROOT, "profiles", "r1_update_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r1_flush_traffic.json" if blocked else "r1_update_traffic.json")) as f:
             tj = json.load(f)
-        if m == M and tj["variant"] == (variant & 0xf):
+        if m == M and (blocked or tj["variant"] == (variant & 0xf)):
             traffic, traffic_src = tj["traffic_bytes_per_launch"], tj["source"]
     except Exception:
         pass
     upd_avg_ms = upd_ms / upd_n
     achieved = alg_bytes / (upd_avg_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": {0: "dense_update_dynamic", 1: "dense_update_tma_staged", 2: "dense_update_direct"}[variant & 0xf],
+    roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
-                "avg_launch_ms": upd_avg_ms, "select_avg_ms": sel_ms / upd_n,
+                "avg_launch_ms": upd_avg_ms, "launches": upd_n, "pivots_per_launch": piv_n / upd_n,
+                "decision_kernels_avg_ms_per_pivot": sel_ms / piv_n,
                 "kernel_share_of_step": upd_ms / (upd_ms + sel_ms), "frac_of_nominal_8TBs": achieved / 8000.0}
+    if blocked:
+        flops = 2.0 * (piv_n / upd_n) * (m + 1) * (n + 1)
+        roofline["fp64_TFLOPs_in_kernel"] = flops / (upd_avg_ms * 1e-3) / 1e12
+        roofline["note"] = ("one launch applies pivots_per_launch pivots: every element is read and written once and runs through "
+                            "that many dependent DFMAs, so the launch is bounded by HBM (algorithmic bytes above) and, at 32 "
+                            "pivots per launch, nearly as long on the FP64 pipe")
+    # the rank-1 path (one pass per pivot) on the same workload, for comparison with earlier rounds
+    rank1 = None
+    if blocked and not args.no_extra:
+        state["variant"] = variant | RANK1
+        start(d)
+        p_save, P = P, min(P, 300)
+        window(d)
+        t_r1 = timed(lambda: window(d))
+        start(d, time_kernels=1)
+        window(d)
+        r = window(d)
+        rank1 = {"pivots_per_sec": world * P / max_over_ranks(t_r1), "kernel": "dense_update_dynamic",
+                 "avg_launch_ms": r["update_ms"] / r["update_launches"],
+                 "roofline_frac": alg_bytes / (r["update_ms"] / r["update_launches"] * 1e-3) / 1e9 / peak}
+        P = p_save
+        state.pop("variant")
+    d.close()
 
     # ---- e2e: host (pinned) buffers through the one-shot C-ABI call, copies inside the timed region
     Th = ctx.pinned((m + 1, n + 1))
@@ -419,11 +455,14 @@ def gpu_arm(args):
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"dense tableau {m}x{n} fp64 random feasible LP per GPU (BASELINE config 4)",
                    "m": m, "n": n, "tableau_bytes": (m + 1) * (n + 1) * 8, "pivots_per_step": P, "seed": SEED,
-                   "variant": variant, "l2": "inputs larger than L2 (1.07 GB tableau vs 126 MB)",
+                   "variant": variant, "path": (f"blocked: {block_k} pivots decided on lazy slices, then one pass over the tableau"
+                                                if blocked else "rank-1: one pass over the tableau per pivot"),
+                   "l2": "inputs larger than L2 (1.07 GB tableau vs 126 MB)",
                    "sharding": "independent LP per rank, no collective" if world > 1 else "single GPU"},
-        "hbm_GBs_whole_step": world * K * P * alg_bytes / t_value / 1e9,
         "roofline": roofline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "extra": extra,
     }
+    if rank1 is not None:
+        extra["rank1_path"] = rank1
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(m, ns)
     if rank == 0:

@@ -18,7 +18,8 @@ KEEP_FINAL = 0x1000      # batched: keep the final tableaux on the device (parit
 FORCE_SMEM = 0x2000      # batched: shared-memory kernel even where the register-resident one applies
 STATIC = 0x1             # dense: TMA-staged elimination with a static task stride (default: work stealing)
 DIRECT = 0x2             # dense: direct-load elimination kernel instead of the TMA-staged default
-BLOCKED = 0x800          # dense: decide up to K pivots on lazily updated slices, apply them in one pass (K = variant bits 16..21, 0 = 32)
+RANK1 = 0x800            # dense: one pass over the tableau per pivot (default for plain / Big-M: up to K pivots decided on lazily
+                         # updated slices, then applied in one pass; K = variant bits 16..21, 0 = 32)
 NO_PDL = 0x400           # dense: plain stream-ordered launches (default: programmatic dependent launch)
 NO_ALTERNATE = 0x200     # dense: do not alternate the sweep direction between pivots
 NCCL_ID_BYTES = 128

@@ -228,9 +228,10 @@ int read_state(lpgpu_dense *d) {
     return LPGPU_OK;
 }
 
-// ---- blocked path (dense_block.cuh): variant bit 0x800, pivots per block in variant bits 16..21 (0 = 32)
+// ---- blocked path (dense_block.cuh): the default for the plain and Big-M methods; variant bit 0x800 selects the
+// rank-1 path instead; pivots per block in variant bits 16..21 (0 = 32)
 bool use_blocked(const lpgpu_dense *d) {
-    return (d->opts.variant & 0x800) && (d->opts.method == LPGPU_PLAIN || d->opts.method == LPGPU_BIGM);
+    return !(d->opts.variant & 0x800) && (d->opts.method == LPGPU_PLAIN || d->opts.method == LPGPU_BIGM);
 }
 
 static BlockBufs make_bufs(const lpgpu_dense *d) {

@@ -101,6 +101,7 @@ def test_random_mixed_lps_dense(ctx, seed, method):
 @pytest.mark.parametrize("shape", [(5, 7), (33, 65), (100, 511), (257, 1030), (64, 2049)])
 @pytest.mark.parametrize("variant", [0, 1, 2, 0x200, 0x201, 0x202, 0x400, 0x401])
 def test_single_pivot_pass_bitwise(ctx, shape, variant):
+    variant |= capi.RANK1
     rows, cols = shape
     rng = np.random.default_rng(rows * 1000 + cols)
     T0 = rng.uniform(-2, 2, size=(rows, cols))
@@ -123,6 +124,7 @@ def test_single_pivot_pass_bitwise(ctx, shape, variant):
 @pytest.mark.parametrize("m,ns", [(32, 32), (64, 64), (200, 120), (300, 500), (512, 512)])
 @pytest.mark.parametrize("variant", [0, 1, 2])
 def test_dense_synth_full_solve(ctx, m, ns, variant):
+    variant |= capi.RANK1                    # the three rank-1 elimination kernels
     T0, basis = O.synth_feasible(1234, 3, m, ns)
     ref = O.solve_f64(T0, basis, threads=4, log_cap=4096)
     got = lp.solve_dense(ctx, T0, basis, log_cap=4096, variant=variant)
@@ -189,15 +191,19 @@ def test_dense_timed_run_reports_kernel_time(ctx):
     m, ns = 512, 512
     d = lp.DenseTableau(ctx, m, m + ns, 1)
     d.synth(1234, 0, ns)
-    d.reset(time_kernels=1)
+    d.reset(time_kernels=1, variant=capi.RANK1)
     r = d.run(20)
     assert r["update_launches"] == 20 and r["update_ms"] > 0 and r["select_ms"] > 0
+    d.reset(time_kernels=1, variant=_blocked(8))          # blocked path: one pass per 8 pivots
+    d.synth(1234, 0, ns)
+    r = d.run(20)
+    assert r["iters"] == 20 and r["update_launches"] == 3 and r["update_ms"] > 0 and r["select_ms"] > 0
     d.close()
 
 
 # ------------------------------------------------------------------ blocked path (delayed rank-1 applications)
 def _blocked(K=0):
-    return capi.BLOCKED | (K << 16)
+    return K << 16          # pivots per block (0 = the default, 32); the blocked path is the default for plain / Big-M
 
 
 @pytest.mark.parametrize("m,ns", [(32, 32), (64, 64), (200, 120), (300, 500), (512, 512)])
@@ -273,7 +279,7 @@ def test_blocked_equals_rank1_path_midsize_bitwise(ctx):
     alternate on one tableau object (reset between them) and still agree."""
     m, ns, Pn = 1024, 3072, 300
     outs = []
-    for variant in (0, _blocked(), _blocked(13)):
+    for variant in (capi.RANK1, _blocked(), _blocked(13)):
         d = lp.DenseTableau(ctx, m, m + ns, 1)
         d.synth(1234, 3, ns)
         d.reset(log_cap=Pn, variant=variant)

@@ -8,7 +8,7 @@ K = int(sys.argv[2]) if len(sys.argv) > 2 else 32
 ctx = lp.Context(0)
 d = lp.DenseTableau(ctx, m, 2 * m, 1)
 d.synth(1234, 0, m)
-d.reset(check_every=640, variant=capi.BLOCKED | (K << 16))
+d.reset(check_every=640, variant=K << 16)
 r = d.run(640)
 print(r["iters"], r["status"])
 d.close()

@@ -70,7 +70,8 @@ typedef struct {
     int n_art;          /* number of trailing artificial columns                         */
     int log_cap;        /* pivots to record in the pivot log (0 = none)                  */
     int check_every;    /* dense: pivots enqueued between host status reads (0 = 64)     */
-    int variant;        /* kernel variant (0 = default)                   */
+    int variant;        /* kernel variant (0 = default): 0x800 = one pass  */
+                        /* over the tableau per pivot instead of one per block of pivots  */
     int time_kernels;   /* dense: bracket every elimination launch with CUDA events      */
     int results_only;   /* lpgpu_solve_dense: do not copy the final tableau back to T    */
 } lpgpu_opts;
@@ -109,6 +110,8 @@ void lpgpu_host_free(lpgpu_ctx *ctx, void *p);
 /* One-shot: upload, pivot to a terminal status (or max_iter), download.  T and basis are
  * updated in place (opts->results_only = 1 leaves T untouched and returns basis, x, z only);
  * pivot_log (2*log_cap ints: column, row) and x (n doubles) may be NULL.
+ * The device-side tableau object is kept in the context and reused by the next call of the same
+ * shape (released by lpgpu_destroy or by a call with another shape).
  * Replaces the missing loop between Source/simplex.c:40 and :67. */
 int lpgpu_solve_dense(lpgpu_ctx *ctx, int m, int n, int R, double *T, size_t ld, int *basis,
                       const lpgpu_opts *opts, int *pivot_log, double *x, lpgpu_result *res);

@@ -40,6 +40,7 @@ int lpgpu_create(lpgpu_ctx **out, int device, void *stream) {
     ctx->cc_minor = prop.minor;
     ctx->hbm_bytes = prop.totalGlobalMem;
     ctx->launches = 0;
+    ctx->solve_cache = nullptr;
     ctx->err[0] = '\0';
     if (stream) {
         ctx->stream = reinterpret_cast<cudaStream_t>(stream);
@@ -59,6 +60,7 @@ void lpgpu_destroy(lpgpu_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->solve_cache) lpgpu_dense_destroy(ctx->solve_cache);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -7,6 +7,8 @@
 
 #include "../../include/lpgpu.h"
 
+struct lpgpu_dense;
+
 struct lpgpu_ctx {
     int device;
     cudaStream_t stream;
@@ -15,6 +17,7 @@ struct lpgpu_ctx {
     int cc_major, cc_minor;
     size_t hbm_bytes;
     long launches;
+    lpgpu_dense *solve_cache;   // tableau object kept between lpgpu_solve_dense calls of one shape (1 GB cudaMalloc / cudaFree per call otherwise)
     char err[512];
 };
 

@@ -648,14 +648,25 @@ int lpgpu_solve_dense(lpgpu_ctx *ctx, int m, int n, int R, double *T, size_t ld,
                       int *pivot_log, double *x, lpgpu_result *res) {
     if (!ctx || !T || !basis || !opts || !res) return LPGPU_EINVAL;
     if (!opts_ok(opts, n, R)) return fail(ctx, LPGPU_EINVAL, "solve_dense: bad options (method/R/n_art)");
-    lpgpu_dense *d = nullptr;
-    int rc = lpgpu_dense_create(ctx, m, n, R, &d);
-    if (rc != LPGPU_OK) return rc;
+    // the tableau object (1 GB of device memory at the headline size) is kept in the context between calls of
+    // the same shape: cudaMalloc / cudaFree of that size cost more than the upload itself
+    lpgpu_dense *d = ctx->solve_cache;
+    int rc = LPGPU_OK;
+    if (!d || d->m != m || d->n != n || d->R != R) {
+        if (d) lpgpu_dense_destroy(d);
+        ctx->solve_cache = d = nullptr;
+        rc = lpgpu_dense_create(ctx, m, n, R, &d);
+        if (rc != LPGPU_OK) return rc;
+        ctx->solve_cache = d;
+    }
     rc = lpgpu_dense_reset(d, opts);
     if (rc == LPGPU_OK) rc = lpgpu_dense_upload(d, T, ld, basis);
     if (rc == LPGPU_OK) rc = lpgpu_dense_run(d, opts->max_iter, res);
     if (rc == LPGPU_OK) rc = lpgpu_dense_download(d, opts->results_only ? nullptr : T, ld, basis, pivot_log, x);
-    lpgpu_dense_destroy(d);
+    if (rc != LPGPU_OK) {           // do not keep an object in an unknown state
+        lpgpu_dense_destroy(d);
+        ctx->solve_cache = nullptr;
+    }
     return rc;
 }
 

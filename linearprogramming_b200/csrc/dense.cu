@@ -254,8 +254,8 @@ static int launch_block_init(lpgpu_dense *d) {
 static int launch_block_step(lpgpu_dense *d, int first) {
     lpgpu_ctx *ctx = d->ctx;
     const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels;
-    LP_CUDA(ctx, launch_pdl(pdl, blk_step_kernel, dim3(SELECT_CLUSTER), dim3(SELECT_THREADS), ctx->stream, make_params(d),
-                            make_bufs(d), first));
+    LP_CUDA(ctx, launch_pdl(pdl, d->R == 2 ? blk_step_kernel<2> : blk_step_kernel<1>, dim3(SELECT_CLUSTER), dim3(SELECT_THREADS),
+                            ctx->stream, make_params(d), make_bufs(d), first));
     if (d->blk_dbg) d->blk_dbg_n++;
     ctx->launches++;
     return LPGPU_OK;
@@ -266,6 +266,7 @@ static int launch_block_flush(lpgpu_dense *d) {
     FlushParams U;
     U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.Fs = d->Ft; U.pcn = d->pcn; U.Pm = d->Pm; U.rowstamp = d->rowstamp; U.steprow = d->steprow; U.st = d->st;
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
+    U.rb = d->fl_rb; U.pf = d->fl_pf;
     blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, ctx->stream>>>(U);
     LP_LAUNCH_CHECK(ctx);
     const unsigned fx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, (d->ld + 255) / 256));
@@ -302,7 +303,10 @@ int size_grid(lpgpu_dense *d) {
     int occf = 0;
     LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_kernel, FL_THREADS, FL_SMEM_BYTES));
     const long fct = (long)((d->ld + FL_COLS - 1) / FL_COLS);
-    const long fsb = ((d->m + d->R + FL_ROWS - 1) / FL_ROWS + FL_RB - 1) / FL_RB;
+    const char *erb = getenv("LPGPU_FL_RB"), *epf = getenv("LPGPU_FL_PF");      // tuning aids
+    d->fl_rb = (erb && atoi(erb) > 0) ? atoi(erb) : FL_RB;
+    d->fl_pf = epf ? atoi(epf) : 1;
+    const long fsb = ((d->m + d->R + FL_ROWS - 1) / FL_ROWS + d->fl_rb - 1) / d->fl_rb;
     d->grid_flush = (int)std::max(1L, std::min((long)ctx->sm_count * std::max(1, occf), fct * fsb));
     return LPGPU_OK;
 }

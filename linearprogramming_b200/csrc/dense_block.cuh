@@ -146,9 +146,10 @@ __device__ __forceinline__ void blk_price(const DenseParams &P, bool bigm, int j
 // the loads it can (tableau column / row, stamps, b, objective row) and only then waits; the second
 // cluster-wide reduction (next pivot's pricing) is left to the next launch: each CTA leaves its best
 // candidate in `cands` (st->k_next = -2) and the next step reduces the 8 of them on entry.
-constexpr int STEP_PB = 4;             // earlier pivot rows per batch of loads in the row phase (64 registers per thread)
-constexpr int STEP_CPT = 3;            // columns per thread in flight in the row phase (covers ld <= 3 * 8192 in one go)
+constexpr int STEP_PB = 8;             // earlier pivot rows per batch of loads in the row phase (64 registers per thread)
+constexpr int STEP_CPT = 2;            // columns per thread in flight in the row phase (covers n <= 2 * 8192 in one go)
 
+template <int RR>
 __global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
 blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     // one scratch / slot array per reduction of a launch: no reuse, so no extra barriers
@@ -176,6 +177,11 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     const int status0 = st->status, iters = st->iters, budget = st->budget;
     const int t = first ? 0 : st->blk_t, seq = st->blk_seq + (first ? 1 : 0);
     const int kn = st->k_next;
+    KeyCand cin = keycand_none();                  // the previous step's per-CTA candidates, requested together with the state
+    if ((threadIdx.x & 31) < SELECT_CLUSTER) {
+        const int ln = threadIdx.x & 31;
+        cin.kp = __ldcg(&B.cands[ln].kp); cin.kq = __ldcg(&B.cands[ln].kq); cin.idx = __ldcg(&B.cands[ln].idx);
+    }
     const bool bigm = (P.method == LPGPU_BIGM);
     const double *oc = B.objcur, *om = B.objcur + P.ld;          // om valid for R == 2 only
     const size_t pcn = P.pcn;
@@ -187,12 +193,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         // ---- entering column: priced by the previous step (one candidate per CTA), or from scratch
         if (kn > 0) k = kn;
         else if (kn == -2) {
-            const int lane = threadIdx.x & 31;
-            KeyCand c = keycand_none();
-            if (lane < SELECT_CLUSTER) {
-                c.kp = __ldcg(&B.cands[lane].kp); c.kq = __ldcg(&B.cands[lane].kq); c.idx = __ldcg(&B.cands[lane].idx);
-            }
-            c = bigm ? warp_key_best<true>(c) : warp_key_best<false>(c);
+            const KeyCand c = bigm ? warp_key_best<true>(cin) : warp_key_best<false>(cin);
             k = c.idx > 0 ? c.idx : 0;
         } else {
             KeyCand c = keycand_none();
@@ -213,8 +214,8 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         } else {
             // ---- column k as it stands after the t pivots of this block, and the ratio test on it
             sig_c = oc[k];                                        // read before the row phase rewrites objcur
-            sig_m = (P.R == 2) ? om[k] : 0.0;
-            if (gtid < P.R) B.Fs[(size_t)t * pcn + P.m + gtid] = oc[(size_t)gtid * P.ld + k];   // objective rows: kept eagerly, same bits
+            sig_m = (RR == 2) ? om[k] : 0.0;
+            if (gtid < RR) B.Fs[(size_t)t * pcn + P.m + gtid] = oc[(size_t)gtid * P.ld + k];   // objective rows: kept eagerly, same bits
             // first row of this thread: everything it needs is requested before anyone waits
             int i = gtid;
             double tv = 0.0, bv = 0.0;
@@ -266,15 +267,15 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
 
     // ---- row r as it stands after the t pivots of this block, scaled; objective rows and next pricing
     double av[STEP_CPT], ocv[STEP_CPT], omv[STEP_CPT];
-    const size_t jb = (size_t)gtid;
+    const size_t jb = 1 + (size_t)gtid;           // columns 1..n; column 0 (b_r') is brp, padding columns stay zero
 #pragma unroll
     for (int cth = 0; cth < STEP_CPT; ++cth) {
         const size_t j = jb + (size_t)cth * GSTRIDE;
         av[cth] = ocv[cth] = omv[cth] = 0.0;
-        if (j < P.ld) {
+        if (j <= (size_t)P.n) {
             av[cth] = P.T[(size_t)r * P.ld + j];
             ocv[cth] = oc[j];
-            if (P.R == 2) omv[cth] = om[j];
+            if (RR == 2) omv[cth] = om[j];
         }
     }
     const int s0r = blk_row_start(B.rowstamp[r], seq);
@@ -285,19 +286,24 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     double *pt = B.Pm + (size_t)t * P.ld;
     const double brp = div_skip_zero(b_r, piv);       // = P[t][0]: column 0 of the row is the b column
     KeyCand c = keycand_none();
-    for (size_t j0 = jb; j0 < P.ld; j0 += (size_t)STEP_CPT * GSTRIDE) {
+    if (gtid == 0) {                              // column 0
+        pt[0] = brp;
+        B.objcur[0] = __fma_rn(-sig_c, brp, oc[0]);
+        if (RR == 2) B.objcur[P.ld] = __fma_rn(-sig_m, brp, om[0]);
+    }
+    for (size_t j0 = jb; j0 <= (size_t)P.n; j0 += (size_t)STEP_CPT * GSTRIDE) {
         if (j0 != jb) {
 #pragma unroll
             for (int cth = 0; cth < STEP_CPT; ++cth) {
                 const size_t j = j0 + (size_t)cth * GSTRIDE;
-                if (j < P.ld) { av[cth] = P.T[(size_t)r * P.ld + j]; ocv[cth] = oc[j]; if (P.R == 2) omv[cth] = om[j]; }
+                if (j <= (size_t)P.n) { av[cth] = P.T[(size_t)r * P.ld + j]; ocv[cth] = oc[j]; if (RR == 2) omv[cth] = om[j]; }
             }
         }
         if (s0r > 0) {                            // the row was a pivot row earlier in this block: restart from its scaled row
 #pragma unroll
             for (int cth = 0; cth < STEP_CPT; ++cth) {
                 const size_t j = j0 + (size_t)cth * GSTRIDE;
-                if (j < P.ld) av[cth] = B.Pm[(size_t)(s0r - 1) * P.ld + j];
+                if (j <= (size_t)P.n) av[cth] = B.Pm[(size_t)(s0r - 1) * P.ld + j];
             }
         }
         for (int sb = s0r; sb < t; sb += STEP_PB) {     // STEP_PB earlier pivot rows x STEP_CPT columns in flight
@@ -306,7 +312,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
             for (int cth = 0; cth < STEP_CPT; ++cth) {
                 const size_t j = j0 + (size_t)cth * GSTRIDE;
 #pragma unroll
-                for (int u = 0; u < STEP_PB; ++u) pv[cth][u] = (sb + u < t && j < P.ld) ? B.Pm[(size_t)(sb + u) * P.ld + j] : 0.0;
+                for (int u = 0; u < STEP_PB; ++u) pv[cth][u] = (sb + u < t && j <= (size_t)P.n) ? B.Pm[(size_t)(sb + u) * P.ld + j] : 0.0;
             }
 #pragma unroll
             for (int u = 0; u < STEP_PB; ++u)
@@ -318,17 +324,17 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
 #pragma unroll
         for (int cth = 0; cth < STEP_CPT; ++cth) {
             const size_t j = j0 + (size_t)cth * GSTRIDE;
-            if (j < P.ld) {
+            if (j <= (size_t)P.n) {
                 const double pr = div_skip_zero(av[cth], piv);
                 pt[j] = pr;
                 const double qc = __fma_rn(-sig_c, pr, ocv[cth]);
                 B.objcur[j] = qc;
                 double qm = 0.0;
-                if (P.R == 2) {
+                if (RR == 2) {
                     qm = __fma_rn(-sig_m, pr, omv[cth]);
                     B.objcur[P.ld + j] = qm;
                 }
-                if (j >= 1 && j <= (size_t)P.n) blk_price(P, bigm, (int)j, qc, qm, c);
+                blk_price(P, bigm, (int)j, qc, qm, c);
             }
         }
     }
@@ -390,6 +396,8 @@ struct FlushParams {
     const PivotState *st;
     int *task_ctr;
     unsigned seq;
+    int rb;                   // row tiles per task (FL_RB; LPGPU_FL_RB overrides it for tuning)
+    int pf;                   // 1: HBM -> L2 prefetch of the next tile
 };
 
 constexpr size_t FL_SMEM_BYTES = (size_t)BLK_KMAX * FL_COLS * 8 + 2 * (size_t)FL_ROWS * BLK_KMAX * 8;
@@ -500,7 +508,7 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
 
     const int nct = (int)((U.ld + FL_COLS - 1) / FL_COLS);
     const int nrt = (U.rows + FL_ROWS - 1) / FL_ROWS;                  // row tiles
-    const int nsb = (nrt + FL_RB - 1) / FL_RB;                         // row super-blocks
+    const int nsb = (nrt + U.rb - 1) / U.rb;                           // row super-blocks
     const long ntasks = (long)nct * nsb;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int wr = warp;                                               // 4 warps stacked over 64 rows x 128 columns
@@ -521,7 +529,7 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
         FlTile t;
         t.j0 = (size_t)(tt % nct) * FL_COLS;
         t.ncols = (int)min((size_t)FL_COLS, U.ld - t.j0);              // a multiple of 16 (ld % 16 == 0)
-        const int rt0 = (int)(tt / nct) * FL_RB, rt1 = min(rt0 + FL_RB, nrt);
+        const int rt0 = (int)(tt / nct) * U.rb, rt1 = min(rt0 + U.rb, nrt);
         if (threadIdx.x == 0) {
             s_task[(it & 1) ^ 1] = (long)atomicAdd(ctr, 1);            // next task; visible after the barriers below
             mbar_arrive_expect_tx(&bar_p, (uint32_t)(kc * t.ncols * 8));
@@ -546,10 +554,10 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
                     if (have) {
                         nx.j0 = (size_t)(nt % nct) * FL_COLS;
                         nx.ncols = (int)min((size_t)FL_COLS, U.ld - nx.j0);
-                        nx.rt = (int)(nt / nct) * FL_RB;
+                        nx.rt = (int)(nt / nct) * U.rb;
                     }
                 }
-                if (have) fl_prefetch_tile(U, nx);
+                if (have && U.pf) fl_prefetch_tile(U, nx);
             }
             if (rt == rt0) { mbar_wait(&bar_p, par_p); par_p ^= 1; }
             mbar_wait(&bar_f[fb], (par_f >> fb) & 1u);

@@ -417,6 +417,22 @@ def gpu_arm(args):
                                      "all_optimal": bool((out5["status"] == lp.OPTIMAL).all()),
                                      "hbm_GBs_algorithmic": n5 * lp5_bytes / t5 / 1e9}
 
+    # ---- extra (N = 1): BASELINE config 5b's tableau (16384 x 65536, 8.6 GB) on ONE GPU through the blocked path,
+    # for comparison with the column-sharded rank-1 runs at N > 1
+    if world == 1 and not args.no_extra and m == M:
+        lm, ln = args.shard_m, 4 * args.shard_m
+        big = lp.DenseTableau(ctx, lm, ln, 1)
+        big.synth(SEED, 0, ln - lm)
+        big.reset(variant=variant, check_every=256)
+        big.run(64)
+        lpv = 256
+        t_big = timed(lambda: big.run(lpv))
+        r_big = big.run(0)
+        big.close()
+        extra["large_tableau_single_gpu"] = {"metric": "pivots_per_sec", "value": lpv / t_big, "unit": "pivots/s",
+                                             "workload": f"one dense tableau {lm}x{ln} fp64 ({(lm + 1) * (ln + 1) * 8 / 1e9:.2f} GB) resident on one GPU, default path",
+                                             "pivots": lpv, "us_per_pivot": 1e6 * t_big / lpv, "iters_after": r_big["iters"]}
+
     # ---- extra (N > 1): BASELINE config 5b, ONE 16384 x 65536 tableau column-sharded over the ranks,
     # candidate + entering-column exchange per pivot over our own NCCL communicator
     if world > 1 and not args.no_extra:

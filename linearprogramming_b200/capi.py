@@ -20,6 +20,7 @@ STATIC = 0x1             # dense: TMA-staged elimination with a static task stri
 DIRECT = 0x2             # dense: direct-load elimination kernel instead of the TMA-staged default
 RANK1 = 0x800            # dense: one pass over the tableau per pivot (default for plain / Big-M: up to K pivots decided on lazily
                          # updated slices, then applied in one pass; K = variant bits 16..21, 0 = 32)
+WS_PASS = 0x100          # dense, blocked path: warp-specialised pass kernel (TMA ring; measured slower, kept as an alternative)
 NO_PDL = 0x400           # dense: plain stream-ordered launches (default: programmatic dependent launch)
 NO_ALTERNATE = 0x200     # dense: do not alternate the sweep direction between pivots
 NCCL_ID_BYTES = 128

@@ -267,7 +267,9 @@ static int launch_block_flush(lpgpu_dense *d) {
     U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.Fs = d->Ft; U.pcn = d->pcn; U.Pm = d->Pm; U.rowstamp = d->rowstamp; U.steprow = d->steprow; U.st = d->st;
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
     U.rb = d->fl_rb; U.pf = d->fl_pf;
-    blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, ctx->stream>>>(U);
+    // variant bit 0x100: the warp-specialised pass (one CTA per SM, TMA ring; slower: see DESIGN.md 4.0)
+    if (!(d->opts.variant & 0x100)) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, ctx->stream>>>(U);
+    else blk_flush_ws_kernel<<<std::min<long>(ctx->sm_count, d->flush_tasks), WS_THREADS, WS_SMEM_BYTES, ctx->stream>>>(U);
     LP_LAUNCH_CHECK(ctx);
     const unsigned fx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, (d->ld + 255) / 256));
     blk_fixrows_kernel<<<dim3(fx, BLK_KMAX), 256, 0, ctx->stream>>>(U);
@@ -308,6 +310,7 @@ int size_grid(lpgpu_dense *d) {
     d->fl_pf = epf ? atoi(epf) : 1;
     const long fsb = ((d->m + d->R + FL_ROWS - 1) / FL_ROWS + d->fl_rb - 1) / d->fl_rb;
     d->grid_flush = (int)std::max(1L, std::min((long)ctx->sm_count * std::max(1, occf), fct * fsb));
+    d->flush_tasks = std::max(1L, fct * fsb);
     return LPGPU_OK;
 }
 
@@ -367,6 +370,8 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     if (e == cudaSuccess) e = cudaMemsetAsync(d->rowstamp, 0, pcn * sizeof(int), ctx->stream);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(blk_flush_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL_SMEM_BYTES);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(blk_flush_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WS_SMEM_BYTES);
     if (e == cudaSuccess) e = cudaHostAlloc(&d->h_st, sizeof(PivotState), cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->T, 0, rows * d->ld * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->prow, 0, d->ld * sizeof(double), ctx->stream);

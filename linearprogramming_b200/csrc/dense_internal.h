@@ -25,6 +25,7 @@ struct lpgpu_dense {
     lpgpu_opts opts;
     int grid_update;
     int grid_flush;         // persistent grid of the blocked path's pass
+    long flush_tasks;       // tasks of one pass
     int fl_rb, fl_pf;       // its row tiles per task and L2 prefetch switch
     int *task_ctr;          // work-stealing counters of the elimination kernel (2 ints)
     unsigned upd_seq;       // elimination launches so far

@@ -206,6 +206,15 @@ def _blocked(K=0):
     return K << 16          # pivots per block (0 = the default, 32); the blocked path is the default for plain / Big-M
 
 
+@pytest.mark.parametrize("m,ns,K", [(64, 64, 0), (300, 500, 7), (512, 512, 32), (700, 1500, 0)])
+def test_blocked_warp_specialised_pass_bitwise(ctx, m, ns, K):
+    """The alternative pass kernel (producer warp + TMA ring, variant WS_PASS) leaves the same bits."""
+    T0, basis = O.synth_feasible(1234, 3, m, ns)
+    ref = O.solve_f64(T0, basis, threads=4, log_cap=8192)
+    got = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K) | capi.WS_PASS)
+    _assert_dense_equal(got, ref)
+
+
 @pytest.mark.parametrize("m,ns", [(32, 32), (64, 64), (200, 120), (300, 500), (512, 512)])
 @pytest.mark.parametrize("K", [0, 1, 2, 5, 32])
 def test_blocked_synth_full_solve_bitwise(ctx, m, ns, K):

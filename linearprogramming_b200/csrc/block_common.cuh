@@ -1,0 +1,116 @@
+// block_common.cuh -- device helpers shared by the blocked path of one tableau (dense_block.cuh) and its
+// column-sharded form (shard.cu): buffers of a block, row stamps, arg-max on order-preserving keys.
+#pragma once
+
+#include "dense_select.cuh"
+
+namespace lpgpu {
+
+constexpr int BLK_KMAX = 32;           // pivots per block at most (shared-memory tile of the pass)
+
+struct KeyCand;
+
+struct BlockBufs {
+    double *Fs;          // BLK_KMAX x pcn: Fs[s*pcn + i] = a_{i,k_s} before step s (the multiplier of row i at step s)
+    KeyCand *cands;      // SELECT_CLUSTER: per-CTA pricing candidates for the next pivot (st->k_next == -2)
+    double *Pm;          // BLK_KMAX x ld: Pm[s*ld + j] = scaled pivot row of step s (col 0 = b_r')
+    double *objcur;      // R x ld: objective rows as of the last decided pivot (row m first)
+    double *bcur;        // pcn: b column as of the last decided pivot (rows < m)
+    int *rowstamp;       // pcn: (block sequence << 8) | (s + 1) if the row was the pivot row of step s of that block
+    int *steprow;        // BLK_KMAX: pivot row of step s of the current block
+    int K;               // pivots per block, 1..BLK_KMAX
+    unsigned long long *dbg;   // LPGPU_BLK_DEBUG=1: 8 globaltimer stamps per launch slot (development aid), else nullptr
+};
+
+__device__ __forceinline__ int blk_row_start(int stamp, int seq) { return ((stamp >> 8) == seq) ? (stamp & 0xff) : 0; }
+
+// ------------------------------------------------------------------ arg-max on order-preserving keys
+// "maximise (p, q), ties to the lowest index" with redux.sync on 64-bit keys instead of shuffle trees
+// of (double, double, int) triples: a warp level is 3 (one key) or 5 (two keys) reductions, a CTA level one
+// barrier, the cluster level one DSMEM exchange.  Only the winning INDEX comes back (and the keys).
+struct KeyCand {
+    unsigned long long kp, kq;     // order-preserving images of p and q
+    int idx;                       // -1 = none
+};
+
+__device__ __forceinline__ KeyCand keycand_none() {
+    KeyCand c;
+    c.kp = 0; c.kq = 0; c.idx = -1;
+    return c;
+}
+
+// any double -> u64 with the same order; -0 and +0 map to the same key (they compare equal)
+__device__ __forceinline__ unsigned long long ord_key(double x) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(x + 0.0);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+
+__device__ __forceinline__ bool keycand_better(const KeyCand &a, const KeyCand &b) {
+    if (a.idx < 0) return false;
+    if (b.idx < 0) return true;
+    if (a.kp != b.kp) return a.kp > b.kp;
+    if (a.kq != b.kq) return a.kq > b.kq;
+    return a.idx < b.idx;
+}
+
+template <bool TWO>
+__device__ __forceinline__ KeyCand warp_key_best(KeyCand c) {
+    constexpr unsigned FULL = 0xffffffffu;
+    bool in = c.idx >= 0;
+    if (__ballot_sync(FULL, in) == 0u) return keycand_none();
+    KeyCand w;
+    w.kp = 0;
+    if (TWO) {
+        const unsigned h = __reduce_max_sync(FULL, in ? (unsigned)(c.kp >> 32) : 0u);
+        in = in && (unsigned)(c.kp >> 32) == h;
+        const unsigned l = __reduce_max_sync(FULL, in ? (unsigned)c.kp : 0u);
+        in = in && (unsigned)c.kp == l;
+        w.kp = ((unsigned long long)h << 32) | l;
+    }
+    const unsigned h = __reduce_max_sync(FULL, in ? (unsigned)(c.kq >> 32) : 0u);
+    in = in && (unsigned)(c.kq >> 32) == h;
+    const unsigned l = __reduce_max_sync(FULL, in ? (unsigned)c.kq : 0u);
+    in = in && (unsigned)c.kq == l;
+    w.kq = ((unsigned long long)h << 32) | l;
+    w.idx = (int)__reduce_min_sync(FULL, in ? (unsigned)c.idx : 0x7fffffffu);
+    return w;
+}
+
+// CTA-wide: per-warp winners through shared memory, one barrier; every warp reduces the winners again, so
+// the result is in all threads.  `scratch`: blockDim.x / 32 entries, used for ONE reduction per launch.
+template <bool TWO>
+__device__ __forceinline__ KeyCand block_key_best(KeyCand c, KeyCand *scratch) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+    c = warp_key_best<TWO>(c);
+    if (lane == 0) scratch[warp] = c;
+    __syncthreads();
+    return warp_key_best<TWO>(lane < nwarp ? scratch[lane] : keycand_none());
+}
+
+// cluster-wide: every CTA pushes its winner into every CTA's `slot` (DSMEM), one cluster barrier
+template <bool TWO>
+__device__ __forceinline__ KeyCand cluster_key_best(cg::cluster_group &cl, KeyCand c, KeyCand *scratch, KeyCand *slot) {
+    c = block_key_best<TWO>(c, scratch);
+    if (threadIdx.x < SELECT_CLUSTER) cl.map_shared_rank(slot, threadIdx.x)[cl.block_rank()] = c;
+    cl.sync();
+    const int lane = threadIdx.x & 31;
+    return warp_key_best<TWO>(lane < SELECT_CLUSTER ? slot[lane] : keycand_none());
+}
+
+// pricing candidate of column j from the (current) objective row values
+__device__ __forceinline__ void blk_price(const DenseParams &P, bool bigm, int j, double oc, double om, KeyCand &c) {
+    KeyCand t;
+    t.idx = j;
+    t.kq = ord_key(oc);
+    if (bigm) {
+        double p = om;
+        if (fabs(p) <= P.eps) p = 0.0;
+        t.kp = ord_key(p);
+        if ((p > 0.0 || (p == 0.0 && oc > P.eps)) && keycand_better(t, c)) c = t;
+    } else {
+        t.kp = 0;
+        if (oc > P.eps && keycand_better(t, c)) c = t;
+    }
+}
+
+}  // namespace lpgpu

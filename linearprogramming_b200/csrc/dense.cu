@@ -234,7 +234,7 @@ bool use_blocked(const lpgpu_dense *d) {
     return !(d->opts.variant & 0x800) && (d->opts.method == LPGPU_PLAIN || d->opts.method == LPGPU_BIGM);
 }
 
-static BlockBufs make_bufs(const lpgpu_dense *d) {
+BlockBufs make_bufs(const lpgpu_dense *d) {
     BlockBufs B;
     B.Fs = d->Ft; B.cands = d->cands; B.Pm = d->Pm; B.objcur = d->objcur; B.bcur = d->bcur; B.rowstamp = d->rowstamp; B.steprow = d->steprow;
     const int k = (d->opts.variant >> 16) & 0x3f;
@@ -243,7 +243,7 @@ static BlockBufs make_bufs(const lpgpu_dense *d) {
     return B;
 }
 
-static int launch_block_init(lpgpu_dense *d) {
+int launch_block_init(lpgpu_dense *d) {
     lpgpu_ctx *ctx = d->ctx;
     blk_init_kernel<<<ctx->sm_count, 1024, 0, ctx->stream>>>(make_params(d), make_bufs(d));
     LP_LAUNCH_CHECK(ctx);
@@ -261,7 +261,7 @@ static int launch_block_step(lpgpu_dense *d, int first) {
     return LPGPU_OK;
 }
 
-static int launch_block_flush(lpgpu_dense *d) {
+int launch_block_flush(lpgpu_dense *d) {
     lpgpu_ctx *ctx = d->ctx;
     FlushParams U;
     U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.Fs = d->Ft; U.pcn = d->pcn; U.Pm = d->Pm; U.rowstamp = d->rowstamp; U.steprow = d->steprow; U.st = d->st;

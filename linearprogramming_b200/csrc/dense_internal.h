@@ -5,9 +5,7 @@
 #include <vector>
 
 #include "ctx.h"
-#include "dense_select.cuh"
-
-namespace lpgpu { struct KeyCand; }
+#include "block_common.cuh"
 
 struct lpgpu_dense {
     lpgpu_ctx *ctx;
@@ -50,5 +48,9 @@ int launch_update(lpgpu_dense *d, double *cnext);
 // rank's exchange region (peer_x: device array of n_peers pointers)
 int launch_update_peers(lpgpu_dense *d, void *const *peer_x, int n_peers, size_t peer_off);
 int read_state(lpgpu_dense *d);
+// blocked path (dense_block.cuh): buffers of the current block, objcur / bcur <- tableau, the pass that applies a block
+BlockBufs make_bufs(const lpgpu_dense *d);
+int launch_block_init(lpgpu_dense *d);
+int launch_block_flush(lpgpu_dense *d);
 
 }  // namespace lpgpu

@@ -285,6 +285,244 @@ shard_select_kernel(ShardParams S) {
     }
 }
 
+// ------------------------------------------------------------------ blocked path, column-sharded (peer-memory transport)
+// The blocked path of dense_block.cuh with the two decisions that need every rank's data exchanged over
+// NVLink inside ONE cluster kernel per pivot and rank:
+//   wait for every rank's pricing candidate of this pivot -> entering column k and its owner;
+//   the OWNER runs its tableau column through the t pivots of the block (its own P, the replicated F) and
+//   stores the result into every rank's exchange region, then the "column complete" flag;
+//   every rank: column -> F[t], ratio test on its replica of b, its slice of row r lazily brought up to
+//   date and scaled -> P[t], objective rows / b updated, local pricing -> candidate of the NEXT pivot posted.
+// The pass that applies a block (blk_flush_kernel) is local: no exchange.  Every rank takes identical
+// decisions from identical data, so no status has to be agreed on.
+constexpr int SSTEP_PB = 8, SSTEP_CPT = 2;
+
+template <int RR>
+__global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
+shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
+    __shared__ KeyCand scr_b[SELECT_THREADS / 32], scr_c[SELECT_THREADS / 32];
+    __shared__ KeyCand slot_b[SELECT_CLUSTER], slot_c[SELECT_CLUSTER];
+    __shared__ double s_pk[BLK_KMAX], s_fr[BLK_KMAX];
+    __shared__ int s_flag;
+    cg::cluster_group cl = cg::this_cluster();
+    const DenseParams &P = S.P;
+    const int crank = (int)cl.block_rank();
+    const int gtid = crank * SELECT_THREADS + (int)threadIdx.x;
+    constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
+
+    PivotState *st = P.st;
+    const int status0 = st->status, iters = st->iters, budget = st->budget;
+    const int t = first ? 0 : st->blk_t, seq = st->blk_seq + (first ? 1 : 0);
+    const bool bigm = (P.method == LPGPU_BIGM);
+    const double *oc = B.objcur, *om = B.objcur + P.ld;
+    const size_t pcn = P.pcn;
+    const int rows = P.m + RR;
+
+    // ---- every rank's candidate of this pivot (posted at the end of the previous step or by the bootstrap)
+    const unsigned pit = S.iter - 1u;
+    const int ppar = (int)(pit & 1u);
+    {
+        int ok = 1;
+        if (threadIdx.x < (unsigned)S.world)
+            ok = spin_until(xptr<unsigned>(S.peer_x[S.rank], XLayout::pair_flag(ppar)) + threadIdx.x, pit + 1u, XCHG_TIMEOUT_NS);
+        if (!__syncthreads_and(ok)) {                       // every CTA of the cluster times out alike
+            cl.sync();
+            if (gtid == 0) { st->status = LPGPU_EXCHANGE_TIMEOUT; st->do_pivot = 0; }
+            return;
+        }
+    }
+    int owner = 0;
+    const Cand best = best_pair(xptr<double>(S.peer_x[S.rank], XLayout::pairs(ppar)), S.world, &owner);
+    const int k = best.idx > 0 ? best.idx : 0;              // GLOBAL column
+    const bool mine = (k > 0) && (owner == S.rank);
+    const int kl = mine ? k - S.col0 + 1 : 0;
+    const int par = (int)(S.iter & 1u);
+    double *mycol = xptr<double>(S.peer_x[S.rank], XLayout::cols(par, pcn));
+
+    int status = status0, r = -1;
+    bool have = false;
+    if (status0 == LPGPU_RUNNING) {
+        if (k == 0) {
+            // nothing prices in anywhere: optimal, unless Big-M left an artificial basic at a positive level
+            int f = 0;
+            if (bigm) {
+                const int nreal = S.n_global - S.n_art;
+                for (int i = (int)threadIdx.x; i < P.m; i += blockDim.x)
+                    if (P.basis[i] > nreal && B.bcur[i] > P.eps) f = 1;
+            }
+            status = __syncthreads_or(f) ? LPGPU_INFEASIBLE : LPGPU_OPTIMAL;       // every CTA scans all rows: same answer
+        } else {
+            // ---- the owner: column k as it stands after the t pivots of this block -> every rank's region
+            if (mine) {
+                if ((int)threadIdx.x < t) s_pk[threadIdx.x] = B.Pm[(size_t)threadIdx.x * P.ld + (size_t)kl];
+                __syncthreads();
+                for (int i = gtid; i < rows; i += GSTRIDE) {
+                    double a;
+                    if (i >= P.m) a = oc[(size_t)(i - P.m) * P.ld + kl];           // objective rows are kept eagerly: same bits
+                    else {
+                        const int s0 = blk_row_start(B.rowstamp[i], seq);
+                        a = s0 ? s_pk[s0 - 1] : P.T[(size_t)i * P.ld + (size_t)kl];
+                        for (int sb = s0; sb < t; sb += 8) {
+                            double fv[8];
+#pragma unroll
+                            for (int u = 0; u < 8; ++u) fv[u] = (sb + u < t) ? B.Fs[(size_t)(sb + u) * pcn + i] : 0.0;
+#pragma unroll
+                            for (int u = 0; u < 8; ++u)
+                                if (sb + u < t) a = __fma_rn(-fv[u], s_pk[sb + u], a);
+                        }
+                    }
+                    for (int g = 0; g < S.world; ++g) xptr<double>(S.peer_x[g], XLayout::cols(par, pcn))[i] = a;
+                }
+                __threadfence_system();                     // this thread's stores into the peers, before the flag below
+                cl.sync();
+                if (gtid < S.world) st_release_sys(xptr<unsigned>(S.peer_x[gtid], XLayout::col_flag(par)), S.iter + 1u);
+            }
+            // ---- every rank: the column of this pivot has landed in its region
+            if (threadIdx.x == 0) s_flag = spin_until(xptr<unsigned>(S.peer_x[S.rank], XLayout::col_flag(par)), S.iter + 1u, XCHG_TIMEOUT_NS) ? 1 : 0;
+            __syncthreads();
+            if (!s_flag) {
+                cl.sync();
+                if (gtid == 0) { st->status = LPGPU_EXCHANGE_TIMEOUT; st->do_pivot = 0; }
+                return;
+            }
+            KeyCand c = keycand_none();
+            for (int i = gtid; i < rows; i += GSTRIDE) {
+                const double a = __ldcg(mycol + i);
+                B.Fs[(size_t)t * pcn + i] = a;
+                if (i < P.m && a > P.eps) {
+                    KeyCand x;
+                    x.kp = 0;
+                    x.kq = ord_key(-(B.bcur[i] / a));
+                    x.idx = i;
+                    if (keycand_better(x, c)) c = x;
+                }
+            }
+            c = cluster_key_best<false>(cl, c, scr_b, slot_b);
+            if (c.idx < 0) status = LPGPU_UNBOUNDED;
+            else if (iters >= P.max_iter) status = LPGPU_ITER_LIMIT;
+            else if (budget > 0) { have = true; r = c.idx; }
+        }
+    }
+    if (!have) {
+        cl.sync();                                          // all state reads are done
+        if (gtid == 0) {
+            st->status = status;
+            st->do_pivot = 0;
+            st->blk_t = t;
+            st->blk_seq = seq;
+            if (S.post) post_pair(S);                       // the same candidate again: peers expect one every iteration
+        }
+        return;
+    }
+
+    // ---- this rank's slice of row r, brought up to date and scaled; objective rows; local pricing
+    const double sig_c = __ldcg(mycol + P.m);
+    const double sig_m = (RR == 2) ? __ldcg(mycol + P.m + 1) : 0.0;
+    const double piv = __ldcg(mycol + r);
+    double av[SSTEP_CPT], ocv[SSTEP_CPT], omv[SSTEP_CPT];
+    const size_t jb = 1 + (size_t)gtid;
+#pragma unroll
+    for (int cth = 0; cth < SSTEP_CPT; ++cth) {
+        const size_t j = jb + (size_t)cth * GSTRIDE;
+        av[cth] = ocv[cth] = omv[cth] = 0.0;
+        if (j <= (size_t)P.n) {
+            av[cth] = P.T[(size_t)r * P.ld + j];
+            ocv[cth] = oc[j];
+            if (RR == 2) omv[cth] = om[j];
+        }
+    }
+    const int s0r = blk_row_start(B.rowstamp[r], seq);
+    const double b_r = B.bcur[r];
+    if ((int)threadIdx.x < t) s_fr[threadIdx.x] = B.Fs[(size_t)threadIdx.x * pcn + r];
+    __syncthreads();
+    double *pt = B.Pm + (size_t)t * P.ld;
+    const double brp = div_skip_zero(b_r, piv);
+    KeyCand c = keycand_none();
+    if (gtid == 0) {                                        // column 0 (the replica of b and the z cells)
+        pt[0] = brp;
+        B.objcur[0] = __fma_rn(-sig_c, brp, oc[0]);
+        if (RR == 2) B.objcur[P.ld] = __fma_rn(-sig_m, brp, om[0]);
+    }
+    for (size_t j0 = jb; j0 <= (size_t)P.n; j0 += (size_t)SSTEP_CPT * GSTRIDE) {
+        if (j0 != jb) {
+#pragma unroll
+            for (int cth = 0; cth < SSTEP_CPT; ++cth) {
+                const size_t j = j0 + (size_t)cth * GSTRIDE;
+                if (j <= (size_t)P.n) { av[cth] = P.T[(size_t)r * P.ld + j]; ocv[cth] = oc[j]; if (RR == 2) omv[cth] = om[j]; }
+            }
+        }
+        if (s0r > 0) {
+#pragma unroll
+            for (int cth = 0; cth < SSTEP_CPT; ++cth) {
+                const size_t j = j0 + (size_t)cth * GSTRIDE;
+                if (j <= (size_t)P.n) av[cth] = B.Pm[(size_t)(s0r - 1) * P.ld + j];
+            }
+        }
+        for (int sb = s0r; sb < t; sb += SSTEP_PB) {
+            double pv[SSTEP_CPT][SSTEP_PB];
+#pragma unroll
+            for (int cth = 0; cth < SSTEP_CPT; ++cth) {
+                const size_t j = j0 + (size_t)cth * GSTRIDE;
+#pragma unroll
+                for (int u = 0; u < SSTEP_PB; ++u) pv[cth][u] = (sb + u < t && j <= (size_t)P.n) ? B.Pm[(size_t)(sb + u) * P.ld + j] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < SSTEP_PB; ++u)
+                if (sb + u < t) {
+#pragma unroll
+                    for (int cth = 0; cth < SSTEP_CPT; ++cth) av[cth] = __fma_rn(-s_fr[sb + u], pv[cth][u], av[cth]);
+                }
+        }
+#pragma unroll
+        for (int cth = 0; cth < SSTEP_CPT; ++cth) {
+            const size_t j = j0 + (size_t)cth * GSTRIDE;
+            if (j <= (size_t)P.n) {
+                const double pr = div_skip_zero(av[cth], piv);
+                pt[j] = pr;
+                const double qc = __fma_rn(-sig_c, pr, ocv[cth]);
+                B.objcur[j] = qc;
+                double qm = 0.0;
+                if (RR == 2) {
+                    qm = __fma_rn(-sig_m, pr, omv[cth]);
+                    B.objcur[P.ld + j] = qm;
+                }
+                blk_price(P, bigm, (int)j, qc, qm, c);
+            }
+        }
+    }
+    for (int i = gtid; i < P.m; i += GSTRIDE)
+        B.bcur[i] = (i == r) ? brp : __fma_rn(-B.Fs[(size_t)t * pcn + i], brp, B.bcur[i]);
+    // ---- this rank's candidate for the next pivot -> every rank
+    c = bigm ? cluster_key_best<true>(cl, c, scr_c, slot_c) : cluster_key_best<false>(cl, c, scr_c, slot_c);
+    if (gtid == 0) {
+        Cand out = cand_none();
+        if (c.idx > 0) {
+            out.idx = c.idx;
+            out.q = __ldcg(B.objcur + c.idx);               // written above, possibly by another CTA
+            out.p = 0.0;
+            if (bigm) {
+                double p = __ldcg(B.objcur + P.ld + c.idx);
+                if (fabs(p) <= P.eps) p = 0.0;
+                out.p = p;
+            }
+        }
+        store_pair(S.sendpair, out, S.col0);
+        post_pair(S);
+        P.basis[r] = k;
+        B.rowstamp[r] = (seq << 8) | (t + 1);
+        B.steprow[t] = r;
+        st->status = status;
+        st->do_pivot = 1;
+        st->r = r;
+        st->k = k;
+        st->iters = iters + 1;
+        st->budget = budget - 1;
+        st->blk_t = t + 1;
+        st->blk_seq = seq;
+        if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
+    }
+}
+
 __global__ void shard_synth_kernel(double *T, size_t ld, int m, int ns, int col0, int ncols, int *basis,
                                    uint64_t seed, uint64_t lp) {
     const size_t total = (size_t)(m + 1) * ld;
@@ -335,6 +573,8 @@ struct lpgpu_shard {
     double *xbuf;
     size_t pcn;
     bool dirty;                       // tableau changed since the last lookahead (upload / synth / reset)
+    bool blk_open;                    // blocked path: steps enqueued since the last pass over the tableau
+    int blk_steps;
     lpgpu_opts opts;
 };
 
@@ -498,7 +738,7 @@ int shard_create_common(lpgpu_ctx *ctx, int rank, int world, int transport, cons
     s->ctx = ctx; s->world = world; s->m = m; s->n = n; s->R = R;
     s->use_nccl = transport == 1; s->use_p2p = transport == 2; s->attached = false; s->comm = nullptr;
     s->xregion = nullptr; s->peer_host = nullptr; s->peer_dev = nullptr; s->iter = 0;
-    s->pairs_buf = s->gath_buf = s->xbuf = nullptr; s->dirty = true;
+    s->pairs_buf = s->gath_buf = s->xbuf = nullptr; s->dirty = true; s->blk_open = false; s->blk_steps = 0;
     lpgpu_default_opts(&s->opts);
     s->opts.method = (R == 1) ? LPGPU_PLAIN : LPGPU_BIGM;
     int rc = LPGPU_OK;
@@ -615,6 +855,8 @@ int lpgpu_shard_reset(lpgpu_shard *s, const lpgpu_opts *opts) {
         if (rc != LPGPU_OK) return rc;
     }
     s->dirty = true;
+    s->blk_open = false;
+    s->blk_steps = 0;
     return LPGPU_OK;
 }
 
@@ -650,6 +892,89 @@ int lpgpu_shard_synth(lpgpu_shard *s, uint64_t seed, uint64_t lp_index, int ns) 
     return LPGPU_OK;
 }
 
+static int shard_finish(lpgpu_shard *s, lpgpu_result *res, int passes) {
+    lpgpu_ctx *ctx = s->ctx;
+    lpgpu_dense *d0 = s->rk[0].d;
+    if (d0->h_st->status == LPGPU_EXCHANGE_TIMEOUT)
+        return fail(ctx, LPGPU_ENCCL, "shard_run: a peer did not post its part of the exchange within %llu s", XCHG_TIMEOUT_NS / 1000000000ull);
+    double zc[2] = {0.0, 0.0};
+    LP_CUDA(ctx, cudaMemcpyAsync(&zc[0], d0->T + (size_t)s->m * d0->ld, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (s->R == 2)
+        LP_CUDA(ctx, cudaMemcpyAsync(&zc[1], d0->T + (size_t)(s->m + 1) * d0->ld, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    memset(res, 0, sizeof *res);
+    res->status = d0->h_st->status;
+    res->iters = d0->h_st->iters;
+    res->z = -zc[0];
+    res->zM = (s->R == 2) ? -zc[1] : 0.0;
+    res->n_logged = std::min(res->iters, d0->log_cap);
+    res->update_launches = passes;
+    return LPGPU_OK;
+}
+
+// Blocked path over the peer-memory transport: one cluster kernel per pivot (exchanges inside), one local
+// pass over the rank's column block per K pivots.  The host loop is a replica on every rank.
+static int shard_run_blocked(lpgpu_shard *s, int max_pivots, lpgpu_result *res) {
+    lpgpu_ctx *ctx = s->ctx;
+    ShardRank &r = s->rk[0];
+    lpgpu_dense *d = r.d;
+    int rc = read_state(d);
+    if (rc != LPGPU_OK) return rc;
+    PivotState st = *d->h_st;
+    st.budget = max_pivots;
+    st.cur = 0;
+    if ((rc = push_state(s, st)) != LPGPU_OK) return rc;
+    const int K = make_bufs(d).K;
+    auto step = [&](int post) -> int {
+        ShardParams S = shard_params(s, r);
+        S.post = post;
+        const int first = s->blk_open ? 0 : 1;
+        if (s->R == 2) shard_blk_step_kernel<2><<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(S, make_bufs(d), first);
+        else shard_blk_step_kernel<1><<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(S, make_bufs(d), first);
+        LP_LAUNCH_CHECK(ctx);
+        return LPGPU_OK;
+    };
+    int passes = 0;
+    auto flush = [&]() -> int {
+        const int rc2 = launch_block_flush(d);
+        s->blk_open = false;
+        s->blk_steps = 0;
+        ++passes;
+        return rc2;
+    };
+    if (s->dirty) {
+        // bootstrap: objective rows / b column out of the tableau, local pricing, candidate posted as iteration iter
+        if ((rc = launch_block_init(d)) != LPGPU_OK) return rc;
+        shard_price_kernel<<<1, SELECT_THREADS, 0, ctx->stream>>>(shard_params(s, r));
+        LP_LAUNCH_CHECK(ctx);
+        s->iter++;
+        s->dirty = false;
+        s->blk_open = false;
+        s->blk_steps = 0;
+    }
+    const int chunk_max = s->opts.check_every;
+    int launched = 0;
+    while (launched < max_pivots) {
+        const int chunk = std::min(chunk_max, max_pivots - launched);
+        for (int c = 0; c < chunk; ++c) {
+            if ((rc = step(1)) != LPGPU_OK) return rc;
+            s->iter++;
+            s->blk_open = true;
+            if (++s->blk_steps >= K && (rc = flush()) != LPGPU_OK) return rc;
+        }
+        launched += chunk;
+        if ((rc = read_state(d)) != LPGPU_OK) return rc;
+        if (d->h_st->status != LPGPU_RUNNING) break;
+    }
+    if (s->blk_open && (rc = flush()) != LPGPU_OK) return rc;
+    if (d->h_st->status == LPGPU_RUNNING) {
+        // budget spent: one decision-only step (same iteration, nothing posted) settles a terminal status
+        if ((rc = step(0)) != LPGPU_OK) return rc;
+    }
+    if ((rc = read_state(d)) != LPGPU_OK) return rc;
+    return shard_finish(s, res, passes);
+}
+
 int lpgpu_shard_run(lpgpu_shard *s, int max_pivots, lpgpu_result *res) {
     if (!s || !res || max_pivots < 0) return LPGPU_EINVAL;
     lpgpu_ctx *ctx = s->ctx;
@@ -663,6 +988,8 @@ int lpgpu_shard_run(lpgpu_shard *s, int max_pivots, lpgpu_result *res) {
     st.cur = 0;
     rc = push_state(s, st);
     if (rc != LPGPU_OK) return rc;
+    // peer-memory transport, default: the blocked path (variant bit 0x800 selects the rank-1 pipeline below)
+    if (s->use_p2p && !(s->opts.variant & 0x800)) return shard_run_blocked(s, max_pivots, res);
     if (s->dirty) {
         // bootstrap: price the tableau as it stands, fetch the entering column from its owner (strided)
         for (ShardRank &r : s->rk) {

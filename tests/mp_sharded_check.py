@@ -24,7 +24,11 @@ def main():
     dist.init_process_group("gloo")                      # host plumbing only; the data path is our own NCCL comm
     ctx = lp.Context(local)
     window = int(os.environ.get("MP_WINDOW", "9"))
-    for transport in os.environ.get("MP_TRANSPORTS", "nccl,p2p").split(","):
+    # peer-memory transport: the blocked path (default; blocks of 32 and of 5 pivots) and the rank-1 pipeline (0x800)
+    runs = [(t, 0) for t in os.environ.get("MP_TRANSPORTS", "nccl,p2p").split(",")]
+    if any(t == "p2p" for t, _ in runs):
+        runs += [("p2p", 5 << 16), ("p2p", 0x800)]
+    for transport, variant in runs:
       for (m, ns, method) in [(64, 48, O.PLAIN), (300, 260, O.PLAIN), (40, 30, O.BIGM)]:
           if method == O.PLAIN:
               T, basis = O.synth_feasible(1234, 7, m, ns)
@@ -43,7 +47,7 @@ def main():
               s = lp.ShardedTableau(ctx, m, n, R, world=world, rank=rank, p2p=True)
               sharding.attach_p2p(dist, s)
           s.upload(T, basis)
-          s.reset(method=method, n_art=n_art, log_cap=8192)
+          s.reset(method=method, n_art=n_art, log_cap=8192, variant=variant)
           if transport == "p2p" and window > 0:
               while True:                                   # windows of 9 pivots: flags keep counting across run calls
                   res = s.run(window)

@@ -440,7 +440,7 @@ def gpu_arm(args):
         sm_, sn_ = args.shard_m, 4 * args.shard_m
         sp = args.shard_pivots
         per_transport = {}
-        for transport in ("p2p", "nccl"):
+        for transport in ("p2p", "p2p_rank1", "nccl"):
             if transport == "nccl":
                 ident = sharding.exchange_nccl_id(dist)
                 sh = lp.ShardedTableau(ctx, sm_, sn_, 1, world=world, rank=rank, nccl_id=ident)
@@ -448,22 +448,27 @@ def gpu_arm(args):
                 sh = lp.ShardedTableau(ctx, sm_, sn_, 1, world=world, rank=rank, p2p=True)
                 sharding.attach_p2p(dist, sh)
             sh.synth(SEED, 0, sn_ - sm_)
-            sh.reset()
-            sh.run(20)
-            per_transport[transport] = max_over_ranks(timed(lambda: sh.run(sp)))
-            r_s = sh.run(0)
+            sh.reset(variant=RANK1 if transport == "p2p_rank1" else 0, check_every=256)
+            sh.run(64 if transport == "p2p" else 20)
+            npv = 4 * sp if transport == "p2p" else sp
+            per_transport[transport] = max_over_ranks(timed(lambda: sh.run(npv))) / npv
+            if transport == "p2p":
+                r_s = sh.run(0)
             barrier()               # p2p: nobody unmaps while a peer may still store into its region
             sh.close()
         t_s = per_transport["p2p"]
         s_bytes = 16 * (sm_ + 1) * (sn_ + 1)
-        extra["column_sharded"] = {"metric": "pivots_per_sec", "value": sp / t_s, "unit": "pivots/s",
+        extra["column_sharded"] = {"metric": "pivots_per_sec", "value": 1.0 / t_s, "unit": "pivots/s",
                                    "workload": f"one dense tableau {sm_}x{sn_} fp64 column-sharded over {world} GPUs",
-                                   "pivots": sp, "us_per_pivot": 1e6 * t_s / sp, "iters_after": r_s["iters"],
-                                   "hbm_GBs_algorithmic_total": sp * s_bytes / t_s / 1e9,
-                                   "frac_of_measured_peak_per_gpu": sp * s_bytes / t_s / 1e9 / world / peak,
-                                   "exchange": "peer-memory stores over NVLink from inside the select / elimination "
-                                               "kernels (32 B candidates, 8*(m+1) B column per pivot)",
-                                   "us_per_pivot_nccl_allgather_transport": 1e6 * per_transport["nccl"] / sp}
+                                   "path": "blocked: per pivot one cluster kernel per rank (candidates and the owner's lazily "
+                                           "updated entering column exchanged as NVLink peer stores inside it), one local pass "
+                                           "over the rank's column block per 32 pivots",
+                                   "pivots": 4 * sp, "us_per_pivot": 1e6 * t_s, "iters_after": r_s["iters"],
+                                   "rank1_pipeline": {"us_per_pivot_peer_memory": 1e6 * per_transport["p2p_rank1"],
+                                                      "us_per_pivot_nccl_allgather": 1e6 * per_transport["nccl"],
+                                                      "pivots_per_sec_peer_memory": 1.0 / per_transport["p2p_rank1"],
+                                                      "hbm_GBs_algorithmic_total": s_bytes / per_transport["p2p_rank1"] / 1e9,
+                                                      "frac_of_measured_peak_per_gpu": s_bytes / per_transport["p2p_rank1"] / 1e9 / world / peak}}
 
     line = {
         "metric": "pivots_per_sec", "value": value, "unit": "pivots/s", "n_gpus": world, "steps": K, "warmup": W,

@@ -177,6 +177,33 @@ def test_sharded_p2p_transport_world1(ctx):
     _assert_equal(res, ref)
 
 
+@pytest.mark.parametrize("variant", [0, 3 << 16, 0x800])
+def test_sharded_p2p_world1_blocked_and_rank1_bigm(ctx, variant):
+    """Peer-memory transport, one rank: the blocked path (default, blocks of 32 and 3) and the rank-1 pipeline on
+    Big-M problems incl. infeasible ones; bit-exact against the oracle."""
+    for seed in range(4):
+        rng = np.random.default_rng(900 + seed)
+        m, ns = int(rng.integers(4, 40)), int(rng.integers(4, 40))
+        A, b, c, rel = H.random_mixed_lp(rng, m, ns)
+        if seed == 3:
+            A = np.vstack([A, A[0]]); b = np.append(b, b[0] - 5.0 if rel[0] != -2 else b[0] + 5.0)
+            rel = np.append(rel, -2 if rel[0] != -2 else 2).astype(np.int32)
+        T, basis, n_art = O.build_tableau(A, b, c, rel, R=2)
+        ref = O.solve_f64(T, basis, method=O.BIGM, n_art=n_art, log_cap=4096)
+        s = lp.ShardedTableau(ctx, T.shape[0] - 2, T.shape[1] - 1, 2, world=1, rank=0, p2p=True)
+        s.upload(T, basis)
+        s.reset(method=O.BIGM, n_art=n_art, log_cap=4096, variant=variant, check_every=4)
+        while True:
+            res = s.run(11)
+            if res["status"] != lp.RUNNING:
+                break
+        out = s.download()
+        s.close()
+        res.update(T=out["T"], basis=out["basis"], log=out["log"][:res["n_logged"]], x=out["x"])
+        _assert_equal(res, ref)
+        assert res["zM"] == ref["zM"]
+
+
 def test_sharded_nccl_two_processes():
     """One process per GPU (torchrun), NCCL and peer-memory transports, bit-compared with the oracle inside the script."""
     import torch

@@ -186,6 +186,113 @@ def test_column_sharded_protocol_matches_single_process_oracle(world, case):
     _spawn(_check_sharded, world, case)
 
 
+# ------------------------------------------------------------------ blocked column-sharded protocol over gloo
+def _fma(a, b, c):
+    """round(a*b + c) with ONE rounding, as the device's __fma_rn (exact rational arithmetic; tiny sizes only)."""
+    from fractions import Fraction
+    return float(Fraction(a) * Fraction(b) + Fraction(c))
+
+
+def _sharded_blocked_emulated(dist, rank, world, T, basis, method, n_art, K, max_iter=10_000):
+    """shard_blk_step_kernel + blk_flush_kernel, restated: up to K pivots are decided on lazily updated slices
+    (the owner's entering column through the block's earlier pivots, every rank's slice of the pivot row), the
+    objective rows and b are kept eagerly, and the block is applied to the local column block in one pass."""
+    R = 1 if method == O.PLAIN else 2
+    m, n = T.shape[0] - R, T.shape[1] - 1
+    c0, nc = S.column_block(n, world, rank)
+    Tl = np.ascontiguousarray(np.concatenate([T[:, :1], T[:, c0:c0 + nc]], axis=1))     # [b | block]
+    obj, bcur = Tl[m:, :].copy(), Tl[:m, 0].copy()
+    basis = basis.copy()
+    F, P, start, log = [], [], {}, []
+
+    def lazy(i, j, upto):
+        s0 = start.get(i, 0)
+        a = P[s0 - 1][j] if s0 else Tl[i, j]
+        for s in range(s0, upto):
+            a = _fma(-F[s][i], P[s][j], a)
+        return a
+
+    def flush():
+        nonlocal F, P, start
+        t = len(F)
+        if t:
+            new = np.array([[lazy(i, j, t) for j in range(1 + nc)] for i in range(m + R)])
+            assert np.array_equal(new[m:, :], obj) and np.array_equal(new[:m, 0], bcur)   # eager copies == the chain
+            Tl[...] = new
+        F, P, start = [], [], {}
+
+    while True:
+        cand = _local_candidate(obj[0, 1:1 + nc], obj[1, 1:1 + nc] if R == 2 else None, c0, method)
+        pairs = [None] * world
+        dist.all_gather_object(pairs, cand)                       # candidates of this pivot
+        best, owner = (0.0, 0.0, -1), 0
+        for g, c in enumerate(pairs):
+            if _better(c, best):
+                best, owner = c, g
+        k, t = best[2], len(F)
+        status = None
+        if k < 0:
+            nreal = n - n_art
+            bad = method == O.BIGM and any(basis[i] > nreal and bcur[i] > EPS for i in range(m))
+            status = O.INFEASIBLE if bad else O.OPTIMAL
+        else:
+            box = [None]
+            if owner == rank:                                     # the owner's column, brought up to date lazily
+                kl = 1 + k - c0
+                box[0] = np.array([lazy(i, kl, t) for i in range(m)] + [obj[q, kl] for q in range(R)])
+            dist.broadcast_object_list(box, src=owner)
+            col = box[0]
+            r, theta = -1, None
+            for i in range(m):
+                if col[i] > EPS:
+                    q = bcur[i] / col[i]
+                    if theta is None or q < theta:
+                        r, theta = i, q
+            if r < 0:
+                status = O.UNBOUNDED
+            elif len(log) >= max_iter:
+                status = O.ITER_LIMIT
+        if status is not None:
+            flush()
+            return status, log, Tl, basis
+        row = np.array([lazy(r, j, t) for j in range(1 + nc)])
+        pr = np.where(row == 0.0, row, row / col[r])              # div_skip_zero
+        for q in range(R):
+            obj[q, :] = [_fma(-col[m + q], pr[j], obj[q, j]) for j in range(1 + nc)]
+        bcur[:] = [pr[0] if i == r else _fma(-col[i], pr[0], bcur[i]) for i in range(m)]
+        F.append(col); P.append(pr)
+        start[r] = t + 1
+        basis[r] = k
+        log.append((k, r))
+        if len(F) >= K:
+            flush()
+
+
+def _check_sharded_blocked(dist, rank, world, case, K):
+    import helpers as H
+    if case == "synth":
+        T, basis = O.synth_feasible(1234, 3, 16, 12)
+        method, n_art = O.PLAIN, 0
+    else:
+        rng = np.random.default_rng(7)
+        A, b, c, rel = H.random_mixed_lp(rng, 10, 8)
+        T, basis, n_art = O.build_tableau(A, b, c, rel, R=2)
+        method = O.BIGM
+    ref = O.solve_f64(T, basis, method=method, n_art=n_art, log_cap=4096)
+    status, log, Tl, bs = _sharded_blocked_emulated(dist, rank, world, T, basis, method, n_art, K)
+    n = T.shape[1] - 1
+    c0, nc = S.column_block(n, world, rank)
+    assert status == ref["status"]
+    assert [list(p) for p in log] == ref["log"].tolist()
+    assert np.array_equal(bs, ref["basis"])
+    assert np.array_equal(Tl[:, 0], ref["T"][:, 0]) and np.array_equal(Tl[:, 1:], ref["T"][:, c0:c0 + nc])
+
+
+@pytest.mark.parametrize("world,case,K", [(2, "synth", 32), (2, "synth", 3), (3, "synth", 5), (2, "bigm", 4)])
+def test_blocked_column_sharded_protocol_matches_oracle(world, case, K):
+    _spawn(_check_sharded_blocked, world, case, K)
+
+
 # ------------------------------------------------------------------ batched sharding + id exchange over gloo
 def _check_batched(dist, rank, world):
     n_lp, m, ns = 37, 8, 8

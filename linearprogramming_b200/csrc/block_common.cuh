@@ -97,19 +97,24 @@ __device__ __forceinline__ KeyCand cluster_key_best(cg::cluster_group &cl, KeyCa
     return warp_key_best<TWO>(lane < SELECT_CLUSTER ? slot[lane] : keycand_none());
 }
 
-// pricing candidate of column j from the (current) objective row values
-__device__ __forceinline__ void blk_price(const DenseParams &P, bool bigm, int j, double oc, double om, KeyCand &c) {
+// pricing candidate of column j from the (current) objective row values.  mode: 0 = cost row alone (plain,
+// two-phase main phase), 1 = Big-M (M row first, cost row second), 2 = two-phase phase one (row m+1 alone)
+enum { PRICE_COST = 0, PRICE_BIGM = 1, PRICE_PHASE1 = 2 };
+
+__device__ __forceinline__ void blk_price(const DenseParams &P, int mode, int j, double oc, double om, KeyCand &c) {
     KeyCand t;
     t.idx = j;
-    t.kq = ord_key(oc);
-    if (bigm) {
+    if (mode == PRICE_BIGM) {
         double p = om;
         if (fabs(p) <= P.eps) p = 0.0;
         t.kp = ord_key(p);
+        t.kq = ord_key(oc);
         if ((p > 0.0 || (p == 0.0 && oc > P.eps)) && keycand_better(t, c)) c = t;
     } else {
+        const double q = (mode == PRICE_PHASE1) ? om : oc;
         t.kp = 0;
-        if (oc > P.eps && keycand_better(t, c)) c = t;
+        t.kq = ord_key(q);
+        if (q > P.eps && keycand_better(t, c)) c = t;
     }
 }
 

@@ -231,7 +231,8 @@ int read_state(lpgpu_dense *d) {
 // ---- blocked path (dense_block.cuh): the default for the plain and Big-M methods; variant bit 0x800 selects the
 // rank-1 path instead; pivots per block in variant bits 16..21 (0 = 32)
 bool use_blocked(const lpgpu_dense *d) {
-    return !(d->opts.variant & 0x800) && (d->opts.method == LPGPU_PLAIN || d->opts.method == LPGPU_BIGM);
+    return !(d->opts.variant & 0x800) &&
+           (d->opts.method == LPGPU_PLAIN || d->opts.method == LPGPU_BIGM || d->opts.method == LPGPU_TWOPHASE);
 }
 
 BlockBufs make_bufs(const lpgpu_dense *d) {
@@ -535,7 +536,25 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
             kinds.clear();
             return LPGPU_OK;
         };
-        while (launched < max_pivots) {
+        // two-phase: the drive-out pivots between the phases are decided by the rank-1 path's full decision
+        // (it scans tableau rows), a few pivots at a time, on a tableau brought up to date first; afterwards the
+        // blocked path re-reads its objective rows and b column and carries on in the main phase
+        auto driveout = [&]() -> int {
+            while (d->h_st->status == LPGPU_RUNNING && d->h_st->phase == PH_DRIVEOUT && launched < max_pivots) {
+                const int chunk = std::min(8, max_pivots - launched);
+                for (int c = 0; c < chunk; ++c) {
+                    int rc2 = launch_select(d, -1, 0);
+                    if (rc2 == LPGPU_OK) rc2 = launch_update(d, nullptr);
+                    if (rc2 != LPGPU_OK) return rc2;
+                }
+                launched += chunk;
+                const int rc2 = read_state(d);
+                if (rc2 != LPGPU_OK) return rc2;
+            }
+            return launch_block_init(d);
+        };
+        if (d->h_st->phase == PH_DRIVEOUT) { rc = driveout(); if (rc != LPGPU_OK) return rc; }
+        while (launched < max_pivots && d->h_st->status == LPGPU_RUNNING) {
             const int chunk = std::min(chunk_max, max_pivots - launched);
             for (int c = 0; c < chunk; ++c) {
                 rc = enqueue(0, d->blk_open ? 0 : 1);
@@ -543,15 +562,24 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
                 d->blk_open = true;
                 if (++d->blk_steps >= K) { rc = flush(); if (rc != LPGPU_OK) return rc; }
             }
-            launched += chunk;
             rc = read_state(d);
             if (rc == LPGPU_OK && timed) rc = collect();
             if (rc != LPGPU_OK) return rc;
+            // launches after a phase switch (or a terminal status) were no-ops: only the applied pivots count
+            launched += (d->h_st->status == LPGPU_RUNNING && d->h_st->phase == PH_DRIVEOUT) ? d->h_st->iters - iters_before : chunk;
+            iters_before = d->h_st->iters;
             if (d->h_st->status != LPGPU_RUNNING) break;
+            if (d->h_st->phase == PH_DRIVEOUT) {
+                if (d->blk_open) { rc = flush(); if (rc != LPGPU_OK) return rc; }
+                rc = driveout();
+                if (rc != LPGPU_OK) return rc;
+                iters_before = d->h_st->iters;
+            }
         }
         if (d->blk_open) { rc = flush(); if (rc != LPGPU_OK) return rc; }
         if (d->h_st->status == LPGPU_RUNNING) {
-            rc = launch_block_step(d, 1);       // decision only (budget is spent): settles a terminal status
+            // decision only (budget is spent): settles a terminal status
+            rc = (d->h_st->phase == PH_DRIVEOUT) ? launch_select(d, -1, 0) : launch_block_step(d, 1);
             if (rc != LPGPU_OK) return rc;
         }
         rc = read_state(d);

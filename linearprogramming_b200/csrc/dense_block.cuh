@@ -78,32 +78,41 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     const bool bigm = (P.method == LPGPU_BIGM);
     const double *oc = B.objcur, *om = B.objcur + P.ld;          // om valid for R == 2 only
     const size_t pcn = P.pcn;
+    // two-phase: phase one prices row m+1 over all columns, the main phase row m without the artificial columns;
+    // the drive-out pivots between them are decided by the rank-1 path on an up-to-date tableau (host loop)
+    const int phase0 = st->phase;
+    const int pmode = bigm ? PRICE_BIGM : (phase0 == PH_ONE ? PRICE_PHASE1 : PRICE_COST);
+    const int jmax = (P.method == LPGPU_TWOPHASE && phase0 == PH_MAIN) ? P.n - P.n_art : P.n;
+    const bool two_keys = bigm;
 
-    int status = status0, k = 0, r = -1;
+    int status = status0, k = 0, r = -1, phase = phase0, p1 = st->phase1_iters;
     bool have = false;
     double sig_c = 0.0, sig_m = 0.0;
-    if (status0 == LPGPU_RUNNING) {
+    if (status0 == LPGPU_RUNNING && phase0 != PH_DRIVEOUT) {
         // ---- entering column: priced by the previous step (one candidate per CTA), or from scratch
         if (kn > 0) k = kn;
         else if (kn == -2) {
-            const KeyCand c = bigm ? warp_key_best<true>(cin) : warp_key_best<false>(cin);
+            const KeyCand c = two_keys ? warp_key_best<true>(cin) : warp_key_best<false>(cin);
             k = c.idx > 0 ? c.idx : 0;
         } else {
             KeyCand c = keycand_none();
-            for (int j = 1 + gtid; j <= P.n; j += GSTRIDE) blk_price(P, bigm, j, oc[j], bigm ? om[j] : 0.0, c);
+            for (int j = 1 + gtid; j <= jmax; j += GSTRIDE) blk_price(P, pmode, j, oc[j], (RR == 2) ? om[j] : 0.0, c);
             c = cluster_key_best<true>(cl, c, scr_a, slot_a);
             k = c.idx > 0 ? c.idx : 0;
         }
         if (k == 0) {
-            // optimal, unless Big-M left an artificial basic at a positive level
+            // nothing prices in: optimal -- unless Big-M or phase one left an artificial basic at a positive level
+            // (infeasible), or phase one is over (drive-out next: the host loop hands over to the rank-1 path)
             KeyCand a = keycand_none();
-            if (bigm) {
+            if (bigm || phase0 == PH_ONE) {
                 const int nreal = P.n - P.n_art;
                 for (int i = gtid; i < P.m; i += GSTRIDE)
                     if (P.basis[i] > nreal && B.bcur[i] > P.eps) { a.idx = i; break; }
             }
             a = cluster_key_best<false>(cl, a, scr_d, slot_d);
-            status = (a.idx >= 0) ? LPGPU_INFEASIBLE : LPGPU_OPTIMAL;
+            if (a.idx >= 0) status = LPGPU_INFEASIBLE;
+            else if (phase0 == PH_ONE) { phase = PH_DRIVEOUT; p1 = iters; }
+            else status = LPGPU_OPTIMAL;
         } else {
             // ---- column k as it stands after the t pivots of this block, and the ratio test on it
             sig_c = oc[k];                                        // read before the row phase rewrites objcur
@@ -153,7 +162,9 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
             st->do_pivot = 0;
             st->blk_t = t;
             st->blk_seq = seq;
-            if (status == LPGPU_RUNNING) st->k_next = k;      // budget ran out: the priced column stays valid
+            st->phase = phase;
+            st->phase1_iters = p1;
+            if (status == LPGPU_RUNNING) st->k_next = (phase == PH_DRIVEOUT) ? 0 : k;   // budget ran out: the priced column stays valid
         }
         return;
     }
@@ -227,7 +238,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
                     qm = __fma_rn(-sig_m, pr, omv[cth]);
                     B.objcur[P.ld + j] = qm;
                 }
-                blk_price(P, bigm, (int)j, qc, qm, c);
+                if (j <= (size_t)jmax) blk_price(P, pmode, (int)j, qc, qm, c);
             }
         }
     }
@@ -236,7 +247,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         B.bcur[i] = (i == r) ? brp : __fma_rn(-B.Fs[(size_t)t * pcn + i], brp, B.bcur[i]);
     stamp(4);
     // ---- this CTA's best candidate for the next pivot; the next launch reduces the SELECT_CLUSTER of them
-    c = bigm ? block_key_best<true>(c, scr_c) : block_key_best<false>(c, scr_c);
+    c = two_keys ? block_key_best<true>(c, scr_c) : block_key_best<false>(c, scr_c);
     if (threadIdx.x == 0) B.cands[rank] = c;
     stamp(5);
 
@@ -251,6 +262,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         st->iters = iters + 1;
         st->budget = budget - 1;
         st->k_next = -2;
+        st->phase1_iters = (phase0 == PH_ONE) ? iters + 1 : p1;
         st->blk_t = t + 1;
         st->blk_seq = seq;
         if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }

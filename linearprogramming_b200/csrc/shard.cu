@@ -486,7 +486,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
                     qm = __fma_rn(-sig_m, pr, omv[cth]);
                     B.objcur[P.ld + j] = qm;
                 }
-                blk_price(P, bigm, (int)j, qc, qm, c);
+                blk_price(P, bigm ? PRICE_BIGM : PRICE_COST, (int)j, qc, qm, c);
             }
         }
     }

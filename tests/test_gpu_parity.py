@@ -242,6 +242,41 @@ def test_blocked_bigm_random_mixed(ctx, seed, K):
     _assert_dense_equal(got, ref)
 
 
+@pytest.mark.parametrize("seed", range(8))
+@pytest.mark.parametrize("K", [0, 3])
+def test_blocked_twophase_windows_and_driveout(ctx, seed, K):
+    """Two-phase through the blocked path: phase one and the main phase in blocks, the drive-out pivots between
+    them through the rank-1 decision; run in windows of 5 pivots with a state read every 3.  Some LPs carry a
+    duplicated equality row (an artificial stays basic at level zero after phase one), some are infeasible."""
+    rng = np.random.default_rng(4000 + seed)
+    m, ns = int(rng.integers(6, 40)), int(rng.integers(6, 40))
+    A, b, c, rel = H.random_mixed_lp(rng, m, ns)
+    if seed % 4 == 1:        # infeasible: contradict the first row
+        A = np.vstack([A, A[0]]); b = np.append(b, b[0] - 5.0 if rel[0] != -2 else b[0] + 5.0)
+        rel = np.append(rel, -2 if rel[0] != -2 else 2).astype(np.int32)
+    if seed % 4 in (2, 3):   # redundant equality: twice the same row
+        i = int(rng.integers(0, m))
+        rel = rel.copy(); rel[i] = 3
+        A = np.vstack([A, A[i]]); b = np.append(b, b[i]); rel = np.append(rel, 3).astype(np.int32)
+    T0, basis, n_art = lp.build_tableau(A, b, c, rel, R=2)
+    ref = O.solve_f64(T0, basis, method=O.TWOPHASE, n_art=n_art, max_iter=5000, log_cap=5000)
+    d = lp.DenseTableau(ctx, T0.shape[0] - 2, T0.shape[1] - 1, 2)
+    d.upload(T0, basis)
+    d.reset(method=O.TWOPHASE, n_art=n_art, max_iter=5000, log_cap=5000, check_every=3, variant=_blocked(K))
+    total = 0
+    while True:
+        r = d.run(5)
+        assert r["iters"] - total <= 5
+        total = r["iters"]
+        if r["status"] != lp.RUNNING:
+            break
+    out = d.download()
+    d.close()
+    assert r["status"] == ref["status"] and r["iters"] == ref["iters"] and r["phase1_iters"] == ref["phase1_iters"]
+    assert out["log"][:r["iters"]].tolist() == ref["log"].tolist() and np.array_equal(out["basis"], ref["basis"])
+    assert np.array_equal(out["T"], ref["T"]) and r["z"] == ref["z"]
+
+
 def test_blocked_statuses_windows_and_limits(ctx):
     # unbounded
     for name in ("unbounded.txt", "unr_inverted.txt"):

@@ -232,7 +232,8 @@ int read_state(lpgpu_dense *d) {
 // rank-1 path instead; pivots per block in variant bits 16..21 (0 = 32)
 bool use_blocked(const lpgpu_dense *d) {
     return !(d->opts.variant & 0x800) &&
-           (d->opts.method == LPGPU_PLAIN || d->opts.method == LPGPU_BIGM || d->opts.method == LPGPU_TWOPHASE);
+           (d->opts.method == LPGPU_PLAIN || d->opts.method == LPGPU_BIGM || d->opts.method == LPGPU_TWOPHASE ||
+            d->opts.method == LPGPU_DUAL);
 }
 
 BlockBufs make_bufs(const lpgpu_dense *d) {
@@ -255,8 +256,9 @@ int launch_block_init(lpgpu_dense *d) {
 static int launch_block_step(lpgpu_dense *d, int first) {
     lpgpu_ctx *ctx = d->ctx;
     const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels;
-    LP_CUDA(ctx, launch_pdl(pdl, d->R == 2 ? blk_step_kernel<2> : blk_step_kernel<1>, dim3(SELECT_CLUSTER), dim3(SELECT_THREADS),
-                            ctx->stream, make_params(d), make_bufs(d), first));
+    void (*kernel)(DenseParams, BlockBufs, int) =
+        d->opts.method == LPGPU_DUAL ? blk_dual_step_kernel : (d->R == 2 ? blk_step_kernel<2> : blk_step_kernel<1>);
+    LP_CUDA(ctx, launch_pdl(pdl, kernel, dim3(SELECT_CLUSTER), dim3(SELECT_THREADS), ctx->stream, make_params(d), make_bufs(d), first));
     if (d->blk_dbg) d->blk_dbg_n++;
     ctx->launches++;
     return LPGPU_OK;

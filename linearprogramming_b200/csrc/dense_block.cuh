@@ -270,6 +270,198 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     stamp(6);
 }
 
+// ------------------------------------------------------------------ dual simplex step (LPGPU_DUAL, R = 1)
+// Same block machinery, decisions in the dual order: leaving row = most negative b (from bcur; the candidates
+// of the NEXT pivot are left per CTA at the end of a step, as in the primal kernel), row r brought up to
+// date lazily, entering column = min sigma_j / a_rj over a_rj < -eps on it, column k brought up to date
+// lazily -> F[t], row scaled by a_rk = F[t][r] -> P[t], objective row and b updated.
+__global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
+blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
+    __shared__ KeyCand scr_a[SELECT_THREADS / 32], scr_b[SELECT_THREADS / 32], scr_c[SELECT_THREADS / 32];
+    __shared__ KeyCand slot_a[SELECT_CLUSTER], slot_b[SELECT_CLUSTER];
+    __shared__ double s_pk[BLK_KMAX], s_fr[BLK_KMAX];
+    cg::cluster_group cl = cg::this_cluster();
+    const int rank = (int)cl.block_rank();
+    const int gtid = rank * SELECT_THREADS + (int)threadIdx.x;
+    constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
+
+    pdl_wait();
+    pdl_launch_dependents();
+    PivotState *st = P.st;
+    const int status0 = st->status, iters = st->iters, budget = st->budget;
+    const int t = first ? 0 : st->blk_t, seq = st->blk_seq + (first ? 1 : 0);
+    const int kn = st->k_next;                       // -2: per-CTA leaving-row candidates are in B.cands
+    KeyCand cin = keycand_none();
+    if ((threadIdx.x & 31) < SELECT_CLUSTER) {
+        const int ln = threadIdx.x & 31;
+        cin.kp = __ldcg(&B.cands[ln].kp); cin.kq = __ldcg(&B.cands[ln].kq); cin.idx = __ldcg(&B.cands[ln].idx);
+    }
+    const double *oc = B.objcur;
+    const size_t pcn = P.pcn;
+
+    int status = status0, k = 0, r = -1;
+    bool have = false;
+    double av[STEP_CPT], ocv[STEP_CPT];
+    const size_t jb = 1 + (size_t)gtid;
+    if (status0 == LPGPU_RUNNING) {
+        // ---- leaving row: most negative b_i < -eps, ties to the lowest row
+        if (kn == -2) r = warp_key_best<false>(cin).idx;
+        else {
+            KeyCand c = keycand_none();
+            for (int i = gtid; i < P.m; i += GSTRIDE) {
+                const double b = B.bcur[i];
+                if (b < -P.eps) {
+                    KeyCand x;
+                    x.kp = 0; x.kq = ord_key(-b); x.idx = i;
+                    if (keycand_better(x, c)) c = x;
+                }
+            }
+            r = cluster_key_best<false>(cl, c, scr_a, slot_a).idx;
+        }
+        if (r < 0) status = LPGPU_OPTIMAL;
+        else {
+            // ---- row r as it stands after the t pivots of this block; entering column on it
+            const int s0r = blk_row_start(B.rowstamp[r], seq);
+#pragma unroll
+            for (int cth = 0; cth < STEP_CPT; ++cth) {
+                const size_t j = jb + (size_t)cth * GSTRIDE;
+                av[cth] = ocv[cth] = 0.0;
+                if (j <= (size_t)P.n) { av[cth] = P.T[(size_t)r * P.ld + j]; ocv[cth] = oc[j]; }
+            }
+            if ((int)threadIdx.x < t) s_fr[threadIdx.x] = B.Fs[(size_t)threadIdx.x * pcn + r];
+            __syncthreads();
+            KeyCand c = keycand_none();
+            // n <= STEP_CPT * GSTRIDE columns are kept in registers across the column phase; wider tableaux recompute
+            for (size_t j0 = jb; j0 <= (size_t)P.n; j0 += (size_t)STEP_CPT * GSTRIDE) {
+                double aw[STEP_CPT], ow[STEP_CPT];
+#pragma unroll
+                for (int cth = 0; cth < STEP_CPT; ++cth) {
+                    const size_t j = j0 + (size_t)cth * GSTRIDE;
+                    aw[cth] = ow[cth] = 0.0;
+                    if (j0 == jb) { aw[cth] = av[cth]; ow[cth] = ocv[cth]; }
+                    else if (j <= (size_t)P.n) { aw[cth] = P.T[(size_t)r * P.ld + j]; ow[cth] = oc[j]; }
+                    if (s0r > 0 && j <= (size_t)P.n) aw[cth] = B.Pm[(size_t)(s0r - 1) * P.ld + j];
+                }
+                for (int sb = s0r; sb < t; sb += STEP_PB) {
+                    double pv[STEP_CPT][STEP_PB];
+#pragma unroll
+                    for (int cth = 0; cth < STEP_CPT; ++cth) {
+                        const size_t j = j0 + (size_t)cth * GSTRIDE;
+#pragma unroll
+                        for (int u = 0; u < STEP_PB; ++u) pv[cth][u] = (sb + u < t && j <= (size_t)P.n) ? B.Pm[(size_t)(sb + u) * P.ld + j] : 0.0;
+                    }
+#pragma unroll
+                    for (int u = 0; u < STEP_PB; ++u)
+                        if (sb + u < t) {
+#pragma unroll
+                            for (int cth = 0; cth < STEP_CPT; ++cth) aw[cth] = __fma_rn(-s_fr[sb + u], pv[cth][u], aw[cth]);
+                        }
+                }
+#pragma unroll
+                for (int cth = 0; cth < STEP_CPT; ++cth) {
+                    const size_t j = j0 + (size_t)cth * GSTRIDE;
+                    if (j0 == jb) av[cth] = aw[cth];
+                    if (j <= (size_t)P.n && aw[cth] < -P.eps) {
+                        KeyCand x;
+                        x.kp = 0; x.kq = ord_key(-(ow[cth] / aw[cth])); x.idx = (int)j;
+                        if (keycand_better(x, c)) c = x;
+                    }
+                }
+            }
+            c = cluster_key_best<false>(cl, c, scr_b, slot_b);
+            if (c.idx < 0) status = LPGPU_INFEASIBLE;
+            else if (iters >= P.max_iter) status = LPGPU_ITER_LIMIT;
+            else if (budget > 0) { have = true; k = c.idx; }
+        }
+    }
+    if (!have) {
+        cl.sync();
+        if (gtid == 0) {
+            st->status = status;
+            st->do_pivot = 0;
+            st->blk_t = t;
+            st->blk_seq = seq;
+            st->k_next = 0;                       // the leaving row is looked for again from bcur
+        }
+        return;
+    }
+
+    // ---- column k as it stands after the t pivots of this block -> F[t]
+    const double sig = oc[k];
+    if (gtid == 0) B.Fs[(size_t)t * pcn + P.m] = sig;
+    if ((int)threadIdx.x < t) s_pk[threadIdx.x] = B.Pm[(size_t)threadIdx.x * P.ld + (size_t)k];
+    __syncthreads();
+    for (int i = gtid; i < P.m; i += GSTRIDE) {
+        const int s0 = blk_row_start(B.rowstamp[i], seq);
+        double a = s0 ? s_pk[s0 - 1] : P.T[(size_t)i * P.ld + (size_t)k];
+        for (int sb = s0; sb < t; sb += 8) {
+            double fv[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) fv[u] = (sb + u < t) ? B.Fs[(size_t)(sb + u) * pcn + i] : 0.0;
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                if (sb + u < t) a = __fma_rn(-fv[u], s_pk[sb + u], a);
+        }
+        B.Fs[(size_t)t * pcn + i] = a;
+    }
+    const double b_r = B.bcur[r];
+    const int s0r = blk_row_start(B.rowstamp[r], seq);
+    cl.sync();                                    // F[t] is complete (the pivot element among it)
+    const double piv = __ldcg(B.Fs + (size_t)t * pcn + r);
+
+    // ---- scaled row -> P[t], objective row, b column, next leaving-row candidate
+    double *pt = B.Pm + (size_t)t * P.ld;
+    const double brp = div_skip_zero(b_r, piv);
+    if (gtid == 0) {
+        pt[0] = brp;
+        B.objcur[0] = __fma_rn(-sig, brp, oc[0]);
+    }
+    for (size_t j0 = jb; j0 <= (size_t)P.n; j0 += (size_t)STEP_CPT * GSTRIDE) {
+#pragma unroll
+        for (int cth = 0; cth < STEP_CPT; ++cth) {
+            const size_t j = j0 + (size_t)cth * GSTRIDE;
+            if (j > (size_t)P.n) continue;
+            double a, o;
+            if (j0 == jb) { a = av[cth]; o = ocv[cth]; }
+            else {                                // wide tableau: the row slice again (rare; same chain, same bits)
+                a = s0r ? B.Pm[(size_t)(s0r - 1) * P.ld + j] : P.T[(size_t)r * P.ld + j];
+                for (int s = s0r; s < t; ++s) a = __fma_rn(-s_fr[s], B.Pm[(size_t)s * P.ld + j], a);
+                o = oc[j];
+            }
+            const double pr = div_skip_zero(a, piv);
+            pt[j] = pr;
+            B.objcur[j] = __fma_rn(-sig, pr, o);
+        }
+    }
+    KeyCand c = keycand_none();
+    for (int i = gtid; i < P.m; i += GSTRIDE) {
+        const double nb = (i == r) ? brp : __fma_rn(-B.Fs[(size_t)t * pcn + i], brp, B.bcur[i]);
+        B.bcur[i] = nb;
+        if (nb < -P.eps) {
+            KeyCand x;
+            x.kp = 0; x.kq = ord_key(-nb); x.idx = i;
+            if (keycand_better(x, c)) c = x;
+        }
+    }
+    c = block_key_best<false>(c, scr_c);
+    if (threadIdx.x == 0) B.cands[rank] = c;
+    if (gtid == 0) {
+        P.basis[r] = k;
+        B.rowstamp[r] = (seq << 8) | (t + 1);
+        B.steprow[t] = r;
+        st->status = status;
+        st->do_pivot = 1;
+        st->r = r;
+        st->k = k;
+        st->iters = iters + 1;
+        st->budget = budget - 1;
+        st->k_next = -2;
+        st->blk_t = t + 1;
+        st->blk_seq = seq;
+        if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
+    }
+}
+
 // ------------------------------------------------------------------ the pass that applies a block
 // CTA tile = FL_ROWS x FL_COLS, 4 warps stacked over the rows; a thread owns 16 rows x 4 columns
 // (two 128-bit accesses per row, 64 accumulator registers).  Per step of the chain a thread needs two

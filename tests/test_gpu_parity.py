@@ -365,6 +365,31 @@ def test_dual_simplex_midsize_and_batched(ctx):
     _assert_batched_equal(gotb, refb)
 
 
+@pytest.mark.parametrize("variant", [0, 4 << 16, capi.RANK1])
+def test_dual_simplex_blocked_windows_and_rank1(ctx, variant):
+    """Dual simplex through the blocked path (default; blocks of 32 and of 4 pivots) and through the rank-1 path,
+    in windows of 7 pivots: all three leave the oracle's bits."""
+    rng = np.random.default_rng(555)
+    for (m, ns, infeasible) in [(120, 90, False), (40, 70, False), (30, 30, True)]:
+        T, basis, _ = H.random_dual_lp(rng, m, ns, infeasible=infeasible)
+        ref = O.solve_f64(T, basis, method=O.DUAL, log_cap=4096)
+        d = lp.DenseTableau(ctx, m, T.shape[1] - 1, 1)
+        d.upload(T, basis)
+        d.reset(method=lp.DUAL, log_cap=4096, check_every=3, variant=variant)
+        total = 0
+        while True:
+            r = d.run(7)
+            assert r["iters"] - total <= 7
+            total = r["iters"]
+            if r["status"] != lp.RUNNING:
+                break
+        out = d.download()
+        d.close()
+        assert r["status"] == ref["status"] == (lp.INFEASIBLE if infeasible else lp.OPTIMAL) and r["iters"] == ref["iters"]
+        assert out["log"][:r["iters"]].tolist() == ref["log"].tolist() and np.array_equal(out["basis"], ref["basis"])
+        assert np.array_equal(out["T"], ref["T"]) and r["z"] == ref["z"] and np.array_equal(out["x"], ref["x"])
+
+
 # ------------------------------------------------------------------ batched path
 def _assert_batched_equal(got, ref, final=None):
     assert np.array_equal(got["status"], ref["status"])

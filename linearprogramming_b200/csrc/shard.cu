@@ -66,6 +66,21 @@ __device__ __forceinline__ void post_pair(const ShardParams &S) {
         st_release_sys(xptr<unsigned>(S.peer_x[g], XLayout::pair_flag(par)) + S.rank, S.iter + 1u);
 }
 
+// The same, one lane per peer (call with the first warp of a CTA, all 32 lanes): the data stores, ONE system
+// fence and the flag go out to all peers at once, instead of a release store per peer in sequence (each of
+// which waits for an NVLink round trip).
+__device__ __forceinline__ void post_pair_lanes(const ShardParams &S, const double (&v)[PAIR_DOUBLES]) {
+    const int par = (int)(S.iter & 1u), g = (int)(threadIdx.x & 31);
+    for (int gg = g; gg < S.world; gg += 32) {
+        double *dst = xptr<double>(S.peer_x[gg], XLayout::pairs(par)) + (size_t)S.rank * PAIR_DOUBLES;
+#pragma unroll
+        for (int q = 0; q < PAIR_DOUBLES; ++q) dst[q] = v[q];
+    }
+    __threadfence_system();
+    for (int gg = g; gg < S.world; gg += 32)
+        st_release_sys(xptr<unsigned>(S.peer_x[gg], XLayout::pair_flag(par)) + S.rank, S.iter + 1u);
+}
+
 // block-wide wait for every rank's candidate of this iteration; false = a peer never posted
 __device__ __forceinline__ bool wait_pairs(const ShardParams &S) {
     const int par = (int)(S.iter & 1u);
@@ -279,9 +294,11 @@ shard_select_kernel(ShardParams S) {
         }
     }
     c = cluster_best(cl, c, scratch, slot_look);
-    if (gtid == 0) {
-        store_pair(S.sendpair, c, S.col0);
-        if (S.peer_x) post_pair(S);
+    if (gtid < 32) {                                        // first warp of CTA 0: one lane per peer
+        double v[PAIR_DOUBLES];
+        store_pair(v, c, S.col0);
+        if (gtid == 0) store_pair(S.sendpair, c, S.col0);
+        if (S.peer_x) post_pair_lanes(S, v);
     }
 }
 
@@ -494,7 +511,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
         B.bcur[i] = (i == r) ? brp : __fma_rn(-B.Fs[(size_t)t * pcn + i], brp, B.bcur[i]);
     // ---- this rank's candidate for the next pivot -> every rank
     c = bigm ? cluster_key_best<true>(cl, c, scr_c, slot_c) : cluster_key_best<false>(cl, c, scr_c, slot_c);
-    if (gtid == 0) {
+    if (gtid < 32) {                                        // first warp of CTA 0: one lane per peer
         Cand out = cand_none();
         if (c.idx > 0) {
             out.idx = c.idx;
@@ -506,8 +523,12 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
                 out.p = p;
             }
         }
-        store_pair(S.sendpair, out, S.col0);
-        post_pair(S);
+        double v[PAIR_DOUBLES];
+        store_pair(v, out, S.col0);
+        if (gtid == 0) store_pair(S.sendpair, out, S.col0); // kept for the re-post of an iteration without a pivot
+        post_pair_lanes(S, v);
+    }
+    if (gtid == 0) {
         P.basis[r] = k;
         B.rowstamp[r] = (seq << 8) | (t + 1);
         B.steprow[t] = r;

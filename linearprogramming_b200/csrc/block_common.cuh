@@ -7,8 +7,16 @@
 namespace lpgpu {
 
 constexpr int BLK_KMAX = 32;           // pivots per block at most (shared-memory tile of the pass)
+constexpr int STEP_CLUSTER_MAX = 16;   // the primal step kernel runs as a cluster of 8 (portable) or 16 CTAs
 
 struct KeyCand;
+
+// what the pass needs to know about a block once the step kernels have moved on to the next one
+// (pipelined blocks: the pass of block b runs while block b+1 is being decided)
+struct BlkInfo {
+    int kc;              // pivots decided in the block
+    int seq;             // its sequence number (the tag of its row stamps)
+};
 
 struct BlockBufs {
     double *Fs;          // BLK_KMAX x pcn: Fs[s*pcn + i] = a_{i,k_s} before step s (the multiplier of row i at step s)
@@ -19,6 +27,14 @@ struct BlockBufs {
     int *rowstamp;       // pcn: (block sequence << 8) | (s + 1) if the row was the pivot row of step s of that block
     int *steprow;        // BLK_KMAX: pivot row of step s of the current block
     int K;               // pivots per block, 1..BLK_KMAX
+    // pipelined blocks (dense.cu, variant bit 0x1000 off): P.T is the tableau as it stood BEFORE the previous block,
+    // whose pass is still running; the lazy chains run through that block's slices first, then this block's
+    const double *Fall;  // both sets of slices, [2][BLK_KMAX] steps each: set `par` is this block's (= Fs / Pm), the other one
+    const double *Pall;  // the previous block's
+    const int *stamp_prev;   // the previous block's row stamps (pend != 0)
+    BlkInfo *info;       // [2]: written for parity `par` by every step launch; [par ^ 1] = the previous block (nullptr: not pipelined)
+    int par;             // parity of this block
+    int pend;            // 1: the previous block has not been applied to P.T
     unsigned long long *dbg;   // LPGPU_BLK_DEBUG=1: 8 globaltimer stamps per launch slot (development aid), else nullptr
 };
 
@@ -88,13 +104,13 @@ __device__ __forceinline__ KeyCand block_key_best(KeyCand c, KeyCand *scratch) {
 }
 
 // cluster-wide: every CTA pushes its winner into every CTA's `slot` (DSMEM), one cluster barrier
-template <bool TWO>
+template <bool TWO, int CL = SELECT_CLUSTER>
 __device__ __forceinline__ KeyCand cluster_key_best(cg::cluster_group &cl, KeyCand c, KeyCand *scratch, KeyCand *slot) {
     c = block_key_best<TWO>(c, scratch);
-    if (threadIdx.x < SELECT_CLUSTER) cl.map_shared_rank(slot, threadIdx.x)[cl.block_rank()] = c;
+    if (threadIdx.x < CL) cl.map_shared_rank(slot, threadIdx.x)[cl.block_rank()] = c;
     cl.sync();
     const int lane = threadIdx.x & 31;
-    return warp_key_best<TWO>(lane < SELECT_CLUSTER ? slot[lane] : keycand_none());
+    return warp_key_best<TWO>(lane < CL ? slot[lane] : keycand_none());
 }
 
 // pricing candidate of column j from the (current) objective row values.  mode: 0 = cost row alone (plain,

@@ -186,6 +186,24 @@ static cudaError_t launch_pdl(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim
     return cudaLaunchKernelEx(&cfg, kernel, args...);
 }
 
+// The same with the cluster shape as a launch attribute (the primal step kernel runs as 8 or 16 CTAs).
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_cluster(bool pdl, int cluster, void (*kernel)(KArgs...), dim3 block, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(cluster);
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 2 : 1;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
 int launch_select(lpgpu_dense *d, int forced_r, int forced_k) {
     lpgpu_ctx *ctx = d->ctx;
     const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels;
@@ -239,6 +257,15 @@ bool use_blocked(const lpgpu_dense *d) {
 BlockBufs make_bufs(const lpgpu_dense *d) {
     BlockBufs B;
     B.Fs = d->Ft; B.cands = d->cands; B.Pm = d->Pm; B.objcur = d->objcur; B.bcur = d->bcur; B.rowstamp = d->rowstamp; B.steprow = d->steprow;
+    B.Fall = d->Ft; B.Pall = d->Pm; B.stamp_prev = nullptr; B.info = nullptr; B.par = 0; B.pend = 0;
+    if (d->pipe_on) {        // pipelined blocks: the set of this block's parity, the other set is the pending block's
+        const bool odd = d->par != 0;
+        B.Fs = odd ? d->Ft2 : d->Ft;
+        B.Pm = odd ? d->Pm2 : d->Pm;
+        B.rowstamp = odd ? d->rowstamp2 : d->rowstamp;   B.stamp_prev = odd ? d->rowstamp : d->rowstamp2;
+        B.steprow = odd ? d->steprow2 : d->steprow;
+        B.info = d->info; B.par = d->par; B.pend = d->pend ? 1 : 0;
+    }
     const int k = (d->opts.variant >> 16) & 0x3f;
     B.K = (k >= 1 && k <= BLK_KMAX) ? k : BLK_KMAX;
     B.dbg = d->blk_dbg ? d->blk_dbg + 8 * (size_t)(d->blk_dbg_n % 4096) : nullptr;
@@ -249,16 +276,171 @@ int launch_block_init(lpgpu_dense *d) {
     lpgpu_ctx *ctx = d->ctx;
     blk_init_kernel<<<ctx->sm_count, 1024, 0, ctx->stream>>>(make_params(d), make_bufs(d));
     LP_LAUNCH_CHECK(ctx);
-    ctx->launches++;
+    if (d->pipe_state == 1) {       // both sets of row stamps start clean
+        LP_CUDA(ctx, cudaMemsetAsync(d->rowstamp, 0, d->pcn * sizeof(int), ctx->stream));
+        LP_CUDA(ctx, cudaMemsetAsync(d->rowstamp2, 0, d->pcn * sizeof(int), ctx->stream));
+    }
     return LPGPU_OK;
 }
+
+// ---- pipelined blocks: the pass of block b runs on a second stream, out of place (T -> T2), while the step kernels of
+// block b+1 decide on T (the tableau BEFORE block b) through the slices of block b and their own.  Variant bit 0x2000
+// (primal methods); the default is the in-place order (steps, pass, steps, ...), which measures faster: DESIGN.md 4.0.
+static bool want_pipeline(const lpgpu_dense *d) {
+    return use_blocked(d) && (d->opts.variant & 0x2000) && !(d->opts.variant & 0x100) && d->opts.method != LPGPU_DUAL;
+}
+
+static void free_pipeline(lpgpu_dense *d) {
+    cudaFree(d->T2); cudaFree(d->rowstamp2); cudaFree(d->steprow2); cudaFree(d->info); cudaFree(d->flush_flag);
+    d->T2 = d->Ft2 = d->Pm2 = nullptr; d->rowstamp2 = d->steprow2 = nullptr; d->info = nullptr; d->flush_flag = nullptr;
+    if (d->stream2) { cudaStreamDestroy(d->stream2); d->stream2 = nullptr; }
+    if (d->ev_steps) { cudaEventDestroy(d->ev_steps); d->ev_steps = nullptr; }
+    if (d->ev_flush) { cudaEventDestroy(d->ev_flush); d->ev_flush = nullptr; }
+}
+
+// Buffers, stream and events of the pipelined path, once per tableau object.  Not having room for the second tableau
+// buffer is not an error: the in-place order is used instead (pipe_state = -1).
+static int setup_pipeline(lpgpu_dense *d) {
+    if (d->pipe_state != 0) return LPGPU_OK;
+    lpgpu_ctx *ctx = d->ctx;
+    const size_t rows = (size_t)d->m + d->R;
+    unsigned *smids = nullptr;
+    cudaError_t e = cudaMalloc(&d->T2, rows * d->ld * sizeof(double));
+    d->Ft2 = d->Ft + d->pcn * BLK_KMAX;             // second halves of the slice buffers (allocated with the object)
+    d->Pm2 = d->Pm + (size_t)BLK_KMAX * d->ld;
+    if (e == cudaSuccess) e = cudaMalloc(&d->rowstamp2, d->pcn * sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc(&d->steprow2, BLK_KMAX * sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc(&d->info, 2 * sizeof(BlkInfo));
+    if (e == cudaSuccess) e = cudaMalloc(&d->flush_flag, sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc(&smids, STEP_CLUSTER_MAX * sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d->stream2, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->ev_steps, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->ev_flush, cudaEventDisableTiming);
+    if (e != cudaSuccess) {
+        cudaFree(smids);
+        free_pipeline(d);
+        cudaGetLastError();
+        d->pipe_state = -1;
+        return LPGPU_OK;
+    }
+    LP_CUDA(ctx, cudaMemsetAsync(d->T2, 0, rows * d->ld * sizeof(double), ctx->stream));
+    LP_CUDA(ctx, cudaMemsetAsync(d->rowstamp2, 0, d->pcn * sizeof(int), ctx->stream));
+    LP_CUDA(ctx, cudaMemsetAsync(d->steprow2, 0, BLK_KMAX * sizeof(int), ctx->stream));
+    LP_CUDA(ctx, cudaMemsetAsync(d->info, 0, 2 * sizeof(BlkInfo), ctx->stream));
+    LP_CUDA(ctx, cudaMemsetAsync(d->flush_flag, 0, sizeof(int), ctx->stream));
+    LP_CUDA(ctx, cudaMemsetAsync(smids, 0xff, STEP_CLUSTER_MAX * sizeof(unsigned), ctx->stream));
+    // the SMs a step-kernel cluster is placed on while the device is idle: the pass leaves them free
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const int cl = d->step_cl_max;
+    LP_CUDA(ctx, launch_cluster(false, cl, blk_probe_kernel, dim3(SELECT_THREADS), ctx->stream, smids));
+    ctx->launches++;
+    unsigned h[STEP_CLUSTER_MAX];
+    LP_CUDA(ctx, cudaMemcpyAsync(h, smids, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(smids);
+    for (unsigned &w : d->resv) w = 0;
+    int distinct = 0;
+    if (!getenv("LPGPU_NO_RESERVE"))
+        for (int q = 0; q < cl; ++q) {
+            const unsigned v = h[q];
+            if (v < 256u && !((d->resv[v >> 5] >> (v & 31u)) & 1u)) { d->resv[v >> 5] |= 1u << (v & 31u); ++distinct; }
+        }
+    if (distinct != cl)
+        for (unsigned &w : d->resv) w = 0;           // no reservation: still correct, the pass and the steps just take turns
+    d->pipe_state = 1;
+    return LPGPU_OK;
+}
+
+// Close the open block: its pass goes to stream2 (after this block's steps), the next block's steps wait for the
+// pass before it (they read its output and reuse its slices).  ev0 / ev1: optional timing events around the pass.
+static int close_block_pipe(lpgpu_dense *d, cudaEvent_t ev0, cudaEvent_t ev1) {
+    lpgpu_ctx *ctx = d->ctx;
+    const bool odd = d->par != 0;
+    FlushParams U;
+    U.Tsrc = d->pend ? d->T2 : d->T;
+    U.T = d->pend ? d->T : d->T2;
+    U.kc_ptr = &d->info[d->par].kc; U.seq_ptr = &d->info[d->par].seq;
+    U.ld = d->ld; U.rows = d->m + d->R; U.Fs = odd ? d->Ft2 : d->Ft; U.pcn = d->pcn; U.Pm = odd ? d->Pm2 : d->Pm;
+    U.rowstamp = odd ? d->rowstamp2 : d->rowstamp; U.steprow = odd ? d->steprow2 : d->steprow; U.st = d->st;
+    U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
+    U.rb = d->fl_rb; U.pf = d->fl_pf;
+    const bool full = d->grid_flush >= ctx->sm_count * 2;       // a full persistent grid: every SM holds CTAs of the pass
+    for (int w = 0; w < 8; ++w) U.resv[w] = full ? d->resv[w] : 0u;
+    U.flag = d->flush_flag;
+    LP_CUDA(ctx, cudaEventRecord(d->ev_steps, ctx->stream));
+    if (d->pend) LP_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, d->ev_flush, 0));
+    LP_CUDA(ctx, cudaStreamWaitEvent(d->stream2, d->ev_steps, 0));
+    if (ev0) LP_CUDA(ctx, cudaEventRecord(ev0, d->stream2));
+    if (d->opts.variant & 0x4000) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, d->stream2>>>(U);
+    else blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, d->stream2>>>(U);
+    LP_LAUNCH_CHECK(ctx);
+    const unsigned fx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, (d->ld + 255) / 256));
+    blk_fixrows_kernel<<<dim3(fx, BLK_KMAX), 256, 0, d->stream2>>>(U);
+    LP_LAUNCH_CHECK(ctx);
+    if (ev1) LP_CUDA(ctx, cudaEventRecord(ev1, d->stream2));
+    LP_CUDA(ctx, cudaEventRecord(d->ev_flush, d->stream2));
+    if (d->pend) std::swap(d->T, d->T2);         // T = the tableau before the block just closed, T2 = where its pass writes
+    d->pend = true;
+    d->par ^= 1;
+    return LPGPU_OK;
+}
+
+// Bring d->T up to date: wait (on the stream, not on the host) for the pass in flight and make its output the tableau.
+static int drain_pipe(lpgpu_dense *d) {
+    lpgpu_ctx *ctx = d->ctx;
+    if (!d->pend) return LPGPU_OK;
+    LP_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, d->ev_flush, 0));
+    std::swap(d->T, d->T2);
+    d->pend = false;
+    return LPGPU_OK;
+}
+
+typedef void (*step_kernel_t)(DenseParams, BlockBufs, int);
+static step_kernel_t step_kernel(int R, bool pipe, int cl) {
+    if (cl == 16)
+        return pipe ? (R == 2 ? blk_step_kernel<2, true, 16> : blk_step_kernel<1, true, 16>)
+                    : (R == 2 ? blk_step_kernel<2, false, 16> : blk_step_kernel<1, false, 16>);
+    return pipe ? (R == 2 ? blk_step_kernel<2, true, 8> : blk_step_kernel<1, true, 8>)
+                : (R == 2 ? blk_step_kernel<2, false, 8> : blk_step_kernel<1, false, 8>);
+}
+
+// CTAs per cluster of the primal step kernel: 16 where the device can place such a cluster (a non-portable size,
+// allowed per kernel), else 8; variant bit 0x8000 and LPGPU_STEP_CL8 keep 8.
+static int probe_step_cluster(lpgpu_dense *d) {
+    d->step_cl_max = SELECT_CLUSTER;
+    if (getenv("LPGPU_STEP_CL8")) return LPGPU_OK;
+    bool ok = true;
+    for (int R = 1; R <= 2 && ok; ++R)
+        for (int pipe = 0; pipe <= 1 && ok; ++pipe)
+            ok = cudaFuncSetAttribute(step_kernel(R, pipe != 0, 16), cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
+    if (ok) ok = cudaFuncSetAttribute(blk_probe_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
+    if (ok) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(16); cfg.blockDim = dim3(SELECT_THREADS / 2);
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 16; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        int n = 0;
+        ok = cudaOccupancyMaxActiveClusters(&n, step_kernel(d->R, true, 16), &cfg) == cudaSuccess && n >= 1;
+    }
+    cudaGetLastError();
+    if (ok) d->step_cl_max = 16;
+    return LPGPU_OK;
+}
+
+static int step_cluster(const lpgpu_dense *d) { return (d->opts.variant & 0x8000) ? SELECT_CLUSTER : d->step_cl_max; }
 
 static int launch_block_step(lpgpu_dense *d, int first) {
     lpgpu_ctx *ctx = d->ctx;
     const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels;
-    void (*kernel)(DenseParams, BlockBufs, int) =
-        d->opts.method == LPGPU_DUAL ? blk_dual_step_kernel : (d->R == 2 ? blk_step_kernel<2> : blk_step_kernel<1>);
-    LP_CUDA(ctx, launch_pdl(pdl, kernel, dim3(SELECT_CLUSTER), dim3(SELECT_THREADS), ctx->stream, make_params(d), make_bufs(d), first));
+    if (d->opts.method == LPGPU_DUAL)
+        LP_CUDA(ctx, launch_pdl(pdl, blk_dual_step_kernel, dim3(SELECT_CLUSTER), dim3(SELECT_THREADS), ctx->stream, make_params(d), make_bufs(d), first));
+    else {
+        const int cl = step_cluster(d);
+        LP_CUDA(ctx, launch_cluster(pdl, cl, step_kernel(d->R, d->pipe_on, cl), dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS), ctx->stream,
+                                    make_params(d), make_bufs(d), first));
+    }
     if (d->blk_dbg) d->blk_dbg_n++;
     ctx->launches++;
     return LPGPU_OK;
@@ -268,16 +450,20 @@ int launch_block_flush(lpgpu_dense *d) {
     lpgpu_ctx *ctx = d->ctx;
     FlushParams U;
     U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.Fs = d->Ft; U.pcn = d->pcn; U.Pm = d->Pm; U.rowstamp = d->rowstamp; U.steprow = d->steprow; U.st = d->st;
+    U.Tsrc = d->T; U.kc_ptr = &d->st->blk_t; U.seq_ptr = &d->st->blk_seq; U.flag = nullptr;
+    for (unsigned &w : U.resv) w = 0;
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
     U.rb = d->fl_rb; U.pf = d->fl_pf;
     // variant bit 0x100: the warp-specialised pass (one CTA per SM, TMA ring; slower: see DESIGN.md 4.0)
-    if (!(d->opts.variant & 0x100)) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, ctx->stream>>>(U);
-    else blk_flush_ws_kernel<<<std::min<long>(ctx->sm_count, d->flush_tasks), WS_THREADS, WS_SMEM_BYTES, ctx->stream>>>(U);
+    // variant bit 0x4000: the pass that loads a whole tile before it computes (the default is software-pipelined in half tiles)
+    if (!(d->opts.variant & 0x100)) {
+        if (d->opts.variant & 0x4000) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, ctx->stream>>>(U);
+        else blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, ctx->stream>>>(U);
+    } else blk_flush_ws_kernel<<<std::min<long>(ctx->sm_count, d->flush_tasks), WS_THREADS, WS_SMEM_BYTES, ctx->stream>>>(U);
     LP_LAUNCH_CHECK(ctx);
     const unsigned fx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, (d->ld + 255) / 256));
     blk_fixrows_kernel<<<dim3(fx, BLK_KMAX), 256, 0, ctx->stream>>>(U);
-    LP_LAUNCH_CHECK(ctx);
-    ctx->launches += 2;
+    LP_LAUNCH_CHECK(ctx);                   // (the macro counts the launch)
     return LPGPU_OK;
 }
 
@@ -340,6 +526,10 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     d->T = nullptr; d->basis = nullptr; d->prow = d->pcol = d->bnext = d->xbuf = nullptr; d->la_dirty = true; d->st = nullptr; d->h_st = nullptr;
     d->log = nullptr; d->log_cap = 0; d->task_ctr = nullptr; d->upd_seq = 0;
     d->Ft = d->Pm = d->objcur = d->bcur = nullptr; d->rowstamp = d->steprow = nullptr; d->cands = nullptr; d->blk_open = false; d->blk_steps = 0;
+    d->pipe_state = 0; d->pipe_on = false; d->pend = false; d->par = 0;
+    d->T2 = d->Ft2 = d->Pm2 = nullptr; d->rowstamp2 = d->steprow2 = nullptr; d->info = nullptr; d->flush_flag = nullptr;
+    d->stream2 = nullptr; d->ev_steps = d->ev_flush = nullptr;
+    for (unsigned &w : d->resv) w = 0;
     lpgpu_default_opts(&d->opts);
     d->opts.method = (R == 1) ? LPGPU_PLAIN : LPGPU_BIGM;
     const size_t rows = (size_t)m + R, pcn = round_up(rows, UPD_TILE_ROWS) + UPD_TILE_ROWS;
@@ -354,25 +544,27 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     if (e == cudaSuccess) e = cudaMalloc(&d->st, sizeof(PivotState));
     if (e == cudaSuccess) e = cudaMalloc(&d->task_ctr, 2 * sizeof(int));
     if (e == cudaSuccess) e = cudaMemsetAsync(d->task_ctr, 0, 2 * sizeof(int), ctx->stream);
-    if (e == cudaSuccess) e = cudaMalloc(&d->Ft, pcn * BLK_KMAX * sizeof(double));
-    if (e == cudaSuccess) e = cudaMalloc(&d->Pm, (size_t)BLK_KMAX * d->ld * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&d->Ft, 2 * pcn * BLK_KMAX * sizeof(double));              // two sets of slices (pipelined blocks)
+    if (e == cudaSuccess) e = cudaMalloc(&d->Pm, 2 * (size_t)BLK_KMAX * d->ld * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&d->objcur, (size_t)R * d->ld * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&d->bcur, pcn * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&d->rowstamp, pcn * sizeof(int));
     if (e == cudaSuccess) e = cudaMalloc(&d->steprow, BLK_KMAX * sizeof(int));
-    if (e == cudaSuccess) e = cudaMalloc(&d->cands, SELECT_CLUSTER * sizeof(KeyCand));
-    if (e == cudaSuccess) e = cudaMemsetAsync(d->cands, 0xff, SELECT_CLUSTER * sizeof(KeyCand), ctx->stream);
+    if (e == cudaSuccess) e = cudaMalloc(&d->cands, STEP_CLUSTER_MAX * sizeof(KeyCand));
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->cands, 0xff, STEP_CLUSTER_MAX * sizeof(KeyCand), ctx->stream);
     d->blk_dbg = nullptr; d->blk_dbg_n = 0;
     if (e == cudaSuccess && getenv("LPGPU_BLK_DEBUG")) {
         e = cudaMalloc(&d->blk_dbg, 4096 * 8 * sizeof(unsigned long long));
         if (e == cudaSuccess) e = cudaMemsetAsync(d->blk_dbg, 0, 4096 * 8 * sizeof(unsigned long long), ctx->stream);
     }
     if (e == cudaSuccess) e = cudaMemsetAsync(d->steprow, 0, BLK_KMAX * sizeof(int), ctx->stream);
-    if (e == cudaSuccess) e = cudaMemsetAsync(d->Ft, 0, pcn * BLK_KMAX * sizeof(double), ctx->stream);
-    if (e == cudaSuccess) e = cudaMemsetAsync(d->Pm, 0, (size_t)BLK_KMAX * d->ld * sizeof(double), ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->Ft, 0, 2 * pcn * BLK_KMAX * sizeof(double), ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->Pm, 0, 2 * (size_t)BLK_KMAX * d->ld * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->rowstamp, 0, pcn * sizeof(int), ctx->stream);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(blk_flush_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL_SMEM_BYTES);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(blk_flush_sp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL_SMEM_BYTES);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(blk_flush_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WS_SMEM_BYTES);
     if (e == cudaSuccess) e = cudaHostAlloc(&d->h_st, sizeof(PivotState), cudaHostAllocDefault);
@@ -386,6 +578,7 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
         return fail(ctx, e == cudaErrorMemoryAllocation ? LPGPU_ENOMEM : LPGPU_ECUDA, "dense_create: %s", cudaGetErrorString(e));
     }
     int rc = size_grid(d);
+    if (rc == LPGPU_OK) rc = probe_step_cluster(d);
     if (rc == LPGPU_OK) rc = lpgpu_dense_reset(d, &d->opts);
     if (rc != LPGPU_OK) { lpgpu_dense_destroy(d); return rc; }
     *out = d;
@@ -396,6 +589,8 @@ void lpgpu_dense_destroy(lpgpu_dense *d) {
     if (!d) return;
     cudaSetDevice(d->ctx->device);
     cudaStreamSynchronize(d->ctx->stream);
+    if (d->stream2) cudaStreamSynchronize(d->stream2);
+    free_pipeline(d);
     for (cudaEvent_t e : d->ev) cudaEventDestroy(e);
     if (d->blk_dbg) {       // development aid: mean time between the step kernel's phase stamps
         std::vector<unsigned long long> h(4096 * 8);
@@ -410,6 +605,8 @@ void lpgpu_dense_destroy(lpgpu_dense *d) {
             if (i + 1 < n && h[8 * (i + 1)]) { gap += (double)(h[8 * (i + 1)] - s[6]); ++gcnt; }
             ++cnt;
         }
+        fprintf(stderr, "[lpgpu blk debug] step cluster max %d, pipeline state %d, reserved SM words %08x %08x %08x %08x %08x\n", d->step_cl_max, d->pipe_state,
+                d->resv[0], d->resv[1], d->resv[2], d->resv[3], d->resv[4]);
         if (cnt) fprintf(stderr, "[lpgpu blk debug] %ld steps: pdl_wait %.2f | column+ratio loop %.2f | best %.2f | row+price loop %.2f | best %.2f | b+state %.2f | gap to next start %.2f us\n",
                          cnt, acc[1] / cnt / 1e3, acc[2] / cnt / 1e3, acc[3] / cnt / 1e3, acc[4] / cnt / 1e3, acc[5] / cnt / 1e3, acc[6] / cnt / 1e3, gcnt ? gap / gcnt / 1e3 : 0.0);
         cudaFree(d->blk_dbg);
@@ -505,6 +702,14 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
         // ---- blocked path: K step kernels (decide a pivot each on lazily updated slices), then one pass over
         // the tableau that applies them all; the tableau is brought up to date before this call returns
         const int K = make_bufs(d).K;
+        // pipelined blocks (variant bit 0x2000): the pass of a block overlaps the decisions of the next one
+        d->pipe_on = false;
+        if (want_pipeline(d)) {
+            rc = setup_pipeline(d);
+            if (rc != LPGPU_OK) return rc;
+            d->pipe_on = d->pipe_state == 1;
+        }
+        const bool pipe = d->pipe_on;
         if (dirty) { rc = launch_block_init(d); if (rc != LPGPU_OK) return rc; }
         std::vector<int> kinds;                 // timed mode: 0 = step, 1 = flush, in launch order
         auto enqueue = [&](int kind, int first) -> int {
@@ -515,11 +720,13 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
                     LP_CUDA(ctx, cudaEventCreate(&ev));
                     d->ev.push_back(ev);
                 }
-                LP_CUDA(ctx, cudaEventRecord(d->ev[e], ctx->stream));
+                if (!(kind && pipe)) LP_CUDA(ctx, cudaEventRecord(d->ev[e], ctx->stream));
             }
-            const int rc2 = kind ? launch_block_flush(d) : launch_block_step(d, first);
+            int rc2;
+            if (kind && pipe) { rc2 = close_block_pipe(d, timed ? d->ev[e] : nullptr, timed ? d->ev[e + 1] : nullptr); }
+            else rc2 = kind ? launch_block_flush(d) : launch_block_step(d, first);
             if (rc2 != LPGPU_OK) return rc2;
-            if (timed) { LP_CUDA(ctx, cudaEventRecord(d->ev[e + 1], ctx->stream)); kinds.push_back(kind); }
+            if (timed) { if (!(kind && pipe)) LP_CUDA(ctx, cudaEventRecord(d->ev[e + 1], ctx->stream)); kinds.push_back(kind); }
             return LPGPU_OK;
         };
         auto flush = [&]() -> int {
@@ -529,7 +736,13 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
             ++done_updates;
             return rc2;
         };
+        // the tableau in d->T is brought up to date (in stream order): open block closed, pass in flight waited for
+        auto settle = [&]() -> int {
+            if (d->blk_open) { const int rc2 = flush(); if (rc2 != LPGPU_OK) return rc2; }
+            return pipe ? drain_pipe(d) : LPGPU_OK;
+        };
         auto collect = [&]() -> int {
+            if (pipe && !kinds.empty()) LP_CUDA(ctx, cudaStreamSynchronize(d->stream2));
             for (size_t i = 0; i < kinds.size(); ++i) {
                 float ms = 0.f;
                 LP_CUDA(ctx, cudaEventElapsedTime(&ms, d->ev[2 * i], d->ev[2 * i + 1]));
@@ -572,13 +785,15 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
             iters_before = d->h_st->iters;
             if (d->h_st->status != LPGPU_RUNNING) break;
             if (d->h_st->phase == PH_DRIVEOUT) {
-                if (d->blk_open) { rc = flush(); if (rc != LPGPU_OK) return rc; }
+                rc = settle();
+                if (rc != LPGPU_OK) return rc;
                 rc = driveout();
                 if (rc != LPGPU_OK) return rc;
                 iters_before = d->h_st->iters;
             }
         }
-        if (d->blk_open) { rc = flush(); if (rc != LPGPU_OK) return rc; }
+        rc = settle();
+        if (rc != LPGPU_OK) return rc;
         if (d->h_st->status == LPGPU_RUNNING) {
             // decision only (budget is spent): settles a terminal status
             rc = (d->h_st->phase == PH_DRIVEOUT) ? launch_select(d, -1, 0) : launch_block_step(d, 1);

@@ -33,6 +33,16 @@ __global__ void blk_init_kernel(DenseParams P, BlockBufs B) {
     for (size_t i = gt; i < (size_t)(P.m + P.R); i += gs) B.rowstamp[i] = 0;
 }
 
+// Which SMs a step-kernel cluster lands on (same cluster shape and CTA size, so one CTA per SM): run once on an idle
+// device; the pass of the pipelined path leaves exactly these SMs free.
+__global__ void __launch_bounds__(SELECT_THREADS) blk_probe_kernel(unsigned *smids) {      // cluster shape and CTA size: launch attributes
+    cg::cluster_group cl = cg::this_cluster();
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    if (threadIdx.x == 0) smids[cl.block_rank()] = smid;
+    cl.sync();
+}
+
 // One pivot of a block: decision + lazy slices + eager objective rows / b column (PLAIN and BIGM).
 // first != 0: the tableau was flushed (or initialised) since the last step: a new block starts.
 // The kernel is a chain of dependent memory round trips (~1 us each), so every phase first issues ALL
@@ -42,17 +52,28 @@ __global__ void blk_init_kernel(DenseParams P, BlockBufs B) {
 constexpr int STEP_PB = 8;             // earlier pivot rows per batch of loads in the row phase (64 registers per thread)
 constexpr int STEP_CPT = 2;            // columns per thread in flight in the row phase (covers n <= 2 * 8192 in one go)
 
-template <int RR>
-__global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
+// CL = CTAs in the cluster (launch attribute): 8 x 1024 threads, or 16 x 512 threads (a non-portable cluster size).  The
+// lazy chains are bounded by LATENCY: the multipliers / pivot-row entries of the earlier steps come from L2 in batches,
+// one dependent round trip per batch (0.85 us; twice that while a pass is streaming the tableau).  Half the threads per
+// CTA means twice the registers per thread, i.e. batches of 32 instead of 8: a whole block's chain in one round trip.
+template <int CL> struct StepShape {
+    static constexpr int TH = (CL == 16) ? SELECT_THREADS / 2 : SELECT_THREADS;   // threads per CTA
+    static constexpr int FB = (CL == 16) ? 32 : 8;              // earlier steps per batch of loads, column phase
+    static constexpr int PB = (CL == 16) ? 16 : STEP_PB;        // ... row phase (x STEP_CPT columns per thread)
+};
+
+template <int RR, bool PIPE, int CL>
+__global__ void __launch_bounds__(StepShape<CL>::TH)
 blk_step_kernel(DenseParams P, BlockBufs B, int first) {
+    constexpr int TH = StepShape<CL>::TH, FB = StepShape<CL>::FB, PB = StepShape<CL>::PB;
     // one scratch / slot array per reduction of a launch: no reuse, so no extra barriers
-    __shared__ KeyCand scr_a[SELECT_THREADS / 32], scr_b[SELECT_THREADS / 32], scr_c[SELECT_THREADS / 32], scr_d[SELECT_THREADS / 32];
-    __shared__ KeyCand slot_a[SELECT_CLUSTER], slot_b[SELECT_CLUSTER], slot_d[SELECT_CLUSTER];
-    __shared__ double s_pk[BLK_KMAX], s_fr[BLK_KMAX];
+    __shared__ KeyCand scr_a[TH / 32], scr_b[TH / 32], scr_c[TH / 32], scr_d[TH / 32];
+    __shared__ KeyCand slot_a[CL], slot_b[CL], slot_d[CL];
+    __shared__ double s_pk[2 * BLK_KMAX], s_fr[2 * BLK_KMAX];      // the previous (pending) block's steps first, then this block's
     cg::cluster_group cl = cg::this_cluster();
     const int rank = (int)cl.block_rank();
-    const int gtid = rank * SELECT_THREADS + (int)threadIdx.x;
-    constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
+    const int gtid = rank * TH + (int)threadIdx.x;
+    constexpr int GSTRIDE = CL * TH;
 
     auto stamp = [&](int slot) {
         if (B.dbg && gtid == 0) {
@@ -70,8 +91,15 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     const int status0 = st->status, iters = st->iters, budget = st->budget;
     const int t = first ? 0 : st->blk_t, seq = st->blk_seq + (first ? 1 : 0);
     const int kn = st->k_next;
+    // pipelined blocks: P.T is the tableau before the previous block (its pass is still running); the lazy chains
+    // run through that block's Kp steps (combined step index c < Kp) and then this block's t steps (c - Kp)
+    // (PIPE = false: the in-place order, Kp = 0 at compile time and the code below is the plain one-block chain)
+    const int Kp = (PIPE && B.pend) ? B.info[B.par ^ 1].kc : 0;
+    const int tc = Kp + t;
+    const int offP = PIPE ? (B.par ^ 1) * BLK_KMAX : 0, offC = PIPE ? B.par * BLK_KMAX - Kp : 0;     // combined step c -> row of Fall / Pall
+    auto srow = [&](int cc) -> size_t { return (size_t)((cc < Kp ? offP : offC) + cc); };
     KeyCand cin = keycand_none();                  // the previous step's per-CTA candidates, requested together with the state
-    if ((threadIdx.x & 31) < SELECT_CLUSTER) {
+    if ((threadIdx.x & 31) < CL) {
         const int ln = threadIdx.x & 31;
         cin.kp = __ldcg(&B.cands[ln].kp); cin.kq = __ldcg(&B.cands[ln].kq); cin.idx = __ldcg(&B.cands[ln].idx);
     }
@@ -97,7 +125,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         } else {
             KeyCand c = keycand_none();
             for (int j = 1 + gtid; j <= jmax; j += GSTRIDE) blk_price(P, pmode, j, oc[j], (RR == 2) ? om[j] : 0.0, c);
-            c = cluster_key_best<true>(cl, c, scr_a, slot_a);
+            c = cluster_key_best<true, CL>(cl, c, scr_a, slot_a);
             k = c.idx > 0 ? c.idx : 0;
         }
         if (k == 0) {
@@ -109,7 +137,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
                 for (int i = gtid; i < P.m; i += GSTRIDE)
                     if (P.basis[i] > nreal && B.bcur[i] > P.eps) { a.idx = i; break; }
             }
-            a = cluster_key_best<false>(cl, a, scr_d, slot_d);
+            a = cluster_key_best<false, CL>(cl, a, scr_d, slot_d);
             if (a.idx >= 0) status = LPGPU_INFEASIBLE;
             else if (phase0 == PH_ONE) { phase = PH_DRIVEOUT; p1 = iters; }
             else status = LPGPU_OPTIMAL;
@@ -121,22 +149,30 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
             // first row of this thread: everything it needs is requested before anyone waits
             int i = gtid;
             double tv = 0.0, bv = 0.0;
-            int rs = 0;
-            if (i < P.m) { tv = P.T[(size_t)i * P.ld + (size_t)k]; rs = B.rowstamp[i]; bv = B.bcur[i]; }
-            if ((int)threadIdx.x < t) s_pk[threadIdx.x] = B.Pm[(size_t)threadIdx.x * P.ld + (size_t)k];
+            int rs = 0, rsp = 0;
+            if (i < P.m) { tv = P.T[(size_t)i * P.ld + (size_t)k]; rs = B.rowstamp[i]; bv = B.bcur[i]; if (Kp) rsp = B.stamp_prev[i]; }
+            if ((int)threadIdx.x < tc) {
+                const int cc = (int)threadIdx.x;
+                s_pk[cc] = B.Pall[srow(cc) * P.ld + (size_t)k];
+            }
             __syncthreads();
             KeyCand c = keycand_none();
             for (; i < P.m; i += GSTRIDE) {
-                if (i != gtid) { tv = P.T[(size_t)i * P.ld + (size_t)k]; rs = B.rowstamp[i]; bv = B.bcur[i]; }
+                if (i != gtid) { tv = P.T[(size_t)i * P.ld + (size_t)k]; rs = B.rowstamp[i]; bv = B.bcur[i]; if (Kp) rsp = B.stamp_prev[i]; }
+                // where this row's chain starts: after its last turn as a pivot row (this block, else the pending one), else at the tableau
                 const int s0 = blk_row_start(rs, seq);
-                double a = s0 ? s_pk[s0 - 1] : tv;
-                for (int sb = s0; sb < t; sb += 8) {              // multipliers of 8 earlier steps in flight (coalesced over rows)
-                    double fv[8];
+                const int c0 = s0 ? Kp + s0 : (Kp ? blk_row_start(rsp, seq - 1) : 0);
+                double a = c0 ? s_pk[c0 - 1] : tv;
+                for (int sb = c0; sb < tc; sb += FB) {            // multipliers of FB earlier steps in flight (coalesced over rows)
+                    double fv[FB];
 #pragma unroll
-                    for (int u = 0; u < 8; ++u) fv[u] = (sb + u < t) ? B.Fs[(size_t)(sb + u) * pcn + i] : 0.0;
+                    for (int u = 0; u < FB; ++u) {
+                        const int cc = sb + u;
+                        fv[u] = (cc < tc) ? B.Fall[srow(cc) * pcn + i] : 0.0;
+                    }
 #pragma unroll
-                    for (int u = 0; u < 8; ++u)
-                        if (sb + u < t) a = __fma_rn(-fv[u], s_pk[sb + u], a);
+                    for (int u = 0; u < FB; ++u)
+                        if (sb + u < tc) a = __fma_rn(-fv[u], s_pk[sb + u], a);
                 }
                 B.Fs[(size_t)t * pcn + i] = a;
                 if (a > P.eps) {
@@ -148,7 +184,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
                 }
             }
             stamp(2);
-            c = cluster_key_best<false>(cl, c, scr_b, slot_b);
+            c = cluster_key_best<false, CL>(cl, c, scr_b, slot_b);
             stamp(3);
             if (c.idx < 0) status = LPGPU_UNBOUNDED;
             else if (iters >= P.max_iter) status = LPGPU_ITER_LIMIT;
@@ -165,6 +201,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
             st->phase = phase;
             st->phase1_iters = p1;
             if (status == LPGPU_RUNNING) st->k_next = (phase == PH_DRIVEOUT) ? 0 : k;   // budget ran out: the priced column stays valid
+            if (B.info) { B.info[B.par].kc = t; B.info[B.par].seq = seq; }
         }
         return;
     }
@@ -183,10 +220,16 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         }
     }
     const int s0r = blk_row_start(B.rowstamp[r], seq);
+    const int c0r = s0r ? Kp + s0r : (Kp ? blk_row_start(B.stamp_prev[r], seq - 1) : 0);
     const double b_r = B.bcur[r];
     const double piv = __ldcg(B.Fs + (size_t)t * pcn + r);                   // written above, possibly by another CTA
-    if ((int)threadIdx.x < t) s_fr[threadIdx.x] = B.Fs[(size_t)threadIdx.x * pcn + r];
+    if ((int)threadIdx.x < tc) {
+        const int cc = (int)threadIdx.x;
+        s_fr[cc] = B.Fall[srow(cc) * pcn + r];
+    }
     __syncthreads();
+    // the scaled pivot row the chain restarts from, if this row was a pivot row in this block or the pending one
+    const double *rrow = c0r > 0 ? B.Pall + srow(c0r - 1) * P.ld : nullptr;
     double *pt = B.Pm + (size_t)t * P.ld;
     const double brp = div_skip_zero(b_r, piv);       // = P[t][0]: column 0 of the row is the b column
     KeyCand c = keycand_none();
@@ -203,24 +246,27 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
                 if (j <= (size_t)P.n) { av[cth] = P.T[(size_t)r * P.ld + j]; ocv[cth] = oc[j]; if (RR == 2) omv[cth] = om[j]; }
             }
         }
-        if (s0r > 0) {                            // the row was a pivot row earlier in this block: restart from its scaled row
+        if (rrow) {                               // the row was a pivot row earlier: restart from its scaled row
 #pragma unroll
             for (int cth = 0; cth < STEP_CPT; ++cth) {
                 const size_t j = j0 + (size_t)cth * GSTRIDE;
-                if (j <= (size_t)P.n) av[cth] = B.Pm[(size_t)(s0r - 1) * P.ld + j];
+                if (j <= (size_t)P.n) av[cth] = rrow[j];
             }
         }
-        for (int sb = s0r; sb < t; sb += STEP_PB) {     // STEP_PB earlier pivot rows x STEP_CPT columns in flight
-            double pv[STEP_CPT][STEP_PB];
+        for (int sb = c0r; sb < tc; sb += PB) {         // PB earlier pivot rows x STEP_CPT columns in flight
+            double pv[STEP_CPT][PB];
 #pragma unroll
             for (int cth = 0; cth < STEP_CPT; ++cth) {
                 const size_t j = j0 + (size_t)cth * GSTRIDE;
 #pragma unroll
-                for (int u = 0; u < STEP_PB; ++u) pv[cth][u] = (sb + u < t && j <= (size_t)P.n) ? B.Pm[(size_t)(sb + u) * P.ld + j] : 0.0;
+                for (int u = 0; u < PB; ++u) {
+                    const int cc = sb + u;
+                    pv[cth][u] = (cc < tc && j <= (size_t)P.n) ? B.Pall[srow(cc) * P.ld + j] : 0.0;
+                }
             }
 #pragma unroll
-            for (int u = 0; u < STEP_PB; ++u)
-                if (sb + u < t) {
+            for (int u = 0; u < PB; ++u)
+                if (sb + u < tc) {
 #pragma unroll
                     for (int cth = 0; cth < STEP_CPT; ++cth) av[cth] = __fma_rn(-s_fr[sb + u], pv[cth][u], av[cth]);
                 }
@@ -265,6 +311,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         st->phase1_iters = (phase0 == PH_ONE) ? iters + 1 : p1;
         st->blk_t = t + 1;
         st->blk_seq = seq;
+        if (B.info) { B.info[B.par].kc = t + 1; B.info[B.par].seq = seq; }
         if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
     }
     stamp(6);
@@ -482,7 +529,12 @@ constexpr int FL_RG = 4;               // rows whose multipliers are in flight t
 constexpr int FL_RB = 4;
 
 struct FlushParams {
-    double *T;
+    double *T;                // where the pass writes
+    const double *Tsrc;       // where it reads: == T in place, the other tableau buffer with pipelined blocks
+    const int *kc_ptr;        // pivots in the block (st->blk_t in place, info[par].kc pipelined)
+    const int *seq_ptr;       // the block's sequence number
+    unsigned resv[8];         // bit smid set: that SM is left to the step kernels of the next block (CTAs landing there exit)
+    int *flag;                // >= seq + 1 once a CTA of this launch runs on an SM that is not reserved
     size_t ld;
     int rows;                 // m + R
     const double *Fs;         // BLK_KMAX x pcn
@@ -508,7 +560,7 @@ struct FlTile {
 
 __device__ __forceinline__ void fl_load_tile(const FlushParams &U, const FlTile &t, int wr, int jc, double2 (&acc)[FL_TR][2]) {
     const int i0 = t.rt * FL_ROWS + FL_TR * wr;
-    const double *tp = U.T + (size_t)i0 * U.ld + t.j0 + jc;
+    const double *tp = U.Tsrc + (size_t)i0 * U.ld + t.j0 + jc;
     const bool ok0 = jc < t.ncols, ok1 = jc + 64 < t.ncols;
 #pragma unroll
     for (int rr = 0; rr < FL_TR; ++rr) {
@@ -522,7 +574,7 @@ __device__ __forceinline__ void fl_load_tile(const FlushParams &U, const FlTile 
 __device__ __forceinline__ void fl_prefetch_tile(const FlushParams &U, const FlTile &t) {
     const int i = t.rt * FL_ROWS + (int)threadIdx.x;
     if ((int)threadIdx.x < FL_ROWS && i < U.rows)
-        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(U.T + (size_t)i * U.ld + t.j0), "r"(t.ncols * 8) : "memory");
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(U.Tsrc + (size_t)i * U.ld + t.j0), "r"(t.ncols * 8) : "memory");
 }
 
 // the chain of kc steps on one thread's 16 x 4 elements, then the store
@@ -608,8 +660,32 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
     pdl_wait();
     int *ctr = U.task_ctr + (U.seq & 1u);
     if (blockIdx.x == 0 && threadIdx.x == 0) U.task_ctr[(U.seq & 1u) ^ 1u] = 0;
-    const int kc = U.st->blk_t;
-    if (kc <= 0) return;
+    if (U.flag) {
+        // Pipelined blocks: the SMs in U.resv are left to the step kernels of the next block.  A CTA that lands on one
+        // leaves as soon as it knows that some CTA of this launch works elsewhere (any one worker finishes the pass:
+        // tasks are claimed from a counter); if none shows up within 20 us it works after all -- placement only ever
+        // costs time, never the result.
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        const int want = (int)(U.seq + 1u);
+        if ((U.resv[(smid >> 5) & 7u] >> (smid & 31u)) & 1u) {         // the same for every thread of the CTA
+            __shared__ int s_leave;
+            if (threadIdx.x == 0) {
+                unsigned long long t0, now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+                bool leave = false;
+                do {
+                    leave = (*(volatile int *)U.flag - want) >= 0;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                } while (!leave && now - t0 < 20000ull);
+                s_leave = leave ? 1 : 0;
+            }
+            __syncthreads();
+            if (s_leave) return;
+        } else if (threadIdx.x == 0) atomicMax(U.flag, want);
+    }
+    const int kc = *U.kc_ptr;
+    if (kc <= 0 && U.Tsrc == U.T) return;                              // nothing to apply (out of place: a plain copy)
 
     const int nct = (int)((U.ld + FL_COLS - 1) / FL_COLS);
     const int nrt = (U.rows + FL_ROWS - 1) / FL_ROWS;                  // row tiles
@@ -678,6 +754,193 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
     }
 }
 
+// ------------------------------------------------------------------ the pass, software-pipelined in half tiles (default)
+// Same tiles, same operands, same chain as blk_flush_kernel; what changes is WHEN a thread's tableau loads are issued.
+// There a CTA loads its whole 64 x 128 tile (32 LDG.128 per thread), waits, runs the chain on it and stores it: memory
+// idles while the CTA computes and the FP64 pipe idles while it loads, and three CTAs per SM in arbitrary phase only
+// partly cover for one another (ncu: DRAM 50 %, FP64 pipe 53 % busy).  Here a thread's 16 rows are two halves of 8:
+// while the chain runs on one half (32 accumulator registers) the loads of the other half -- of this tile, or of the
+// first half of the CTA's next tile -- are in flight, so every CTA keeps both the memory system and the FP64 pipe busy
+// all the time.  Registers: the same 64 accumulators.
+constexpr int FL_HR = FL_TR / 2;       // rows per half
+
+template <int NR>
+__device__ __forceinline__ void fl_load_rows(const FlushParams &U, const FlTile &t, int row0, int jc, double2 (&acc)[NR][2]) {
+    const double *tp = U.Tsrc + (size_t)row0 * U.ld + t.j0 + jc;
+    const bool ok0 = jc < t.ncols, ok1 = jc + 64 < t.ncols;
+#pragma unroll
+    for (int rr = 0; rr < NR; ++rr) {
+        const bool rowok = row0 + rr < U.rows;
+        acc[rr][0] = (ok0 && rowok) ? ld_stream2(tp + (size_t)rr * U.ld) : make_double2(0.0, 0.0);
+        acc[rr][1] = (ok1 && rowok) ? ld_stream2(tp + (size_t)rr * U.ld + 64) : make_double2(0.0, 0.0);
+    }
+}
+
+template <int NR>
+__device__ __forceinline__ void fl_store_rows(const FlushParams &U, const FlTile &t, int row0, int jc, double2 (&acc)[NR][2]) {
+    double *tp = U.T + (size_t)row0 * U.ld + t.j0 + jc;
+    const bool ok0 = jc < t.ncols, ok1 = jc + 64 < t.ncols;
+#pragma unroll
+    for (int rr = 0; rr < NR; ++rr) {
+        const bool rowok = row0 + rr < U.rows;
+        if (ok0 && rowok) st_stream2(tp + (size_t)rr * U.ld, acc[rr][0]);
+        if (ok1 && rowok) st_stream2(tp + (size_t)rr * U.ld + 64, acc[rr][1]);
+    }
+}
+
+// the chain of kc steps on NR rows x 4 columns of one thread (fw: the multipliers of its first row, pw: its column pair)
+template <int NR>
+__device__ __forceinline__ void fl_chain_rows(int kc, const double *fw, const double *pw, double2 (&acc)[NR][2]) {
+    int s = 0;
+    for (; s + 1 < kc; s += 2) {
+        double2 p[2][2];                                  // [step][column pair]
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+            for (int q = 0; q < 2; ++q) p[e][q] = *reinterpret_cast<const double2 *>(pw + (size_t)(s + e) * FL_COLS + 64 * q);
+#pragma unroll
+        for (int rg = 0; rg < NR; rg += FL_RG) {
+            double2 f[2][FL_RG / 2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                for (int u = 0; u < FL_RG / 2; ++u) f[e][u] = *reinterpret_cast<const double2 *>(fw + (size_t)(s + e) * FL_ROWS + rg + 2 * u);
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                for (int u = 0; u < FL_RG / 2; ++u)
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        acc[rg + 2 * u][q].x = __fma_rn(-f[e][u].x, p[e][q].x, acc[rg + 2 * u][q].x);
+                        acc[rg + 2 * u][q].y = __fma_rn(-f[e][u].x, p[e][q].y, acc[rg + 2 * u][q].y);
+                        acc[rg + 2 * u + 1][q].x = __fma_rn(-f[e][u].y, p[e][q].x, acc[rg + 2 * u + 1][q].x);
+                        acc[rg + 2 * u + 1][q].y = __fma_rn(-f[e][u].y, p[e][q].y, acc[rg + 2 * u + 1][q].y);
+                    }
+            asm volatile("" ::: "memory");
+        }
+    }
+    if (s < kc) {
+        double2 p[2];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) p[q] = *reinterpret_cast<const double2 *>(pw + (size_t)s * FL_COLS + 64 * q);
+#pragma unroll
+        for (int rr = 0; rr < NR; ++rr) {
+            const double f = fw[(size_t)s * FL_ROWS + rr];
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                acc[rr][q].x = __fma_rn(-f, p[q].x, acc[rr][q].x);
+                acc[rr][q].y = __fma_rn(-f, p[q].y, acc[rr][q].y);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_sp_kernel(FlushParams U) {
+    extern __shared__ __align__(128) unsigned char fl_smem[];
+    double *sP = reinterpret_cast<double *>(fl_smem);                                 // [BLK_KMAX][FL_COLS]
+    double *sF = sP + (size_t)BLK_KMAX * FL_COLS;                                     // [2][BLK_KMAX][FL_ROWS]
+    __shared__ __align__(8) uint64_t bar_p, bar_f[2];
+    __shared__ long s_task[2];
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bar_p, 1);
+        mbar_init(&bar_f[0], 1);
+        mbar_init(&bar_f[1], 1);
+        fence_mbar_init();
+    }
+    pdl_wait();
+    int *ctr = U.task_ctr + (U.seq & 1u);
+    if (blockIdx.x == 0 && threadIdx.x == 0) U.task_ctr[(U.seq & 1u) ^ 1u] = 0;
+    if (U.flag) {       // pipelined blocks: see blk_flush_kernel
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        const int want = (int)(U.seq + 1u);
+        if ((U.resv[(smid >> 5) & 7u] >> (smid & 31u)) & 1u) {
+            __shared__ int s_leave;
+            if (threadIdx.x == 0) {
+                unsigned long long t0, now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+                bool leave = false;
+                do {
+                    leave = (*(volatile int *)U.flag - want) >= 0;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                } while (!leave && now - t0 < 20000ull);
+                s_leave = leave ? 1 : 0;
+            }
+            __syncthreads();
+            if (s_leave) return;
+        } else if (threadIdx.x == 0) atomicMax(U.flag, want);
+    }
+    const int kc = *U.kc_ptr;
+    if (kc <= 0 && U.Tsrc == U.T) return;
+
+    const int nct = (int)((U.ld + FL_COLS - 1) / FL_COLS);
+    const int nrt = (U.rows + FL_ROWS - 1) / FL_ROWS;
+    const int nsb = (nrt + U.rb - 1) / U.rb;
+    const long ntasks = (long)nct * nsb;
+    const int lane = threadIdx.x & 31, wr = threadIdx.x >> 5;
+    const int jc = 2 * lane;
+    const uint32_t FBYTES = (uint32_t)(kc * FL_ROWS * 8);
+    auto issue_f = [&](int rt, int fb) {
+        mbar_arrive_expect_tx(&bar_f[fb], FBYTES);
+        for (int s = 0; s < kc; ++s)
+            tma_load_1d(sF + ((size_t)fb * BLK_KMAX + s) * FL_ROWS, U.Fs + (size_t)s * U.pcn + (size_t)rt * FL_ROWS, (uint32_t)(FL_ROWS * 8), &bar_f[fb]);
+    };
+    auto tile_of = [&](long tt, int k) {             // k-th tile of task tt
+        FlTile t;
+        t.j0 = (size_t)(tt % nct) * FL_COLS;
+        t.ncols = (int)min((size_t)FL_COLS, U.ld - t.j0);
+        t.rt = (int)(tt / nct) * U.rb + k;
+        return t;
+    };
+
+    if (threadIdx.x == 0) s_task[0] = (long)atomicAdd(ctr, 1);
+    __syncthreads();
+    uint32_t par_p = 0, par_f = 0;
+    double2 acc0[FL_HR][2], acc1[FL_HR][2];            // the two halves of a thread's 16 rows
+    bool pre = false;                                  // acc0 already holds (is being loaded with) the first half of the coming tile
+    for (int it = 0;; ++it) {
+        const long tt = s_task[it & 1];
+        if (tt >= ntasks) break;
+        FlTile t = tile_of(tt, 0);
+        const int rt0 = t.rt, rt1 = min(rt0 + U.rb, nrt);
+        if (threadIdx.x == 0) {
+            s_task[(it & 1) ^ 1] = (long)atomicAdd(ctr, 1);            // next task; visible after the barriers below
+            mbar_arrive_expect_tx(&bar_p, (uint32_t)(kc * t.ncols * 8));
+            for (int s = 0; s < kc; ++s) tma_load_1d(sP + (size_t)s * FL_COLS, U.Pm + (size_t)s * U.ld + t.j0, (uint32_t)(t.ncols * 8), &bar_p);
+            issue_f(rt0, 0);
+        }
+        for (int rt = rt0; rt < rt1; ++rt) {
+            const int fb = (rt - rt0) & 1;
+            t.rt = rt;
+            const int row0 = rt * FL_ROWS + FL_TR * wr;
+            if (!pre) fl_load_rows<FL_HR>(U, t, row0, jc, acc0);
+            fl_load_rows<FL_HR>(U, t, row0 + FL_HR, jc, acc1);           // in flight while the chain runs on the first half
+            if (threadIdx.x == 0 && rt + 1 < rt1) issue_f(rt + 1, fb ^ 1);
+            if (rt == rt0) { mbar_wait(&bar_p, par_p); par_p ^= 1; }
+            mbar_wait(&bar_f[fb], (par_f >> fb) & 1u);
+            par_f ^= 1u << fb;
+            const double *fw = sF + (size_t)fb * BLK_KMAX * FL_ROWS + FL_TR * wr;
+            fl_chain_rows<FL_HR>(kc, fw, sP + jc, acc0);
+            fl_store_rows<FL_HR>(U, t, row0, jc, acc0);
+            // the tile after this one (same task, or the first tile of the next task once its claim is visible):
+            // its first half is requested now and arrives while the chain runs on the second half
+            FlTile nx = t;
+            pre = true;
+            if (rt + 1 < rt1) nx.rt = rt + 1;
+            else {
+                const long nt = s_task[(it & 1) ^ 1];
+                pre = (rt > rt0) && nt < ntasks;       // the claim was published before tile rt0's closing barrier
+                if (pre) nx = tile_of(nt, 0);
+            }
+            if (pre) fl_load_rows<FL_HR>(U, nx, nx.rt * FL_ROWS + FL_TR * wr, jc, acc0);
+            fl_chain_rows<FL_HR>(kc, fw + FL_HR, sP + jc, acc1);
+            fl_store_rows<FL_HR>(U, t, row0 + FL_HR, jc, acc1);
+            __syncthreads();       // sF[fb] may be refilled (two tiles ahead), and at the last tile sP and s_task
+        }
+    }
+}
+
 // ------------------------------------------------------------------ warp-specialised pass (variant bit 0x100; NOT the default)
 // One CTA per SM: warp 4 (one lane) is the PRODUCER -- it claims tasks and keeps a two-stage ring of tableau
 // tiles (64 rows x 1 KB bulk copies), their multipliers and, per task, the pivot-row segments filled by
@@ -732,7 +995,7 @@ __global__ void __launch_bounds__(WS_THREADS, 1) blk_flush_ws_kernel(FlushParams
     pdl_wait();
     int *ctr = U.task_ctr + (U.seq & 1u);
     if (blockIdx.x == 0 && threadIdx.x == 0) U.task_ctr[(U.seq & 1u) ^ 1u] = 0;
-    const int kc = U.st->blk_t;
+    const int kc = *U.kc_ptr;
     if (kc <= 0) return;
     __syncthreads();
 
@@ -766,7 +1029,7 @@ __global__ void __launch_bounds__(WS_THREADS, 1) blk_flush_ws_kernel(FlushParams
                 mbar_arrive_expect_tx(&full[st], (uint32_t)(nr * ncols * 8 + kc * FL_ROWS * 8));
                 double *dstT = sT + (size_t)st * FL_ROWS * FL_COLS;
                 for (int rr = 0; rr < nr; ++rr)
-                    tma_load_1d(dstT + (size_t)rr * FL_COLS, U.T + (size_t)(i0 + rr) * U.ld + j0, (uint32_t)(ncols * 8), &full[st]);
+                    tma_load_1d(dstT + (size_t)rr * FL_COLS, U.Tsrc + (size_t)(i0 + rr) * U.ld + j0, (uint32_t)(ncols * 8), &full[st]);
                 for (int s = 0; s < kc; ++s)
                     tma_load_1d(sF + ((size_t)st * BLK_KMAX + s) * FL_ROWS, U.Fs + (size_t)s * U.pcn + (size_t)i0, (uint32_t)(FL_ROWS * 8), &full[st]);
             }
@@ -818,7 +1081,7 @@ __global__ void __launch_bounds__(WS_THREADS, 1) blk_flush_ws_kernel(FlushParams
 // Rows that were a pivot row inside the block: restart from the scaled pivot row of their LAST such step
 // and run the steps after it.  grid = (column chunks, BLK_KMAX); block y = step s.
 __global__ void __launch_bounds__(256) blk_fixrows_kernel(FlushParams U) {
-    const int kc = U.st->blk_t, bseq = U.st->blk_seq, s0 = (int)blockIdx.y;
+    const int kc = *U.kc_ptr, bseq = *U.seq_ptr, s0 = (int)blockIdx.y;
     if (s0 >= kc) return;
     const int r = U.steprow[s0];
     if (blk_row_start(U.rowstamp[r], bseq) != s0 + 1) return;      // the row was a pivot row again later in the block

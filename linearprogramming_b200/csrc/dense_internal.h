@@ -36,6 +36,19 @@ struct lpgpu_dense {
     long blk_dbg_n;
     bool blk_open;          // step kernels were enqueued since the last flush
     int blk_steps;          // ... how many
+    int step_cl_max;        // CTAs per cluster the primal step kernel may use: 16 where the device places such clusters, else 8
+    // pipelined blocks (dense.cu): the pass of block b (stream2, T -> T2) runs while block b+1 is decided (ctx->stream)
+    int pipe_state;         // 0 = not set up yet, 1 = ready, -1 = unavailable (second tableau buffer did not fit)
+    bool pipe_on;           // this run call uses it
+    bool pend;              // a block's pass is in flight: T = the tableau before that block, T2 = where the pass writes
+    int par;                // parity of the open / next block: which set of slices, stamps and info it uses
+    double *T2, *Ft2, *Pm2;
+    int *rowstamp2, *steprow2;
+    lpgpu::BlkInfo *info;   // [2]
+    int *flush_flag;        // a pass's CTAs on reserved SMs leave once a worker CTA is known to exist
+    cudaStream_t stream2;
+    cudaEvent_t ev_steps, ev_flush;
+    unsigned resv[8];       // SMs left to the step kernels while a pass runs (bit per %smid)
 };
 
 namespace lpgpu {

@@ -203,7 +203,8 @@ def test_dense_timed_run_reports_kernel_time(ctx):
 
 # ------------------------------------------------------------------ blocked path (delayed rank-1 applications)
 def _blocked(K=0):
-    return K << 16          # pivots per block (0 = the default, 32); the blocked path is the default for plain / Big-M
+    # pivots per block (0 = the default, 32); the blocked path is the default; K >= 100: K - 100 pivots per block, pipelined blocks
+    return ((K % 100) << 16) | (capi.PIPELINED if K >= 100 else 0)
 
 
 @pytest.mark.parametrize("m,ns,K", [(64, 64, 0), (300, 500, 7), (512, 512, 32), (700, 1500, 0)])
@@ -228,7 +229,7 @@ def test_blocked_synth_full_solve_bitwise(ctx, m, ns, K):
 
 
 @pytest.mark.parametrize("seed", range(10))
-@pytest.mark.parametrize("K", [0, 3])
+@pytest.mark.parametrize("K", [0, 3, 103, 100])
 def test_blocked_bigm_random_mixed(ctx, seed, K):
     rng = np.random.default_rng(seed)
     m, ns = int(rng.integers(3, 40)), int(rng.integers(3, 40))
@@ -243,7 +244,7 @@ def test_blocked_bigm_random_mixed(ctx, seed, K):
 
 
 @pytest.mark.parametrize("seed", range(8))
-@pytest.mark.parametrize("K", [0, 3])
+@pytest.mark.parametrize("K", [0, 3, 103, 100])
 def test_blocked_twophase_windows_and_driveout(ctx, seed, K):
     """Two-phase through the blocked path: phase one and the main phase in blocks, the drive-out pivots between
     them through the rank-1 decision; run in windows of 5 pivots with a state read every 3.  Some LPs carry a
@@ -334,6 +335,70 @@ def test_blocked_equals_rank1_path_midsize_bitwise(ctx):
         assert r["iters"] == outs[0][0]["iters"] == Pn and r["z"] == outs[0][0]["z"]
         assert np.array_equal(o["log"], outs[0][1]["log"]) and np.array_equal(o["basis"], outs[0][1]["basis"])
         assert np.array_equal(o["T"], outs[0][1]["T"])
+
+
+@pytest.mark.parametrize("m,ns", [(64, 64), (300, 500), (700, 1500)])
+@pytest.mark.parametrize("K", [0, 1, 5, 13])
+def test_pipelined_blocks_equal_inplace_blocks_and_oracle(ctx, m, ns, K):
+    """PIPELINED = the pass of block b out of place on a second stream while block b+1 is decided through the slices
+    of both blocks; default = steps, pass, steps in place on one stream.  Same bits, and the oracle's."""
+    T0, basis = O.synth_feasible(99, 2, m, ns)
+    ref = O.solve_f64(T0, basis, threads=4, log_cap=8192)
+    a = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K) | capi.PIPELINED)
+    b = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K))
+    _assert_dense_equal(a, ref)
+    _assert_dense_equal(b, ref)
+    assert _same_bits(a["T"], b["T"])
+    # the step kernel as a cluster of 8 CTAs (default: 16 where the device places such clusters), and the pass kernel that
+    # loads a whole tile before it computes (default: software-pipelined halves)
+    for extra in (capi.STEP_CL8, capi.STEP_CL8 | capi.PIPELINED, capi.WHOLE_TILE_PASS, capi.WHOLE_TILE_PASS | capi.PIPELINED):
+        c = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K) | extra)
+        _assert_dense_equal(c, ref)
+
+
+def test_pipelined_blocks_windows_of_odd_sizes(ctx):
+    """Run calls of 1, 2, 33, 64, 7, ... pivots on one tableau object: every call drains the pipeline (the tableau
+    is up to date when it returns, whichever of the two buffers holds it) and the next call starts a fresh block."""
+    m, ns = 300, 212
+    T0, basis = O.synth_feasible(78, 6, m, ns)
+    d = lp.DenseTableau(ctx, m, m + ns, 1)
+    d.upload(T0, basis)
+    d.reset(log_cap=4096, check_every=5, variant=_blocked(4) | capi.PIPELINED)
+    total, sizes, q = 0, [1, 2, 33, 64, 7, 9, 100, 3], 0
+    while True:
+        r = d.run(sizes[q % len(sizes)])
+        q += 1
+        total = r["iters"]
+        if r["status"] != lp.RUNNING:
+            break
+        part = O.solve_f64(T0, basis, max_iter=total)
+        assert np.array_equal(d.download()["T"], part["T"])
+    ref = O.solve_f64(T0, basis, log_cap=4096)
+    out = d.download()
+    assert r["status"] == ref["status"] == lp.OPTIMAL and r["iters"] == ref["iters"]
+    assert out["log"][:r["iters"]].tolist() == ref["log"].tolist() and np.array_equal(out["T"], ref["T"])
+    d.close()
+
+
+def test_pipelined_blocks_full_grid_2048x8192_bitwise(ctx):
+    """Large enough for the pass to run as a full persistent grid (the case in which it leaves the step kernels'
+    SMs free): 400 pivots, pipelined and in place, against the rank-1 path and the oracle."""
+    m, ns, Pn = 2048, 6144, 400
+    outs = []
+    for variant in (capi.RANK1, 0, capi.PIPELINED, _blocked(24) | capi.PIPELINED):
+        d = lp.DenseTableau(ctx, m, m + ns, 1)
+        d.synth(1234, 7, ns)
+        d.reset(log_cap=Pn, variant=variant)
+        r = d.run(150)
+        r = d.run(Pn - 150)
+        outs.append((r, d.download()))
+        d.close()
+    T0, basis0 = lp.synth_host(1234, 7, m, ns)
+    ref = O.solve_f64(T0, basis0, max_iter=Pn, threads=16, log_cap=Pn)
+    for r, o in outs:
+        assert r["iters"] == Pn and r["z"] == ref["z"]
+        assert o["log"][:Pn].tolist() == ref["log"].tolist() and np.array_equal(o["basis"], ref["basis"])
+        assert np.array_equal(o["T"], ref["T"])
 
 
 # ------------------------------------------------------------------ dual simplex (SURVEY section 8 f3)

@@ -11,7 +11,13 @@ piv = int(sys.argv[2]) if len(sys.argv) > 2 else 640
 ctx = lp.Context(0)
 d = lp.DenseTableau(ctx, m, 2 * m, 1)
 ref_log = None
-for name, variant in (("rank1", capi.RANK1), ("blocked32", 0), ("blocked16", 16 << 16), ("blocked24", 24 << 16), ("blocked8", 8 << 16)):
+names = (("rank1", capi.RANK1), ("blocked32", 0), ("blocked24", 24 << 16), ("blocked16", 16 << 16), ("blocked8", 8 << 16),
+         ("pipe32", capi.PIPELINED), ("pipe24", (24 << 16) | capi.PIPELINED))
+if os.environ.get("BLK_ONLY"):
+    names = tuple(x for x in names if x[0] in os.environ["BLK_ONLY"].split(","))
+if os.environ.get("BLK_VARIANTS"):      # name=variant,name=variant (hex allowed), always after the rank-1 reference run
+    names = (("rank1", capi.RANK1),) + tuple((kv.split("=")[0], int(kv.split("=")[1], 0)) for kv in os.environ["BLK_VARIANTS"].split(","))
+for name, variant in names:
     for timed in (0, 1):
         d.synth(1234, 0, m)
         d.reset(log_cap=piv, check_every=max(64, piv), variant=variant, time_kernels=timed)

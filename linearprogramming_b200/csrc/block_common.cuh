@@ -35,6 +35,8 @@ struct BlockBufs {
     BlkInfo *info;       // [2]: written for parity `par` by every step launch; [par ^ 1] = the previous block (nullptr: not pipelined)
     int par;             // parity of this block
     int pend;            // 1: the previous block has not been applied to P.T
+    int l2keep;          // 1: the slices are read and written with the L2 evict-last priority (they are re-read every step
+                         //    while the pass streams the whole tableau through the same L2)
     unsigned long long *dbg;   // LPGPU_BLK_DEBUG=1: 8 globaltimer stamps per launch slot (development aid), else nullptr
 };
 

@@ -258,6 +258,7 @@ BlockBufs make_bufs(const lpgpu_dense *d) {
     BlockBufs B;
     B.Fs = d->Ft; B.cands = d->cands; B.Pm = d->Pm; B.objcur = d->objcur; B.bcur = d->bcur; B.rowstamp = d->rowstamp; B.steprow = d->steprow;
     B.Fall = d->Ft; B.Pall = d->Pm; B.stamp_prev = nullptr; B.info = nullptr; B.par = 0; B.pend = 0;
+    B.l2keep = 0;
     if (d->pipe_on) {        // pipelined blocks: the set of this block's parity, the other set is the pending block's
         const bool odd = d->par != 0;
         B.Fs = odd ? d->Ft2 : d->Ft;
@@ -265,6 +266,7 @@ BlockBufs make_bufs(const lpgpu_dense *d) {
         B.rowstamp = odd ? d->rowstamp2 : d->rowstamp;   B.stamp_prev = odd ? d->rowstamp : d->rowstamp2;
         B.steprow = odd ? d->steprow2 : d->steprow;
         B.info = d->info; B.par = d->par; B.pend = d->pend ? 1 : 0;
+        B.l2keep = (d->l2hint & 2) ? 1 : 0;
     }
     const int k = (d->opts.variant >> 16) & 0x3f;
     B.K = (k >= 1 && k <= BLK_KMAX) ? k : BLK_KMAX;
@@ -284,10 +286,10 @@ int launch_block_init(lpgpu_dense *d) {
 }
 
 // ---- pipelined blocks: the pass of block b runs on a second stream, out of place (T -> T2), while the step kernels of
-// block b+1 decide on T (the tableau BEFORE block b) through the slices of block b and their own.  Variant bit 0x2000
-// (primal methods); the default is the in-place order (steps, pass, steps, ...), which measures faster: DESIGN.md 4.0.
+// block b+1 decide on T (the tableau BEFORE block b) through the slices of block b and their own.  Default for the primal
+// methods; variant bit 0x2000 (or no room for the second tableau buffer) keeps the in-place order: steps, pass, steps, ...
 static bool want_pipeline(const lpgpu_dense *d) {
-    return use_blocked(d) && (d->opts.variant & 0x2000) && !(d->opts.variant & 0x100) && d->opts.method != LPGPU_DUAL;
+    return use_blocked(d) && !(d->opts.variant & (0x2000 | 0x100)) && d->opts.method != LPGPU_DUAL && !getenv("LPGPU_NO_PIPELINE");
 }
 
 static void free_pipeline(lpgpu_dense *d) {
@@ -351,6 +353,8 @@ static int setup_pipeline(lpgpu_dense *d) {
     return LPGPU_OK;
 }
 
+static int launch_pass_kernel(lpgpu_dense *d, const FlushParams &U, cudaStream_t stream);
+
 // Close the open block: its pass goes to stream2 (after this block's steps), the next block's steps wait for the
 // pass before it (they read its output and reuse its slices).  ev0 / ev1: optional timing events around the pass.
 static int close_block_pipe(lpgpu_dense *d, cudaEvent_t ev0, cudaEvent_t ev1) {
@@ -364,16 +368,18 @@ static int close_block_pipe(lpgpu_dense *d, cudaEvent_t ev0, cudaEvent_t ev1) {
     U.rowstamp = odd ? d->rowstamp2 : d->rowstamp; U.steprow = odd ? d->steprow2 : d->steprow; U.st = d->st;
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
     U.rb = d->fl_rb; U.pf = d->fl_pf;
-    const bool full = d->grid_flush >= ctx->sm_count * 2;       // a full persistent grid: every SM holds CTAs of the pass
+    const bool full = d->grid_flush >= ctx->sm_count * 2;   // a full persistent grid: every SM holds CTAs of the pass
     for (int w = 0; w < 8; ++w) U.resv[w] = full ? d->resv[w] : 0u;
     U.flag = d->flush_flag;
+    U.l2first = (d->l2hint & 1) ? 1 : 0;
     LP_CUDA(ctx, cudaEventRecord(d->ev_steps, ctx->stream));
     if (d->pend) LP_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, d->ev_flush, 0));
     LP_CUDA(ctx, cudaStreamWaitEvent(d->stream2, d->ev_steps, 0));
     if (ev0) LP_CUDA(ctx, cudaEventRecord(ev0, d->stream2));
-    if (d->opts.variant & 0x4000) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, d->stream2>>>(U);
-    else blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, d->stream2>>>(U);
-    LP_LAUNCH_CHECK(ctx);
+    {
+        const int rcp = launch_pass_kernel(d, U, d->stream2);
+        if (rcp != LPGPU_OK) return rcp;
+    }
     const unsigned fx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, (d->ld + 255) / 256));
     blk_fixrows_kernel<<<dim3(fx, BLK_KMAX), 256, 0, d->stream2>>>(U);
     LP_LAUNCH_CHECK(ctx);
@@ -446,21 +452,32 @@ static int launch_block_step(lpgpu_dense *d, int first) {
     return LPGPU_OK;
 }
 
+// which pass kernel: variant bit 0x4000 = the one that loads a whole tile before it computes, else the software-pipelined default
+static int launch_pass_kernel(lpgpu_dense *d, const FlushParams &U, cudaStream_t stream) {
+    lpgpu_ctx *ctx = d->ctx;
+    if (d->opts.variant & 0x4000) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
+    else blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
+    LP_LAUNCH_CHECK(ctx);
+    return LPGPU_OK;
+}
+
 int launch_block_flush(lpgpu_dense *d) {
     lpgpu_ctx *ctx = d->ctx;
     FlushParams U;
     U.T = d->T; U.ld = d->ld; U.rows = d->m + d->R; U.Fs = d->Ft; U.pcn = d->pcn; U.Pm = d->Pm; U.rowstamp = d->rowstamp; U.steprow = d->steprow; U.st = d->st;
-    U.Tsrc = d->T; U.kc_ptr = &d->st->blk_t; U.seq_ptr = &d->st->blk_seq; U.flag = nullptr;
+    U.Tsrc = d->T; U.kc_ptr = &d->st->blk_t; U.seq_ptr = &d->st->blk_seq; U.flag = nullptr; U.l2first = 0;
     for (unsigned &w : U.resv) w = 0;
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
     U.rb = d->fl_rb; U.pf = d->fl_pf;
     // variant bit 0x100: the warp-specialised pass (one CTA per SM, TMA ring; slower: see DESIGN.md 4.0)
     // variant bit 0x4000: the pass that loads a whole tile before it computes (the default is software-pipelined in half tiles)
     if (!(d->opts.variant & 0x100)) {
-        if (d->opts.variant & 0x4000) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, ctx->stream>>>(U);
-        else blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, ctx->stream>>>(U);
-    } else blk_flush_ws_kernel<<<std::min<long>(ctx->sm_count, d->flush_tasks), WS_THREADS, WS_SMEM_BYTES, ctx->stream>>>(U);
-    LP_LAUNCH_CHECK(ctx);
+        const int rcp = launch_pass_kernel(d, U, ctx->stream);
+        if (rcp != LPGPU_OK) return rcp;
+    } else {
+        blk_flush_ws_kernel<<<std::min<long>(ctx->sm_count, d->flush_tasks), WS_THREADS, WS_SMEM_BYTES, ctx->stream>>>(U);
+        LP_LAUNCH_CHECK(ctx);
+    }
     const unsigned fx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, (d->ld + 255) / 256));
     blk_fixrows_kernel<<<dim3(fx, BLK_KMAX), 256, 0, ctx->stream>>>(U);
     LP_LAUNCH_CHECK(ctx);                   // (the macro counts the launch)
@@ -527,6 +544,7 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     d->log = nullptr; d->log_cap = 0; d->task_ctr = nullptr; d->upd_seq = 0;
     d->Ft = d->Pm = d->objcur = d->bcur = nullptr; d->rowstamp = d->steprow = nullptr; d->cands = nullptr; d->blk_open = false; d->blk_steps = 0;
     d->pipe_state = 0; d->pipe_on = false; d->pend = false; d->par = 0;
+    { const char *eh = getenv("LPGPU_L2HINT"); d->l2hint = eh ? atoi(eh) : 3; }
     d->T2 = d->Ft2 = d->Pm2 = nullptr; d->rowstamp2 = d->steprow2 = nullptr; d->info = nullptr; d->flush_flag = nullptr;
     d->stream2 = nullptr; d->ev_steps = d->ev_flush = nullptr;
     for (unsigned &w : d->resv) w = 0;
@@ -702,7 +720,7 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
         // ---- blocked path: K step kernels (decide a pivot each on lazily updated slices), then one pass over
         // the tableau that applies them all; the tableau is brought up to date before this call returns
         const int K = make_bufs(d).K;
-        // pipelined blocks (variant bit 0x2000): the pass of a block overlaps the decisions of the next one
+        // pipelined blocks (default; variant bit 0x2000 = in place): the pass of a block overlaps the decisions of the next one
         d->pipe_on = false;
         if (want_pipeline(d)) {
             rc = setup_pipeline(d);

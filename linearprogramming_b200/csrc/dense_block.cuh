@@ -96,6 +96,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     // (PIPE = false: the in-place order, Kp = 0 at compile time and the code below is the plain one-block chain)
     const int Kp = (PIPE && B.pend) ? B.info[B.par ^ 1].kc : 0;
     const int tc = Kp + t;
+    const uint64_t pol = l2_policy(B.l2keep ? 2 : 0);
     const int offP = PIPE ? (B.par ^ 1) * BLK_KMAX : 0, offC = PIPE ? B.par * BLK_KMAX - Kp : 0;     // combined step c -> row of Fall / Pall
     auto srow = [&](int cc) -> size_t { return (size_t)((cc < Kp ? offP : offC) + cc); };
     KeyCand cin = keycand_none();                  // the previous step's per-CTA candidates, requested together with the state
@@ -153,7 +154,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
             if (i < P.m) { tv = P.T[(size_t)i * P.ld + (size_t)k]; rs = B.rowstamp[i]; bv = B.bcur[i]; if (Kp) rsp = B.stamp_prev[i]; }
             if ((int)threadIdx.x < tc) {
                 const int cc = (int)threadIdx.x;
-                s_pk[cc] = B.Pall[srow(cc) * P.ld + (size_t)k];
+                s_pk[cc] = ld_hint(B.Pall + srow(cc) * P.ld + (size_t)k, pol);
             }
             __syncthreads();
             KeyCand c = keycand_none();
@@ -168,13 +169,13 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
 #pragma unroll
                     for (int u = 0; u < FB; ++u) {
                         const int cc = sb + u;
-                        fv[u] = (cc < tc) ? B.Fall[srow(cc) * pcn + i] : 0.0;
+                        fv[u] = (cc < tc) ? ld_hint(B.Fall + srow(cc) * pcn + i, pol) : 0.0;
                     }
 #pragma unroll
                     for (int u = 0; u < FB; ++u)
                         if (sb + u < tc) a = __fma_rn(-fv[u], s_pk[sb + u], a);
                 }
-                B.Fs[(size_t)t * pcn + i] = a;
+                st_hint(B.Fs + (size_t)t * pcn + i, a, pol);
                 if (a > P.eps) {
                     KeyCand x;
                     x.kp = 0;
@@ -225,7 +226,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     const double piv = __ldcg(B.Fs + (size_t)t * pcn + r);                   // written above, possibly by another CTA
     if ((int)threadIdx.x < tc) {
         const int cc = (int)threadIdx.x;
-        s_fr[cc] = B.Fall[srow(cc) * pcn + r];
+        s_fr[cc] = ld_hint(B.Fall + srow(cc) * pcn + r, pol);
     }
     __syncthreads();
     // the scaled pivot row the chain restarts from, if this row was a pivot row in this block or the pending one
@@ -250,7 +251,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
 #pragma unroll
             for (int cth = 0; cth < STEP_CPT; ++cth) {
                 const size_t j = j0 + (size_t)cth * GSTRIDE;
-                if (j <= (size_t)P.n) av[cth] = rrow[j];
+                if (j <= (size_t)P.n) av[cth] = ld_hint(rrow + j, pol);
             }
         }
         for (int sb = c0r; sb < tc; sb += PB) {         // PB earlier pivot rows x STEP_CPT columns in flight
@@ -261,7 +262,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
 #pragma unroll
                 for (int u = 0; u < PB; ++u) {
                     const int cc = sb + u;
-                    pv[cth][u] = (cc < tc && j <= (size_t)P.n) ? B.Pall[srow(cc) * P.ld + j] : 0.0;
+                    pv[cth][u] = (cc < tc && j <= (size_t)P.n) ? ld_hint(B.Pall + srow(cc) * P.ld + j, pol) : 0.0;
                 }
             }
 #pragma unroll
@@ -276,7 +277,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
             const size_t j = j0 + (size_t)cth * GSTRIDE;
             if (j <= (size_t)P.n) {
                 const double pr = div_skip_zero(av[cth], piv);
-                pt[j] = pr;
+                st_hint(pt + j, pr, pol);
                 const double qc = __fma_rn(-sig_c, pr, ocv[cth]);
                 B.objcur[j] = qc;
                 double qm = 0.0;
@@ -535,6 +536,7 @@ struct FlushParams {
     const int *seq_ptr;       // the block's sequence number
     unsigned resv[8];         // bit smid set: that SM is left to the step kernels of the next block (CTAs landing there exit)
     int *flag;                // >= seq + 1 once a CTA of this launch runs on an SM that is not reserved
+    int l2first;              // 1: the tableau goes through L2 with the evict-first priority (blk_flush_sp_kernel)
     size_t ld;
     int rows;                 // m + R
     const double *Fs;         // BLK_KMAX x pcn
@@ -765,26 +767,26 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U)
 constexpr int FL_HR = FL_TR / 2;       // rows per half
 
 template <int NR>
-__device__ __forceinline__ void fl_load_rows(const FlushParams &U, const FlTile &t, int row0, int jc, double2 (&acc)[NR][2]) {
+__device__ __forceinline__ void fl_load_rows(const FlushParams &U, const FlTile &t, int row0, int jc, double2 (&acc)[NR][2], uint64_t pol) {
     const double *tp = U.Tsrc + (size_t)row0 * U.ld + t.j0 + jc;
     const bool ok0 = jc < t.ncols, ok1 = jc + 64 < t.ncols;
 #pragma unroll
     for (int rr = 0; rr < NR; ++rr) {
         const bool rowok = row0 + rr < U.rows;
-        acc[rr][0] = (ok0 && rowok) ? ld_stream2(tp + (size_t)rr * U.ld) : make_double2(0.0, 0.0);
-        acc[rr][1] = (ok1 && rowok) ? ld_stream2(tp + (size_t)rr * U.ld + 64) : make_double2(0.0, 0.0);
+        acc[rr][0] = (ok0 && rowok) ? ld_stream2_hint(tp + (size_t)rr * U.ld, pol) : make_double2(0.0, 0.0);
+        acc[rr][1] = (ok1 && rowok) ? ld_stream2_hint(tp + (size_t)rr * U.ld + 64, pol) : make_double2(0.0, 0.0);
     }
 }
 
 template <int NR>
-__device__ __forceinline__ void fl_store_rows(const FlushParams &U, const FlTile &t, int row0, int jc, double2 (&acc)[NR][2]) {
+__device__ __forceinline__ void fl_store_rows(const FlushParams &U, const FlTile &t, int row0, int jc, double2 (&acc)[NR][2], uint64_t pol) {
     double *tp = U.T + (size_t)row0 * U.ld + t.j0 + jc;
     const bool ok0 = jc < t.ncols, ok1 = jc + 64 < t.ncols;
 #pragma unroll
     for (int rr = 0; rr < NR; ++rr) {
         const bool rowok = row0 + rr < U.rows;
-        if (ok0 && rowok) st_stream2(tp + (size_t)rr * U.ld, acc[rr][0]);
-        if (ok1 && rowok) st_stream2(tp + (size_t)rr * U.ld + 64, acc[rr][1]);
+        if (ok0 && rowok) st_stream2_hint(tp + (size_t)rr * U.ld, acc[rr][0], pol);
+        if (ok1 && rowok) st_stream2_hint(tp + (size_t)rr * U.ld + 64, acc[rr][1], pol);
     }
 }
 
@@ -897,6 +899,7 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_sp_kernel(FlushParams
     if (threadIdx.x == 0) s_task[0] = (long)atomicAdd(ctr, 1);
     __syncthreads();
     uint32_t par_p = 0, par_f = 0;
+    const uint64_t pol = l2_policy(U.l2first ? 1 : 0);
     double2 acc0[FL_HR][2], acc1[FL_HR][2];            // the two halves of a thread's 16 rows
     bool pre = false;                                  // acc0 already holds (is being loaded with) the first half of the coming tile
     for (int it = 0;; ++it) {
@@ -914,15 +917,15 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_sp_kernel(FlushParams
             const int fb = (rt - rt0) & 1;
             t.rt = rt;
             const int row0 = rt * FL_ROWS + FL_TR * wr;
-            if (!pre) fl_load_rows<FL_HR>(U, t, row0, jc, acc0);
-            fl_load_rows<FL_HR>(U, t, row0 + FL_HR, jc, acc1);           // in flight while the chain runs on the first half
+            if (!pre) fl_load_rows<FL_HR>(U, t, row0, jc, acc0, pol);
+            fl_load_rows<FL_HR>(U, t, row0 + FL_HR, jc, acc1, pol);      // in flight while the chain runs on the first half
             if (threadIdx.x == 0 && rt + 1 < rt1) issue_f(rt + 1, fb ^ 1);
             if (rt == rt0) { mbar_wait(&bar_p, par_p); par_p ^= 1; }
             mbar_wait(&bar_f[fb], (par_f >> fb) & 1u);
             par_f ^= 1u << fb;
             const double *fw = sF + (size_t)fb * BLK_KMAX * FL_ROWS + FL_TR * wr;
             fl_chain_rows<FL_HR>(kc, fw, sP + jc, acc0);
-            fl_store_rows<FL_HR>(U, t, row0, jc, acc0);
+            fl_store_rows<FL_HR>(U, t, row0, jc, acc0, pol);
             // the tile after this one (same task, or the first tile of the next task once its claim is visible):
             // its first half is requested now and arrives while the chain runs on the second half
             FlTile nx = t;
@@ -933,9 +936,9 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_sp_kernel(FlushParams
                 pre = (rt > rt0) && nt < ntasks;       // the claim was published before tile rt0's closing barrier
                 if (pre) nx = tile_of(nt, 0);
             }
-            if (pre) fl_load_rows<FL_HR>(U, nx, nx.rt * FL_ROWS + FL_TR * wr, jc, acc0);
+            if (pre) fl_load_rows<FL_HR>(U, nx, nx.rt * FL_ROWS + FL_TR * wr, jc, acc0, pol);
             fl_chain_rows<FL_HR>(kc, fw + FL_HR, sP + jc, acc1);
-            fl_store_rows<FL_HR>(U, t, row0 + FL_HR, jc, acc1);
+            fl_store_rows<FL_HR>(U, t, row0 + FL_HR, jc, acc1, pol);
             __syncthreads();       // sF[fb] may be refilled (two tiles ahead), and at the last tile sP and s_task
         }
     }

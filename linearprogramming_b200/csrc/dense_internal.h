@@ -36,6 +36,7 @@ struct lpgpu_dense {
     long blk_dbg_n;
     bool blk_open;          // step kernels were enqueued since the last flush
     int blk_steps;          // ... how many
+    int l2hint;             // pipelined blocks: bit 0 = the pass streams the tableau with L2 evict-first, bit 1 = slices evict-last
     int step_cl_max;        // CTAs per cluster the primal step kernel may use: 16 where the device places such clusters, else 8
     // pipelined blocks (dense.cu): the pass of block b (stream2, T -> T2) runs while block b+1 is decided (ctx->stream)
     int pipe_state;         // 0 = not set up yet, 1 = ready, -1 = unavailable (second tableau buffer did not fit)

@@ -203,8 +203,9 @@ def test_dense_timed_run_reports_kernel_time(ctx):
 
 # ------------------------------------------------------------------ blocked path (delayed rank-1 applications)
 def _blocked(K=0):
-    # pivots per block (0 = the default, 32); the blocked path is the default; K >= 100: K - 100 pivots per block, pipelined blocks
-    return ((K % 100) << 16) | (capi.PIPELINED if K >= 100 else 0)
+    # pivots per block (0 = the default, 32); the blocked path with pipelined blocks is the default; K >= 100: K - 100 pivots per
+    # block, blocks applied in place
+    return ((K % 100) << 16) | (capi.INPLACE if K >= 100 else 0)
 
 
 @pytest.mark.parametrize("m,ns,K", [(64, 64, 0), (300, 500, 7), (512, 512, 32), (700, 1500, 0)])
@@ -340,18 +341,18 @@ def test_blocked_equals_rank1_path_midsize_bitwise(ctx):
 @pytest.mark.parametrize("m,ns", [(64, 64), (300, 500), (700, 1500)])
 @pytest.mark.parametrize("K", [0, 1, 5, 13])
 def test_pipelined_blocks_equal_inplace_blocks_and_oracle(ctx, m, ns, K):
-    """PIPELINED = the pass of block b out of place on a second stream while block b+1 is decided through the slices
-    of both blocks; default = steps, pass, steps in place on one stream.  Same bits, and the oracle's."""
+    """Default = pipelined blocks (the pass of block b out of place on a second stream while block b+1 is decided
+    through the slices of both blocks); INPLACE = steps, pass, steps on one stream.  Same bits, and the oracle's."""
     T0, basis = O.synth_feasible(99, 2, m, ns)
     ref = O.solve_f64(T0, basis, threads=4, log_cap=8192)
-    a = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K) | capi.PIPELINED)
-    b = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K))
+    a = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K))
+    b = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K) | capi.INPLACE)
     _assert_dense_equal(a, ref)
     _assert_dense_equal(b, ref)
     assert _same_bits(a["T"], b["T"])
     # the step kernel as a cluster of 8 CTAs (default: 16 where the device places such clusters), and the pass kernel that
     # loads a whole tile before it computes (default: software-pipelined halves)
-    for extra in (capi.STEP_CL8, capi.STEP_CL8 | capi.PIPELINED, capi.WHOLE_TILE_PASS, capi.WHOLE_TILE_PASS | capi.PIPELINED):
+    for extra in (capi.STEP_CL8, capi.STEP_CL8 | capi.INPLACE, capi.WHOLE_TILE_PASS, capi.WHOLE_TILE_PASS | capi.INPLACE):
         c = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K) | extra)
         _assert_dense_equal(c, ref)
 
@@ -363,7 +364,7 @@ def test_pipelined_blocks_windows_of_odd_sizes(ctx):
     T0, basis = O.synth_feasible(78, 6, m, ns)
     d = lp.DenseTableau(ctx, m, m + ns, 1)
     d.upload(T0, basis)
-    d.reset(log_cap=4096, check_every=5, variant=_blocked(4) | capi.PIPELINED)
+    d.reset(log_cap=4096, check_every=5, variant=_blocked(4))
     total, sizes, q = 0, [1, 2, 33, 64, 7, 9, 100, 3], 0
     while True:
         r = d.run(sizes[q % len(sizes)])
@@ -385,7 +386,7 @@ def test_pipelined_blocks_full_grid_2048x8192_bitwise(ctx):
     SMs free): 400 pivots, pipelined and in place, against the rank-1 path and the oracle."""
     m, ns, Pn = 2048, 6144, 400
     outs = []
-    for variant in (capi.RANK1, 0, capi.PIPELINED, _blocked(24) | capi.PIPELINED):
+    for variant in (capi.RANK1, 0, capi.INPLACE, _blocked(24), capi.STEP_CL8):
         d = lp.DenseTableau(ctx, m, m + ns, 1)
         d.synth(1234, 7, ns)
         d.reset(log_cap=Pn, variant=variant)

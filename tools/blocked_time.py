@@ -12,7 +12,7 @@ ctx = lp.Context(0)
 d = lp.DenseTableau(ctx, m, 2 * m, 1)
 ref_log = None
 names = (("rank1", capi.RANK1), ("blocked32", 0), ("blocked24", 24 << 16), ("blocked16", 16 << 16), ("blocked8", 8 << 16),
-         ("pipe32", capi.PIPELINED), ("pipe24", (24 << 16) | capi.PIPELINED))
+         ("inplace32", capi.INPLACE), ("inplace24", (24 << 16) | capi.INPLACE))
 if os.environ.get("BLK_ONLY"):
     names = tuple(x for x in names if x[0] in os.environ["BLK_ONLY"].split(","))
 if os.environ.get("BLK_VARIANTS"):      # name=variant,name=variant (hex allowed), always after the rank-1 reference run

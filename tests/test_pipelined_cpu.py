@@ -153,8 +153,8 @@ def test_pipelined_blocks_restated_unbounded_and_limit():
     p = Pipelined(T, basis, 2)
     p.run(100)
     assert p.status == ref["status"] == O.UNBOUNDED and p.log == ref["log"].tolist() and np.array_equal(p.T, ref["T"])
-    T, basis = O.synth_feasible(1234, 0, 8, 8)
-    ref = O.solve_f64(T, basis, max_iter=5, log_cap=16)
+    T, basis = O.synth_feasible(1234, 3, 9, 7)
+    ref = O.solve_f64(T, basis, max_iter=3, log_cap=16)
     p = Pipelined(T, basis, 2)
-    p.run(100, max_iter=5)
+    p.run(100, max_iter=3)
     assert p.status == ref["status"] == O.ITER_LIMIT and p.log == ref["log"].tolist() and np.array_equal(p.T, ref["T"])

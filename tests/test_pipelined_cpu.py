@@ -127,11 +127,21 @@ class Pipelined:
         self._drain()                   # every run call leaves self.T up to date
 
 
-@pytest.mark.parametrize("K", [1, 2, 3, 5, 32])
-@pytest.mark.parametrize("sizes", [[10**6], [1, 2, 7, 3, 11, 4]])
-def test_pipelined_blocks_restated_match_oracle(K, sizes):
-    T, basis = O.synth_feasible(1234, 3, 9, 7)
+def _lp(seed, m=10, ns=8):
+    """all-<= LP with mixed-sign A and c (slack basis, plain method): a handful of pivots, rows that pivot twice"""
+    rng = np.random.default_rng(seed)
+    A, b, c, rel = H.random_mixed_lp(rng, m, ns, p_ge=0, p_eq=0, neg_b=0)
+    T, basis, n_art = O.build_tableau(A, b, c, rel, R=1)
+    assert n_art == 0
+    return T, basis
+
+
+@pytest.mark.parametrize("K", [1, 2, 3, 32])
+@pytest.mark.parametrize("seed,sizes", [(2, [10**6]), (8, [10**6]), (8, [1, 2, 3]), (11, [2, 1]), (16, [10**6])])
+def test_pipelined_blocks_restated_match_oracle(K, seed, sizes):
+    T, basis = _lp(seed) if seed < 16 else O.synth_feasible(1234, 3, 16, 12)
     ref = O.solve_f64(T, basis, log_cap=4096)
+    assert ref["iters"] >= 5
     p = Pipelined(T, basis, K)
     q = 0
     while p.status is None:
@@ -153,8 +163,8 @@ def test_pipelined_blocks_restated_unbounded_and_limit():
     p = Pipelined(T, basis, 2)
     p.run(100)
     assert p.status == ref["status"] == O.UNBOUNDED and p.log == ref["log"].tolist() and np.array_equal(p.T, ref["T"])
-    T, basis = O.synth_feasible(1234, 3, 9, 7)
-    ref = O.solve_f64(T, basis, max_iter=3, log_cap=16)
+    T, basis = _lp(8)
+    ref = O.solve_f64(T, basis, max_iter=5, log_cap=16)
     p = Pipelined(T, basis, 2)
-    p.run(100, max_iter=3)
+    p.run(100, max_iter=5)
     assert p.status == ref["status"] == O.ITER_LIMIT and p.log == ref["log"].tolist() and np.array_equal(p.T, ref["T"])

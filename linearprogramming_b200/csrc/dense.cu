@@ -420,6 +420,7 @@ static int probe_step_cluster(lpgpu_dense *d) {
         for (int pipe = 0; pipe <= 1 && ok; ++pipe)
             ok = cudaFuncSetAttribute(step_kernel(R, pipe != 0, 16), cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
     if (ok) ok = cudaFuncSetAttribute(blk_probe_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
+    if (ok) ok = cudaFuncSetAttribute(blk_dual_step_kernel<16>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
     if (ok) {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(16); cfg.blockDim = dim3(SELECT_THREADS / 2);
@@ -440,9 +441,11 @@ static int step_cluster(const lpgpu_dense *d) { return (d->opts.variant & 0x8000
 static int launch_block_step(lpgpu_dense *d, int first) {
     lpgpu_ctx *ctx = d->ctx;
     const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels;
-    if (d->opts.method == LPGPU_DUAL)
-        LP_CUDA(ctx, launch_pdl(pdl, blk_dual_step_kernel, dim3(SELECT_CLUSTER), dim3(SELECT_THREADS), ctx->stream, make_params(d), make_bufs(d), first));
-    else {
+    if (d->opts.method == LPGPU_DUAL) {
+        const int cl = step_cluster(d);
+        LP_CUDA(ctx, launch_cluster(pdl, cl, cl == 16 ? blk_dual_step_kernel<16> : blk_dual_step_kernel<8>, dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS),
+                                    ctx->stream, make_params(d), make_bufs(d), first));
+    } else {
         const int cl = step_cluster(d);
         LP_CUDA(ctx, launch_cluster(pdl, cl, step_kernel(d->R, d->pipe_on, cl), dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS), ctx->stream,
                                     make_params(d), make_bufs(d), first));

@@ -323,15 +323,17 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
 // of the NEXT pivot are left per CTA at the end of a step, as in the primal kernel), row r brought up to
 // date lazily, entering column = min sigma_j / a_rj over a_rj < -eps on it, column k brought up to date
 // lazily -> F[t], row scaled by a_rk = F[t][r] -> P[t], objective row and b updated.
-__global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
+template <int CL>
+__global__ void __launch_bounds__(StepShape<CL>::TH)
 blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
-    __shared__ KeyCand scr_a[SELECT_THREADS / 32], scr_b[SELECT_THREADS / 32], scr_c[SELECT_THREADS / 32];
-    __shared__ KeyCand slot_a[SELECT_CLUSTER], slot_b[SELECT_CLUSTER];
+    constexpr int TH = StepShape<CL>::TH, FB = StepShape<CL>::FB, PB = StepShape<CL>::PB;      // cluster shape: see blk_step_kernel
+    __shared__ KeyCand scr_a[TH / 32], scr_b[TH / 32], scr_c[TH / 32];
+    __shared__ KeyCand slot_a[CL], slot_b[CL];
     __shared__ double s_pk[BLK_KMAX], s_fr[BLK_KMAX];
     cg::cluster_group cl = cg::this_cluster();
     const int rank = (int)cl.block_rank();
-    const int gtid = rank * SELECT_THREADS + (int)threadIdx.x;
-    constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
+    const int gtid = rank * TH + (int)threadIdx.x;
+    constexpr int GSTRIDE = CL * TH;
 
     pdl_wait();
     pdl_launch_dependents();
@@ -340,7 +342,7 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
     const int t = first ? 0 : st->blk_t, seq = st->blk_seq + (first ? 1 : 0);
     const int kn = st->k_next;                       // -2: per-CTA leaving-row candidates are in B.cands
     KeyCand cin = keycand_none();
-    if ((threadIdx.x & 31) < SELECT_CLUSTER) {
+    if ((threadIdx.x & 31) < CL) {
         const int ln = threadIdx.x & 31;
         cin.kp = __ldcg(&B.cands[ln].kp); cin.kq = __ldcg(&B.cands[ln].kq); cin.idx = __ldcg(&B.cands[ln].idx);
     }
@@ -364,7 +366,7 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
                     if (keycand_better(x, c)) c = x;
                 }
             }
-            r = cluster_key_best<false>(cl, c, scr_a, slot_a).idx;
+            r = cluster_key_best<false, CL>(cl, c, scr_a, slot_a).idx;
         }
         if (r < 0) status = LPGPU_OPTIMAL;
         else {
@@ -390,16 +392,16 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
                     else if (j <= (size_t)P.n) { aw[cth] = P.T[(size_t)r * P.ld + j]; ow[cth] = oc[j]; }
                     if (s0r > 0 && j <= (size_t)P.n) aw[cth] = B.Pm[(size_t)(s0r - 1) * P.ld + j];
                 }
-                for (int sb = s0r; sb < t; sb += STEP_PB) {
-                    double pv[STEP_CPT][STEP_PB];
+                for (int sb = s0r; sb < t; sb += PB) {
+                    double pv[STEP_CPT][PB];
 #pragma unroll
                     for (int cth = 0; cth < STEP_CPT; ++cth) {
                         const size_t j = j0 + (size_t)cth * GSTRIDE;
 #pragma unroll
-                        for (int u = 0; u < STEP_PB; ++u) pv[cth][u] = (sb + u < t && j <= (size_t)P.n) ? B.Pm[(size_t)(sb + u) * P.ld + j] : 0.0;
+                        for (int u = 0; u < PB; ++u) pv[cth][u] = (sb + u < t && j <= (size_t)P.n) ? B.Pm[(size_t)(sb + u) * P.ld + j] : 0.0;
                     }
 #pragma unroll
-                    for (int u = 0; u < STEP_PB; ++u)
+                    for (int u = 0; u < PB; ++u)
                         if (sb + u < t) {
 #pragma unroll
                             for (int cth = 0; cth < STEP_CPT; ++cth) aw[cth] = __fma_rn(-s_fr[sb + u], pv[cth][u], aw[cth]);
@@ -416,7 +418,7 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
                     }
                 }
             }
-            c = cluster_key_best<false>(cl, c, scr_b, slot_b);
+            c = cluster_key_best<false, CL>(cl, c, scr_b, slot_b);
             if (c.idx < 0) status = LPGPU_INFEASIBLE;
             else if (iters >= P.max_iter) status = LPGPU_ITER_LIMIT;
             else if (budget > 0) { have = true; k = c.idx; }
@@ -442,12 +444,12 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
     for (int i = gtid; i < P.m; i += GSTRIDE) {
         const int s0 = blk_row_start(B.rowstamp[i], seq);
         double a = s0 ? s_pk[s0 - 1] : P.T[(size_t)i * P.ld + (size_t)k];
-        for (int sb = s0; sb < t; sb += 8) {
-            double fv[8];
+        for (int sb = s0; sb < t; sb += FB) {
+            double fv[FB];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) fv[u] = (sb + u < t) ? B.Fs[(size_t)(sb + u) * pcn + i] : 0.0;
+            for (int u = 0; u < FB; ++u) fv[u] = (sb + u < t) ? B.Fs[(size_t)(sb + u) * pcn + i] : 0.0;
 #pragma unroll
-            for (int u = 0; u < 8; ++u)
+            for (int u = 0; u < FB; ++u)
                 if (sb + u < t) a = __fma_rn(-fv[u], s_pk[sb + u], a);
         }
         B.Fs[(size_t)t * pcn + i] = a;

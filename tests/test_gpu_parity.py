@@ -431,10 +431,10 @@ def test_dual_simplex_midsize_and_batched(ctx):
     _assert_batched_equal(gotb, refb)
 
 
-@pytest.mark.parametrize("variant", [0, 4 << 16, capi.RANK1])
+@pytest.mark.parametrize("variant", [0, 4 << 16, capi.STEP_CL8, (4 << 16) | capi.STEP_CL8, capi.RANK1])
 def test_dual_simplex_blocked_windows_and_rank1(ctx, variant):
-    """Dual simplex through the blocked path (default; blocks of 32 and of 4 pivots) and through the rank-1 path,
-    in windows of 7 pivots: all three leave the oracle's bits."""
+    """Dual simplex through the blocked path (default; blocks of 32 and of 4 pivots; step kernel as a cluster of 16 x 512
+    and of 8 x 1024 threads) and through the rank-1 path, in windows of 7 pivots: all leave the oracle's bits."""
     rng = np.random.default_rng(555)
     for (m, ns, infeasible) in [(120, 90, False), (40, 70, False), (30, 30, True)]:
         T, basis, _ = H.random_dual_lp(rng, m, ns, infeasible=infeasible)

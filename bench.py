@@ -342,6 +342,17 @@ def gpu_arm(args):
     if blocked:
         flops = 2.0 * (piv_n / upd_n) * (m + 1) * (n + 1)
         roofline["fp64_TFLOPs_in_kernel"] = flops / (upd_avg_ms * 1e-3) / 1e12
+        # the FP64 side's ceiling for this instruction mix (outer-product DFMAs with both operands fetched from shared memory
+        # every step) was measured with tools/dfma_peak.cu on this pool's B200: 25.3 TFLOP/s on 148 SMs; the pipelined pass
+        # runs on the SMs the step cluster leaves it
+        sms_pass = 148 - 16 if pipelined else 148
+        fp64_ceiling = 25.3 * sms_pass / 148
+        t_hbm_ms, t_fp64_ms = alg_bytes / (peak * 1e9) * 1e3, flops / (fp64_ceiling * 1e12) * 1e3
+        roofline["fp64_ceiling_TFLOPs"] = fp64_ceiling
+        roofline["fp64_ceiling_source"] = "measured: tools/dfma_peak.cu, outer 16 x 4, operands from shared memory, 12 warps/SM (DESIGN.md 4.0), scaled to the SMs of the pass"
+        roofline["fp64_frac_of_ceiling"] = roofline["fp64_TFLOPs_in_kernel"] / fp64_ceiling
+        roofline["co_bound_floor_ms"] = max(t_hbm_ms, t_fp64_ms)
+        roofline["frac_of_co_bound_floor"] = max(t_hbm_ms, t_fp64_ms) / upd_avg_ms
         roofline["note"] = ("one launch applies pivots_per_launch pivots: every element is read and written once and runs through "
                             "that many dependent DFMAs, so the launch is bounded by HBM (algorithmic bytes above) and, at 32 "
                             "pivots per launch, nearly as long on the FP64 pipe")

@@ -70,8 +70,11 @@ typedef struct {
     int n_art;          /* number of trailing artificial columns                         */
     int log_cap;        /* pivots to record in the pivot log (0 = none)                  */
     int check_every;    /* dense: pivots enqueued between host status reads (0 = 64)     */
-    int variant;        /* kernel variant (0 = default): 0x800 = one pass  */
-                        /* over the tableau per pivot instead of one per block of pivots  */
+    int variant;        /* kernel variant (0 = default): 0x800 = one pass */
+                        /* over the tableau per pivot instead of one per block of pivots; */
+                        /* 0x2000 = blocks applied in place (default: the pass of a block  */
+                        /* overlaps the decisions of the next one and needs a second       */
+                        /* tableau buffer on the device); bits 16..21 = pivots per block   */
     int time_kernels;   /* dense: bracket every elimination launch with CUDA events      */
     int results_only;   /* lpgpu_solve_dense: do not copy the final tableau back to T    */
 } lpgpu_opts;

@@ -1095,7 +1095,14 @@ __global__ void __launch_bounds__(256) blk_fixrows_kernel(FlushParams U) {
     __syncthreads();
     for (size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x; j < U.ld; j += (size_t)gridDim.x * blockDim.x) {
         double a = U.Pm[(size_t)s0 * U.ld + j];
-        for (int s = s0 + 1; s < kc; ++s) a = __fma_rn(-s_f[s], U.Pm[(size_t)s * U.ld + j], a);
+        for (int sb = s0 + 1; sb < kc; sb += 16) {            // 16 later pivot rows in flight: one round trip per batch, not per step
+            double pv[16];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) pv[u] = (sb + u < kc) ? U.Pm[(size_t)(sb + u) * U.ld + j] : 0.0;
+#pragma unroll
+            for (int u = 0; u < 16; ++u)
+                if (sb + u < kc) a = __fma_rn(-s_f[sb + u], pv[u], a);
+        }
         U.T[(size_t)r * U.ld + j] = a;
     }
 }

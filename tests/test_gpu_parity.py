@@ -402,6 +402,21 @@ def test_pipelined_blocks_full_grid_2048x8192_bitwise(ctx):
         assert np.array_equal(o["T"], ref["T"])
 
 
+@pytest.mark.parametrize("method", [O.BIGM, O.TWOPHASE])
+def test_pipelined_blocks_two_objective_rows_full_grid_bitwise(ctx, method):
+    """Big-M and two-phase (R = 2) on a mixed-relation LP large enough for the pass to run as a full persistent grid next
+    to the step cluster: the first 500 pivots, pipelined and in place, against the oracle (log, basis, tableau)."""
+    rng = np.random.default_rng(2024)
+    A, b, c, rel = H.random_mixed_lp(rng, 2048, 5000)
+    T0, basis, n_art = lp.build_tableau(A, b, c, rel, R=2)
+    Pn = 500
+    ref = O.solve_f64(T0, basis, method=method, n_art=n_art, max_iter=Pn, threads=16, log_cap=Pn)
+    for variant in (0, capi.INPLACE):
+        got = lp.solve_dense(ctx, T0, basis, method=method, n_art=n_art, max_iter=Pn, log_cap=Pn, variant=variant)
+        _assert_dense_equal(got, ref)
+    assert ref["iters"] == Pn
+
+
 # ------------------------------------------------------------------ dual simplex (SURVEY section 8 f3)
 @pytest.mark.parametrize("seed", range(8))
 def test_dual_simplex_dense_bitwise(ctx, seed):

@@ -487,6 +487,19 @@ int launch_block_flush(lpgpu_dense *d) {
     return LPGPU_OK;
 }
 
+// Bring d->T up to date, in stream order: the open block is closed and applied, the pass in flight waited for.  A run call
+// of the pipelined path leaves both pending (its results come from the eagerly kept objective rows / b column), so that the
+// next run call continues the pipeline; everything else that touches the tableau calls this first.
+int settle_dense(lpgpu_dense *d) {
+    if (d->blk_open) {
+        const int rc = d->pipe_on ? close_block_pipe(d, nullptr, nullptr) : launch_block_flush(d);
+        if (rc != LPGPU_OK) return rc;
+        d->blk_open = false;
+        d->blk_steps = 0;
+    }
+    return drain_pipe(d);
+}
+
 }  // namespace lpgpu
 
 namespace {
@@ -609,6 +622,7 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
 void lpgpu_dense_destroy(lpgpu_dense *d) {
     if (!d) return;
     cudaSetDevice(d->ctx->device);
+    if (d->T && d->st) settle_dense(d);
     cudaStreamSynchronize(d->ctx->stream);
     if (d->stream2) cudaStreamSynchronize(d->stream2);
     free_pipeline(d);
@@ -646,6 +660,7 @@ int lpgpu_dense_reset(lpgpu_dense *d, const lpgpu_opts *opts) {
     lpgpu_ctx *ctx = d->ctx;
     if (!opts_ok(opts, d->n, d->R)) return fail(ctx, LPGPU_EINVAL, "dense_reset: bad options (method/R/n_art)");
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    { const int rcs = settle_dense(d); if (rcs != LPGPU_OK) return rcs; }
     d->opts = *opts;
     if (d->opts.check_every <= 0) d->opts.check_every = 64;
     if (opts->log_cap > d->log_cap) {
@@ -675,6 +690,7 @@ int lpgpu_dense_upload(lpgpu_dense *d, const double *T, size_t ld, const int *ba
     lpgpu_ctx *ctx = d->ctx;
     if (ld < (size_t)d->n + 1) return fail(ctx, LPGPU_EINVAL, "dense_upload: ld %zu < n+1", ld);
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    { const int rcs = settle_dense(d); if (rcs != LPGPU_OK) return rcs; }
     LP_CUDA(ctx, cudaMemcpy2DAsync(d->T, d->ld * sizeof(double), T, ld * sizeof(double), ((size_t)d->n + 1) * sizeof(double),
                                    (size_t)d->m + d->R, cudaMemcpyHostToDevice, ctx->stream));
     LP_CUDA(ctx, cudaMemcpyAsync(d->basis, basis, (size_t)d->m * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
@@ -688,6 +704,7 @@ int lpgpu_dense_synth(lpgpu_dense *d, uint64_t seed, uint64_t lp_index, int ns) 
     lpgpu_ctx *ctx = d->ctx;
     if (d->R != 1 || ns < 1 || ns + d->m != d->n) return fail(ctx, LPGPU_EINVAL, "dense_synth: needs R=1 and n = ns + m");
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    { const int rcs = settle_dense(d); if (rcs != LPGPU_OK) return rcs; }
     dense_synth_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(d->T, d->ld, d->m, ns, d->basis, seed, lp_index);
     LP_LAUNCH_CHECK(ctx);
     d->la_dirty = true;
@@ -708,7 +725,10 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
             d->ev.push_back(e);
         }
     }
-    int rc = read_state(d);
+    // a pipelined run call leaves its last block(s) pending; anything but another pipelined run call needs the tableau itself
+    int rc = LPGPU_OK;
+    if (!(use_blocked(d) && want_pipeline(d) && d->pipe_state == 1 && d->pipe_on && !timed)) rc = settle_dense(d);
+    if (rc == LPGPU_OK) rc = read_state(d);
     if (rc != LPGPU_OK) return rc;
     d->h_st->budget = max_pivots;
     const bool dirty = d->la_dirty;
@@ -789,7 +809,7 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
             }
             return launch_block_init(d);
         };
-        if (d->h_st->phase == PH_DRIVEOUT) { rc = driveout(); if (rc != LPGPU_OK) return rc; }
+        if (d->h_st->phase == PH_DRIVEOUT) { rc = settle(); if (rc == LPGPU_OK) rc = driveout(); if (rc != LPGPU_OK) return rc; }
         while (launched < max_pivots && d->h_st->status == LPGPU_RUNNING) {
             const int chunk = std::min(chunk_max, max_pivots - launched);
             for (int c = 0; c < chunk; ++c) {
@@ -813,16 +833,20 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
                 iters_before = d->h_st->iters;
             }
         }
-        rc = settle();
-        if (rc != LPGPU_OK) return rc;
+        // pipelined and still running: the open block and the pass in flight stay pending, so that the next run call
+        // continues the pipeline (z comes from the eagerly kept objective rows; download / reset / upload / ... settle first)
+        const bool keep_pending = pipe && !timed && d->h_st->status == LPGPU_RUNNING && d->h_st->phase != PH_DRIVEOUT;
+        if (!keep_pending) { rc = settle(); if (rc != LPGPU_OK) return rc; }
         if (d->h_st->status == LPGPU_RUNNING) {
             // decision only (budget is spent): settles a terminal status
-            rc = (d->h_st->phase == PH_DRIVEOUT) ? launch_select(d, -1, 0) : launch_block_step(d, 1);
+            rc = (d->h_st->phase == PH_DRIVEOUT) ? launch_select(d, -1, 0) : launch_block_step(d, d->blk_open ? 0 : 1);
             if (rc != LPGPU_OK) return rc;
         }
         rc = read_state(d);
         if (rc == LPGPU_OK && timed) rc = collect();
         if (rc != LPGPU_OK) return rc;
+        // the decision-only step may have found a terminal status (or the end of phase one): nothing stays pending then
+        if (d->h_st->status != LPGPU_RUNNING || d->h_st->phase == PH_DRIVEOUT) { rc = settle(); if (rc != LPGPU_OK) return rc; }
     }
     while (!blocked && launched < max_pivots) {
         const int chunk = std::min(chunk_max, max_pivots - launched);
@@ -862,9 +886,11 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
     }
     // objective cells
     double zc[2] = {0.0, 0.0};
-    LP_CUDA(ctx, cudaMemcpyAsync(&zc[0], d->T + (size_t)d->m * d->ld, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    // with blocks pending the tableau's own objective cells are behind: the eagerly kept objective rows hold the same bits
+    const double *zsrc = (d->pend || d->blk_open) ? d->objcur : d->T + (size_t)d->m * d->ld;
+    LP_CUDA(ctx, cudaMemcpyAsync(&zc[0], zsrc, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     if (d->R == 2)
-        LP_CUDA(ctx, cudaMemcpyAsync(&zc[1], d->T + (size_t)(d->m + 1) * d->ld, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+        LP_CUDA(ctx, cudaMemcpyAsync(&zc[1], zsrc + d->ld, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     res->status = d->h_st->status;
     res->iters = d->h_st->iters;
@@ -884,6 +910,7 @@ int lpgpu_dense_pivot(lpgpu_dense *d, int r, int k) {
     lpgpu_ctx *ctx = d->ctx;
     if (r < 0 || r >= d->m || k < 1 || k > d->n) return fail(ctx, LPGPU_EINVAL, "dense_pivot: (r=%d,k=%d) out of range", r, k);
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    { const int rcs = settle_dense(d); if (rcs != LPGPU_OK) return rcs; }
     d->la_dirty = true;
     int rc = launch_select(d, r, k);
     if (rc != LPGPU_OK) return rc;
@@ -897,6 +924,7 @@ int lpgpu_dense_download(lpgpu_dense *d, double *T, size_t ld, int *basis, int *
     if (!d) return LPGPU_EINVAL;
     lpgpu_ctx *ctx = d->ctx;
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (T || x) { const int rcs = settle_dense(d); if (rcs != LPGPU_OK) return rcs; }
     if (T) {
         if (ld < (size_t)d->n + 1) return fail(ctx, LPGPU_EINVAL, "dense_download: ld %zu < n+1", ld);
         LP_CUDA(ctx, cudaMemcpy2DAsync(T, ld * sizeof(double), d->T, d->ld * sizeof(double), ((size_t)d->n + 1) * sizeof(double),

@@ -95,6 +95,8 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     // run through that block's Kp steps (combined step index c < Kp) and then this block's t steps (c - Kp)
     // (PIPE = false: the in-place order, Kp = 0 at compile time and the code below is the plain one-block chain)
     const int Kp = (PIPE && B.pend) ? B.info[B.par ^ 1].kc : 0;
+    const int seqp = (PIPE && B.pend) ? B.info[B.par ^ 1].seq : -1;      // the pending block's own sequence number (not seq - 1: a
+                                                                         // decision-only launch between two run calls also counts one up)
     const int tc = Kp + t;
     const uint64_t pol = l2_policy(B.l2keep ? 2 : 0);
     const int offP = PIPE ? (B.par ^ 1) * BLK_KMAX : 0, offC = PIPE ? B.par * BLK_KMAX - Kp : 0;     // combined step c -> row of Fall / Pall
@@ -162,7 +164,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
                 if (i != gtid) { tv = P.T[(size_t)i * P.ld + (size_t)k]; rs = B.rowstamp[i]; bv = B.bcur[i]; if (Kp) rsp = B.stamp_prev[i]; }
                 // where this row's chain starts: after its last turn as a pivot row (this block, else the pending one), else at the tableau
                 const int s0 = blk_row_start(rs, seq);
-                const int c0 = s0 ? Kp + s0 : (Kp ? blk_row_start(rsp, seq - 1) : 0);
+                const int c0 = s0 ? Kp + s0 : (Kp ? blk_row_start(rsp, seqp) : 0);
                 double a = c0 ? s_pk[c0 - 1] : tv;
                 for (int sb = c0; sb < tc; sb += FB) {            // multipliers of FB earlier steps in flight (coalesced over rows)
                     double fv[FB];
@@ -221,7 +223,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         }
     }
     const int s0r = blk_row_start(B.rowstamp[r], seq);
-    const int c0r = s0r ? Kp + s0r : (Kp ? blk_row_start(B.stamp_prev[r], seq - 1) : 0);
+    const int c0r = s0r ? Kp + s0r : (Kp ? blk_row_start(B.stamp_prev[r], seqp) : 0);
     const double b_r = B.bcur[r];
     const double piv = __ldcg(B.Fs + (size_t)t * pcn + r);                   // written above, possibly by another CTA
     if ((int)threadIdx.x < tc) {

@@ -381,6 +381,40 @@ def test_pipelined_blocks_windows_of_odd_sizes(ctx):
     d.close()
 
 
+def test_pipelined_blocks_stay_pending_across_run_calls(ctx):
+    """A pipelined run call that ends RUNNING leaves its open block and the pass in flight pending (z comes from the eagerly
+    kept objective row); the next call continues the block.  Many short calls without a download in between, then a forced
+    pivot / a reset to the rank-1 path in the middle (both settle the tableau first): the oracle's bits."""
+    m, ns = 300, 212
+    T0, basis = O.synth_feasible(79, 4, m, ns)
+    ref = O.solve_f64(T0, basis, log_cap=4096)
+    d = lp.DenseTableau(ctx, m, m + ns, 1)
+    d.upload(T0, basis)
+    d.reset(log_cap=4096, check_every=4, variant=_blocked(5))
+    sizes, q, total = [3, 1, 4, 1, 5, 9, 2, 6], 0, 0
+    while True:
+        r = d.run(sizes[q % len(sizes)])
+        q += 1
+        total = r["iters"]
+        if r["status"] != lp.RUNNING:
+            break
+        assert r["z"] == O.solve_f64(T0, basis, max_iter=total)["z"]       # from objcur while blocks are pending
+    out = d.download()
+    assert r["status"] == ref["status"] and r["iters"] == ref["iters"] and r["z"] == ref["z"]
+    assert out["log"][:r["iters"]].tolist() == ref["log"].tolist() and np.array_equal(out["T"], ref["T"])
+    # pending blocks, then a switch of path without a download: reset() must settle first
+    d.upload(T0, basis)
+    d.reset(log_cap=4096, variant=_blocked(7))
+    d.run(10)
+    part = O.solve_f64(T0, basis, max_iter=10)
+    d.reset(log_cap=4096, variant=capi.RANK1)
+    r2 = d.run(10**6)
+    ref2 = O.solve_f64(part["T"], part["basis"], log_cap=4096)
+    assert r2["status"] == ref2["status"] and r2["iters"] == ref2["iters"]
+    assert np.array_equal(d.download()["T"], ref2["T"])
+    d.close()
+
+
 def test_pipelined_blocks_full_grid_2048x8192_bitwise(ctx):
     """Large enough for the pass to run as a full persistent grid (the case in which it leaves the step kernels'
     SMs free): 400 pivots, pipelined and in place, against the rank-1 path and the oracle."""

@@ -42,7 +42,7 @@ class Pipelined:
 
     def _lazy(self, i, j, Kp, t, seq):
         s0 = _row_start(self.stamp[self.par][i], seq)
-        c0 = Kp + s0 if s0 else (_row_start(self.stamp[self.par ^ 1][i], seq - 1) if Kp else 0)
+        c0 = Kp + s0 if s0 else (_row_start(self.stamp[self.par ^ 1][i], self.info[self.par ^ 1][1]) if Kp else 0)
         if c0:
             q, s = self._src(c0 - 1, Kp)
             a = self.P[q][s][j]
@@ -85,7 +85,7 @@ class Pipelined:
             self.T, self.T2 = self.T2, self.T
             self.pend = False
 
-    def run(self, budget, max_iter=10**9):
+    def run(self, budget, max_iter=10**9, lazy=False):
         m, n = self.m, self.n
         while budget > 0 and self.status is None:
             first = not self.open
@@ -124,7 +124,13 @@ class Pipelined:
             self.info[self.par] = [t + 1, seq]
             if self.t >= self.K:
                 self._close_block()
-        self._drain()                   # every run call leaves self.T up to date
+        if not lazy or self.status is not None:
+            self._drain()               # self.T is up to date (download / reset / a terminal status settle the tableau)
+        elif not self.open:
+            # the device's decision-only launch at the end of a run call starts a block of its own (first = 1) that stays
+            # empty: the sequence number moves on without a block -- the pending block is found by ITS number (info), not seq - 1
+            self.seq += 1
+            self.info[self.par] = [0, self.seq]
 
 
 def _lp(seed, m=10, ns=8):
@@ -153,6 +159,20 @@ def test_pipelined_blocks_restated_match_oracle(K, seed, sizes):
     assert p.status == ref["status"] == O.OPTIMAL
     assert p.log == ref["log"].tolist() and np.array_equal(p.basis, ref["basis"])
     assert np.array_equal(p.T, ref["T"])
+
+
+@pytest.mark.parametrize("K", [1, 2, 3])
+def test_pipelined_blocks_restated_stay_pending_across_run_calls(K):
+    """Run calls that leave the open block and the pass in flight pending (as lpgpu_dense_run does while RUNNING)."""
+    T, basis = _lp(8)
+    ref = O.solve_f64(T, basis, log_cap=4096)
+    p = Pipelined(T, basis, K)
+    sizes, q = [1, 2, 1, 3], 0
+    while p.status is None:
+        p.run(sizes[q % len(sizes)], lazy=True)
+        q += 1
+        assert p.obj[0] == O.solve_f64(T, basis, max_iter=len(p.log))["T"][p.m, 0]
+    assert p.status == ref["status"] and p.log == ref["log"].tolist() and np.array_equal(p.T, ref["T"])
 
 
 def test_pipelined_blocks_restated_unbounded_and_limit():

@@ -123,6 +123,12 @@ int lpgpu_solve_dense(lpgpu_ctx *ctx, int m, int n, int R, double *T, size_t ld,
 int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out);
 void lpgpu_dense_destroy(lpgpu_dense *d);
 int lpgpu_dense_upload(lpgpu_dense *d, const double *T, size_t ld, const int *basis);
+/* The same without blocking the host (pinned buffers: lpgpu_host_alloc): the copy runs on a stream of
+ * its own, ordered after everything enqueued for this tableau before and before everything enqueued
+ * for it afterwards, so the upload of the next problem into one tableau object overlaps
+ * lpgpu_dense_run on another.  T and basis must stay untouched until the next call on d returns.
+ * (New: the reference solves one model per newSimplex call, Source/simplex.c:27-73.)                */
+int lpgpu_dense_upload_async(lpgpu_dense *d, const double *T, size_t ld, const int *basis);
 /* synthetic feasible LP generated on the device; needs n = ns + m, R = 1 */
 int lpgpu_dense_synth(lpgpu_dense *d, uint64_t seed, uint64_t lp_index, int ns);
 /* resets iteration state (status RUNNING, iters 0, phase from opts->method) */

@@ -71,6 +71,7 @@ SIGNATURES = {
     "lpgpu_dense_create": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.POINTER(_vp)]),
     "lpgpu_dense_destroy": (None, [_vp]),
     "lpgpu_dense_upload": (C.c_int, [_vp, _vp, C.c_size_t, _vp]),
+    "lpgpu_dense_upload_async": (C.c_int, [_vp, _vp, C.c_size_t, _vp]),
     "lpgpu_dense_synth": (C.c_int, [_vp, C.c_uint64, C.c_uint64, C.c_int]),
     "lpgpu_dense_reset": (C.c_int, [_vp, C.POINTER(Opts)]),
     "lpgpu_dense_run": (C.c_int, [_vp, C.c_int, C.POINTER(Result)]),

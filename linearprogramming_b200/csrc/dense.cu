@@ -491,6 +491,11 @@ int launch_block_flush(lpgpu_dense *d) {
 // of the pipelined path leaves both pending (its results come from the eagerly kept objective rows / b column), so that the
 // next run call continues the pipeline; everything else that touches the tableau calls this first.
 int settle_dense(lpgpu_dense *d) {
+    if (d->up_pending) {         // an asynchronous upload (lpgpu_dense_upload_async): everything on the context's stream comes after it
+        const cudaError_t e = cudaStreamWaitEvent(d->ctx->stream, d->ev_up, 0);
+        if (e != cudaSuccess) return fail(d->ctx, LPGPU_ECUDA, "settle: %s", cudaGetErrorString(e));
+        d->up_pending = false;
+    }
     if (d->blk_open) {
         const int rc = d->pipe_on ? close_block_pipe(d, nullptr, nullptr) : launch_block_flush(d);
         if (rc != LPGPU_OK) return rc;
@@ -560,6 +565,7 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     d->log = nullptr; d->log_cap = 0; d->task_ctr = nullptr; d->upd_seq = 0;
     d->Ft = d->Pm = d->objcur = d->bcur = nullptr; d->rowstamp = d->steprow = nullptr; d->cands = nullptr; d->blk_open = false; d->blk_steps = 0;
     d->pipe_state = 0; d->pipe_on = false; d->pend = false; d->par = 0;
+    d->up_stream = nullptr; d->ev_up = d->ev_up_ready = nullptr; d->up_pending = false;
     { const char *eh = getenv("LPGPU_L2HINT"); d->l2hint = eh ? atoi(eh) : 3; }
     d->T2 = d->Ft2 = d->Pm2 = nullptr; d->rowstamp2 = d->steprow2 = nullptr; d->info = nullptr; d->flush_flag = nullptr;
     d->stream2 = nullptr; d->ev_steps = d->ev_flush = nullptr;
@@ -626,6 +632,9 @@ void lpgpu_dense_destroy(lpgpu_dense *d) {
     cudaStreamSynchronize(d->ctx->stream);
     if (d->stream2) cudaStreamSynchronize(d->stream2);
     free_pipeline(d);
+    if (d->up_stream) { cudaStreamSynchronize(d->up_stream); cudaStreamDestroy(d->up_stream); }
+    if (d->ev_up) cudaEventDestroy(d->ev_up);
+    if (d->ev_up_ready) cudaEventDestroy(d->ev_up_ready);
     for (cudaEvent_t e : d->ev) cudaEventDestroy(e);
     if (d->blk_dbg) {       // development aid: mean time between the step kernel's phase stamps
         std::vector<unsigned long long> h(4096 * 8);
@@ -699,6 +708,32 @@ int lpgpu_dense_upload(lpgpu_dense *d, const double *T, size_t ld, const int *ba
     return LPGPU_OK;
 }
 
+// The same upload without blocking the host: the copy runs on a stream of its own, after everything enqueued for this
+// tableau so far, and everything enqueued for it later (run, download, ...) comes after the copy.  With pinned host
+// buffers the transfer of the NEXT problem into one tableau object overlaps lpgpu_dense_run on another one.  The host
+// buffers must stay untouched until the next call on this object returns (or lpgpu_sync).
+int lpgpu_dense_upload_async(lpgpu_dense *d, const double *T, size_t ld, const int *basis) {
+    if (!d || !T || !basis) return LPGPU_EINVAL;
+    lpgpu_ctx *ctx = d->ctx;
+    if (ld < (size_t)d->n + 1) return fail(ctx, LPGPU_EINVAL, "dense_upload_async: ld %zu < n+1", ld);
+    LP_CUDA(ctx, cudaSetDevice(ctx->device));
+    { const int rcs = settle_dense(d); if (rcs != LPGPU_OK) return rcs; }
+    if (!d->up_stream) {
+        LP_CUDA(ctx, cudaStreamCreateWithFlags(&d->up_stream, cudaStreamNonBlocking));
+        LP_CUDA(ctx, cudaEventCreateWithFlags(&d->ev_up, cudaEventDisableTiming));
+        LP_CUDA(ctx, cudaEventCreateWithFlags(&d->ev_up_ready, cudaEventDisableTiming));
+    }
+    LP_CUDA(ctx, cudaEventRecord(d->ev_up_ready, ctx->stream));              // the tableau's earlier work (passes, downloads) is done first
+    LP_CUDA(ctx, cudaStreamWaitEvent(d->up_stream, d->ev_up_ready, 0));
+    LP_CUDA(ctx, cudaMemcpy2DAsync(d->T, d->ld * sizeof(double), T, ld * sizeof(double), ((size_t)d->n + 1) * sizeof(double),
+                                   (size_t)d->m + d->R, cudaMemcpyHostToDevice, d->up_stream));
+    LP_CUDA(ctx, cudaMemcpyAsync(d->basis, basis, (size_t)d->m * sizeof(int), cudaMemcpyHostToDevice, d->up_stream));
+    LP_CUDA(ctx, cudaEventRecord(d->ev_up, d->up_stream));
+    d->up_pending = true;
+    d->la_dirty = true;
+    return LPGPU_OK;
+}
+
 int lpgpu_dense_synth(lpgpu_dense *d, uint64_t seed, uint64_t lp_index, int ns) {
     if (!d) return LPGPU_EINVAL;
     lpgpu_ctx *ctx = d->ctx;
@@ -727,7 +762,7 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
     }
     // a pipelined run call leaves its last block(s) pending; anything but another pipelined run call needs the tableau itself
     int rc = LPGPU_OK;
-    if (!(use_blocked(d) && want_pipeline(d) && d->pipe_state == 1 && d->pipe_on && !timed)) rc = settle_dense(d);
+    if (d->up_pending || !(use_blocked(d) && want_pipeline(d) && d->pipe_state == 1 && d->pipe_on && !timed)) rc = settle_dense(d);
     if (rc == LPGPU_OK) rc = read_state(d);
     if (rc != LPGPU_OK) return rc;
     d->h_st->budget = max_pivots;

@@ -50,6 +50,10 @@ struct lpgpu_dense {
     cudaStream_t stream2;
     cudaEvent_t ev_steps, ev_flush;
     unsigned resv[8];       // SMs left to the step kernels while a pass runs (bit per %smid)
+    // lpgpu_dense_upload_async: copy stream, "copy done" / "tableau free" events
+    cudaStream_t up_stream;
+    cudaEvent_t ev_up, ev_up_ready;
+    bool up_pending;
 };
 
 namespace lpgpu {

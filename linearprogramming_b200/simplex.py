@@ -137,6 +137,17 @@ class DenseTableau:
         capi.check(self.ctx.handle, capi.lib().lpgpu_dense_upload(self._h, _ptr(T), T.shape[1], _ptr(basis)),
                    "lpgpu_dense_upload")
 
+    def upload_async(self, T, basis):
+        """upload() without blocking the host: T and basis (pinned: Context.pinned) must stay untouched until the next
+        call on this object returns; the copy overlaps whatever runs on OTHER tableau objects meanwhile."""
+        if T.dtype != np.float64 or basis.dtype != np.int32 or not T.flags.c_contiguous or not basis.flags.c_contiguous:
+            raise ValueError("upload_async needs C-contiguous float64 / int32 arrays (no hidden copies)")
+        if T.shape != (self.m + self.R, self.n + 1) or basis.shape != (self.m,):
+            raise ValueError("shape mismatch")
+        self._async_refs = (T, basis)           # keep the buffers alive while the copy is in flight
+        capi.check(self.ctx.handle, capi.lib().lpgpu_dense_upload_async(self._h, _ptr(T), T.shape[1], _ptr(basis)),
+                   "lpgpu_dense_upload_async")
+
     def synth(self, seed, lp_index, ns):
         capi.check(self.ctx.handle, capi.lib().lpgpu_dense_synth(self._h, seed, lp_index, ns), "lpgpu_dense_synth")
 

@@ -415,6 +415,38 @@ def test_pipelined_blocks_stay_pending_across_run_calls(ctx):
     d.close()
 
 
+def test_dense_upload_async_stream_of_problems(ctx):
+    """lpgpu_dense_upload_async: the next problem travels into one tableau object (pinned buffers, own copy stream) while
+    another object pivots; runs, downloads and further uploads on an object are ordered after its asynchronous upload."""
+    m, ns = 256, 192
+    lps = [O.synth_feasible(500 + q, q, m, ns) for q in range(5)]
+    refs = [O.solve_f64(T, b, log_cap=4096) for T, b in lps]
+    objs = [lp.DenseTableau(ctx, m, m + ns, 1), lp.DenseTableau(ctx, m, m + ns, 1)]
+    bufs = [(ctx.pinned((m + 1, m + ns + 1)), ctx.pinned((m,), np.int32)) for _ in range(2)]
+    bufs[0][0][...] = lps[0][0]; bufs[0][1][...] = lps[0][1]
+    objs[0].upload_async(*bufs[0])
+    for q in range(5):
+        X = objs[q % 2]
+        if q + 1 < 5:
+            Tn, bn = bufs[(q + 1) % 2]
+            Tn[...] = lps[q + 1][0]; bn[...] = lps[q + 1][1]
+            objs[(q + 1) % 2].upload_async(Tn, bn)
+        X.reset(log_cap=4096, check_every=16)
+        r = X.run(10 if q == 2 else 10**6)            # problem 2 is left RUNNING with blocks pending: the next upload settles it
+        out = X.download()
+        ref = refs[q] if q != 2 else O.solve_f64(*lps[2], max_iter=10, log_cap=4096)
+        assert r["iters"] == ref["iters"] and out["log"][:r["iters"]].tolist() == ref["log"].tolist()
+        assert np.array_equal(out["T"], ref["T"]) and np.array_equal(out["basis"], ref["basis"])
+    # an asynchronous upload followed directly by a blocking one and by a device synth: the last writer wins
+    objs[0].upload_async(*bufs[0])
+    objs[0].upload(*lps[3])
+    objs[0].reset(log_cap=4096)
+    r = objs[0].run(10**6)
+    assert r["iters"] == refs[3]["iters"] and np.array_equal(objs[0].download()["T"], refs[3]["T"])
+    for o in objs:
+        o.close()
+
+
 def test_pipelined_blocks_full_grid_2048x8192_bitwise(ctx):
     """Large enough for the pass to run as a full persistent grid (the case in which it leaves the step kernels'
     SMs free): 400 pivots, pipelined and in place, against the rank-1 path and the oracle."""

@@ -299,7 +299,8 @@ def gpu_arm(args):
     # ---- roofline of the dominant kernel: same region, every pass over the tableau bracketed by events
     RANK1, INPLACE, WHOLE_TILE = 0x800, 0x2000, 0x4000
     blocked = not (variant & RANK1)
-    pipelined = blocked and not (variant & INPLACE)
+    # the default picks pipelined blocks from about 0.4 GB of tableau on (csrc/dense.cu want_pipeline); 0x1000 forces them
+    pipelined = blocked and not (variant & INPLACE) and bool((variant & 0x1000) or (m + 1) * ((n + 1 + 15) // 16 * 16) * 8 >= (384 << 20))
     block_k = ((variant >> 16) & 0x3f) or 32
 
     def kernel_times():

@@ -20,9 +20,10 @@ STATIC = 0x1             # dense: TMA-staged elimination with a static task stri
 DIRECT = 0x2             # dense: direct-load elimination kernel instead of the TMA-staged default
 RANK1 = 0x800            # dense: one pass over the tableau per pivot (default for plain / Big-M: up to K pivots decided on lazily
                          # updated slices, then applied in one pass; K = variant bits 16..21, 0 = 32)
-INPLACE = 0x2000         # dense, blocked path: steps, pass, steps, ... in place on one stream.  Default for the primal methods: pipelined
-                         # blocks -- the pass of a block runs out of place on a second stream while the next block is decided through
-                         # the slices of both blocks (bit-identical, 1.25x faster on 8192 x 16384; needs a second tableau buffer)
+INPLACE = 0x2000         # dense, blocked path: steps, pass, steps, ... in place on one stream
+PIPELINED = 0x1000       # dense, blocked path (primal methods): pipelined blocks -- the pass of a block runs out of place on a second
+                         # stream while the next block is decided through the slices of both blocks (bit-identical; needs a second
+                         # tableau buffer).  Default (neither bit): pipelined from about 0.4 GB of tableau on, in place below
 WHOLE_TILE_PASS = 0x4000 # dense, blocked path: the pass kernel that loads a whole tile before it computes (default: software-pipelined halves)
 STEP_CL8 = 0x8000        # dense, blocked path: primal step kernel as a cluster of 8 CTAs (default: 16 where the device allows it)
 WS_PASS = 0x100          # dense, blocked path: warp-specialised pass kernel (TMA ring; measured slower, kept as an alternative)

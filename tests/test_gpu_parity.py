@@ -203,9 +203,9 @@ def test_dense_timed_run_reports_kernel_time(ctx):
 
 # ------------------------------------------------------------------ blocked path (delayed rank-1 applications)
 def _blocked(K=0):
-    # pivots per block (0 = the default, 32); the blocked path with pipelined blocks is the default; K >= 100: K - 100 pivots per
-    # block, blocks applied in place
-    return ((K % 100) << 16) | (capi.INPLACE if K >= 100 else 0)
+    # pivots per block (0 = the default, 32), PIPELINED blocks whatever the size (the default picks them from 0.4 GB on);
+    # K >= 100: K - 100 pivots per block, blocks applied in place
+    return ((K % 100) << 16) | (capi.INPLACE if K >= 100 else capi.PIPELINED)
 
 
 @pytest.mark.parametrize("m,ns,K", [(64, 64, 0), (300, 500, 7), (512, 512, 32), (700, 1500, 0)])
@@ -431,7 +431,7 @@ def test_dense_upload_async_stream_of_problems(ctx):
             Tn, bn = bufs[(q + 1) % 2]
             Tn[...] = lps[q + 1][0]; bn[...] = lps[q + 1][1]
             objs[(q + 1) % 2].upload_async(Tn, bn)
-        X.reset(log_cap=4096, check_every=16)
+        X.reset(log_cap=4096, check_every=16, variant=capi.PIPELINED)
         r = X.run(10 if q == 2 else 10**6)            # problem 2 is left RUNNING with blocks pending: the next upload settles it
         out = X.download()
         ref = refs[q] if q != 2 else O.solve_f64(*lps[2], max_iter=10, log_cap=4096)
@@ -452,7 +452,7 @@ def test_pipelined_blocks_full_grid_2048x8192_bitwise(ctx):
     SMs free): 400 pivots, pipelined and in place, against the rank-1 path and the oracle."""
     m, ns, Pn = 2048, 6144, 400
     outs = []
-    for variant in (capi.RANK1, 0, capi.INPLACE, _blocked(24), capi.STEP_CL8):
+    for variant in (capi.RANK1, 0, capi.PIPELINED, capi.INPLACE, _blocked(24), capi.STEP_CL8 | capi.PIPELINED):
         d = lp.DenseTableau(ctx, m, m + ns, 1)
         d.synth(1234, 7, ns)
         d.reset(log_cap=Pn, variant=variant)
@@ -477,7 +477,7 @@ def test_pipelined_blocks_two_objective_rows_full_grid_bitwise(ctx, method):
     T0, basis, n_art = lp.build_tableau(A, b, c, rel, R=2)
     Pn = 500
     ref = O.solve_f64(T0, basis, method=method, n_art=n_art, max_iter=Pn, threads=16, log_cap=Pn)
-    for variant in (0, capi.INPLACE):
+    for variant in (capi.PIPELINED, capi.INPLACE):
         got = lp.solve_dense(ctx, T0, basis, method=method, n_art=n_art, max_iter=Pn, log_cap=Pn, variant=variant)
         _assert_dense_equal(got, ref)
     assert ref["iters"] == Pn

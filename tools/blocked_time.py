@@ -30,7 +30,8 @@ for name, variant in names:
         if timed:
             print(f"{name:10s} timed: step/select {r['select_ms'] / (piv - 32) * 1e3:8.2f} us/pivot, pass {r['update_ms'] / max(1, r['update_launches']):8.4f} ms x {r['update_launches']}")
         else:
-            print(f"{name:10s} {(piv - 32) / dt:10.1f} pivots/s  ({dt / (piv - 32) * 1e6:7.2f} us/pivot)  iters {r['iters']}")
+            done = max(1, r['iters'] - 32)            # the LP may reach its optimum before the window ends
+            print(f"{name:10s} {done / dt:10.1f} pivots/s  ({dt / done * 1e6:7.2f} us/pivot)  iters {r['iters']}")
     log = d.download(want_T=False)["log"] if hasattr(d, "download") else None
     if ref_log is None:
         ref_log = log

@@ -716,7 +716,7 @@ int lpgpu_dense_upload(lpgpu_dense *d, const double *T, size_t ld, const int *ba
 // The same upload without blocking the host: the copy runs on a stream of its own, after everything enqueued for this
 // tableau so far, and everything enqueued for it later (run, download, ...) comes after the copy.  With pinned host
 // buffers the transfer of the NEXT problem into one tableau object overlaps lpgpu_dense_run on another one.  The host
-// buffers must stay untouched until the next call on this object returns (or lpgpu_sync).
+// buffers must stay untouched until the next call on this object (run, reset, download, ...) returns.
 int lpgpu_dense_upload_async(lpgpu_dense *d, const double *T, size_t ld, const int *basis) {
     if (!d || !T || !basis) return LPGPU_EINVAL;
     lpgpu_ctx *ctx = d->ctx;

@@ -711,6 +711,30 @@ def test_cfg4_full_size_window_properties(ctx):
     d.close()
 
 
+def test_cfg4_full_size_pipelined_equals_inplace_bitwise(ctx):
+    """8192 x 16384, 200 pivots in run calls of 70 + 130 (six full blocks and a partial one, blocks left pending between the
+    calls): the default (pipelined at this size) and the in-place order leave the same pivot log, basis and tableau, bit
+    for bit; basic columns are exact unit vectors and b stays >= 0."""
+    m = ns = 8192
+    outs = []
+    for variant in (0, capi.INPLACE):
+        d = lp.DenseTableau(ctx, m, m + ns, 1)
+        d.synth(1234, 0, ns)
+        d.reset(log_cap=256, variant=variant)
+        z1 = d.run(70)["z"]
+        r = d.run(130)
+        assert r["iters"] == 200 and r["z"] >= z1
+        outs.append(d.download())
+        d.close()
+    a, b = outs
+    assert a["log"][:200].tolist() == b["log"][:200].tolist() and np.array_equal(a["basis"], b["basis"])
+    assert _same_bits(a["T"], b["T"])
+    T = a["T"]
+    assert np.all(T[:m, 0] >= 0.0)
+    sub = T[:, a["basis"]]
+    assert np.array_equal(sub[:m], np.eye(m)) and np.all(sub[m] == 0.0)
+
+
 def test_dense_lookahead_is_dropped_across_upload_and_forced_pivot(ctx):
     """The select kernel prices one pivot ahead; an upload, a device synth or a forced pivot between run()
     calls must invalidate that lookahead."""

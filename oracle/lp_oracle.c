@@ -22,7 +22,7 @@ typedef struct {
     size_t ld;
     int *basis;
     double eps;
-    int method, n_art, threads;
+    int method, n_art, threads, pricing;
 } lpo_ctx;
 
 #define AT(c, i, j) ((c)->T[(size_t)(i) * (c)->ld + (size_t)(j)])
@@ -35,7 +35,10 @@ static int price_single(const lpo_ctx *c, int row, int jmax) {
     double bv = 0.0;
     for (int j = 1; j <= jmax; ++j) {
         double v = AT(c, row, j);
-        if (v > c->eps && (best == 0 || v > bv)) { best = j; bv = v; }
+        if (v > c->eps && (best == 0 || v > bv)) {
+            best = j; bv = v;
+            if (c->pricing == 1) break;          /* Bland: the lowest eligible column */
+        }
     }
     return best;
 }
@@ -52,6 +55,7 @@ static int price_bigm(const lpo_ctx *c) {
         int eligible = (p > 0.0) || (p == 0.0 && q > c->eps);
         if (!eligible) continue;
         if (best == 0 || p > bp || (p == bp && q > bq)) { best = j; bp = p; bq = q; }
+        if (c->pricing == 1) break;              /* Bland: the lowest eligible column */
     }
     return best;
 }
@@ -142,8 +146,9 @@ int lpo_solve_f64(int m, int n, int R, double *T, size_t ld, int *basis,
     if (ld < (size_t)n + 1) return -1;
     if ((opts->method == LPO_PLAIN || opts->method == LPO_DUAL) != (R == 1)) return -1;
     if (opts->n_art < 0 || opts->n_art > n) return -1;
+    if (opts->pricing != 0 && (opts->pricing != 1 || opts->method == LPO_DUAL)) return -1;
     lpo_ctx c = { m, n, R, T, ld, basis, opts->eps, opts->method, opts->n_art,
-                  opts->threads > 0 ? opts->threads : 1 };
+                  opts->threads > 0 ? opts->threads : 1, opts->pricing };
     int phase = (opts->method == LPO_TWOPHASE) ? LPO_PH_ONE : LPO_PH_MAIN;
     int status = LPO_RUNNING, iters = 0, p1 = 0;
     while (status == LPO_RUNNING) {

@@ -50,6 +50,9 @@ typedef struct {
     int method;      /* LPO_PLAIN (R=1) | LPO_BIGM (R=2) | LPO_TWOPHASE (R=2) | LPO_DUAL (R=1) */
     int n_art;       /* artificial columns = the LAST n_art columns of the tableau   */
     int threads;     /* OpenMP threads for the elimination (results do not depend)   */
+    int pricing;     /* 0 = largest reduced cost, ties -> lowest column (Dantzig);
+                      * 1 = Bland: the LOWEST eligible column (with the lowest-row ratio tie-break: no cycling).
+                      * fp64 primal methods only (the reference prices nothing)  */
 } lpo_opts;
 
 typedef struct {

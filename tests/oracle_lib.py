@@ -17,9 +17,12 @@ PLAIN, BIGM, TWOPHASE, DUAL = 0, 1, 2, 3
 STATUS_NAMES = ["OPTIMAL", "UNBOUNDED", "INFEASIBLE", "ITER_LIMIT", "RUNNING", "OVERFLOW"]
 
 
+DANTZIG, BLAND = 0, 1          # lpo_opts.pricing
+
+
 class Opts(C.Structure):
     _fields_ = [("eps", C.c_double), ("max_iter", C.c_int), ("method", C.c_int),
-                ("n_art", C.c_int), ("threads", C.c_int)]
+                ("n_art", C.c_int), ("threads", C.c_int), ("pricing", C.c_int)]
 
 
 class Result(C.Structure):
@@ -96,7 +99,7 @@ def _ip(a):
     return a.ctypes.data_as(C.POINTER(C.c_int))
 
 
-def solve_f64(T, basis, method=PLAIN, n_art=0, eps=1e-9, max_iter=1 << 30, threads=1, log_cap=None, R=None):
+def solve_f64(T, basis, method=PLAIN, n_art=0, eps=1e-9, max_iter=1 << 30, threads=1, log_cap=None, R=None, pricing=0):
     """Solve in place on copies; returns dict(status, iters, z, zM, T, basis, log, x, phase1_iters)."""
     T = np.array(T, dtype=np.float64, order="C", copy=True)
     basis = np.array(basis, dtype=np.int32, copy=True)
@@ -108,7 +111,7 @@ def solve_f64(T, basis, method=PLAIN, n_art=0, eps=1e-9, max_iter=1 << 30, threa
         log_cap = 4 * (m + n) + 64
     log = np.full((log_cap, 2), -1, dtype=np.int32)
     res = Result()
-    opts = Opts(eps, int(min(max_iter, 2**31 - 1)), method, n_art, threads)
+    opts = Opts(eps, int(min(max_iter, 2**31 - 1)), method, n_art, threads, pricing)
     rc = lib().lpo_solve_f64(m, n, R, _dp(T), ld, _ip(basis), C.byref(opts), _ip(log), log_cap, C.byref(res))
     assert rc == 0, "oracle rejected arguments"
     x = np.zeros(n)
@@ -118,7 +121,7 @@ def solve_f64(T, basis, method=PLAIN, n_art=0, eps=1e-9, max_iter=1 << 30, threa
 
 
 def solve_batched_f64(T_all, basis_all, method=PLAIN, n_art=0, eps=1e-9, max_iter=1 << 30, threads=1,
-                      log_cap=0):
+                      log_cap=0, pricing=0):
     T_all = np.array(T_all, dtype=np.float64, order="C", copy=True)
     basis_all = np.array(basis_all, dtype=np.int32, order="C", copy=True)
     n_lp, rows, ld = T_all.shape
@@ -129,7 +132,7 @@ def solve_batched_f64(T_all, basis_all, method=PLAIN, n_art=0, eps=1e-9, max_ite
     z = np.zeros(n_lp)
     x = np.zeros((n_lp, n))
     log = np.full((n_lp, max(log_cap, 1), 2), -1, np.int32)
-    opts = Opts(eps, int(min(max_iter, 2**31 - 1)), method, n_art, threads)
+    opts = Opts(eps, int(min(max_iter, 2**31 - 1)), method, n_art, threads, pricing)
     rc = lib().lpo_solve_batched_f64(n_lp, m, n, R, _dp(T_all), _ip(basis_all), C.byref(opts), _ip(status),
                                      _ip(iters), _dp(z), _dp(x), _ip(log) if log_cap else None, log_cap)
     assert rc == 0

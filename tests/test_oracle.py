@@ -334,3 +334,41 @@ def test_oracle_synthetic_family_agrees_with_scipy_highs(seed):
     res = scipy_opt.linprog(-T[m, 1:ns + 1], A_ub=T[:m, 1:ns + 1], b_ub=T[:m, 0], bounds=(0, None), method="highs")
     assert got["status"] == O.OPTIMAL and res.status == 0
     assert got["z"] == pytest.approx(-res.fun, rel=1e-9)
+
+
+# ------------------------------------------------------------------ pricing option: Bland's rule
+def _beale():
+    """Beale's cycling example: max 3/4 x1 - 20 x2 + 1/2 x3 - 6 x4,  1/4 x1 - 8 x2 - x3 + 9 x4 <= 0,
+    1/2 x1 - 12 x2 - 1/2 x3 + 3 x4 <= 0,  x3 <= 1; optimum 5/4.  Every entry is a dyadic fraction, so fp64 is exact."""
+    A = np.array([[0.25, -8.0, -1.0, 9.0], [0.5, -12.0, -0.5, 3.0], [0.0, 0.0, 1.0, 0.0]])
+    b = np.array([0.0, 0.0, 1.0])
+    c = np.array([0.75, -20.0, 0.5, -6.0])
+    T, basis, n_art = O.build_tableau(A, b, c, np.full(3, -2, np.int32), R=1)
+    assert n_art == 0
+    return T, basis
+
+
+def test_bland_pricing_breaks_beales_cycle():
+    T, basis = _beale()
+    dantzig = O.solve_f64(T, basis, max_iter=600, log_cap=600)
+    assert dantzig["status"] == O.ITER_LIMIT                      # largest reduced cost + lowest-row ties: the 6-pivot cycle
+    assert dantzig["log"][:6].tolist() == dantzig["log"][6:12].tolist()
+    bland = O.solve_f64(T, basis, max_iter=600, log_cap=600, pricing=O.BLAND)
+    assert bland["status"] == O.OPTIMAL and bland["z"] == 1.25 and bland["iters"] < 20
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_bland_pricing_reaches_the_same_optimum(seed):
+    rng = np.random.default_rng(900 + seed)
+    A, b, c, rel = H.random_mixed_lp(rng, 12, 10)
+    for method, R in ((O.BIGM, 2), (O.TWOPHASE, 2)):
+        T, basis, n_art = O.build_tableau(A, b, c, rel, R=R)
+        d = O.solve_f64(T, basis, method=method, n_art=n_art, max_iter=5000)
+        bl = O.solve_f64(T, basis, method=method, n_art=n_art, max_iter=5000, pricing=O.BLAND, log_cap=64)
+        assert bl["status"] == d["status"]
+        if d["status"] == O.OPTIMAL:
+            assert abs(bl["z"] - d["z"]) <= 1e-9 * max(1.0, abs(d["z"]))
+    # the first Bland pivot enters the LOWEST column with a positive reduced cost
+    T, basis = O.synth_feasible(1234, seed, 10, 8)
+    bl = O.solve_f64(T, basis, pricing=O.BLAND, log_cap=8)
+    assert bl["log"][0][0] == 1 + int(np.argmax(T[10, 1:] > 1e-9))

@@ -59,6 +59,13 @@ extern "C" {
                                * <= 0), b may be negative; leaving row = most negative b_i, entering
                                * column = min sigma_j / a_rj over a_rj < 0      */
 
+/* lpgpu_opts.variant bit: Bland's rule -- the LOWEST eligible column enters (default: the largest reduced
+ * cost, ties to the lowest column).  With the lowest-row tie-break of the ratio test it cannot cycle
+ * (Beale's example runs into the iteration limit under the default rule).  Primal methods, dense and
+ * batched paths; LPGPU_EINVAL for the dual simplex and the column-sharded path.  SURVEY.md 8 (f4): the
+ * reference has no pricing at all (Source/simplex.c:57-63).                                            */
+#define LPGPU_VARIANT_BLAND 0x400000
+
 typedef struct lpgpu_ctx lpgpu_ctx;         /* one per process and GPU           */
 typedef struct lpgpu_dense lpgpu_dense;     /* one large device-resident tableau */
 typedef struct lpgpu_batched lpgpu_batched; /* many small tableaux               */

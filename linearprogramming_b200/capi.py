@@ -26,6 +26,8 @@ PIPELINED = 0x1000       # dense, blocked path (primal methods): pipelined block
                          # tableau buffer).  Default (neither bit): pipelined from about 0.4 GB of tableau on, in place below
 WHOLE_TILE_PASS = 0x4000 # dense, blocked path: the pass kernel that loads a whole tile before it computes (default: software-pipelined halves)
 STEP_CL8 = 0x8000        # dense, blocked path: primal step kernel as a cluster of 8 CTAs (default: 16 where the device allows it)
+BLAND = 0x400000         # dense and batched, primal methods: Bland's rule -- the LOWEST eligible column enters (default: the largest
+                         # reduced cost, ties to the lowest column); with the lowest-row ratio tie-break it cannot cycle
 WS_PASS = 0x100          # dense, blocked path: warp-specialised pass kernel (TMA ring; measured slower, kept as an alternative)
 NO_PDL = 0x400           # dense: plain stream-ordered launches (default: programmatic dependent launch)
 NO_ALTERNATE = 0x200     # dense: do not alternate the sweep direction between pivots

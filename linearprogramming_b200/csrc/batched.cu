@@ -142,6 +142,7 @@ int lpgpu_batched_run(lpgpu_batched *b, const lpgpu_opts *opts, float *kernel_ms
     BatchedParams B;
     B.T_all = b->T_all; B.basis_all = b->basis_all; B.n_lp = b->n_lp; B.m = b->m; B.n = b->n; B.R = b->R;
     B.eps = opts->eps; B.max_iter = opts->max_iter; B.method = opts->method; B.n_art = opts->n_art;
+    B.bland = (opts->variant & 0x400000) ? 1 : 0;       // Bland's rule: through the shared-memory kernel (decide())
     B.log_cap = b->log_cap; B.status = b->status; B.iters = b->iters; B.z = b->z; B.x = b->x;
     B.basis_out = b->basis_out; B.log = opts->log_cap > 0 ? b->log : nullptr;
     B.T_final = want_final ? b->T_final : nullptr;
@@ -150,7 +151,7 @@ int lpgpu_batched_run(lpgpu_batched *b, const lpgpu_opts *opts, float *kernel_ms
     // (batched_reg.cuh); everything else (Big-M, two-phase, other shapes, variant bit 0x2000): the
     // shared-memory kernel.  Grid = a whole number of resident CTAs per SM; each CTA walks LPs
     // p = blockIdx, blockIdx + grid, ...
-    const bool plain = opts->method == LPGPU_PLAIN && b->R == 1 && !(opts->variant & 0x2000);
+    const bool plain = opts->method == LPGPU_PLAIN && b->R == 1 && !(opts->variant & (0x2000 | 0x400000));
     int kind = 0;
     if (plain && b->m <= RegSmall::MAX_M && b->n <= RegSmall::MAX_N) kind = 1;
     else if (plain && b->m <= RegWide::MAX_M && b->n <= RegWide::MAX_N) kind = 2;

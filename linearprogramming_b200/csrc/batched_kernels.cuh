@@ -23,7 +23,7 @@ struct BatchedParams {
     long n_lp;
     int m, n, R;
     double eps;
-    int max_iter, method, n_art;
+    int max_iter, method, n_art, bland;
     int log_cap;
     int *status, *iters;   // n_lp
     double *z;             // n_lp (may be null)
@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(BATCH_THREADS) batched_simplex_kernel(BatchedP
         DenseParams P;
         P.T = S; P.ld = (size_t)ld1; P.m = m; P.n = n; P.R = R; P.basis = basis;
         P.prow = prow; P.pcol = pcol; P.pcn = 0; P.bnext = nullptr; P.st = nullptr; P.log = nullptr; P.log_cap = 0;
-        P.eps = B.eps; P.max_iter = B.max_iter; P.method = B.method; P.n_art = B.n_art;
+        P.eps = B.eps; P.max_iter = B.max_iter; P.method = B.method; P.n_art = B.n_art; P.bland = B.bland;
 
         int status = LPGPU_RUNNING, phase = (B.method == LPGPU_TWOPHASE) ? PH_ONE : PH_MAIN, iters = 0, p1 = 0;
         int *plog = B.log ? B.log + (size_t)p * 2 * B.log_cap : nullptr;

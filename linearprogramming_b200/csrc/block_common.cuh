@@ -119,19 +119,22 @@ __device__ __forceinline__ KeyCand cluster_key_best(cg::cluster_group &cl, KeyCa
 // two-phase main phase), 1 = Big-M (M row first, cost row second), 2 = two-phase phase one (row m+1 alone)
 enum { PRICE_COST = 0, PRICE_BIGM = 1, PRICE_PHASE1 = 2 };
 
+// BL: Bland's rule -- every eligible column gets the same key, the arg-max's tie-break (lowest column) decides.  A template
+// parameter, not a run-time test: the step kernel sits at its register limit and the default rule must not pay for the option.
+template <bool BL = false>
 __device__ __forceinline__ void blk_price(const DenseParams &P, int mode, int j, double oc, double om, KeyCand &c) {
     KeyCand t;
     t.idx = j;
     if (mode == PRICE_BIGM) {
         double p = om;
         if (fabs(p) <= P.eps) p = 0.0;
-        t.kp = ord_key(p);
-        t.kq = ord_key(oc);
+        t.kp = BL ? 0ull : ord_key(p);
+        t.kq = BL ? 1ull : ord_key(oc);
         if ((p > 0.0 || (p == 0.0 && oc > P.eps)) && keycand_better(t, c)) c = t;
     } else {
         const double q = (mode == PRICE_PHASE1) ? om : oc;
         t.kp = 0;
-        t.kq = ord_key(q);
+        t.kq = BL ? 1ull : ord_key(q);
         if (q > P.eps && keycand_better(t, c)) c = t;
     }
 }

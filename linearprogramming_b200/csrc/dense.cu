@@ -140,10 +140,10 @@ dense_select_kernel(DenseParams P, int forced_r, int forced_k) {
             if (bigm) {
                 double p = __fma_rn(fm, pr, om[j]);
                 if (fabs(p) <= P.eps) p = 0.0;
-                t.p = p; t.q = q;
+                t.p = P.bland ? 0.0 : p; t.q = P.bland ? 1.0 : q;
                 if ((p > 0.0 || (p == 0.0 && q > P.eps)) && cand_better(t, c)) c = t;
             } else {
-                t.p = 0.0; t.q = q;
+                t.p = 0.0; t.q = P.bland ? 1.0 : q;
                 if (q > P.eps && cand_better(t, c)) c = t;
             }
         }
@@ -166,6 +166,7 @@ DenseParams make_params(const lpgpu_dense *d) {
     P.basis = d->basis; P.prow = d->prow; P.pcol = d->pcol; P.pcn = d->pcn; P.bnext = d->bnext; P.st = d->st;
     P.log = d->log; P.log_cap = d->log_cap;
     P.eps = d->opts.eps; P.max_iter = d->opts.max_iter; P.method = d->opts.method; P.n_art = d->opts.n_art;
+    P.bland = (d->opts.variant & 0x400000) ? 1 : 0;
     return P;
 }
 
@@ -407,12 +408,16 @@ static int drain_pipe(lpgpu_dense *d) {
 }
 
 typedef void (*step_kernel_t)(DenseParams, BlockBufs, int);
-static step_kernel_t step_kernel(int R, bool pipe, int cl) {
+template <bool BL>
+static step_kernel_t step_kernel_bl(int R, bool pipe, int cl) {
     if (cl == 16)
-        return pipe ? (R == 2 ? blk_step_kernel<2, true, 16> : blk_step_kernel<1, true, 16>)
-                    : (R == 2 ? blk_step_kernel<2, false, 16> : blk_step_kernel<1, false, 16>);
-    return pipe ? (R == 2 ? blk_step_kernel<2, true, 8> : blk_step_kernel<1, true, 8>)
-                : (R == 2 ? blk_step_kernel<2, false, 8> : blk_step_kernel<1, false, 8>);
+        return pipe ? (R == 2 ? blk_step_kernel<2, true, 16, BL> : blk_step_kernel<1, true, 16, BL>)
+                    : (R == 2 ? blk_step_kernel<2, false, 16, BL> : blk_step_kernel<1, false, 16, BL>);
+    return pipe ? (R == 2 ? blk_step_kernel<2, true, 8, BL> : blk_step_kernel<1, true, 8, BL>)
+                : (R == 2 ? blk_step_kernel<2, false, 8, BL> : blk_step_kernel<1, false, 8, BL>);
+}
+static step_kernel_t step_kernel(int R, bool pipe, int cl, bool bland = false) {
+    return bland ? step_kernel_bl<true>(R, pipe, cl) : step_kernel_bl<false>(R, pipe, cl);
 }
 
 // CTAs per cluster of the primal step kernel: 16 where the device can place such a cluster (a non-portable size,
@@ -423,7 +428,8 @@ static int probe_step_cluster(lpgpu_dense *d) {
     bool ok = true;
     for (int R = 1; R <= 2 && ok; ++R)
         for (int pipe = 0; pipe <= 1 && ok; ++pipe)
-            ok = cudaFuncSetAttribute(step_kernel(R, pipe != 0, 16), cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
+            ok = cudaFuncSetAttribute(step_kernel(R, pipe != 0, 16), cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
+                 cudaFuncSetAttribute(step_kernel(R, pipe != 0, 16, true), cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
     if (ok) ok = cudaFuncSetAttribute(blk_probe_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
     if (ok) ok = cudaFuncSetAttribute(blk_dual_step_kernel<16>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
     if (ok) {
@@ -452,7 +458,7 @@ static int launch_block_step(lpgpu_dense *d, int first) {
                                     ctx->stream, make_params(d), make_bufs(d), first));
     } else {
         const int cl = step_cluster(d);
-        LP_CUDA(ctx, launch_cluster(pdl, cl, step_kernel(d->R, d->pipe_on, cl), dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS), ctx->stream,
+        LP_CUDA(ctx, launch_cluster(pdl, cl, step_kernel(d->R, d->pipe_on, cl, (d->opts.variant & 0x400000) != 0), dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS), ctx->stream,
                                     make_params(d), make_bufs(d), first));
     }
     if (d->blk_dbg) d->blk_dbg_n++;
@@ -551,6 +557,7 @@ bool opts_ok(const lpgpu_opts *o, int n, int R) {
     if (o->method != LPGPU_PLAIN && o->method != LPGPU_BIGM && o->method != LPGPU_TWOPHASE && o->method != LPGPU_DUAL) return false;
     if ((o->method == LPGPU_PLAIN || o->method == LPGPU_DUAL) != (R == 1)) return false;
     if (o->n_art < 0 || o->n_art > n || o->max_iter < 0 || o->log_cap < 0 || !(o->eps >= 0.0)) return false;
+    if ((o->variant & 0x400000) && o->method == LPGPU_DUAL) return false;      // Bland's rule: primal methods
     return true;
 }
 

@@ -62,7 +62,7 @@ template <int CL> struct StepShape {
     static constexpr int PB = (CL == 16) ? 16 : STEP_PB;        // ... row phase (x STEP_CPT columns per thread)
 };
 
-template <int RR, bool PIPE, int CL>
+template <int RR, bool PIPE, int CL, bool BL>
 __global__ void __launch_bounds__(StepShape<CL>::TH)
 blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     constexpr int TH = StepShape<CL>::TH, FB = StepShape<CL>::FB, PB = StepShape<CL>::PB;
@@ -127,7 +127,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
             k = c.idx > 0 ? c.idx : 0;
         } else {
             KeyCand c = keycand_none();
-            for (int j = 1 + gtid; j <= jmax; j += GSTRIDE) blk_price(P, pmode, j, oc[j], (RR == 2) ? om[j] : 0.0, c);
+            for (int j = 1 + gtid; j <= jmax; j += GSTRIDE) blk_price<BL>(P, pmode, j, oc[j], (RR == 2) ? om[j] : 0.0, c);
             c = cluster_key_best<true, CL>(cl, c, scr_a, slot_a);
             k = c.idx > 0 ? c.idx : 0;
         }
@@ -287,7 +287,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
                     qm = __fma_rn(-sig_m, pr, omv[cth]);
                     B.objcur[P.ld + j] = qm;
                 }
-                if (j <= (size_t)jmax) blk_price(P, pmode, (int)j, qc, qm, c);
+                if (j <= (size_t)jmax) blk_price<BL>(P, pmode, (int)j, qc, qm, c);
             }
         }
     }

@@ -34,6 +34,8 @@ struct DenseParams {
     int max_iter;
     int method;
     int n_art;
+    int bland;          // 1: Bland's rule -- every eligible column gets the same key, so the arg-max's tie-break (lowest
+                        // column) picks the entering column (variant bit 0x400000, primal methods)
 };
 
 constexpr int SELECT_THREADS = 1024;
@@ -64,7 +66,7 @@ __device__ __forceinline__ Cand price_row(const DenseParams &P, int row, int jma
         const double v = x[j];
         if (v > P.eps) {
             Cand t;
-            t.p = 0.0; t.q = v; t.idx = j;
+            t.p = 0.0; t.q = P.bland ? 1.0 : v; t.idx = j;
             if (cand_better(t, c)) c = t;
         }
     }
@@ -81,7 +83,7 @@ __device__ __forceinline__ Cand price_bigm(const DenseParams &P, Cand *scratch) 
         if (fabs(p) <= P.eps) p = 0.0;
         if (p > 0.0 || (p == 0.0 && q > P.eps)) {
             Cand t;
-            t.p = p; t.q = q; t.idx = j;
+            t.p = P.bland ? 0.0 : p; t.q = P.bland ? 1.0 : q; t.idx = j;
             if (cand_better(t, c)) c = t;
         }
     }

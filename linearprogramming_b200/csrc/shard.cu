@@ -864,6 +864,7 @@ int lpgpu_shard_reset(lpgpu_shard *s, const lpgpu_opts *opts) {
     if (!s || !opts) return LPGPU_EINVAL;
     lpgpu_ctx *ctx = s->ctx;
     if (opts->method == LPGPU_TWOPHASE) return fail(ctx, LPGPU_EINVAL, "shard_reset: the column-sharded path prices PLAIN and BIGM only");
+    if (opts->variant & 0x400000) return fail(ctx, LPGPU_EINVAL, "shard_reset: Bland's rule is not built for the column-sharded path");
     if ((opts->method == LPGPU_PLAIN) != (s->R == 1) || opts->n_art < 0 || opts->n_art > s->n)
         return fail(ctx, LPGPU_EINVAL, "shard_reset: bad options (method/R/n_art)");
     s->opts = *opts;

@@ -48,6 +48,10 @@ int lpf_solve_model(void *ctx, const lpf_model *mo, int method_if_needed, lpf_so
     lpgpu_default_opts(&o);
     o.method = method;
     o.n_art = n_art;
+    {   /* LPGPU_PRICING=bland: the lowest eligible column enters (anti-cycling), primal methods */
+        const char *pe = getenv("LPGPU_PRICING");
+        if (pe && !strcmp(pe, "bland") && method != LPGPU_DUAL) o.variant |= LPGPU_VARIANT_BLAND;
+    }
     o.log_cap = 16 * (mo->m + n) + 64;
     o.max_iter = 0x7fffffff;
     int *log = (int *)malloc(sizeof(int) * 2 * (size_t)o.log_cap);

@@ -158,6 +158,10 @@ void newSimplex(LPModel *model) {
         lpgpu_default_opts(&o);
         o.method = method;
         o.n_art = n_art;
+        {   /* LPGPU_PRICING=bland: the lowest eligible column enters (anti-cycling), primal methods */
+            const char *pe = getenv("LPGPU_PRICING");
+            if (pe && !strcmp(pe, "bland") && method != LPGPU_DUAL) o.variant |= LPGPU_VARIANT_BLAND;
+        }
         o.log_cap = 16 * (m + n) + 64;
         int *plog = (int *)calloc((size_t)o.log_cap * 2, sizeof(int));
         double *x = (double *)calloc((size_t)n, sizeof(double));

@@ -274,7 +274,7 @@ class ShardedTableau:
             pass
 
 
-def solve_batched(ctx, T_all, basis_all, method=PLAIN, n_art=0, eps=1e-9, max_iter=2**31 - 1, log_cap=0):
+def solve_batched(ctx, T_all, basis_all, method=PLAIN, n_art=0, eps=1e-9, max_iter=2**31 - 1, log_cap=0, variant=0):
     """One-shot batched solve: n_lp tableaux (n_lp, m+R, n+1) in host memory."""
     T_all = np.ascontiguousarray(T_all, np.float64)
     basis_all = np.ascontiguousarray(basis_all, np.int32)
@@ -287,7 +287,8 @@ def solve_batched(ctx, T_all, basis_all, method=PLAIN, n_art=0, eps=1e-9, max_it
     x = np.zeros((n_lp, n))
     basis_out = np.zeros((n_lp, m), np.int32)
     log = np.full((n_lp, max(log_cap, 1), 2), -1, np.int32)
-    o = capi.default_opts(eps=eps, max_iter=int(min(max_iter, 2**31 - 1)), method=method, n_art=n_art, log_cap=log_cap)
+    o = capi.default_opts(eps=eps, max_iter=int(min(max_iter, 2**31 - 1)), method=method, n_art=n_art, log_cap=log_cap,
+                          variant=variant)
     rc = capi.lib().lpgpu_solve_batched(ctx.handle, n_lp, m, n, R, _ptr(T_all), _ptr(basis_all), C.byref(o),
                                         _ptr(status), _ptr(iters), _ptr(z), _ptr(x), _ptr(basis_out),
                                         _ptr(log) if log_cap else None)

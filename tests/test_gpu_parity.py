@@ -483,6 +483,48 @@ def test_pipelined_blocks_two_objective_rows_full_grid_bitwise(ctx, method):
     assert ref["iters"] == Pn
 
 
+# ------------------------------------------------------------------ pricing option: Bland's rule
+@pytest.mark.parametrize("variant", [capi.RANK1, capi.INPLACE, capi.PIPELINED, (3 << 16) | capi.PIPELINED, capi.STEP_CL8 | capi.INPLACE])
+def test_bland_pricing_dense_bitwise(ctx, variant):
+    """variant bit BLAND: the lowest eligible column enters.  Rank-1 path, blocks in place and pipelined: the oracle's
+    (pricing = Bland) pivot log, basis and tableau, for the plain method, Big-M and two-phase; Beale's cycling example
+    runs into the iteration limit under the default rule and is solved under Bland."""
+    T0, basis = O.synth_feasible(321, 2, 150, 120)
+    ref = O.solve_f64(T0, basis, pricing=O.BLAND, log_cap=8192, threads=4)
+    got = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=variant | capi.BLAND)
+    _assert_dense_equal(got, ref)
+    assert got["log"].tolist() != O.solve_f64(T0, basis, log_cap=8192)["log"].tolist()      # a different path than the default rule
+    rng = np.random.default_rng(31)
+    for seed in range(4):
+        A, b, c, rel = H.random_mixed_lp(rng, 20 + seed, 16)
+        for method in (O.BIGM, O.TWOPHASE):
+            T, bs, n_art = lp.build_tableau(A, b, c, rel, R=2)
+            ref = O.solve_f64(T, bs, method=method, n_art=n_art, max_iter=5000, log_cap=5000, pricing=O.BLAND)
+            got = lp.solve_dense(ctx, T, bs, method=method, n_art=n_art, max_iter=5000, log_cap=5000, variant=variant | capi.BLAND)
+            _assert_dense_equal(got, ref)
+    A = np.array([[0.25, -8.0, -1.0, 9.0], [0.5, -12.0, -0.5, 3.0], [0.0, 0.0, 1.0, 0.0]])
+    T, bs, _ = lp.build_tableau(A, np.array([0.0, 0.0, 1.0]), np.array([0.75, -20.0, 0.5, -6.0]), np.full(3, -2, np.int32), R=1)
+    cyc = lp.solve_dense(ctx, T, bs, max_iter=120, log_cap=120, variant=variant)
+    assert cyc["status"] == lp.ITER_LIMIT
+    ok = lp.solve_dense(ctx, T, bs, max_iter=120, log_cap=120, variant=variant | capi.BLAND)
+    assert ok["status"] == lp.OPTIMAL and ok["z"] == 1.25
+    _assert_dense_equal(ok, O.solve_f64(T, bs, max_iter=120, log_cap=120, pricing=O.BLAND))
+
+
+def test_bland_pricing_batched_and_refusals(ctx):
+    T, basis = O.synth_feasible_batch(77, 0, 300, 24, 20)
+    ref = O.solve_batched_f64(T, basis, threads=4, pricing=O.BLAND)
+    got = lp.solve_batched(ctx, T, basis, variant=capi.BLAND)          # routed to the shared-memory kernel (decide())
+    _assert_batched_equal(got, ref)
+    assert not np.array_equal(ref["iters"], O.solve_batched_f64(T, basis, threads=4)["iters"])
+    rng = np.random.default_rng(5)
+    Td, bd, _ = H.random_dual_lp(rng, 12, 10)
+    d = lp.DenseTableau(ctx, 12, Td.shape[1] - 1, 1)
+    with pytest.raises(Exception):
+        d.reset(method=lp.DUAL, variant=capi.BLAND)                    # primal methods only
+    d.close()
+
+
 # ------------------------------------------------------------------ dual simplex (SURVEY section 8 f3)
 @pytest.mark.parametrize("seed", range(8))
 def test_dual_simplex_dense_bitwise(ctx, seed):

@@ -80,3 +80,15 @@ def test_synth_host_matches_oracle_bitwise(m, ns):
     To, bo = O.synth_feasible(1234, 9, m, ns)
     Tp, bp = lp.synth_host(1234, 9, m, ns)
     assert np.array_equal(To, Tp) and np.array_equal(bo, bp)
+
+
+def test_header_constants_match_the_ctypes_mirror():
+    """Every #define of include/lpgpu.h that capi.py restates (statuses, methods, error codes, option bits) has the same value."""
+    import re
+    hdr = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "lpgpu.h")).read()
+    defs = {k: int(v, 0) for k, v in re.findall(r"#define\s+LPGPU_(\w+)\s+\(?(-?(?:0x[0-9a-fA-F]+|\d+))\)?", hdr)}
+    for name in ("OK", "EINVAL", "ENODEV", "ECUDA", "ENOMEM", "ENCCL", "OPTIMAL", "UNBOUNDED", "INFEASIBLE", "ITER_LIMIT",
+                 "RUNNING", "PLAIN", "BIGM", "TWOPHASE", "DUAL"):
+        assert defs[name] == getattr(capi, name), name
+    assert defs["VARIANT_BLAND"] == capi.BLAND
+    assert defs["NCCL_ID_BYTES"] == capi.NCCL_ID_BYTES and defs["IPC_HANDLE_BYTES"] == capi.IPC_HANDLE_BYTES

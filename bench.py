@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--variant", type=lambda s: int(s, 0), default=None, help="dense kernel variant override")
     ap.add_argument("--no-extra", action="store_true", help="skip the batched (config 3) extra measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the sharded-vs-oracle check that precedes the timing")
     ap.add_argument("--m", type=int, default=M, help=argparse.SUPPRESS)     # debugging at reduced size only
     ap.add_argument("--shard-m", type=int, default=16384, help="rows of the column-sharded extra (N > 1); n = 4m")
     ap.add_argument("--shard-pivots", type=int, default=200)
@@ -245,6 +246,39 @@ def gpu_arm(args):
     n = m + ns
     P, K, W = args.pivots, args.steps, max(args.warmup, 0)
     alg_bytes = 16 * (m + 1) * (n + 1)
+
+    # ---- N > 1: bit-exact check of the column-sharded path against the oracle at THIS world size, before anything is
+    # timed (the driver reaches more than one real GPU only through this script): small cases (plain, Big-M, two-phase,
+    # Bland; blocks of 32 and 5, rank-1 pipeline) over the peer-memory transport, then the first 64 pivots of the
+    # config-5b tableau against the single-tableau path.  Outcome -> config.sharded_parity; a failure fails the run.
+    sharded_parity = None
+    if world > 1 and not args.no_extra and not args.no_parity:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import sharded_parity as SP
+        from linearprogramming_b200 import sharding as _shd
+
+        class _HostDist:
+            """object collectives over a gloo group (host plumbing of the checks; the data path is the library's own)"""
+            def __init__(self):
+                self.g = dist.new_group(backend="gloo")
+            def get_rank(self): return rank
+            def get_world_size(self): return world
+            def barrier(self): dist.barrier(group=self.g)
+            def all_gather_object(self, out, obj): dist.all_gather_object(out, obj, group=self.g)
+            def broadcast_object_list(self, box, src=0): dist.broadcast_object_list(box, src=src, group=self.g)
+            def gather_object(self, obj, parts, dst=0): dist.gather_object(obj, parts, dst=dst, group=self.g)
+
+        hd = _HostDist()
+        pctx = lp.Context(local)
+        t0p = time.perf_counter()
+        try:
+            runs = SP.check_small(lp, _shd, hd, pctx, rank, world, transports=("p2p",))
+            SP.check_large_prefix(lp, _shd, hd, pctx, rank, world, args.shard_m, 4 * args.shard_m, pivots=64)
+            sharded_parity = f"ok ({runs} solves vs oracle + first 64 pivots of {args.shard_m}x{4 * args.shard_m} vs the single-tableau path, world {world}, {time.perf_counter() - t0p:.0f} s)"
+        except AssertionError as e:
+            sharded_parity = "FAILED: " + str(e)[:300]
+        pctx.close()
+        barrier()
     variant = args.variant if args.variant is not None else int(os.environ.get("LPGPU_VARIANT", "0"), 0)
 
     stream = torch.cuda.Stream()
@@ -297,10 +331,11 @@ def gpu_arm(args):
     value = world * K * P / t_value
 
     # ---- roofline of the dominant kernel: same region, every pass over the tableau bracketed by events
-    RANK1, INPLACE, WHOLE_TILE = 0x800, 0x2000, 0x4000
+    from linearprogramming_b200 import capi as _capi
+    RANK1, INPLACE, WHOLE_TILE, PIPELINED_BIT = _capi.RANK1, _capi.INPLACE, _capi.WHOLE_TILE_PASS, _capi.PIPELINED
     blocked = not (variant & RANK1)
     # the default picks pipelined blocks from about 0.4 GB of tableau on (csrc/dense.cu want_pipeline); 0x1000 forces them
-    pipelined = blocked and not (variant & INPLACE) and bool((variant & 0x1000) or (m + 1) * ((n + 1 + 15) // 16 * 16) * 8 >= (384 << 20))
+    pipelined = blocked and not (variant & INPLACE) and bool((variant & PIPELINED_BIT) or (m + 1) * ((n + 1 + 15) // 16 * 16) * 8 >= (384 << 20))
     block_k = ((variant >> 16) & 0x3f) or 32
 
     def kernel_times():
@@ -438,13 +473,39 @@ def gpu_arm(args):
     t_e2e_stream = max_over_ranks(timed(lambda: [e2e_stream_step() for _ in range(K)]))
     for o in objs:
         o.close()
-    e2e = {"value": world * K * P / t_e2e_stream, "unit": "pivots/s",
+    # ---- e2e headline: what the reference's entry point does -- ONE lpgpu_solve_dense call per model (Source/simplex.c:27-73):
+    # upload the 1.07 GB tableau from pinned host memory, pivot to OPTIMAL (about 17k pivots), read x / basis / status back
+    golden = None
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "cfg4_full_solve.json")) as f:
+            golden = json.load(f)
+    except Exception:
+        pass
+    full = {"iters": 0, "status": None, "z": None}
+
+    def e2e_full_step():
+        bh[...] = b0
+        r = lp.solve_dense(ctx, Th, bh, results_only=True, inplace=True, variant=variant, check_every=256)
+        full.update(iters=r["iters"], status=r["status"], z=r["z"], basis=bh.copy())
+        return r
+
+    e2e_full_step()                                     # warm-up (allocations of the cached tableau object are behind us anyway)
+    KF = max(1, min(K, 5))
+    t_full = max_over_ranks(timed(lambda: [e2e_full_step() for _ in range(KF)]))
+    full_parity = "no golden record"
+    if golden is not None and m == golden["m"] and rank == 0:
+        okg = (lp.STATUS_NAMES[full["status"]] == golden["status"] and full["iters"] == golden["iters"] and
+               float(full["z"]).hex() == golden["z_hex"] and full["basis"].tolist() == golden["basis"])
+        full_parity = "ok" if okg else f"FAILED: status/iters/z/basis {lp.STATUS_NAMES[full['status']]}/{full['iters']}/{full['z']!r} vs golden {golden['status']}/{golden['iters']}/{golden['z']!r}"
+    e2e = {"value": world * KF * full["iters"] / t_full, "unit": "pivots/s",
            "h2d_bytes_per_step": int((m + 1) * (n + 1) * 8 + m * 4), "d2h_bytes_per_step": int(n * 8 + m * 4 + 64),
-           "api": ("stream of problems over two tableau objects: lpgpu_dense_upload_async (step i+1) | lpgpu_dense_reset, "
-                   "lpgpu_dense_run(max_iter = pivots per step), lpgpu_dense_download(x, basis) (step i); every step's upload "
-                   "and read-back are inside the timed region, the upload overlaps the previous step's pivots"),
-           "one_shot_call": {"value": world * K * P / t_e2e, "unit": "pivots/s",
-                             "api": "lpgpu_solve_dense (upload, max_iter = pivots per step, results_only read-back; nothing overlapped)"}}
+           "api": "ONE lpgpu_solve_dense per step on pinned host buffers: upload, pivot to OPTIMAL, read x / basis / status back",
+           "pivots_per_step": full["iters"], "status": lp.STATUS_NAMES.get(full["status"], "?"), "ms_per_solve": 1e3 * t_full / KF,
+           "steps": KF, "golden": full_parity,
+           "window_one_shot": {"value": world * K * P / t_e2e, "unit": "pivots/s", "pivots_per_step": P,
+                               "api": "lpgpu_solve_dense(max_iter = pivots per step): one upload per window of pivots, nothing overlapped"},
+           "window_streamed": {"value": world * K * P / t_e2e_stream, "unit": "pivots/s", "pivots_per_step": P,
+                               "api": "two tableau objects: lpgpu_dense_upload_async of window i+1 overlaps lpgpu_dense_run of window i"}}
 
     # ---- extra: batched path, BASELINE config 3 (100k LPs m=32 n=64 per GPU, one LP per CTA in smem)
     extra = {}
@@ -468,7 +529,7 @@ def gpu_arm(args):
                             "frac_of_measured_peak_per_gpu": bn * lp_bytes / t_b / 1e9 / peak}
         # BASELINE config 5a: m=64 n=128, instances sharded over the ranks by contiguous index range
         from linearprogramming_b200 import sharding as _sh
-        n5 = args.batched5 if world > 1 else min(args.batched5, 200_000)
+        n5 = args.batched5                   # the whole 1 M-LP job at every N (67 GB of tableaux fit one B200)
         lo5, hi5 = _sh.lp_range(n5, world, rank)
         b5 = lp.BatchedLPs(ctx, hi5 - lo5, 64, 128, 1)
         b5.synth(SEED, lo5, 64)
@@ -480,7 +541,7 @@ def gpu_arm(args):
         lp5_bytes = 8 * (65 * 129 + 128 + 4)
         extra["batched_m64_n128"] = {"metric": "LPs_per_sec", "value": n5 / t5, "unit": "LPs/s",
                                      "workload": f"{n5} LPs m=64 n=128 fp64 sharded by index range over {world} GPU(s), "
-                                                 "no collective (BASELINE config 5a" + ("" if world > 1 else ", 1-GPU sample") + ")",
+                                                 "no collective (BASELINE config 5a)",
                                      "kernel": "batched_reg_kernel<4,16,4>", "kernel_ms": t5 * 1e3,
                                      "mean_pivots_per_lp": float(out5["iters"].mean()),
                                      "all_optimal": bool((out5["status"] == lp.OPTIMAL).all()),
@@ -488,16 +549,24 @@ def gpu_arm(args):
 
     # ---- extra (N = 1): BASELINE config 5b's tableau (16384 x 65536, 8.6 GB) on ONE GPU through the blocked path,
     # for comparison with the column-sharded rank-1 runs at N > 1
-    if world == 1 and not args.no_extra and m == M:
+    big_n1 = None
+    if rank == 0 and not args.no_extra and m == M:
         lm, ln = args.shard_m, 4 * args.shard_m
         big = lp.DenseTableau(ctx, lm, ln, 1)
         big.synth(SEED, 0, ln - lm)
         big.reset(variant=variant, check_every=256)
         big.run(64)
         lpv = 256
-        t_big = timed(lambda: big.run(lpv))
+        torch.cuda.synchronize()
+        eb0, eb1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        eb0.record(stream)
+        big.run(lpv)
+        eb1.record(stream)
+        torch.cuda.synchronize()
+        t_big = eb0.elapsed_time(eb1) * 1e-3          # rank 0 alone (no collective in this leg)
         r_big = big.run(0)
         big.close()
+        big_n1 = lpv / t_big
         extra["large_tableau_single_gpu"] = {"metric": "pivots_per_sec", "value": lpv / t_big, "unit": "pivots/s",
                                              "workload": f"one dense tableau {lm}x{ln} fp64 ({(lm + 1) * (ln + 1) * 8 / 1e9:.2f} GB) resident on one GPU, default path",
                                              "pivots": lpv, "us_per_pivot": 1e6 * t_big / lpv, "iters_after": r_big["iters"]}
@@ -505,6 +574,7 @@ def gpu_arm(args):
     # ---- extra (N > 1): BASELINE config 5b, ONE 16384 x 65536 tableau column-sharded over the ranks,
     # candidate + entering-column exchange per pivot over our own NCCL communicator
     if world > 1 and not args.no_extra:
+        barrier()
         from linearprogramming_b200 import sharding
         sm_, sn_ = args.shard_m, 4 * args.shard_m
         sp = args.shard_pivots
@@ -523,6 +593,9 @@ def gpu_arm(args):
             per_transport[transport] = max_over_ranks(timed(lambda: sh.run(npv))) / npv
             if transport == "p2p":
                 r_s = sh.run(0)
+                its = [None] * world
+                dist.all_gather_object(its, (r_s["iters"], r_s["status"], float(r_s["z"]).hex()))
+                ranks_agree = all(v == its[0] for v in its)
             barrier()               # p2p: nobody unmaps while a peer may still store into its region
             sh.close()
         t_s = per_transport["p2p"]
@@ -532,25 +605,55 @@ def gpu_arm(args):
                                    "path": "blocked: per pivot one cluster kernel per rank (candidates and the owner's lazily "
                                            "updated entering column exchanged as NVLink peer stores inside it), one local pass "
                                            "over the rank's column block per 32 pivots",
-                                   "pivots": 4 * sp, "us_per_pivot": 1e6 * t_s, "iters_after": r_s["iters"],
+                                   "pivots": 4 * sp, "us_per_pivot": 1e6 * t_s, "iters_after": r_s["iters"], "ranks_agree": ranks_agree,
                                    "rank1_pipeline": {"us_per_pivot_peer_memory": 1e6 * per_transport["p2p_rank1"],
                                                       "us_per_pivot_nccl_allgather": 1e6 * per_transport["nccl"],
                                                       "pivots_per_sec_peer_memory": 1.0 / per_transport["p2p_rank1"],
                                                       "hbm_GBs_algorithmic_total": s_bytes / per_transport["p2p_rank1"] / 1e9,
                                                       "frac_of_measured_peak_per_gpu": s_bytes / per_transport["p2p_rank1"] / 1e9 / world / peak}}
 
+    # ---- the secondary results BASELINE's metric asks for, inside a dict the driver keeps whole (short keys, rounded)
+    def r3(v):
+        return None if v is None else float(f"{v:.4g}")
+    sec = {}
+    if rank1 is not None:
+        sec["rank1_kernel"] = {"frac": r3(rank1["roofline_frac"]), "ms": r3(rank1["avg_launch_ms"]), "pivots_per_s": r3(rank1["pivots_per_sec"])}
+    if inplace is not None:
+        sec["blocks_in_place"] = {"pivots_per_s": r3(inplace["pivots_per_sec"]), "pass_ms": r3(inplace["avg_launch_ms"])}
+    if "batched" in extra:
+        sec["batched_cfg3"] = {"lps_per_s": r3(extra["batched"]["value"]), "frac": r3(extra["batched"]["frac_of_measured_peak_per_gpu"]), "n_lp": world * BN_LP}
+    if "batched_m64_n128" in extra:
+        b5x = extra["batched_m64_n128"]
+        sec["batched_cfg5a"] = {"lps_per_s": r3(b5x["value"]), "n_lp": n5, "frac": r3(b5x["hbm_GBs_algorithmic"] / world / peak)}
+    if big_n1 is not None or world > 1:
+        bn1 = [big_n1]
+        if world > 1:
+            dist.broadcast_object_list(bn1, src=0)
+        big_n1 = bn1[0]
+    if big_n1 is not None:
+        sec["cfg5b_one_gpu"] = {"pivots_per_s": r3(big_n1)}
+    if "column_sharded" in extra:
+        cs = extra["column_sharded"]
+        sec["column_sharded"] = {"pivots_per_s": r3(cs["value"]), "us_per_pivot": r3(cs["us_per_pivot"]),
+                                 "strong_eff_vs_n1": r3(cs["value"] / (world * big_n1)) if big_n1 else None,
+                                 "ranks_agree": cs["ranks_agree"], "nccl_rank1_us": r3(cs["rank1_pipeline"]["us_per_pivot_nccl_allgather"])}
+    roofline["secondary"] = sec
+
+    config = {"workload": f"dense tableau {m}x{n} fp64 random feasible LP per GPU (BASELINE config 4)",
+              "m": m, "n": n, "tableau_bytes": (m + 1) * (n + 1) * 8, "pivots_per_step": P, "seed": SEED,
+              "variant": variant, "path": ((f"blocked, pipelined: {block_k} pivots decided on lazy slices while the pass that applies "
+                                            "the previous block runs out of place on a second stream") if pipelined else
+                                           f"blocked: {block_k} pivots decided on lazy slices, then one pass over the tableau"
+                                           if blocked else "rank-1: one pass over the tableau per pivot"),
+              "l2": "inputs larger than L2 (1.07 GB tableau vs 126 MB)",
+              "sharding": "independent LP per rank, no collective" if world > 1 else "single GPU",
+              "full_solve_parity": full_parity}
+    if sharded_parity is not None:
+        config["sharded_parity"] = sharded_parity
     line = {
         "metric": "pivots_per_sec", "value": value, "unit": "pivots/s", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": 1e3 * t_value / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"dense tableau {m}x{n} fp64 random feasible LP per GPU (BASELINE config 4)",
-                   "m": m, "n": n, "tableau_bytes": (m + 1) * (n + 1) * 8, "pivots_per_step": P, "seed": SEED,
-                   "variant": variant, "path": ((f"blocked, pipelined: {block_k} pivots decided on lazy slices while the pass that applies "
-                                                 "the previous block runs out of place on a second stream") if pipelined else
-                                                f"blocked: {block_k} pivots decided on lazy slices, then one pass over the tableau"
-                                                if blocked else "rank-1: one pass over the tableau per pivot"),
-                   "l2": "inputs larger than L2 (1.07 GB tableau vs 126 MB)",
-                   "sharding": "independent LP per rank, no collective" if world > 1 else "single GPU"},
+        "dtype": "f64", "data": "synthetic", "config": config,
         "roofline": roofline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "extra": extra,
     }
     if rank1 is not None:
@@ -564,6 +667,10 @@ def gpu_arm(args):
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
+    failed = [v for v in (sharded_parity, full_parity) if isinstance(v, str) and v.startswith("FAILED")]
+    if failed:
+        sys.stderr.write("bench.py: parity check failed: " + " | ".join(failed) + "\n")
+        sys.exit(3)
 
 
 def _reserve_stdout():

@@ -59,12 +59,33 @@ extern "C" {
                                * <= 0), b may be negative; leaving row = most negative b_i, entering
                                * column = min sigma_j / a_rj over a_rj < 0      */
 
-/* lpgpu_opts.variant bit: Bland's rule -- the LOWEST eligible column enters (default: the largest reduced
- * cost, ties to the lowest column).  With the lowest-row tie-break of the ratio test it cannot cycle
- * (Beale's example runs into the iteration limit under the default rule).  Primal methods, dense and
- * batched paths; LPGPU_EINVAL for the dual simplex and the column-sharded path.  SURVEY.md 8 (f4): the
- * reference has no pricing at all (Source/simplex.c:57-63).                                            */
-#define LPGPU_VARIANT_BLAND 0x400000
+/* ---- lpgpu_opts.variant: every public bit has a name (0 = the default path) -----------------------------
+ * Pricing rule (primal methods, dense and batched paths, column-sharded path):
+ *   BLAND   the LOWEST eligible column enters (default: the largest reduced cost, ties to the lowest column).  With
+ *           the lowest-row tie-break of the ratio test it cannot cycle (Beale's example runs into the iteration
+ *           limit under the default rule).  LPGPU_EINVAL for the dual simplex.  SURVEY.md 8 (f4): the reference has
+ *           no pricing at all (Source/simplex.c:57-63).
+ *   DEVEX   reference-framework pricing: sigma_j^2 / w_j is maximised, the weights w_j follow Devex's update
+ *           (DESIGN.md section 3); dense path and batched shared-memory kernel, primal methods.
+ * Dense path, which kernels run (all bit-identical):                                        */
+#define LPGPU_VARIANT_UPD_STATIC    0x1        /* rank-1 path: TMA-staged elimination, static task stride (default: work stealing) */
+#define LPGPU_VARIANT_UPD_DIRECT    0x2        /* rank-1 path: direct-load elimination kernel                                      */
+#define LPGPU_VARIANT_UPD_MASK      0xf
+#define LPGPU_VARIANT_NO_ALTERNATE  0x200      /* rank-1 path: do not alternate the sweep direction between pivots                 */
+#define LPGPU_VARIANT_NO_PDL        0x400      /* plain stream-ordered launches (default: programmatic dependent launch)           */
+#define LPGPU_VARIANT_RANK1         0x800      /* one pass over the tableau per pivot (default: one pass per block of pivots)      */
+#define LPGPU_VARIANT_PIPELINED     0x1000     /* blocked path: always pipeline the pass of a block with the next block's decisions */
+#define LPGPU_VARIANT_INPLACE       0x2000     /* blocked path: never pipeline (steps, pass, steps, ... on one stream, in place)    */
+                                               /* neither bit: pipelined from about 0.4 GB of tableau on                           */
+#define LPGPU_VARIANT_WHOLE_TILE    0x4000     /* blocked path: the pass kernel that loads a whole tile before it computes         */
+#define LPGPU_VARIANT_STEP_CL8      0x8000     /* blocked path: step kernel as a portable 8-CTA cluster (default: 16 CTAs)         */
+#define LPGPU_VARIANT_BLOCK_K(k)    (((k) & 0x3f) << 16)   /* blocked path: pivots per block, 1..32 (0 = 32)                       */
+#define LPGPU_VARIANT_BLOCK_K_MASK  0x3f0000
+#define LPGPU_VARIANT_BLAND         0x400000
+#define LPGPU_VARIANT_DEVEX         0x800000
+/* Batched path only (distinct from the dense bits, so one opts struct can be handed to both paths):                */
+#define LPGPU_VARIANT_BATCH_KEEP_FINAL 0x1000000   /* keep the final tableaux on the device (lpgpu_batched_download T_final)  */
+#define LPGPU_VARIANT_BATCH_SMEM       0x2000000   /* shared-memory kernel even where a register-resident one applies        */
 
 typedef struct lpgpu_ctx lpgpu_ctx;         /* one per process and GPU           */
 typedef struct lpgpu_dense lpgpu_dense;     /* one large device-resident tableau */
@@ -77,12 +98,7 @@ typedef struct {
     int n_art;          /* number of trailing artificial columns                         */
     int log_cap;        /* pivots to record in the pivot log (0 = none)                  */
     int check_every;    /* dense: pivots enqueued between host status reads (0 = 64)     */
-    int variant;        /* kernel variant (0 = default): 0x800 = one pass */
-                        /* over the tableau per pivot instead of one per block of pivots; */
-                        /* 0x2000 = blocks applied in place, 0x1000 = pipelined blocks (the */
-                        /* pass of a block overlaps the decisions of the next one; needs a  */
-                        /* second tableau buffer on the device); default: pipelined from    */
-                        /* about 0.4 GB of tableau on; bits 16..21 = pivots per block       */
+    int variant;        /* OR of LPGPU_VARIANT_* bits (0 = default)                      */
     int time_kernels;   /* dense: bracket every elimination launch with CUDA events      */
     int results_only;   /* lpgpu_solve_dense: do not copy the final tableau back to T    */
 } lpgpu_opts;

@@ -14,23 +14,36 @@ OK, EINVAL, ENODEV, ECUDA, ENOMEM, ENCCL = 0, -1, -2, -3, -4, -5
 OPTIMAL, UNBOUNDED, INFEASIBLE, ITER_LIMIT, RUNNING = 0, 1, 2, 3, 4
 PLAIN, BIGM, TWOPHASE, DUAL = 0, 1, 2, 3
 STATUS_NAMES = {0: "OPTIMAL", 1: "UNBOUNDED", 2: "INFEASIBLE", 3: "ITER_LIMIT", 4: "RUNNING"}
-KEEP_FINAL = 0x1000      # batched: keep the final tableaux on the device (parity tests)
-FORCE_SMEM = 0x2000      # batched: shared-memory kernel even where the register-resident one applies
-STATIC = 0x1             # dense: TMA-staged elimination with a static task stride (default: work stealing)
-DIRECT = 0x2             # dense: direct-load elimination kernel instead of the TMA-staged default
-RANK1 = 0x800            # dense: one pass over the tableau per pivot (default for plain / Big-M: up to K pivots decided on lazily
-                         # updated slices, then applied in one pass; K = variant bits 16..21, 0 = 32)
-INPLACE = 0x2000         # dense, blocked path: steps, pass, steps, ... in place on one stream
-PIPELINED = 0x1000       # dense, blocked path (primal methods): pipelined blocks -- the pass of a block runs out of place on a second
-                         # stream while the next block is decided through the slices of both blocks (bit-identical; needs a second
-                         # tableau buffer).  Default (neither bit): pipelined from about 0.4 GB of tableau on, in place below
-WHOLE_TILE_PASS = 0x4000 # dense, blocked path: the pass kernel that loads a whole tile before it computes (default: software-pipelined halves)
-STEP_CL8 = 0x8000        # dense, blocked path: primal step kernel as a cluster of 8 CTAs (default: 16 where the device allows it)
-BLAND = 0x400000         # dense and batched, primal methods: Bland's rule -- the LOWEST eligible column enters (default: the largest
-                         # reduced cost, ties to the lowest column); with the lowest-row ratio tie-break it cannot cycle
-WS_PASS = 0x100          # dense, blocked path: warp-specialised pass kernel (TMA ring; measured slower, kept as an alternative)
-NO_PDL = 0x400           # dense: plain stream-ordered launches (default: programmatic dependent launch)
-NO_ALTERNATE = 0x200     # dense: do not alternate the sweep direction between pivots
+def _header_defines():
+    """#define LPGPU_<NAME> <integer> of include/lpgpu.h: the header is the one place option bits are defined."""
+    import re
+    hdr = os.path.join(os.path.dirname(HERE), "include", "lpgpu.h")
+    text = open(hdr).read()
+    return {k: int(v, 0) for k, v in re.findall(r"#define\s+LPGPU_(\w+)\s+\(?(-?(?:0x[0-9a-fA-F]+|\d+))\)?", text)}
+
+
+_H = _header_defines()
+# lpgpu_opts.variant bits (include/lpgpu.h; DESIGN.md section 4 says what each selects)
+KEEP_FINAL = _H["VARIANT_BATCH_KEEP_FINAL"]    # batched: keep the final tableaux on the device (parity tests)
+FORCE_SMEM = _H["VARIANT_BATCH_SMEM"]          # batched: shared-memory kernel even where a register-resident one applies
+STATIC = _H["VARIANT_UPD_STATIC"]              # dense, rank-1 path: static task stride (default: work stealing)
+DIRECT = _H["VARIANT_UPD_DIRECT"]              # dense, rank-1 path: direct-load elimination kernel
+NO_ALTERNATE = _H["VARIANT_NO_ALTERNATE"]      # dense, rank-1 path: do not alternate the sweep direction between pivots
+NO_PDL = _H["VARIANT_NO_PDL"]                  # dense: plain stream-ordered launches (default: programmatic dependent launch)
+RANK1 = _H["VARIANT_RANK1"]                    # dense: one pass over the tableau per pivot (default: one pass per block of pivots)
+PIPELINED = _H["VARIANT_PIPELINED"]            # dense, blocked path: always pipeline the pass with the next block's decisions
+INPLACE = _H["VARIANT_INPLACE"]                # dense, blocked path: never pipeline (default: by size)
+WHOLE_TILE_PASS = _H["VARIANT_WHOLE_TILE"]     # dense, blocked path: the pass kernel that loads a whole tile before it computes
+STEP_CL8 = _H["VARIANT_STEP_CL8"]              # dense, blocked path: step kernel as a portable 8-CTA cluster
+BLAND = _H["VARIANT_BLAND"]                    # Bland's rule (primal methods)
+DEVEX = _H["VARIANT_DEVEX"]                    # Devex reference-framework pricing (primal methods)
+
+
+def BLOCK_K(k):
+    """variant bits for `k` pivots per block (1..32)."""
+    return (int(k) & 0x3f) << 16
+
+
 NCCL_ID_BYTES = 128
 IPC_HANDLE_BYTES = 64
 

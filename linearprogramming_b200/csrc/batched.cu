@@ -18,7 +18,8 @@ struct lpgpu_batched {
     int *basis_all;
     int *status, *iters, *basis_out, *log;
     double *z, *x, *T_final;
-    int log_cap;
+    int log_cap;          // active limit = opts->log_cap of the last run (stride of the log, download length)
+    int log_alloc;        // what the device buffer has room for
     bool want_final;
     cudaEvent_t e0, e1;
 };
@@ -33,6 +34,7 @@ bool batched_opts_ok(const lpgpu_opts *o, int n, int R) {
     if (o->method != LPGPU_PLAIN && o->method != LPGPU_BIGM && o->method != LPGPU_TWOPHASE && o->method != LPGPU_DUAL) return false;
     if ((o->method == LPGPU_PLAIN || o->method == LPGPU_DUAL) != (R == 1)) return false;
     if (o->n_art < 0 || o->n_art > n || o->max_iter < 0 || o->log_cap < 0 || !(o->eps >= 0.0)) return false;
+    if ((o->variant & LPGPU_VARIANT_BLAND) && o->method == LPGPU_DUAL) return false;      // Bland's rule: primal methods (include/lpgpu.h)
     return true;
 }
 
@@ -53,7 +55,7 @@ int lpgpu_batched_create(lpgpu_ctx *ctx, long n_lp, int m, int n, int R, lpgpu_b
     b->ctx = ctx; b->n_lp = n_lp; b->m = m; b->n = n; b->R = R;
     b->tsz = (size_t)(m + R) * (size_t)(n + 1);
     b->T_all = nullptr; b->basis_all = nullptr; b->status = b->iters = b->basis_out = b->log = nullptr;
-    b->z = b->x = b->T_final = nullptr; b->log_cap = 0; b->want_final = false; b->e0 = b->e1 = nullptr;
+    b->z = b->x = b->T_final = nullptr; b->log_cap = 0; b->log_alloc = 0; b->want_final = false; b->e0 = b->e1 = nullptr;
     const size_t nl = (size_t)std::max(1L, n_lp);
     cudaError_t e = cudaSuccess;
     if (e == cudaSuccess) e = cudaMalloc(&b->T_all, nl * b->tsz * sizeof(double) + 16);
@@ -126,32 +128,33 @@ int lpgpu_batched_run(lpgpu_batched *b, const lpgpu_opts *opts, float *kernel_ms
     if (kernel_ms) *kernel_ms = 0.f;
     if (b->n_lp == 0) return LPGPU_OK;
     const size_t nl = (size_t)b->n_lp;
-    if (opts->log_cap > b->log_cap) {
+    if (opts->log_cap > b->log_alloc) {
         LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         cudaFree(b->log);
         b->log = nullptr;
-        b->log_cap = 0;
+        b->log_alloc = 0;
         LP_CUDA(ctx, cudaMalloc(&b->log, nl * 2 * (size_t)opts->log_cap * sizeof(int)));
-        b->log_cap = opts->log_cap;
+        b->log_alloc = opts->log_cap;
     }
+    b->log_cap = opts->log_cap;       // stride and download length: the caller's pivot_log holds n_lp * 2 * opts->log_cap ints
     if (opts->log_cap > 0) LP_CUDA(ctx, cudaMemsetAsync(b->log, 0xff, nl * 2 * (size_t)b->log_cap * sizeof(int), ctx->stream));
-    const bool want_final = (opts->variant & 0x1000) != 0;   // parity tests: keep the final tableaux
+    const bool want_final = (opts->variant & LPGPU_VARIANT_BATCH_KEEP_FINAL) != 0;   // parity tests: keep the final tableaux
     if (want_final && !b->T_final) LP_CUDA(ctx, cudaMalloc(&b->T_final, nl * b->tsz * sizeof(double)));
     b->want_final = want_final;
 
     BatchedParams B;
     B.T_all = b->T_all; B.basis_all = b->basis_all; B.n_lp = b->n_lp; B.m = b->m; B.n = b->n; B.R = b->R;
     B.eps = opts->eps; B.max_iter = opts->max_iter; B.method = opts->method; B.n_art = opts->n_art;
-    B.bland = (opts->variant & 0x400000) ? 1 : 0;       // Bland's rule: through the shared-memory kernel (decide())
+    B.bland = (opts->variant & LPGPU_VARIANT_BLAND) ? 1 : 0;       // Bland's rule: through the shared-memory kernel (decide())
     B.log_cap = b->log_cap; B.status = b->status; B.iters = b->iters; B.z = b->z; B.x = b->x;
     B.basis_out = b->basis_out; B.log = opts->log_cap > 0 ? b->log : nullptr;
     B.T_final = want_final ? b->T_final : nullptr;
 
     // Kernel choice.  Plain method on shapes that fit a register tile: the register-resident kernel
-    // (batched_reg.cuh); everything else (Big-M, two-phase, other shapes, variant bit 0x2000): the
+    // (batched_reg.cuh); everything else (Big-M, two-phase, other shapes, LPGPU_VARIANT_BATCH_SMEM): the
     // shared-memory kernel.  Grid = a whole number of resident CTAs per SM; each CTA walks LPs
     // p = blockIdx, blockIdx + grid, ...
-    const bool plain = opts->method == LPGPU_PLAIN && b->R == 1 && !(opts->variant & (0x2000 | 0x400000));
+    const bool plain = opts->method == LPGPU_PLAIN && b->R == 1 && !(opts->variant & (LPGPU_VARIANT_BATCH_SMEM | LPGPU_VARIANT_BLAND));
     int kind = 0;
     if (plain && b->m <= RegSmall::MAX_M && b->n <= RegSmall::MAX_N) kind = 1;
     else if (plain && b->m <= RegWide::MAX_M && b->n <= RegWide::MAX_N) kind = 2;
@@ -198,7 +201,7 @@ int lpgpu_batched_download(lpgpu_batched *b, int *status, int *iters, double *z,
         if (pivot_log && b->log_cap > 0)
             LP_CUDA(ctx, cudaMemcpyAsync(pivot_log, b->log, nl * 2 * (size_t)b->log_cap * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         if (T_final) {
-            if (!b->want_final || !b->T_final) return fail(ctx, LPGPU_EINVAL, "batched_download: final tableaux were not kept (variant bit 0x1000)");
+            if (!b->want_final || !b->T_final) return fail(ctx, LPGPU_EINVAL, "batched_download: final tableaux were not kept (LPGPU_VARIANT_BATCH_KEEP_FINAL)");
             LP_CUDA(ctx, cudaMemcpyAsync(T_final, b->T_final, nl * b->tsz * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
         }
     }

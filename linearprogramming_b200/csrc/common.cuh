@@ -171,18 +171,15 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t by
                  : "memory");
 }
 
+// Bounded: a protocol error (a copy that never lands) traps after about 2^28 polls -- seconds -- instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred P1;\n"
-        "LAB_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
-        "@P1 bra DONE;\n"
-        "bra LAB_WAIT;\n"
-        "DONE:\n"
-        "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
+    for (uint32_t spin = 0; spin < (1u << 28); ++spin) {
+        uint32_t ok;
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (ok) return;
+    }
+    __trap();
 }
 
 // 1-D bulk asynchronous copy global -> shared through the TMA unit (SASS: UBLKCP).
@@ -208,6 +205,13 @@ template <int N>
 __device__ __forceinline__ void tma_store_wait() {
     asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
+
+// ------------------------------------------------------------------ cluster entry barrier (split)
+// Distributed shared memory of another CTA may only be touched once that CTA has started.  Every cluster kernel
+// arrives at kernel entry and waits right before its first possible remote access: by then all CTAs of the
+// cluster have long been scheduled, so the wait costs nothing on the critical path, and the rule holds.
+__device__ __forceinline__ void cluster_entry_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_entry_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 
 // ------------------------------------------------------------------ programmatic dependent launch
 // Kernels launched with cudaLaunchAttributeProgrammaticStreamSerialization may become resident while

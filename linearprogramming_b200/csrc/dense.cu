@@ -40,11 +40,13 @@ dense_select_kernel(DenseParams P, int forced_r, int forced_k) {
     const int gtid = rank * SELECT_THREADS + (int)threadIdx.x;
     constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
 
+    cluster_entry_arrive();     // DSMEM rule: no remote access before every CTA of the cluster has started (wait below)
     pdl_wait();                 // the elimination pass before this launch has completed
     pdl_launch_dependents();    // the next elimination pass may set itself up behind this kernel
     PivotState *st = P.st;
     int r = -1, k = 0, cur = st->cur, phase = st->phase;
     bool fast = false;
+    cluster_entry_wait();
 
     if (forced_k > 0) {
         r = forced_r;
@@ -166,7 +168,7 @@ DenseParams make_params(const lpgpu_dense *d) {
     P.basis = d->basis; P.prow = d->prow; P.pcol = d->pcol; P.pcn = d->pcn; P.bnext = d->bnext; P.st = d->st;
     P.log = d->log; P.log_cap = d->log_cap;
     P.eps = d->opts.eps; P.max_iter = d->opts.max_iter; P.method = d->opts.method; P.n_art = d->opts.n_art;
-    P.bland = (d->opts.variant & 0x400000) ? 1 : 0;
+    P.bland = (d->opts.variant & LPGPU_VARIANT_BLAND) ? 1 : 0;
     return P;
 }
 
@@ -207,7 +209,7 @@ static cudaError_t launch_cluster(bool pdl, int cluster, void (*kernel)(KArgs...
 
 int launch_select(lpgpu_dense *d, int forced_r, int forced_k) {
     lpgpu_ctx *ctx = d->ctx;
-    const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels;
+    const bool pdl = !(d->opts.variant & LPGPU_VARIANT_NO_PDL) && !d->opts.time_kernels;
     LP_CUDA(ctx, launch_pdl(pdl, dense_select_kernel, dim3(SELECT_CLUSTER), dim3(SELECT_THREADS), ctx->stream,
                             make_params(d), forced_r, forced_k));
     ctx->launches++;
@@ -231,9 +233,9 @@ static int launch_update_impl(lpgpu_dense *d, double *cnext, void *const *peer_x
     // variant: low nibble 0 = TMA-staged kernel with work stealing (default), 1 = TMA-staged with a
     //          static task stride, 2 = direct-load kernel;
     //          0x200 = do NOT alternate the sweep direction between pivots
-    U.alternate = (d->opts.variant & 0x200) ? 0 : 1;
-    const int kind = d->opts.variant & 0xf;
-    const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels && cnext == nullptr && n_peers == 0;
+    U.alternate = (d->opts.variant & LPGPU_VARIANT_NO_ALTERNATE) ? 0 : 1;
+    const int kind = d->opts.variant & LPGPU_VARIANT_UPD_MASK;
+    const bool pdl = !(d->opts.variant & LPGPU_VARIANT_NO_PDL) && !d->opts.time_kernels && cnext == nullptr && n_peers == 0;
     LP_CUDA(ctx, launch_pdl(pdl, kind == 2 ? dense_update_direct : kind == 1 ? dense_update_tma_staged : dense_update_dynamic, dim3(d->grid_update),
                             dim3(UPD_THREADS), ctx->stream, U));
     ctx->launches++;
@@ -250,7 +252,7 @@ int read_state(lpgpu_dense *d) {
 // ---- blocked path (dense_block.cuh): the default for the plain and Big-M methods; variant bit 0x800 selects the
 // rank-1 path instead; pivots per block in variant bits 16..21 (0 = 32)
 bool use_blocked(const lpgpu_dense *d) {
-    return !(d->opts.variant & 0x800) &&
+    return !(d->opts.variant & LPGPU_VARIANT_RANK1) &&
            (d->opts.method == LPGPU_PLAIN || d->opts.method == LPGPU_BIGM || d->opts.method == LPGPU_TWOPHASE ||
             d->opts.method == LPGPU_DUAL);
 }
@@ -269,7 +271,7 @@ BlockBufs make_bufs(const lpgpu_dense *d) {
         B.info = d->info; B.par = d->par; B.pend = d->pend ? 1 : 0;
         B.l2keep = (d->l2hint & 2) ? 1 : 0;
     }
-    const int k = (d->opts.variant >> 16) & 0x3f;
+    const int k = (d->opts.variant & LPGPU_VARIANT_BLOCK_K_MASK) >> 16;
     B.K = (k >= 1 && k <= BLK_KMAX) ? k : BLK_KMAX;
     B.dbg = d->blk_dbg ? d->blk_dbg + 8 * (size_t)(d->blk_dbg_n % 4096) : nullptr;
     return B;
@@ -293,8 +295,8 @@ int launch_block_init(lpgpu_dense *d) {
 // 4096, pipelined 1.12x / 1.45x faster at m = 6144 / 8192).  variant bit 0x1000 forces pipelined blocks, 0x2000 (or no
 // room for the second tableau buffer) the in-place order: steps, pass, steps, ...
 static bool want_pipeline(const lpgpu_dense *d) {
-    if (!use_blocked(d) || (d->opts.variant & (0x2000 | 0x100)) || d->opts.method == LPGPU_DUAL || getenv("LPGPU_NO_PIPELINE")) return false;
-    if (d->opts.variant & 0x1000) return true;
+    if (!use_blocked(d) || (d->opts.variant & LPGPU_VARIANT_INPLACE) || d->opts.method == LPGPU_DUAL || getenv("LPGPU_NO_PIPELINE")) return false;
+    if (d->opts.variant & LPGPU_VARIANT_PIPELINED) return true;
     return ((size_t)d->m + d->R) * d->ld * sizeof(double) >= ((size_t)384 << 20);
 }
 
@@ -447,18 +449,18 @@ static int probe_step_cluster(lpgpu_dense *d) {
     return LPGPU_OK;
 }
 
-static int step_cluster(const lpgpu_dense *d) { return (d->opts.variant & 0x8000) ? SELECT_CLUSTER : d->step_cl_max; }
+static int step_cluster(const lpgpu_dense *d) { return (d->opts.variant & LPGPU_VARIANT_STEP_CL8) ? SELECT_CLUSTER : d->step_cl_max; }
 
 static int launch_block_step(lpgpu_dense *d, int first) {
     lpgpu_ctx *ctx = d->ctx;
-    const bool pdl = !(d->opts.variant & 0x400) && !d->opts.time_kernels;
+    const bool pdl = !(d->opts.variant & LPGPU_VARIANT_NO_PDL) && !d->opts.time_kernels;
     if (d->opts.method == LPGPU_DUAL) {
         const int cl = step_cluster(d);
         LP_CUDA(ctx, launch_cluster(pdl, cl, cl == 16 ? blk_dual_step_kernel<16> : blk_dual_step_kernel<8>, dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS),
                                     ctx->stream, make_params(d), make_bufs(d), first));
     } else {
         const int cl = step_cluster(d);
-        LP_CUDA(ctx, launch_cluster(pdl, cl, step_kernel(d->R, d->pipe_on, cl, (d->opts.variant & 0x400000) != 0), dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS), ctx->stream,
+        LP_CUDA(ctx, launch_cluster(pdl, cl, step_kernel(d->R, d->pipe_on, cl, (d->opts.variant & LPGPU_VARIANT_BLAND) != 0), dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS), ctx->stream,
                                     make_params(d), make_bufs(d), first));
     }
     if (d->blk_dbg) d->blk_dbg_n++;
@@ -469,7 +471,7 @@ static int launch_block_step(lpgpu_dense *d, int first) {
 // which pass kernel: variant bit 0x4000 = the one that loads a whole tile before it computes, else the software-pipelined default
 static int launch_pass_kernel(lpgpu_dense *d, const FlushParams &U, cudaStream_t stream) {
     lpgpu_ctx *ctx = d->ctx;
-    if (d->opts.variant & 0x4000) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
+    if (d->opts.variant & LPGPU_VARIANT_WHOLE_TILE) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
     else blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
     LP_LAUNCH_CHECK(ctx);
     return LPGPU_OK;
@@ -483,14 +485,9 @@ int launch_block_flush(lpgpu_dense *d) {
     for (unsigned &w : U.resv) w = 0;
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
     U.rb = d->fl_rb; U.pf = d->fl_pf;
-    // variant bit 0x100: the warp-specialised pass (one CTA per SM, TMA ring; slower: see DESIGN.md 4.0)
-    // variant bit 0x4000: the pass that loads a whole tile before it computes (the default is software-pipelined in half tiles)
-    if (!(d->opts.variant & 0x100)) {
+    {
         const int rcp = launch_pass_kernel(d, U, ctx->stream);
         if (rcp != LPGPU_OK) return rcp;
-    } else {
-        blk_flush_ws_kernel<<<std::min<long>(ctx->sm_count, d->flush_tasks), WS_THREADS, WS_SMEM_BYTES, ctx->stream>>>(U);
-        LP_LAUNCH_CHECK(ctx);
     }
     const unsigned fx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, (d->ld + 255) / 256));
     blk_fixrows_kernel<<<dim3(fx, BLK_KMAX), 256, 0, ctx->stream>>>(U);
@@ -535,7 +532,7 @@ int size_grid(lpgpu_dense *d) {
     LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3, dense_update_dynamic, UPD_THREADS, 0));
     LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, dense_update_direct, UPD_THREADS, 0));
     LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, dense_update_tma_staged, UPD_THREADS, 0));
-    const int kind = d->opts.variant & 0xf;
+    const int kind = d->opts.variant & LPGPU_VARIANT_UPD_MASK;
     const int occ = std::max(1, kind == 2 ? occ0 : kind == 1 ? occ1 : occ3);
     const long nct = (long)((d->ld + UPD_TILE_COLS - 1) / UPD_TILE_COLS);
     const long nrb = (d->m + d->R + UPD_TILE_ROWS - 1) / UPD_TILE_ROWS;
@@ -557,7 +554,7 @@ bool opts_ok(const lpgpu_opts *o, int n, int R) {
     if (o->method != LPGPU_PLAIN && o->method != LPGPU_BIGM && o->method != LPGPU_TWOPHASE && o->method != LPGPU_DUAL) return false;
     if ((o->method == LPGPU_PLAIN || o->method == LPGPU_DUAL) != (R == 1)) return false;
     if (o->n_art < 0 || o->n_art > n || o->max_iter < 0 || o->log_cap < 0 || !(o->eps >= 0.0)) return false;
-    if ((o->variant & 0x400000) && o->method == LPGPU_DUAL) return false;      // Bland's rule: primal methods
+    if ((o->variant & LPGPU_VARIANT_BLAND) && o->method == LPGPU_DUAL) return false;      // Bland's rule: primal methods
     return true;
 }
 
@@ -574,7 +571,7 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     d->ctx = ctx; d->m = m; d->n = n; d->R = R;
     d->ld = round_up((size_t)n + 1, 16);
     d->T = nullptr; d->basis = nullptr; d->prow = d->pcol = d->bnext = d->xbuf = nullptr; d->la_dirty = true; d->st = nullptr; d->h_st = nullptr;
-    d->log = nullptr; d->log_cap = 0; d->task_ctr = nullptr; d->upd_seq = 0;
+    d->log = nullptr; d->log_cap = 0; d->log_alloc = 0; d->task_ctr = nullptr; d->upd_seq = 0;
     d->Ft = d->Pm = d->objcur = d->bcur = nullptr; d->rowstamp = d->steprow = nullptr; d->cands = nullptr; d->blk_open = false; d->blk_steps = 0;
     d->pipe_state = 0; d->pipe_on = false; d->pend = false; d->par = 0;
     d->up_stream = nullptr; d->ev_up = d->ev_up_ready = nullptr; d->up_pending = false;
@@ -617,8 +614,6 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
         e = cudaFuncSetAttribute(blk_flush_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL_SMEM_BYTES);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(blk_flush_sp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL_SMEM_BYTES);
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(blk_flush_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WS_SMEM_BYTES);
     if (e == cudaSuccess) e = cudaHostAlloc(&d->h_st, sizeof(PivotState), cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->T, 0, rows * d->ld * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->prow, 0, d->ld * sizeof(double), ctx->stream);
@@ -684,14 +679,17 @@ int lpgpu_dense_reset(lpgpu_dense *d, const lpgpu_opts *opts) {
     { const int rcs = settle_dense(d); if (rcs != LPGPU_OK) return rcs; }
     d->opts = *opts;
     if (d->opts.check_every <= 0) d->opts.check_every = 64;
-    if (opts->log_cap > d->log_cap) {
+    // the buffer only ever grows (log_alloc); the ACTIVE limit is this call's opts->log_cap: the kernels log against it,
+    // n_logged and the download length follow it (a caller's pivot_log holds 2 * opts->log_cap ints, no more)
+    if (opts->log_cap > d->log_alloc) {
         LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         cudaFree(d->log);
         d->log = nullptr;
-        d->log_cap = 0;
+        d->log_alloc = 0;
         LP_CUDA(ctx, cudaMalloc(&d->log, (size_t)opts->log_cap * 2 * sizeof(int)));
-        d->log_cap = opts->log_cap;
+        d->log_alloc = opts->log_cap;
     }
+    d->log_cap = opts->log_cap;
     if (d->log_cap > 0) LP_CUDA(ctx, cudaMemsetAsync(d->log, 0xff, (size_t)d->log_cap * 2 * sizeof(int), ctx->stream));
     LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // h_st may still be in flight
     PivotState s;
@@ -971,7 +969,7 @@ int lpgpu_dense_download(lpgpu_dense *d, double *T, size_t ld, int *basis, int *
     if (!d) return LPGPU_EINVAL;
     lpgpu_ctx *ctx = d->ctx;
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
-    if (T || x) { const int rcs = settle_dense(d); if (rcs != LPGPU_OK) return rcs; }
+    { const int rcs = settle_dense(d); if (rcs != LPGPU_OK) return rcs; }      // always: the basis / log copies must not race a pending asynchronous upload either
     if (T) {
         if (ld < (size_t)d->n + 1) return fail(ctx, LPGPU_EINVAL, "dense_download: ld %zu < n+1", ld);
         LP_CUDA(ctx, cudaMemcpy2DAsync(T, ld * sizeof(double), d->T, d->ld * sizeof(double), ((size_t)d->n + 1) * sizeof(double),

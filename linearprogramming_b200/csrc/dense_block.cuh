@@ -83,6 +83,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         }
     };
     stamp(0);
+    cluster_entry_arrive();     // DSMEM rule: no remote access before every CTA of the cluster has started (wait below)
     pdl_wait();
     pdl_launch_dependents();
     stamp(1);
@@ -91,6 +92,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     const int status0 = st->status, iters = st->iters, budget = st->budget;
     const int t = first ? 0 : st->blk_t, seq = st->blk_seq + (first ? 1 : 0);
     const int kn = st->k_next;
+    cluster_entry_wait();
     // pipelined blocks: P.T is the tableau before the previous block (its pass is still running); the lazy chains
     // run through that block's Kp steps (combined step index c < Kp) and then this block's t steps (c - Kp)
     // (PIPE = false: the in-place order, Kp = 0 at compile time and the code below is the plain one-block chain)
@@ -337,12 +339,14 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
     const int gtid = rank * TH + (int)threadIdx.x;
     constexpr int GSTRIDE = CL * TH;
 
+    cluster_entry_arrive();
     pdl_wait();
     pdl_launch_dependents();
     PivotState *st = P.st;
     const int status0 = st->status, iters = st->iters, budget = st->budget;
     const int t = first ? 0 : st->blk_t, seq = st->blk_seq + (first ? 1 : 0);
     const int kn = st->k_next;                       // -2: per-CTA leaving-row candidates are in B.cands
+    cluster_entry_wait();
     KeyCand cin = keycand_none();
     if ((threadIdx.x & 31) < CL) {
         const int ln = threadIdx.x & 31;
@@ -945,143 +949,6 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_sp_kernel(FlushParams
             fl_store_rows<FL_HR>(U, t, row0 + FL_HR, jc, acc1, pol);
             __syncthreads();       // sF[fb] may be refilled (two tiles ahead), and at the last tile sP and s_task
         }
-    }
-}
-
-// ------------------------------------------------------------------ warp-specialised pass (variant bit 0x100; NOT the default)
-// One CTA per SM: warp 4 (one lane) is the PRODUCER -- it claims tasks and keeps a two-stage ring of tableau
-// tiles (64 rows x 1 KB bulk copies), their multipliers and, per task, the pivot-row segments filled by
-// the TMA unit; warps 0..3 are CONSUMERS -- tile from shared memory into registers, the chain of K steps,
-// registers straight back to HBM.  The tile after the one on the FP64 pipe is always in flight, so HBM
-// streams continuously instead of in step with the CTAs' compute phases.  Measured: 0.73 ms per 32 pivots
-// against 0.48 ms of blk_flush_kernel -- one 64 KB tile in flight per SM does not cover the HBM latency, and
-// the 224 KB of shared memory leave no room for a third stage (the 3-CTA kernel keeps 192 KB of tiles in
-// REGISTERS).  Kept as a measured alternative.
-constexpr int WS_CONSUMERS = 4;
-constexpr int WS_THREADS = (WS_CONSUMERS + 1) * 32;
-constexpr int WS_STAGES = 2;
-constexpr size_t WS_T_BYTES = (size_t)FL_ROWS * FL_COLS * 8;                       // 64 KB
-constexpr size_t WS_F_BYTES = (size_t)BLK_KMAX * FL_ROWS * 8;                      // 16 KB
-constexpr size_t WS_P_BYTES = (size_t)BLK_KMAX * FL_COLS * 8;                      // 32 KB
-constexpr size_t WS_SMEM_BYTES = WS_STAGES * (WS_T_BYTES + WS_F_BYTES) + 2 * WS_P_BYTES;   // 224 KB
-
-struct WsDesc {
-    long j0;            // first column of the tile; -1 = no more work
-    int ncols, rt, pb, newtask, lasttile;
-};
-
-// bounded wait: a protocol error traps instead of hanging the GPU
-__device__ __forceinline__ void mbar_wait_bounded(uint64_t *bar, uint32_t parity) {
-    for (long spin = 0; spin < (1L << 31); ++spin) {
-        uint32_t ok;
-        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
-                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-        if (ok) return;
-    }
-    __trap();
-}
-
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-
-__global__ void __launch_bounds__(WS_THREADS, 1) blk_flush_ws_kernel(FlushParams U) {
-    extern __shared__ __align__(128) unsigned char ws_smem[];
-    double *sT = reinterpret_cast<double *>(ws_smem);                                  // [WS_STAGES][FL_ROWS][FL_COLS]
-    double *sF = sT + WS_STAGES * (size_t)FL_ROWS * FL_COLS;                           // [WS_STAGES][BLK_KMAX][FL_ROWS]
-    double *sP = sF + WS_STAGES * (size_t)BLK_KMAX * FL_ROWS;                          // [2][BLK_KMAX][FL_COLS]
-    __shared__ __align__(8) uint64_t full[WS_STAGES], empty[WS_STAGES], pfull[2], pempty[2];
-    __shared__ WsDesc desc[WS_STAGES];
-
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < WS_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], WS_CONSUMERS); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&pfull[b], 1); mbar_init(&pempty[b], WS_CONSUMERS); }
-        fence_mbar_init();
-    }
-    pdl_wait();
-    int *ctr = U.task_ctr + (U.seq & 1u);
-    if (blockIdx.x == 0 && threadIdx.x == 0) U.task_ctr[(U.seq & 1u) ^ 1u] = 0;
-    const int kc = *U.kc_ptr;
-    if (kc <= 0) return;
-    __syncthreads();
-
-    const int nct = (int)((U.ld + FL_COLS - 1) / FL_COLS);
-    const int nrt = (U.rows + FL_ROWS - 1) / FL_ROWS;
-    const int nsb = (nrt + U.rb - 1) / U.rb;
-    const long ntasks = (long)nct * nsb;
-
-    if (warp == WS_CONSUMERS) {
-        // ------------------------------------------------------------ producer
-        if (lane != 0) return;
-        int n = 0, ntask_seen = 0;                 // tiles issued, tasks started
-        while (true) {
-            const long tt = (long)atomicAdd(ctr, 1);
-            if (tt >= ntasks) break;
-            const long j0 = (long)(tt % nct) * FL_COLS;
-            const int ncols = (int)min((size_t)FL_COLS, U.ld - (size_t)j0);
-            const int rt0 = (int)(tt / nct) * U.rb, rt1 = min(rt0 + U.rb, nrt);
-            const int pb = ntask_seen & 1;
-            // pivot-row segments of this column tile (buffer pb was released by the consumers of task ntask_seen - 2)
-            if (ntask_seen >= 2) mbar_wait_bounded(&pempty[pb], ((ntask_seen >> 1) - 1) & 1);
-            mbar_arrive_expect_tx(&pfull[pb], (uint32_t)(kc * ncols * 8));
-            for (int s = 0; s < kc; ++s)
-                tma_load_1d(sP + ((size_t)pb * BLK_KMAX + s) * FL_COLS, U.Pm + (size_t)s * U.ld + j0, (uint32_t)(ncols * 8), &pfull[pb]);
-            for (int rt = rt0; rt < rt1; ++rt, ++n) {
-                const int st = n % WS_STAGES;
-                if (n >= WS_STAGES) mbar_wait_bounded(&empty[st], ((n / WS_STAGES) - 1) & 1);
-                const int i0 = rt * FL_ROWS, nr = min(FL_ROWS, U.rows - i0);
-                desc[st].j0 = j0; desc[st].ncols = ncols; desc[st].rt = rt; desc[st].pb = pb;
-                desc[st].newtask = (rt == rt0); desc[st].lasttile = (rt == rt1 - 1);
-                mbar_arrive_expect_tx(&full[st], (uint32_t)(nr * ncols * 8 + kc * FL_ROWS * 8));
-                double *dstT = sT + (size_t)st * FL_ROWS * FL_COLS;
-                for (int rr = 0; rr < nr; ++rr)
-                    tma_load_1d(dstT + (size_t)rr * FL_COLS, U.Tsrc + (size_t)(i0 + rr) * U.ld + j0, (uint32_t)(ncols * 8), &full[st]);
-                for (int s = 0; s < kc; ++s)
-                    tma_load_1d(sF + ((size_t)st * BLK_KMAX + s) * FL_ROWS, U.Fs + (size_t)s * U.pcn + (size_t)i0, (uint32_t)(FL_ROWS * 8), &full[st]);
-            }
-            ++ntask_seen;
-        }
-        // end marker
-        const int st = n % WS_STAGES;
-        if (n >= WS_STAGES) mbar_wait_bounded(&empty[st], ((n / WS_STAGES) - 1) & 1);
-        desc[st].j0 = -1;
-        mbar_arrive(&full[st]);
-        return;
-    }
-
-    // ---------------------------------------------------------------- consumers
-    const int wr = warp;                           // 4 warps stacked over the 64 rows of a tile
-    const int jc = 2 * lane;
-    int ptask = 0;                                 // tasks seen (P buffer parity bookkeeping)
-    for (int n = 0;; ++n) {
-        const int st = n % WS_STAGES;
-        mbar_wait_bounded(&full[st], (n / WS_STAGES) & 1);
-        const WsDesc dsc = desc[st];
-        if (dsc.j0 < 0) break;
-        if (dsc.newtask) { mbar_wait_bounded(&pfull[dsc.pb], (ptask >> 1) & 1); }
-        FlTile t;
-        t.j0 = (size_t)dsc.j0; t.ncols = dsc.ncols; t.rt = dsc.rt;
-        const int i0 = t.rt * FL_ROWS + FL_TR * wr;
-        const bool ok0 = jc < t.ncols, ok1 = jc + 64 < t.ncols;
-        double2 acc[FL_TR][2];
-        const double *tsrc = sT + (size_t)st * FL_ROWS * FL_COLS + (size_t)(FL_TR * wr) * FL_COLS + jc;
-#pragma unroll
-        for (int rr = 0; rr < FL_TR; ++rr) {
-            const bool rowok = i0 + rr < U.rows;
-            acc[rr][0] = (ok0 && rowok) ? *reinterpret_cast<const double2 *>(tsrc + (size_t)rr * FL_COLS) : make_double2(0.0, 0.0);
-            acc[rr][1] = (ok1 && rowok) ? *reinterpret_cast<const double2 *>(tsrc + (size_t)rr * FL_COLS + 64) : make_double2(0.0, 0.0);
-        }
-        fl_chain_tile(kc, sF + (size_t)st * BLK_KMAX * FL_ROWS + FL_TR * wr, sP + (size_t)dsc.pb * BLK_KMAX * FL_COLS + jc, acc);
-        // the stage (tile and multipliers) and, after a task's last tile, the P buffer go back to the producer
-        fence_proxy_async();                       // our reads of the stage are ordered before the TMA unit's next writes
-        __syncwarp();
-        if (lane == 0) {
-            mbar_arrive(&empty[st]);
-            if (dsc.lasttile) mbar_arrive(&pempty[dsc.pb]);
-        }
-        if (dsc.lasttile) ++ptask;
-        fl_store_tile(U, t, wr, jc, acc);
     }
 }
 

@@ -19,7 +19,8 @@ struct lpgpu_dense {
     lpgpu::PivotState *st;
     lpgpu::PivotState *h_st;       // pinned mirror
     int *log;
-    int log_cap;
+    int log_cap;            // ACTIVE limit = opts.log_cap of the last reset (what the kernels log against, n_logged and the download length)
+    int log_alloc;          // pivots the device buffer has room for (only ever grows)
     lpgpu_opts opts;
     int grid_update;
     int grid_flush;         // persistent grid of the blocked path's pass

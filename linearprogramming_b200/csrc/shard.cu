@@ -194,9 +194,11 @@ shard_select_kernel(ShardParams S) {
     const int gtid = rank * SELECT_THREADS + (int)threadIdx.x;
     constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
 
+    cluster_entry_arrive();     // DSMEM rule: no remote access before every CTA of the cluster has started
     PivotState *st = P.st;
     const int status0 = st->status, iters = st->iters, budget = st->budget;
     const int k = S.sh->k_next, owner = S.sh->owner;
+    cluster_entry_wait();
     if (status0 != LPGPU_RUNNING) {
         cl.sync();
         if (gtid == 0) {
@@ -327,6 +329,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
     const int gtid = crank * SELECT_THREADS + (int)threadIdx.x;
     constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
 
+    cluster_entry_arrive();     // DSMEM rule: no remote access before every CTA of the cluster has started
     PivotState *st = P.st;
     const int status0 = st->status, iters = st->iters, budget = st->budget;
     const int t = first ? 0 : st->blk_t, seq = st->blk_seq + (first ? 1 : 0);
@@ -334,6 +337,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
     const double *oc = B.objcur, *om = B.objcur + P.ld;
     const size_t pcn = P.pcn;
     const int rows = P.m + RR;
+    cluster_entry_wait();
 
     // ---- every rank's candidate of this pivot (posted at the end of the previous step or by the bootstrap)
     const unsigned pit = S.iter - 1u;
@@ -864,7 +868,7 @@ int lpgpu_shard_reset(lpgpu_shard *s, const lpgpu_opts *opts) {
     if (!s || !opts) return LPGPU_EINVAL;
     lpgpu_ctx *ctx = s->ctx;
     if (opts->method == LPGPU_TWOPHASE) return fail(ctx, LPGPU_EINVAL, "shard_reset: the column-sharded path prices PLAIN and BIGM only");
-    if (opts->variant & 0x400000) return fail(ctx, LPGPU_EINVAL, "shard_reset: Bland's rule is not built for the column-sharded path");
+    if (opts->variant & LPGPU_VARIANT_BLAND) return fail(ctx, LPGPU_EINVAL, "shard_reset: Bland's rule is not built for the column-sharded path");
     if ((opts->method == LPGPU_PLAIN) != (s->R == 1) || opts->n_art < 0 || opts->n_art > s->n)
         return fail(ctx, LPGPU_EINVAL, "shard_reset: bad options (method/R/n_art)");
     s->opts = *opts;
@@ -1011,7 +1015,7 @@ int lpgpu_shard_run(lpgpu_shard *s, int max_pivots, lpgpu_result *res) {
     rc = push_state(s, st);
     if (rc != LPGPU_OK) return rc;
     // peer-memory transport, default: the blocked path (variant bit 0x800 selects the rank-1 pipeline below)
-    if (s->use_p2p && !(s->opts.variant & 0x800)) return shard_run_blocked(s, max_pivots, res);
+    if (s->use_p2p && !(s->opts.variant & LPGPU_VARIANT_RANK1)) return shard_run_blocked(s, max_pivots, res);
     if (s->dirty) {
         // bootstrap: price the tableau as it stands, fetch the entering column from its owner (strided)
         for (ShardRank &r : s->rk) {

@@ -108,6 +108,7 @@ int main(int argc, char **argv) {
             printf("\titeration %d: column %d enters, row %d leaves\n", p + 1, col, row);
         }
         printf("> %s after %d iteration(s)\n", status_name(sol.status), sol.iters);
+        if (sol.status == LPGPU_ITER_LIMIT) printf("\tpivot cap reached (a degenerate model may cycle): try LPGPU_PRICING=bland or raise LPGPU_MAX_ITER\n");
         if (sol.status == LPGPU_OPTIMAL) {
             printf("\t%s z = %.10g\n", mo.sense == 1 ? "max" : "min", sol.z);
             for (int v = 0; v < sol.n_named; ++v) printf("\t%s = %.10g\n", sol.names[v], sol.values[v]);

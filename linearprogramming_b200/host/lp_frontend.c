@@ -5,6 +5,7 @@
 #include "lp_frontend.h"
 
 #include <ctype.h>
+#include <errno.h>
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -52,10 +53,11 @@ static int rat_parse(const char *s, lpf_rat *out) {
     if (slash) {
         *slash = '\0';
         if (!buf[0] || !slash[1] || dot) return -1;
+        errno = 0;
         long p = strtol(buf, &end, 10);
-        if (*end) return -1;
+        if (*end || errno == ERANGE) return -1;
         long q = strtol(slash + 1, &end, 10);
-        if (*end || q <= 0) return -1;
+        if (*end || q <= 0 || errno == ERANGE) return -1;
         return rat_norm(p, q, out);
     }
     if (dot) {
@@ -76,8 +78,9 @@ static int rat_parse(const char *s, lpf_rat *out) {
         if (!seen_digit) return -1;
         return rat_norm(neg ? -num : num, den, out);
     }
+    errno = 0;
     long v = strtol(buf, &end, 10);
-    if (*end) return -1;
+    if (*end || errno == ERANGE) return -1;     /* a coefficient that does not fit a long is an error, not LONG_MAX */
     *out = rat_int(v);
     return 0;
 }
@@ -313,7 +316,7 @@ static int split_sections(const char *text, raw_model *r, lpf_model *m) {
                     int sense = strcmp(stmt, "max") == 0 ? 1 : strcmp(stmt, "min") == 0 ? -1 : 0;
                     if (!sense) { free(stmt); return fail(m, "Objective function invalid."); }   /* e.g. "ma:" (testdata.txt:2) */
                     if (r->have_objective) { free(stmt); return fail(m, "There can be only ONE Objective function!"); }
-                    if (parse_formula(colon + 1, &r->objective, m) != 0) { free(stmt); return -1; }
+                    if (parse_formula(colon + 1, &r->objective, m) != 0) { formula_free(&r->objective); free(stmt); return -1; }
                     r->have_objective = 1;
                     r->sense = sense;
                     const formula_t *f = &r->objective;
@@ -324,7 +327,7 @@ static int split_sections(const char *text, raw_model *r, lpf_model *m) {
                         r->cap = r->cap ? r->cap * 2 : 8;
                         r->st = (formula_t *)realloc(r->st, sizeof(formula_t) * (size_t)r->cap);
                     }
-                    if (parse_formula(stmt, &r->st[r->nst], m) != 0) { free(stmt); return -1; }
+                    if (parse_formula(stmt, &r->st[r->nst], m) != 0) { formula_free(&r->st[r->nst]); free(stmt); return -1; }
                     r->nst++;
                 }
                 ns = 0;
@@ -541,10 +544,11 @@ int lpf_parse_file_mode(const char *path, int dual, lpf_model *m) {
     memset(m, 0, sizeof *m);
     FILE *f = fopen(path, "rb");
     if (!f) return fail(m, "File not readable or does not exist.");
-    fseek(f, 0, SEEK_END);
-    long sz = ftell(f);
-    fseek(f, 0, SEEK_SET);
+    long sz = -1;
+    if (fseek(f, 0, SEEK_END) == 0) sz = ftell(f);
+    if (sz < 0 || fseek(f, 0, SEEK_SET) != 0) { fclose(f); return fail(m, "File not readable or does not exist."); }   /* unseekable path */
     char *buf = (char *)malloc((size_t)sz + 1);
+    if (!buf) { fclose(f); return fail(m, "Out of memory while reading the model file."); }
     size_t got = fread(buf, 1, (size_t)sz, f);
     buf[got] = '\0';
     fclose(f);

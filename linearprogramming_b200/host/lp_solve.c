@@ -53,7 +53,10 @@ int lpf_solve_model(void *ctx, const lpf_model *mo, int method_if_needed, lpf_so
         if (pe && !strcmp(pe, "bland") && method != LPGPU_DUAL) o.variant |= LPGPU_VARIANT_BLAND;
     }
     o.log_cap = 16 * (mo->m + n) + 64;
-    o.max_iter = 0x7fffffff;
+    {   /* "message, never hang": a cycling model ends with ITERATION LIMIT (LPGPU_MAX_ITER overrides the cap) */
+        const char *me = getenv("LPGPU_MAX_ITER");
+        o.max_iter = (me && atol(me) > 0) ? (int)(atol(me) > 0x7fffffffL ? 0x7fffffffL : atol(me)) : 50 * (mo->m + n) + 1000;
+    }
     int *log = (int *)malloc(sizeof(int) * 2 * (size_t)o.log_cap);
     double *x = (double *)calloc((size_t)n, sizeof(double));
     lpgpu_result res;

@@ -21,6 +21,11 @@
  *   LPGPU_METHOD=dual            dual simplex: standardise with the reference's LPStandardize(model, 1)
  *                                (Source/simplex.c:177-178; the menu entry "2. Dual Simplex Method" of
  *                                Source/router.c:32-34 calls nothing) and pivot with LPGPU_DUAL
+ *   LPGPU_PRICING=bland          Bland's rule (anti-cycling), primal methods
+ *   LPGPU_MAX_ITER=<n>           pivot cap (default 50 * (m + n) + 1000: "message, never hang")
+ *   LPGPU_PRINT_TABLEAU=1        print the textbook tableau  C_B | X_B | b | a_ij  with the sigma_j row after
+ *                                every iteration (the layout SimplexMatrix's fields imply: basicCosts = C_B,
+ *                                basicVars = X_B, b in column 0, Source/matrix.h:13-21); models up to 64 columns
  */
 #include "public.h"
 #include "simplex.h"
@@ -62,6 +67,87 @@ static int choose_method(void) {
         if (chosen >= 1 && chosen <= 2) break;
     }
     return chosen == 1 ? LPGPU_BIGM : LPGPU_TWOPHASE;
+}
+
+/* pivot cap of the host front ends: a cycling model ends with ITERATION LIMIT and a hint, never with a hang */
+static int pivot_cap(int m, int n) {
+    const char *e = getenv("LPGPU_MAX_ITER");
+    if (e && atol(e) > 0) return (int)(atol(e) > 0x7fffffffL ? 0x7fffffffL : atol(e));
+    return 50 * (m + n) + 1000;
+}
+
+#define PRINT_TABLEAU_MAX_COLS 64
+
+static void column_name(char *out, size_t cap, const SimplexMatrix *sm, int n0, int col) {
+    if (col >= 1 && col <= n0) snprintf(out, cap, "%s", sm->varNames[col - 1]);
+    else snprintf(out, cap, "a%d", col - n0);
+}
+
+/* The textbook tableau after `iter` pivots:  C_B | X_B | b | a_i1 .. a_in, then the sigma_j row(s) with -z in the
+ * b column.  cost[j-1] = c_j of the standard form; artificial columns cost -M (Big M) or 0 in the cost row. */
+static void print_tableau(const SimplexMatrix *sm, int m, int n, int n0, int R, int method, const double *T, size_t ld,
+                          const int *basis, const double *cost, int iter, int enter, int leave) {
+    char nm[16];
+    int i, j;
+    if (iter == 0) printf("\n> Initial tableau\n\n");
+    else {
+        column_name(nm, sizeof nm, sm, n0, enter);
+        printf("\n> Tableau after iteration %d (%s enters, row %d leaves)\n\n", iter, nm, leave + 1);
+    }
+    printf("\t%8s %6s %12s |", "C_B", "X_B", "b");
+    for (j = 1; j <= n; j++) { column_name(nm, sizeof nm, sm, n0, j); printf(" %10s", nm); }
+    printf("\n\t%8s %6s %12s |", "", "c_j", "");
+    for (j = 1; j <= n; j++) {
+        if (j > n0 && method == LPGPU_BIGM) printf(" %10s", "-M");
+        else printf(" %10.6g", j <= n0 ? cost[j - 1] : 0.0);
+    }
+    printf("\n");
+    for (i = 0; i < m; i++) {
+        const int bj = basis[i];
+        column_name(nm, sizeof nm, sm, n0, bj);
+        if (bj > n0 && method == LPGPU_BIGM) printf("\t%8s", "-M");
+        else printf("\t%8.6g", (bj >= 1 && bj <= n0) ? cost[bj - 1] : 0.0);
+        printf(" %6s %12.6g |", nm, T[(size_t)i * ld]);
+        for (j = 1; j <= n; j++) printf(" %10.6g", T[(size_t)i * ld + (size_t)j]);
+        printf("\n");
+    }
+    printf("\t%8s %6s %12.6g |", "sigma_j", "-z", T[(size_t)m * ld]);
+    for (j = 1; j <= n; j++) printf(" %10.6g", T[(size_t)m * ld + (size_t)j]);
+    printf("\n");
+    if (R == 2) {
+        printf("\t%8s %6s %12.6g |", method == LPGPU_BIGM ? "sigma^M" : "sigma^I", method == LPGPU_BIGM ? "-z_M" : "-w", T[(size_t)(m + 1) * ld]);
+        for (j = 1; j <= n; j++) printf(" %10.6g", T[(size_t)(m + 1) * ld + (size_t)j]);
+        printf("\n");
+    }
+}
+
+/* LPGPU_PRINT_TABLEAU=1: the same solve, one pivot per lpgpu_dense_run call on a device-resident tableau
+ * (include/lpgpu.h), the tableau read back and printed after every iteration.  Same pivots, same bits as the
+ * one-shot call; meant for small models. */
+static int solve_with_tableau_print(lpgpu_ctx *ctx, const SimplexMatrix *sm, int m, int n, int n0, int R, double *T, size_t ld,
+                                    int *basis, const lpgpu_opts *o, int *plog, double *x, lpgpu_result *res) {
+    lpgpu_dense *d = NULL;
+    double *cost = (double *)calloc((size_t)n0 + 1, sizeof(double));
+    int j, rc = lpgpu_dense_create(ctx, m, n, R, &d);
+    for (j = 0; j < n0; j++) cost[j] = T[(size_t)m * ld + 1 + (size_t)j];
+    if (rc == LPGPU_OK) rc = lpgpu_dense_reset(d, o);
+    if (rc == LPGPU_OK) rc = lpgpu_dense_upload(d, T, ld, basis);
+    if (rc == LPGPU_OK) print_tableau(sm, m, n, n0, R, o->method, T, ld, basis, cost, 0, 0, 0);
+    memset(res, 0, sizeof *res);
+    res->status = LPGPU_RUNNING;
+    int done = 0;
+    while (rc == LPGPU_OK && res->status == LPGPU_RUNNING && done < o->max_iter) {
+        rc = lpgpu_dense_run(d, 1, res);
+        if (rc != LPGPU_OK || res->iters == done) break;           /* terminal status without a pivot */
+        done = res->iters;
+        rc = lpgpu_dense_download(d, T, ld, basis, plog, NULL);
+        if (rc == LPGPU_OK && done <= o->log_cap) print_tableau(sm, m, n, n0, R, o->method, T, ld, basis, cost, done, plog[2 * (done - 1)], plog[2 * (done - 1) + 1]);
+    }
+    if (rc == LPGPU_OK && res->status == LPGPU_RUNNING) rc = lpgpu_dense_run(d, 0, res);   /* settles OPTIMAL / ITER_LIMIT */
+    if (rc == LPGPU_OK) rc = lpgpu_dense_download(d, T, ld, basis, plog, x);
+    if (d) lpgpu_dense_destroy(d);
+    free(cost);
+    return rc;
 }
 
 void newSimplex(LPModel *model) {
@@ -163,10 +249,13 @@ void newSimplex(LPModel *model) {
             if (pe && !strcmp(pe, "bland") && method != LPGPU_DUAL) o.variant |= LPGPU_VARIANT_BLAND;
         }
         o.log_cap = 16 * (m + n) + 64;
+        o.max_iter = pivot_cap(m, n);
         int *plog = (int *)calloc((size_t)o.log_cap * 2, sizeof(int));
         double *x = (double *)calloc((size_t)n, sizeof(double));
         lpgpu_result res;
-        rc = lpgpu_solve_dense(ctx, m, n, R, T, ld, basis, &o, plog, x, &res);
+        const char *pt = getenv("LPGPU_PRINT_TABLEAU");
+        if (pt && atoi(pt) > 0 && n <= PRINT_TABLEAU_MAX_COLS) rc = solve_with_tableau_print(ctx, &sm, m, n, n0, R, T, ld, basis, &o, plog, x, &res);
+        else rc = lpgpu_solve_dense(ctx, m, n, R, T, ld, basis, &o, plog, x, &res);
         if (rc != LPGPU_OK) {
             printf("ERROR: GPU solve failed (%d): %s\n", rc, lpgpu_last_error(ctx));
         } else {
@@ -181,6 +270,9 @@ void newSimplex(LPModel *model) {
                 printf(", row %d leaves\n", row + 1);
             }
             printf("\n> %s after %d iteration(s)\n", status_text(res.status), res.iters);
+            if (res.status == LPGPU_ITER_LIMIT)
+                printf("\tThe pivot cap of %d was reached (a degenerate model may cycle under largest-coefficient pricing):\n"
+                       "\ttry LPGPU_PRICING=bland, or raise the cap with LPGPU_MAX_ITER.\n", o.max_iter);
             if (res.status == LPGPU_OPTIMAL) {
                 const double zstd = res.z + constant;
                 printf("\t%s z = %.10g\n", sense == 1 ? "max" : "min", sense == 1 ? zstd : -zstd);

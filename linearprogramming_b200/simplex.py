@@ -324,7 +324,7 @@ class BatchedLPs:
         o = capi.default_opts(eps=eps, max_iter=int(min(max_iter, 2**31 - 1)), method=method, n_art=n_art,
                               log_cap=log_cap,
                               variant=(capi.KEEP_FINAL if keep_final else 0) | (capi.FORCE_SMEM if force_smem else 0) | variant)
-        self._log_cap = max(self._log_cap, log_cap)
+        self._log_cap = log_cap          # the library's stride / download length is this run's log_cap
         self._keep = keep_final
         ms = C.c_float(0.0)
         capi.check(self.ctx.handle, capi.lib().lpgpu_batched_run(self._h, C.byref(o), C.byref(ms) if timed else None),

@@ -90,5 +90,17 @@ def test_header_constants_match_the_ctypes_mirror():
     for name in ("OK", "EINVAL", "ENODEV", "ECUDA", "ENOMEM", "ENCCL", "OPTIMAL", "UNBOUNDED", "INFEASIBLE", "ITER_LIMIT",
                  "RUNNING", "PLAIN", "BIGM", "TWOPHASE", "DUAL"):
         assert defs[name] == getattr(capi, name), name
-    assert defs["VARIANT_BLAND"] == capi.BLAND
+    # every option bit of lpgpu_opts.variant is a #define of the header; capi.py reads them from there
+    for cname, hname in (("BLAND", "VARIANT_BLAND"), ("DEVEX", "VARIANT_DEVEX"), ("RANK1", "VARIANT_RANK1"), ("PIPELINED", "VARIANT_PIPELINED"),
+                         ("INPLACE", "VARIANT_INPLACE"), ("WHOLE_TILE_PASS", "VARIANT_WHOLE_TILE"), ("STEP_CL8", "VARIANT_STEP_CL8"),
+                         ("NO_PDL", "VARIANT_NO_PDL"), ("NO_ALTERNATE", "VARIANT_NO_ALTERNATE"), ("STATIC", "VARIANT_UPD_STATIC"),
+                         ("DIRECT", "VARIANT_UPD_DIRECT"), ("KEEP_FINAL", "VARIANT_BATCH_KEEP_FINAL"), ("FORCE_SMEM", "VARIANT_BATCH_SMEM")):
+        assert defs[hname] == getattr(capi, cname), cname
+    bits = [defs[h] for h in defs if h.startswith("VARIANT_") and not h.endswith("_MASK")]
+    assert len(set(bits)) == len(bits), "two option bits share a value"
+    assert capi.BLOCK_K(5) & defs["VARIANT_BLOCK_K_MASK"] == 5 << 16
+    # no magic variant numbers left in the product's host code
+    for f in ("dense.cu", "batched.cu", "shard.cu"):
+        text = open(os.path.join(ROOT, "linearprogramming_b200", "csrc", f)).read()
+        assert not re.search(r"variant\s*&\s*\(?0x", text), f
     assert defs["NCCL_ID_BYTES"] == capi.NCCL_ID_BYTES and defs["IPC_HANDLE_BYTES"] == capi.IPC_HANDLE_BYTES

@@ -208,13 +208,44 @@ def _blocked(K=0):
     return ((K % 100) << 16) | (capi.INPLACE if K >= 100 else capi.PIPELINED)
 
 
-@pytest.mark.parametrize("m,ns,K", [(64, 64, 0), (300, 500, 7), (512, 512, 32), (700, 1500, 0)])
-def test_blocked_warp_specialised_pass_bitwise(ctx, m, ns, K):
-    """The alternative pass kernel (producer warp + TMA ring, variant WS_PASS) leaves the same bits."""
-    T0, basis = O.synth_feasible(1234, 3, m, ns)
-    ref = O.solve_f64(T0, basis, threads=4, log_cap=8192)
-    got = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K) | capi.WS_PASS)
-    _assert_dense_equal(got, ref)
+def test_log_cap_shrinks_between_calls_no_overflow(ctx):
+    """the device log buffer only grows, the ACTIVE limit is this call's log_cap.  Same shape solved
+    twice on one context with a decreasing log_cap; the second pivot_log is guard padded and must keep its guard,
+    n_logged = min(iters, log_cap), and log_cap = 0 with a non-NULL pivot_log writes nothing."""
+    import ctypes as C
+    T0, basis0 = O.synth_feasible(1234, 3, 96, 96)
+    ref = O.solve_f64(T0, basis0, log_cap=4096)
+    assert ref["iters"] > 12
+    first = lp.solve_dense(ctx, T0, basis0, log_cap=1000)
+    assert first["n_logged"] == ref["iters"] and first["log"].tolist() == ref["log"].tolist()
+    for cap in (10, 0):
+        T = np.array(T0, order="C", copy=True)
+        basis = np.array(basis0, np.int32, copy=True)
+        guard = np.full((cap + 64, 2), -77, np.int32)
+        o = capi.default_opts(log_cap=cap)
+        res = capi.Result()
+        x = np.zeros(T.shape[1] - 1)
+        rc = capi.lib().lpgpu_solve_dense(ctx.handle, 96, 192, 1, T.ctypes.data_as(C.c_void_p), T.shape[1], basis.ctypes.data_as(C.c_void_p),
+                                          C.byref(o), guard.ctypes.data_as(C.c_void_p), x.ctypes.data_as(C.c_void_p), C.byref(res))
+        assert rc == 0 and res.iters == ref["iters"] and res.n_logged == min(ref["iters"], cap)
+        assert guard[:cap].tolist() == ref["log"][:cap].tolist()
+        assert (guard[cap:] == -77).all(), "pivot_log written beyond 2 * log_cap ints"
+        assert np.array_equal(T, ref["T"])
+    # batched handle API: the stride and the copy length follow this run's log_cap, not the largest one seen
+    Tb, bb = O.synth_feasible_batch(1234, 0, 64, 16, 16)
+    refb = O.solve_batched_f64(Tb, bb, log_cap=64)
+    bt = lp.BatchedLPs(ctx, 64, 16, 32)
+    bt.upload(Tb, bb)
+    for cap in (64, 4):
+        o = capi.default_opts(log_cap=cap)
+        rc = capi.lib().lpgpu_batched_run(bt._h, C.byref(o), None)
+        assert rc == 0
+        guard = np.full((64 * cap + 64, 2), -77, np.int32)
+        rc = capi.lib().lpgpu_batched_download(bt._h, None, None, None, None, None, guard.ctypes.data_as(C.c_void_p), None)
+        assert rc == 0
+        assert np.array_equal(guard[:64 * cap].reshape(64, cap, 2), refb["log"][:, :cap, :])
+        assert (guard[64 * cap:] == -77).all(), "batched pivot_log written beyond n_lp * 2 * log_cap ints"
+    bt.close()
 
 
 @pytest.mark.parametrize("m,ns", [(32, 32), (64, 64), (200, 120), (300, 500), (512, 512)])
@@ -775,6 +806,78 @@ def test_cfg4_full_size_pipelined_equals_inplace_bitwise(ctx):
     assert np.all(T[:m, 0] >= 0.0)
     sub = T[:, a["basis"]]
     assert np.array_equal(sub[:m], np.eye(m)) and np.all(sub[m] == 0.0)
+
+
+def test_cfg4_full_size_default_path_96_pivots_vs_oracle(ctx):
+    """BASELINE config 4 (8192 x 16384) on the DEFAULT path (pipelined blocks at this size), compared with the ORACLE:
+    96 pivots in two run calls of 40 + 56 -- three blocks of 32, the second left open and the first one's pass left
+    pending across the call boundary, both tableau buffers used -- then pivot log, basis and the whole tableau
+    bit for bit against O.solve_f64(max_iter = 96)."""
+    import os
+    m = ns = 8192
+    d = lp.DenseTableau(ctx, m, m + ns, 1)
+    d.synth(1234, 0, ns)
+    d.reset(log_cap=128)
+    r1 = d.run(40)
+    assert r1["iters"] == 40 and r1["status"] == lp.RUNNING
+    r2 = d.run(56)
+    assert r2["iters"] == 96 and r2["status"] == lp.RUNNING and r2["z"] >= r1["z"]
+    out = d.download()
+    d.close()
+    T0, basis0 = lp.synth_host(1234, 0, m, ns)
+    ref = O.solve_f64(T0, basis0, max_iter=96, threads=os.cpu_count() or 8, log_cap=128)
+    assert ref["iters"] == 96
+    assert out["log"][:96].tolist() == ref["log"].tolist()
+    assert np.array_equal(out["basis"], ref["basis"])
+    assert _same_bits(out["T"], ref["T"])
+    assert r2["z"] == ref["z"]
+
+
+def _golden_cfg4(name="cfg4_full_solve.json"):
+    import json
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name)
+    if not os.path.exists(path):
+        pytest.skip(f"{path} not generated (python oracle/gen_golden_cfg4.py)")
+    return json.load(open(path))
+
+
+def _check_against_golden(ctx, g, variant=0, window=None):
+    import hashlib
+    m = g["m"]
+    ns = g["n"] - m
+    d = lp.DenseTableau(ctx, m, m + ns, 1)
+    d.synth(g["seed"], g["lp"], ns)
+    d.reset(log_cap=g["iters"] + 64, variant=variant, check_every=256)
+    if window:
+        r = d.run(window)
+        while r["status"] == lp.RUNNING:
+            r = d.run(window)
+    else:
+        r = d.run(2**31 - 1)
+    out = d.download(want_T=False)
+    d.close()
+    assert lp.STATUS_NAMES[r["status"]] == g["status"] and r["iters"] == g["iters"]
+    log = np.ascontiguousarray(out["log"][:r["iters"]], np.int32)
+    for k, h in g["log_prefix_sha256"].items():
+        assert hashlib.sha256(log[:int(k)].tobytes()).hexdigest() == h, f"pivot log diverges from the oracle within the first {k} pivots"
+    assert hashlib.sha256(log.tobytes()).hexdigest() == g["log_sha256"]
+    assert out["basis"].tolist() == g["basis"]
+    assert float(r["z"]).hex() == g["z_hex"]
+    assert hashlib.sha256(np.ascontiguousarray(out["x"]).tobytes()).hexdigest() == g["x_sha256"]
+
+
+def test_cfg4_whole_solve_matches_golden(ctx):
+    """The WHOLE config-4 solve on the default path: status, iteration count, z (exact bits), final basis, x and the
+    SHA-256 of the pivot log equal the oracle's record in tests/golden/cfg4_full_solve.json (oracle/gen_golden_cfg4.py)."""
+    _check_against_golden(ctx, _golden_cfg4())
+
+
+@pytest.mark.parametrize("variant,window", [(0, None), (capi.PIPELINED, 37), (capi.INPLACE, None), (capi.RANK1, None)])
+def test_small_whole_solve_matches_golden(ctx, variant, window):
+    """The same check at m = 512 (tests/golden/cfg4_full_solve_m512.json) for every path, incl. pipelined blocks in run
+    calls of 37 pivots."""
+    _check_against_golden(ctx, _golden_cfg4("cfg4_full_solve_m512.json"), variant=variant, window=window)
 
 
 def test_dense_lookahead_is_dropped_across_upload_and_forced_pivot(ctx):

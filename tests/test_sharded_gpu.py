@@ -204,13 +204,15 @@ def test_sharded_p2p_world1_blocked_and_rank1_bigm(ctx, variant):
         assert res["zM"] == ref["zM"]
 
 
-def test_sharded_nccl_two_processes():
-    """One process per GPU (torchrun), NCCL and peer-memory transports, bit-compared with the oracle inside the script."""
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_sharded_real_peers(world):
+    """One process per GPU (torchrun) at world = 2 / 4 / 8, NCCL and peer-memory transports, plain / Big-M / two-phase /
+    Bland, every output bit-compared with the oracle inside the script (tests/sharded_parity.py)."""
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs two GPUs")
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
-           "127.0.0.1", "--master-port", "29631", os.path.join(ROOT, "tests", "mp_sharded_check.py")]
-    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
+           "127.0.0.1", "--master-port", str(29631 + world), os.path.join(ROOT, "tests", "mp_sharded_check.py")]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-3000:]
-    assert "sharded nccl ok" in p.stdout
+    assert "sharded parity ok" in p.stdout

@@ -71,14 +71,16 @@ extern "C" {
 #define LPGPU_VARIANT_UPD_STATIC    0x1        /* rank-1 path: TMA-staged elimination, static task stride (default: work stealing) */
 #define LPGPU_VARIANT_UPD_DIRECT    0x2        /* rank-1 path: direct-load elimination kernel                                      */
 #define LPGPU_VARIANT_UPD_MASK      0xf
+#define LPGPU_VARIANT_DFMA_PASS     0x100      /* blocked path: the pass with scalar DFMAs, software-pipelined in half tiles (default: DMMA) */
 #define LPGPU_VARIANT_NO_ALTERNATE  0x200      /* rank-1 path: do not alternate the sweep direction between pivots                 */
 #define LPGPU_VARIANT_NO_PDL        0x400      /* plain stream-ordered launches (default: programmatic dependent launch)           */
 #define LPGPU_VARIANT_RANK1         0x800      /* one pass over the tableau per pivot (default: one pass per block of pivots)      */
 #define LPGPU_VARIANT_PIPELINED     0x1000     /* blocked path: always pipeline the pass of a block with the next block's decisions */
 #define LPGPU_VARIANT_INPLACE       0x2000     /* blocked path: never pipeline (steps, pass, steps, ... on one stream, in place)    */
                                                /* neither bit: pipelined from about 0.4 GB of tableau on                           */
-#define LPGPU_VARIANT_WHOLE_TILE    0x4000     /* blocked path: the pass kernel that loads a whole tile before it computes         */
+#define LPGPU_VARIANT_WHOLE_TILE    0x4000     /* blocked path: scalar-DFMA pass that loads a whole tile before it computes          */
 #define LPGPU_VARIANT_STEP_CL8      0x8000     /* blocked path: step kernel as a portable 8-CTA cluster (default: 16 CTAs)         */
+#define LPGPU_VARIANT_STEP_LAUNCHES 0x40      /* pipelined blocks: one step-kernel launch per pivot (default: one persistent launch per block) */
 #define LPGPU_VARIANT_BLOCK_K(k)    (((k) & 0x3f) << 16)   /* blocked path: pivots per block, 1..32 (0 = 32)                       */
 #define LPGPU_VARIANT_BLOCK_K_MASK  0x3f0000
 #define LPGPU_VARIANT_BLAND         0x400000

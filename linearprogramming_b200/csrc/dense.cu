@@ -12,6 +12,8 @@
 #include "dense_internal.h"
 #include "dense_update.cuh"
 #include "dense_block.cuh"
+#include "dense_block_mma.cuh"
+#include "dense_steps.cuh"
 
 using namespace lpgpu;
 
@@ -300,7 +302,76 @@ static bool want_pipeline(const lpgpu_dense *d) {
     return ((size_t)d->m + d->R) * d->ld * sizeof(double) >= ((size_t)384 << 20);
 }
 
+typedef void (*steps_kernel_t)(DenseParams, BlockBufs, StepsArgs);
+static steps_kernel_t steps_kernel(int R, bool bland) {
+    return bland ? (R == 2 ? blk_steps_kernel<2, true> : blk_steps_kernel<1, true>) : (R == 2 ? blk_steps_kernel<2, false> : blk_steps_kernel<1, false>);
+}
+
+// The persistent step kernel of pipelined blocks: grid, partition, shared memory, exchange slots, and the SMs the grid lands on
+// while the device is idle (the pass leaves them free).  Unavailable (steps_state = -1) is not an error: the per-pivot launches
+// of blk_step_kernel are used instead.
+static int setup_steps(lpgpu_dense *d) {
+    if (d->steps_state != 0) return LPGPU_OK;
+    lpgpu_ctx *ctx = d->ctx;
+    d->steps_state = -1;
+    int G = 32;
+    { const char *e = getenv("LPGPU_STEP_CTAS"); if (e && atoi(e) > 0) G = atoi(e); }      // tuning aid
+    G = std::max(1, std::min(G, std::min(STEPS_GMAX, ctx->sm_count / 2)));
+    const int rpc = (int)((((size_t)d->m + G - 1) / G + 1) & ~(size_t)1);
+    const int cpc = (int)(((d->ld + G - 1) / G + 1) & ~(size_t)1);
+    const size_t budget = 200 * 1024, per_step = ((size_t)rpc + cpc) * sizeof(double);
+    const int S = (int)std::min<size_t>(BLK_KMAX, budget / per_step);
+    const size_t smem = (size_t)S * per_step;
+    cudaError_t e = cudaSuccess;
+    for (int R = 1; R <= 2 && e == cudaSuccess; ++R)
+        for (int bl = 0; bl <= 1 && e == cudaSuccess; ++bl)
+            e = cudaFuncSetAttribute(steps_kernel(R, bl != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(blk_steps_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int occ = 0;
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, steps_kernel(d->R, false), STEPS_TH, smem);
+    unsigned *smids = nullptr;
+    if (e == cudaSuccess && occ >= 1) e = cudaMalloc(&d->xch, 2 * STEPS_GMAX * sizeof(XSlot));
+    if (e == cudaSuccess && occ >= 1) e = cudaMemsetAsync(d->xch, 0, 2 * STEPS_GMAX * sizeof(XSlot), ctx->stream);
+    if (e == cudaSuccess && occ >= 1) e = cudaMalloc(&smids, STEPS_GMAX * sizeof(unsigned));
+    if (e != cudaSuccess || occ < 1) { cudaFree(smids); cudaFree(d->xch); d->xch = nullptr; cudaGetLastError(); return LPGPU_OK; }
+    LP_CUDA(ctx, cudaMemsetAsync(smids, 0xff, STEPS_GMAX * sizeof(unsigned), ctx->stream));
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (d->stream2) LP_CUDA(ctx, cudaStreamSynchronize(d->stream2));
+    blk_steps_probe_kernel<<<G, STEPS_TH, smem, ctx->stream>>>(smids);
+    LP_LAUNCH_CHECK(ctx);
+    unsigned h[STEPS_GMAX];
+    LP_CUDA(ctx, cudaMemcpyAsync(h, smids, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+    LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(smids);
+    for (unsigned &w : d->resv_steps) w = 0;
+    int distinct = 0;
+    if (!getenv("LPGPU_NO_RESERVE"))
+        for (int q = 0; q < G; ++q) {
+            const unsigned v = h[q];
+            if (v < 256u && !((d->resv_steps[v >> 5] >> (v & 31u)) & 1u)) { d->resv_steps[v >> 5] |= 1u << (v & 31u); ++distinct; }
+        }
+    if (distinct != G)
+        for (unsigned &w : d->resv_steps) w = 0;     // no reservation: still correct, the grid just starts when the pass has left room
+    d->steps_G = G; d->steps_rpc = rpc; d->steps_cpc = cpc; d->steps_S = S; d->steps_smem = smem;
+    d->xch_seq = 1;
+    d->steps_state = 1;
+    return LPGPU_OK;
+}
+
+static int launch_block_steps(lpgpu_dense *d, int nsteps, int first) {
+    lpgpu_ctx *ctx = d->ctx;
+    StepsArgs A;
+    A.xch = static_cast<XSlot *>(d->xch);
+    A.xbase = d->xch_seq;
+    d->xch_seq += 2u * (unsigned)nsteps + 4u;        // at most one pricing, two exchanges per pivot and one closing decision
+    A.nsteps = nsteps; A.first = first; A.smem_steps = d->steps_S; A.rpc = d->steps_rpc; A.cpc = d->steps_cpc;
+    steps_kernel(d->R, (d->opts.variant & LPGPU_VARIANT_BLAND) != 0)<<<d->steps_G, STEPS_TH, d->steps_smem, ctx->stream>>>(make_params(d), make_bufs(d), A);
+    LP_LAUNCH_CHECK(ctx);
+    return LPGPU_OK;
+}
+
 static void free_pipeline(lpgpu_dense *d) {
+    cudaFree(d->xch); d->xch = nullptr;
     cudaFree(d->T2); cudaFree(d->rowstamp2); cudaFree(d->steprow2); cudaFree(d->info); cudaFree(d->flush_flag);
     d->T2 = d->Ft2 = d->Pm2 = nullptr; d->rowstamp2 = d->steprow2 = nullptr; d->info = nullptr; d->flush_flag = nullptr;
     if (d->stream2) { cudaStreamDestroy(d->stream2); d->stream2 = nullptr; }
@@ -377,7 +448,7 @@ static int close_block_pipe(lpgpu_dense *d, cudaEvent_t ev0, cudaEvent_t ev1) {
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
     U.rb = d->fl_rb; U.pf = d->fl_pf;
     const bool full = d->grid_flush >= ctx->sm_count * 2;   // a full persistent grid: every SM holds CTAs of the pass
-    for (int w = 0; w < 8; ++w) U.resv[w] = full ? d->resv[w] : 0u;
+    for (int w = 0; w < 8; ++w) U.resv[w] = full ? (d->persist_on ? d->resv_steps[w] : d->resv[w]) : 0u;
     U.flag = d->flush_flag;
     U.l2first = (d->l2hint & 1) ? 1 : 0;
     LP_CUDA(ctx, cudaEventRecord(d->ev_steps, ctx->stream));
@@ -468,11 +539,13 @@ static int launch_block_step(lpgpu_dense *d, int first) {
     return LPGPU_OK;
 }
 
-// which pass kernel: variant bit 0x4000 = the one that loads a whole tile before it computes, else the software-pipelined default
+// which pass kernel: default = the DMMA pass (dense_block_mma.cuh); LPGPU_VARIANT_DFMA_PASS = scalar DFMAs, software-pipelined in half
+// tiles (round 1's default); LPGPU_VARIANT_WHOLE_TILE = scalar DFMAs, whole tile loaded before it computes
 static int launch_pass_kernel(lpgpu_dense *d, const FlushParams &U, cudaStream_t stream) {
     lpgpu_ctx *ctx = d->ctx;
     if (d->opts.variant & LPGPU_VARIANT_WHOLE_TILE) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
-    else blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
+    else if (d->opts.variant & LPGPU_VARIANT_DFMA_PASS) blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
+    else blk_flush_mma_kernel<<<d->grid_flush, FL_THREADS, MM_SMEM_BYTES, stream>>>(U);      // default: DMMA as the FMA engine
     LP_LAUNCH_CHECK(ctx);
     return LPGPU_OK;
 }
@@ -538,7 +611,10 @@ int size_grid(lpgpu_dense *d) {
     const long nrb = (d->m + d->R + UPD_TILE_ROWS - 1) / UPD_TILE_ROWS;
     d->grid_update = (int)std::max(1L, std::min((long)ctx->sm_count * occ, nct * nrb));
     int occf = 0;
-    LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_kernel, FL_THREADS, FL_SMEM_BYTES));
+    if (d->opts.variant & (LPGPU_VARIANT_WHOLE_TILE | LPGPU_VARIANT_DFMA_PASS))
+        LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, (d->opts.variant & LPGPU_VARIANT_WHOLE_TILE) ? blk_flush_kernel : blk_flush_sp_kernel, FL_THREADS, FL_SMEM_BYTES));
+    else
+        LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_mma_kernel, FL_THREADS, MM_SMEM_BYTES));
     const long fct = (long)((d->ld + FL_COLS - 1) / FL_COLS);
     const char *erb = getenv("LPGPU_FL_RB"), *epf = getenv("LPGPU_FL_PF");      // tuning aids
     d->fl_rb = (erb && atoi(erb) > 0) ? atoi(erb) : FL_RB;
@@ -574,6 +650,8 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     d->log = nullptr; d->log_cap = 0; d->log_alloc = 0; d->task_ctr = nullptr; d->upd_seq = 0;
     d->Ft = d->Pm = d->objcur = d->bcur = nullptr; d->rowstamp = d->steprow = nullptr; d->cands = nullptr; d->blk_open = false; d->blk_steps = 0;
     d->pipe_state = 0; d->pipe_on = false; d->pend = false; d->par = 0;
+    d->xch = nullptr; d->xch_seq = 1; d->steps_state = 0; d->steps_G = d->steps_rpc = d->steps_cpc = d->steps_S = 0; d->steps_smem = 0; d->persist_on = false;
+    for (unsigned &w : d->resv_steps) w = 0;
     d->up_stream = nullptr; d->ev_up = d->ev_up_ready = nullptr; d->up_pending = false;
     { const char *eh = getenv("LPGPU_L2HINT"); d->l2hint = eh ? atoi(eh) : 3; }
     d->T2 = d->Ft2 = d->Pm2 = nullptr; d->rowstamp2 = d->steprow2 = nullptr; d->info = nullptr; d->flush_flag = nullptr;
@@ -614,6 +692,8 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
         e = cudaFuncSetAttribute(blk_flush_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL_SMEM_BYTES);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(blk_flush_sp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL_SMEM_BYTES);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(blk_flush_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MM_SMEM_BYTES);
     if (e == cudaSuccess) e = cudaHostAlloc(&d->h_st, sizeof(PivotState), cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->T, 0, rows * d->ld * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->prow, 0, d->ld * sizeof(double), ctx->stream);
@@ -796,9 +876,18 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
             d->pipe_on = d->pipe_state == 1;
         }
         const bool pipe = d->pipe_on;
+        // pipelined blocks of the primal methods: one persistent launch decides all the pivots of a block (dense_steps.cuh);
+        // LPGPU_VARIANT_STEP_LAUNCHES keeps one launch of the step cluster per pivot
+        d->persist_on = false;
+        if (pipe && d->opts.method != LPGPU_DUAL && !(d->opts.variant & LPGPU_VARIANT_STEP_LAUNCHES)) {
+            rc = setup_steps(d);
+            if (rc != LPGPU_OK) return rc;
+            d->persist_on = d->steps_state == 1;
+        }
+        const bool persist = d->persist_on;
         if (dirty) { rc = launch_block_init(d); if (rc != LPGPU_OK) return rc; }
         std::vector<int> kinds;                 // timed mode: 0 = step, 1 = flush, in launch order
-        auto enqueue = [&](int kind, int first) -> int {
+        auto enqueue = [&](int kind, int first, int nsteps = 1) -> int {
             const size_t e = 2 * kinds.size();
             if (timed) {
                 while (d->ev.size() < e + 2) {
@@ -810,7 +899,7 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
             }
             int rc2;
             if (kind && pipe) { rc2 = close_block_pipe(d, timed ? d->ev[e] : nullptr, timed ? d->ev[e + 1] : nullptr); }
-            else rc2 = kind ? launch_block_flush(d) : launch_block_step(d, first);
+            else rc2 = kind ? launch_block_flush(d) : (persist ? launch_block_steps(d, nsteps, first) : launch_block_step(d, first));
             if (rc2 != LPGPU_OK) return rc2;
             if (timed) { if (!(kind && pipe)) LP_CUDA(ctx, cudaEventRecord(d->ev[e + 1], ctx->stream)); kinds.push_back(kind); }
             return LPGPU_OK;
@@ -857,11 +946,14 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
         if (d->h_st->phase == PH_DRIVEOUT) { rc = settle(); if (rc == LPGPU_OK) rc = driveout(); if (rc != LPGPU_OK) return rc; }
         while (launched < max_pivots && d->h_st->status == LPGPU_RUNNING) {
             const int chunk = std::min(chunk_max, max_pivots - launched);
-            for (int c = 0; c < chunk; ++c) {
-                rc = enqueue(0, d->blk_open ? 0 : 1);
+            for (int c = 0; c < chunk;) {
+                const int nst = persist ? std::min(chunk - c, K - d->blk_steps) : 1;     // persistent: all the pivots the block still has room for
+                rc = enqueue(0, d->blk_open ? 0 : 1, nst);
                 if (rc != LPGPU_OK) return rc;
                 d->blk_open = true;
-                if (++d->blk_steps >= K) { rc = flush(); if (rc != LPGPU_OK) return rc; }
+                d->blk_steps += nst;
+                c += nst;
+                if (d->blk_steps >= K) { rc = flush(); if (rc != LPGPU_OK) return rc; }
             }
             rc = read_state(d);
             if (rc == LPGPU_OK && timed) rc = collect();
@@ -884,7 +976,8 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
         if (!keep_pending) { rc = settle(); if (rc != LPGPU_OK) return rc; }
         if (d->h_st->status == LPGPU_RUNNING) {
             // decision only (budget is spent): settles a terminal status
-            rc = (d->h_st->phase == PH_DRIVEOUT) ? launch_select(d, -1, 0) : launch_block_step(d, d->blk_open ? 0 : 1);
+            rc = (d->h_st->phase == PH_DRIVEOUT) ? launch_select(d, -1, 0)
+                 : persist ? launch_block_steps(d, 0, d->blk_open ? 0 : 1) : launch_block_step(d, d->blk_open ? 0 : 1);
             if (rc != LPGPU_OK) return rc;
         }
         rc = read_state(d);
@@ -937,6 +1030,7 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
     if (d->R == 2)
         LP_CUDA(ctx, cudaMemcpyAsync(&zc[1], zsrc + d->ld, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (d->h_st->status == LPGPU_STEP_TIMEOUT) return fail(ctx, LPGPU_ECUDA, "dense_run: the CTAs of the persistent step kernel lost each other (exchange timeout)");
     res->status = d->h_st->status;
     res->iters = d->h_st->iters;
     res->phase1_iters = (d->opts.method == LPGPU_TWOPHASE) ? d->h_st->phase1_iters : 0;

@@ -51,6 +51,14 @@ struct lpgpu_dense {
     cudaStream_t stream2;
     cudaEvent_t ev_steps, ev_flush;
     unsigned resv[8];       // SMs left to the step kernels while a pass runs (bit per %smid)
+    // persistent step kernel (dense_steps.cuh): one launch of steps_G CTAs decides all the pivots of a block
+    void *xch;              // XSlot[2][STEPS_GMAX]: the CTAs' all-to-all through L2
+    unsigned xch_seq;       // next exchange sequence number (strictly increasing over the life of the object)
+    int steps_state;        // 0 = not set up yet, 1 = ready, -1 = unavailable
+    int steps_G, steps_rpc, steps_cpc, steps_S;
+    size_t steps_smem;
+    unsigned resv_steps[8]; // SMs that grid was placed on while the device was idle
+    bool persist_on;        // this run call uses it
     // lpgpu_dense_upload_async: copy stream, "copy done" / "tableau free" events
     cudaStream_t up_stream;
     cudaEvent_t ev_up, ev_up_ready;

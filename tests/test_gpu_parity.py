@@ -382,8 +382,9 @@ def test_pipelined_blocks_equal_inplace_blocks_and_oracle(ctx, m, ns, K):
     _assert_dense_equal(b, ref)
     assert _same_bits(a["T"], b["T"])
     # the step kernel as a cluster of 8 CTAs (default: 16 where the device places such clusters), and the pass kernel that
-    # loads a whole tile before it computes (default: software-pipelined halves)
-    for extra in (capi.STEP_CL8, capi.STEP_CL8 | capi.INPLACE, capi.WHOLE_TILE_PASS, capi.WHOLE_TILE_PASS | capi.INPLACE):
+    # loads a whole tile before it computes / the scalar-DFMA pass software-pipelined in halves (default: the DMMA pass)
+    for extra in (capi.STEP_CL8, capi.STEP_CL8 | capi.INPLACE, capi.WHOLE_TILE_PASS, capi.WHOLE_TILE_PASS | capi.INPLACE,
+                  capi.DFMA_PASS, capi.DFMA_PASS | capi.INPLACE):
         c = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K) | extra)
         _assert_dense_equal(c, ref)
 

@@ -189,7 +189,8 @@ int lpgpu_batched_download(lpgpu_batched *b, int *status, int *iters, double *z,
  * candidate each -- the arg-max over those picks the entering column -- and (b) the entering
  * column itself, from the rank that owns it; the ratio test then runs redundantly on every
  * rank, so no (ratio, row) exchange is needed in this layout.
- * Methods: LPGPU_PLAIN and LPGPU_BIGM.
+ * Methods: LPGPU_PLAIN and LPGPU_BIGM on every transport; LPGPU_TWOPHASE on the blocked path over the peer-memory
+ * transport (phase switch inside the step kernel, drive-out pivots as forced steps).  LPGPU_VARIANT_BLAND is honoured.
  *   id128 != NULL : one rank per process, exchange = ncclAllGather over NVLink (libnccl is
  *                   dlopen'ed here).  Rank 0 makes the id with lpgpu_shard_unique_id and the
  *                   host ships its 128 bytes to the other ranks by any means it has.

@@ -50,6 +50,8 @@ struct ShardParams {
     void *const *peer_x;     // world pointers: every rank's exchange region, own included
     unsigned iter;           // pipeline iteration, counted identically on every rank
     int post;                // 0: decide only, post nothing (the extra select that ends a run call)
+    int forced_r;            // blocked path, two-phase drive-out: >= 0 = pivot in THIS row on its lowest eligible (non-artificial,
+                             // |a| > eps) global column, found and agreed on inside the step kernel; -1 = the normal decision
 };
 
 constexpr unsigned long long XCHG_TIMEOUT_NS = 30ull * 1000 * 1000 * 1000;
@@ -116,7 +118,14 @@ __device__ __forceinline__ Cand best_pair(const double *pairs, int world, int *o
 __global__ void __launch_bounds__(SELECT_THREADS) shard_price_kernel(ShardParams S) {
     __shared__ Cand scratch[SELECT_THREADS / 32];
     const DenseParams &P = S.P;
-    Cand c = (P.method == LPGPU_BIGM) ? price_bigm(P, scratch) : price_row(P, P.m, P.n, scratch);
+    Cand c;
+    if (P.method == LPGPU_BIGM) c = price_bigm(P, scratch);
+    else if (P.method == LPGPU_TWOPHASE && P.st->phase == PH_ONE) c = price_row(P, P.m + 1, P.n, scratch);
+    else {
+        // main phase of the two-phase method: the artificial columns (the last n_art GLOBAL columns) are not priced
+        const int jmax = (P.method == LPGPU_TWOPHASE) ? max(0, min(P.n, S.n_global - S.n_art - S.col0 + 1)) : P.n;
+        c = price_row(P, P.m, jmax, scratch);
+    }
     if (threadIdx.x == 0) {
         store_pair(S.sendpair, c, S.col0);
         if (S.peer_x) post_pair(S);
@@ -287,10 +296,10 @@ shard_select_kernel(ShardParams S) {
             if (bigm) {
                 double p = __fma_rn(fm, pr, om[j]);
                 if (fabs(p) <= P.eps) p = 0.0;
-                t.p = p; t.q = q;
+                t.p = P.bland ? 0.0 : p; t.q = P.bland ? 1.0 : q;
                 if ((p > 0.0 || (p == 0.0 && q > P.eps)) && cand_better(t, c)) c = t;
             } else {
-                t.p = 0.0; t.q = q;
+                t.p = 0.0; t.q = P.bland ? 1.0 : q;
                 if (q > P.eps && cand_better(t, c)) c = t;
             }
         }
@@ -316,7 +325,13 @@ shard_select_kernel(ShardParams S) {
 // decisions from identical data, so no status has to be agreed on.
 constexpr int SSTEP_PB = 8, SSTEP_CPT = 2;
 
-template <int RR>
+// Two-phase (R = 2): phase one prices row m+1 over all columns, the main phase row m without the artificial columns (GLOBAL
+// column > n_global - n_art); when phase one prices nothing in anywhere the kernel checks the artificials (infeasible) or
+// sets the phase to drive-out and stops.  The drive-out pivots are forced steps (S.forced_r >= 0, one-step blocks on an
+// up-to-date tableau, host loop of shard_run_blocked): every rank offers the lowest eligible column of its slice of that
+// row, the lowest global column wins, its owner ships the column, and the row is pivoted without a ratio test.
+// BL: Bland's rule (every eligible column gets the same key; the lowest global column wins the exchange).
+template <int RR, bool BL>
 __global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
 shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
     __shared__ KeyCand scr_b[SELECT_THREADS / 32], scr_c[SELECT_THREADS / 32];
@@ -337,11 +352,38 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
     const double *oc = B.objcur, *om = B.objcur + P.ld;
     const size_t pcn = P.pcn;
     const int rows = P.m + RR;
+    const int phase0 = st->phase;
+    int phase = phase0, p1 = st->phase1_iters;
+    const bool forced = S.forced_r >= 0;
+    const int pmode = bigm ? PRICE_BIGM : (phase0 == PH_ONE ? PRICE_PHASE1 : PRICE_COST);
+    // local columns that may be priced: all of them, or (main phase of the two-phase method) the non-artificial ones
+    const int jmax = (P.method == LPGPU_TWOPHASE && phase0 != PH_ONE) ? max(0, min(P.n, S.n_global - S.n_art - S.col0 + 1)) : P.n;
     cluster_entry_wait();
 
     // ---- every rank's candidate of this pivot (posted at the end of the previous step or by the bootstrap)
     const unsigned pit = S.iter - 1u;
     const int ppar = (int)(pit & 1u);
+    if (forced && status0 == LPGPU_RUNNING) {
+        // drive-out: this rank's offer = the lowest non-artificial column of its slice of row forced_r with |a| > eps
+        // (the tableau is up to date: forced steps are one-step blocks).  Posted under the number the wait below expects.
+        __shared__ KeyCand scr_f[SELECT_THREADS / 32];
+        __shared__ KeyCand slot_f[SELECT_CLUSTER];
+        const int jreal = max(0, min(P.n, S.n_global - S.n_art - S.col0 + 1));
+        const double *xr = P.T + (size_t)S.forced_r * P.ld;
+        KeyCand c = keycand_none();
+        for (int j = 1 + gtid; j <= jreal; j += GSTRIDE)
+            if (fabs(xr[j]) > P.eps) { c.kp = 0; c.kq = 1; c.idx = j; break; }
+        c = cluster_key_best<false>(cl, c, scr_f, slot_f);          // equal keys: the lowest local column
+        if (gtid < 32) {
+            Cand out = cand_none();
+            if (c.idx > 0) { out.idx = c.idx; out.p = 0.0; out.q = 1.0; }
+            double v[PAIR_DOUBLES];
+            store_pair(v, out, S.col0);
+            ShardParams Sp = S;
+            Sp.iter = pit;
+            post_pair_lanes(Sp, v);
+        }
+    }
     {
         int ok = 1;
         if (threadIdx.x < (unsigned)S.world)
@@ -362,16 +404,22 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
 
     int status = status0, r = -1;
     bool have = false;
-    if (status0 == LPGPU_RUNNING) {
-        if (k == 0) {
-            // nothing prices in anywhere: optimal, unless Big-M left an artificial basic at a positive level
+    if (status0 == LPGPU_RUNNING && (forced || phase0 != PH_DRIVEOUT)) {
+        if (k == 0 && forced) {
+            // drive-out: no rank has an eligible entry in this row -- no pivot, the host tries the next artificial row
+        } else if (k == 0) {
+            // nothing prices in anywhere: optimal -- unless Big-M or phase one left an artificial basic at a positive level
+            // (infeasible), or phase one is over (drive-out next: forced steps from the host loop)
             int f = 0;
-            if (bigm) {
+            if (bigm || phase0 == PH_ONE) {
                 const int nreal = S.n_global - S.n_art;
                 for (int i = (int)threadIdx.x; i < P.m; i += blockDim.x)
                     if (P.basis[i] > nreal && B.bcur[i] > P.eps) f = 1;
             }
-            status = __syncthreads_or(f) ? LPGPU_INFEASIBLE : LPGPU_OPTIMAL;       // every CTA scans all rows: same answer
+            f = __syncthreads_or(f);                                               // every CTA scans all rows: same answer
+            if (f) status = LPGPU_INFEASIBLE;
+            else if (phase0 == PH_ONE) { phase = PH_DRIVEOUT; p1 = iters; }
+            else status = LPGPU_OPTIMAL;
         } else {
             // ---- the owner: column k as it stands after the t pivots of this block -> every rank's region
             if (mine) {
@@ -419,7 +467,10 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
                 }
             }
             c = cluster_key_best<false>(cl, c, scr_b, slot_b);
-            if (c.idx < 0) status = LPGPU_UNBOUNDED;
+            if (forced) {                                   // drive-out: the row is given, no ratio test
+                if (iters >= P.max_iter) status = LPGPU_ITER_LIMIT;
+                else if (budget > 0) { have = true; r = S.forced_r; }
+            } else if (c.idx < 0) status = LPGPU_UNBOUNDED;
             else if (iters >= P.max_iter) status = LPGPU_ITER_LIMIT;
             else if (budget > 0) { have = true; r = c.idx; }
         }
@@ -431,7 +482,9 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
             st->do_pivot = 0;
             st->blk_t = t;
             st->blk_seq = seq;
-            if (S.post) post_pair(S);                       // the same candidate again: peers expect one every iteration
+            st->phase = phase;
+            st->phase1_iters = p1;
+            if (S.post && !forced) post_pair(S);            // the same candidate again: peers expect one every iteration
         }
         return;
     }
@@ -507,7 +560,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
                     qm = __fma_rn(-sig_m, pr, omv[cth]);
                     B.objcur[P.ld + j] = qm;
                 }
-                blk_price(P, bigm ? PRICE_BIGM : PRICE_COST, (int)j, qc, qm, c);
+                if (j <= (size_t)jmax) blk_price<BL>(P, pmode, (int)j, qc, qm, c);
             }
         }
     }
@@ -515,16 +568,20 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
         B.bcur[i] = (i == r) ? brp : __fma_rn(-B.Fs[(size_t)t * pcn + i], brp, B.bcur[i]);
     // ---- this rank's candidate for the next pivot -> every rank
     c = bigm ? cluster_key_best<true>(cl, c, scr_c, slot_c) : cluster_key_best<false>(cl, c, scr_c, slot_c);
-    if (gtid < 32) {                                        // first warp of CTA 0: one lane per peer
-        Cand out = cand_none();
+    if (gtid < 32 && !forced) {                             // first warp of CTA 0: one lane per peer (a forced step posts nothing:
+        Cand out = cand_none();                             // the host re-prices once the drive-out is over)
         if (c.idx > 0) {
             out.idx = c.idx;
-            out.q = __ldcg(B.objcur + c.idx);               // written above, possibly by another CTA
             out.p = 0.0;
-            if (bigm) {
-                double p = __ldcg(B.objcur + P.ld + c.idx);
-                if (fabs(p) <= P.eps) p = 0.0;
-                out.p = p;
+            if (BL) out.q = 1.0;                            // Bland: equal keys, the lowest global column wins the exchange
+            else if (pmode == PRICE_PHASE1) out.q = __ldcg(B.objcur + P.ld + c.idx);
+            else {
+                out.q = __ldcg(B.objcur + c.idx);           // written above, possibly by another CTA
+                if (bigm) {
+                    double p = __ldcg(B.objcur + P.ld + c.idx);
+                    if (fabs(p) <= P.eps) p = 0.0;
+                    out.p = p;
+                }
             }
         }
         double v[PAIR_DOUBLES];
@@ -544,6 +601,8 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
         st->budget = budget - 1;
         st->blk_t = t + 1;
         st->blk_seq = seq;
+        st->phase = phase;
+        st->phase1_iters = (phase0 == PH_ONE) ? iters + 1 : p1;
         if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
     }
 }
@@ -600,6 +659,7 @@ struct lpgpu_shard {
     bool dirty;                       // tableau changed since the last lookahead (upload / synth / reset)
     bool blk_open;                    // blocked path: steps enqueued since the last pass over the tableau
     int blk_steps;
+    bool drv_active;                  // two-phase: the drive-out's forced steps are under way (exchange numbering, see shard_run_blocked)
     lpgpu_opts opts;
 };
 
@@ -623,7 +683,7 @@ ShardParams shard_params(const lpgpu_shard *s, const ShardRank &r) {
     S.P = make_params(r.d);
     S.rank = r.rank; S.world = s->world; S.col0 = r.col0; S.n_global = s->n; S.n_art = s->opts.n_art;
     S.sh = r.sh; S.sendpair = r.sendpair; S.pairs = r.pairs; S.sendcol = r.sendcol; S.gathered = r.gathered;
-    S.peer_x = s->use_p2p ? s->peer_dev : nullptr; S.iter = s->iter; S.post = 1;
+    S.peer_x = s->use_p2p ? s->peer_dev : nullptr; S.iter = s->iter; S.post = 1; S.forced_r = -1;
     return S;
 }
 
@@ -763,7 +823,7 @@ int shard_create_common(lpgpu_ctx *ctx, int rank, int world, int transport, cons
     s->ctx = ctx; s->world = world; s->m = m; s->n = n; s->R = R;
     s->use_nccl = transport == 1; s->use_p2p = transport == 2; s->attached = false; s->comm = nullptr;
     s->xregion = nullptr; s->peer_host = nullptr; s->peer_dev = nullptr; s->iter = 0;
-    s->pairs_buf = s->gath_buf = s->xbuf = nullptr; s->dirty = true; s->blk_open = false; s->blk_steps = 0;
+    s->pairs_buf = s->gath_buf = s->xbuf = nullptr; s->dirty = true; s->blk_open = false; s->blk_steps = 0; s->drv_active = false;
     lpgpu_default_opts(&s->opts);
     s->opts.method = (R == 1) ? LPGPU_PLAIN : LPGPU_BIGM;
     int rc = LPGPU_OK;
@@ -867,8 +927,9 @@ void lpgpu_shard_destroy(lpgpu_shard *s) {
 int lpgpu_shard_reset(lpgpu_shard *s, const lpgpu_opts *opts) {
     if (!s || !opts) return LPGPU_EINVAL;
     lpgpu_ctx *ctx = s->ctx;
-    if (opts->method == LPGPU_TWOPHASE) return fail(ctx, LPGPU_EINVAL, "shard_reset: the column-sharded path prices PLAIN and BIGM only");
-    if (opts->variant & LPGPU_VARIANT_BLAND) return fail(ctx, LPGPU_EINVAL, "shard_reset: Bland's rule is not built for the column-sharded path");
+    if (opts->method == LPGPU_DUAL) return fail(ctx, LPGPU_EINVAL, "shard_reset: the column-sharded path runs the primal methods");
+    if (opts->method == LPGPU_TWOPHASE && !(s->use_p2p && !(opts->variant & LPGPU_VARIANT_RANK1)))
+        return fail(ctx, LPGPU_EINVAL, "shard_reset: the two-phase method runs on the blocked path over the peer-memory transport (lpgpu_shard_create_p2p, no LPGPU_VARIANT_RANK1)");
     if ((opts->method == LPGPU_PLAIN) != (s->R == 1) || opts->n_art < 0 || opts->n_art > s->n)
         return fail(ctx, LPGPU_EINVAL, "shard_reset: bad options (method/R/n_art)");
     s->opts = *opts;
@@ -883,6 +944,7 @@ int lpgpu_shard_reset(lpgpu_shard *s, const lpgpu_opts *opts) {
     s->dirty = true;
     s->blk_open = false;
     s->blk_steps = 0;
+    s->drv_active = false;
     return LPGPU_OK;
 }
 
@@ -935,6 +997,8 @@ static int shard_finish(lpgpu_shard *s, lpgpu_result *res, int passes) {
     res->zM = (s->R == 2) ? -zc[1] : 0.0;
     res->n_logged = std::min(res->iters, d0->log_cap);
     res->update_launches = passes;
+    res->phase = d0->h_st->phase;
+    res->phase1_iters = (s->opts.method == LPGPU_TWOPHASE) ? d0->h_st->phase1_iters : 0;
     return LPGPU_OK;
 }
 
@@ -951,12 +1015,15 @@ static int shard_run_blocked(lpgpu_shard *s, int max_pivots, lpgpu_result *res) 
     st.cur = 0;
     if ((rc = push_state(s, st)) != LPGPU_OK) return rc;
     const int K = make_bufs(d).K;
-    auto step = [&](int post) -> int {
+    const bool bland = (s->opts.variant & LPGPU_VARIANT_BLAND) != 0;
+    auto step = [&](int post, int forced_r = -1) -> int {
         ShardParams S = shard_params(s, r);
         S.post = post;
+        S.forced_r = forced_r;
         const int first = s->blk_open ? 0 : 1;
-        if (s->R == 2) shard_blk_step_kernel<2><<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(S, make_bufs(d), first);
-        else shard_blk_step_kernel<1><<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(S, make_bufs(d), first);
+        auto kern = s->R == 2 ? (bland ? shard_blk_step_kernel<2, true> : shard_blk_step_kernel<2, false>)
+                              : (bland ? shard_blk_step_kernel<1, true> : shard_blk_step_kernel<1, false>);
+        kern<<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(S, make_bufs(d), first);
         LP_LAUNCH_CHECK(ctx);
         return LPGPU_OK;
     };
@@ -968,34 +1035,83 @@ static int shard_run_blocked(lpgpu_shard *s, int max_pivots, lpgpu_result *res) 
         ++passes;
         return rc2;
     };
-    if (s->dirty) {
-        // bootstrap: objective rows / b column out of the tableau, local pricing, candidate posted as iteration iter
-        if ((rc = launch_block_init(d)) != LPGPU_OK) return rc;
+    auto bootstrap = [&]() -> int {
+        // objective rows / b column out of the tableau, local pricing, candidate posted as iteration iter
+        int rc2 = launch_block_init(d);
+        if (rc2 != LPGPU_OK) return rc2;
         shard_price_kernel<<<1, SELECT_THREADS, 0, ctx->stream>>>(shard_params(s, r));
         LP_LAUNCH_CHECK(ctx);
         s->iter++;
         s->dirty = false;
         s->blk_open = false;
         s->blk_steps = 0;
-    }
-    const int chunk_max = s->opts.check_every;
+        return LPGPU_OK;
+    };
     int launched = 0;
-    while (launched < max_pivots) {
+    // Two-phase, between the phases: artificial variables still basic (at level zero) are driven out by FORCED steps -- the
+    // lowest such row that has an eligible entry, on its lowest non-artificial column -- one-step blocks on an up-to-date
+    // tableau, the offer / column exchange inside the step kernel.  The host loop is a replica on every rank (the basis is).
+    // Exchange numbering: a forced step posts its offers under the number BEFORE its own and nothing under its own, so one
+    // number is skipped on the way in and one on the way out; successive exchanges then keep alternating their slot parity.
+    auto driveout = [&]() -> int {
+        int rc2 = LPGPU_OK;
+        if (s->blk_open && (rc2 = flush()) != LPGPU_OK) return rc2;
+        if (!s->drv_active) { s->iter++; s->drv_active = true; }
+        std::vector<int> hb((size_t)s->m);
+        const int nreal = s->n - s->opts.n_art;
+        bool pivoted = true;
+        while (pivoted && launched < max_pivots && d->h_st->status == LPGPU_RUNNING) {
+            pivoted = false;
+            LP_CUDA(ctx, cudaMemcpyAsync(hb.data(), d->basis, hb.size() * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+            LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            for (int i = 0; i < s->m && !pivoted && d->h_st->status == LPGPU_RUNNING; ++i) {
+                if (hb[(size_t)i] <= nreal) continue;
+                const int before = d->h_st->iters;
+                if ((rc2 = step(0, i)) != LPGPU_OK) return rc2;
+                s->iter++;
+                s->blk_open = true;
+                if ((rc2 = flush()) != LPGPU_OK) return rc2;         // a one-step block (or nothing, if the row had no eligible entry)
+                if ((rc2 = read_state(d)) != LPGPU_OK) return rc2;
+                if (d->h_st->iters > before) { pivoted = true; ++launched; }
+            }
+        }
+        if (!pivoted && d->h_st->status == LPGPU_RUNNING) {
+            // no artificial row is left that can be pivoted on: the main phase starts (state is a replica: same write on every rank)
+            PivotState ns = *d->h_st;
+            ns.phase = PH_MAIN;
+            ns.budget = std::max(0, max_pivots - launched);
+            if ((rc2 = push_state(s, ns)) != LPGPU_OK) return rc2;
+            s->iter++;
+            s->drv_active = false;
+            s->dirty = true;
+        }
+        return LPGPU_OK;
+    };
+    if (d->h_st->status == LPGPU_RUNNING && d->h_st->phase == PH_DRIVEOUT && (rc = driveout()) != LPGPU_OK) return rc;
+    const int chunk_max = s->opts.check_every;
+    while (launched < max_pivots && d->h_st->status == LPGPU_RUNNING && d->h_st->phase != PH_DRIVEOUT) {
+        if (s->dirty && (rc = bootstrap()) != LPGPU_OK) return rc;
         const int chunk = std::min(chunk_max, max_pivots - launched);
+        const int before = d->h_st->iters;
         for (int c = 0; c < chunk; ++c) {
             if ((rc = step(1)) != LPGPU_OK) return rc;
             s->iter++;
             s->blk_open = true;
             if (++s->blk_steps >= K && (rc = flush()) != LPGPU_OK) return rc;
         }
-        launched += chunk;
         if ((rc = read_state(d)) != LPGPU_OK) return rc;
+        // steps after a phase switch (or a terminal status) were no-ops: only the applied pivots count
+        launched += (d->h_st->status == LPGPU_RUNNING && d->h_st->phase == PH_DRIVEOUT) ? d->h_st->iters - before : chunk;
         if (d->h_st->status != LPGPU_RUNNING) break;
+        if (d->h_st->phase == PH_DRIVEOUT && (rc = driveout()) != LPGPU_OK) return rc;
     }
     if (s->blk_open && (rc = flush()) != LPGPU_OK) return rc;
-    if (d->h_st->status == LPGPU_RUNNING) {
+    if (d->h_st->status == LPGPU_RUNNING && d->h_st->phase != PH_DRIVEOUT) {
         // budget spent: one decision-only step (same iteration, nothing posted) settles a terminal status
+        if (s->dirty && (rc = bootstrap()) != LPGPU_OK) return rc;
         if ((rc = step(0)) != LPGPU_OK) return rc;
+        if ((rc = read_state(d)) != LPGPU_OK) return rc;
+        // the decision may have ended phase one: nothing is pending then, the next run call starts with the drive-out
     }
     if ((rc = read_state(d)) != LPGPU_OK) return rc;
     return shard_finish(s, res, passes);

@@ -140,13 +140,73 @@ def test_sharded_equals_single_gpu_path_bitwise_midsize(ctx):
         assert np.array_equal(many["T"], one["T"]) and r2["z"] == r1["z"]
 
 
-def test_sharded_rejects_twophase_and_bad_shapes(ctx):
+def test_sharded_rejects_bad_shapes_and_twophase_off_the_blocked_path(ctx):
     with pytest.raises(lp.LpgpuError):
         lp.ShardedTableau(ctx, 4, 3, 1, world=4)             # more ranks than columns
-    s = lp.ShardedTableau(ctx, 4, 8, 2, world=2)
+    s = lp.ShardedTableau(ctx, 4, 8, 2, world=2)             # in-process ranks: the rank-1 pipeline, no two-phase there
     with pytest.raises(lp.LpgpuError):
         s.reset(method=lp.TWOPHASE, n_art=2)
     s.close()
+    s = lp.ShardedTableau(ctx, 4, 8, 1, world=1, rank=0, p2p=True)
+    with pytest.raises(lp.LpgpuError):
+        s.reset(method=lp.DUAL)
+    s.close()
+
+
+def _solve_p2p_world1(ctx, T, basis, method, n_art, variant=0, window=11, check_every=4):
+    R = 1 if method == O.PLAIN else 2
+    s = lp.ShardedTableau(ctx, T.shape[0] - R, T.shape[1] - 1, R, world=1, rank=0, p2p=True)
+    s.upload(T, basis)
+    s.reset(method=method, n_art=n_art, log_cap=8192, variant=variant, check_every=check_every)
+    while True:
+        res = s.run(window)
+        if res["status"] != lp.RUNNING:
+            break
+    out = s.download()
+    s.close()
+    res.update(T=out["T"], basis=out["basis"], log=out["log"][:res["n_logged"]], x=out["x"])
+    return res
+
+
+@pytest.mark.parametrize("variant", [0, 3 << 16])
+@pytest.mark.parametrize("seed", range(8))
+def test_sharded_p2p_world1_twophase(ctx, seed, variant):
+    """Two-phase method on the column-sharded blocked path (one rank over the peer-memory transport): phase switch inside
+    the step kernel, drive-out by forced steps from the host loop, main phase without the artificial columns; random
+    mixed-relation LPs incl. infeasible ones and redundant equality rows (artificials left basic at level zero, so the
+    drive-out has work), run calls of 11 and of 1 pivots.  Bit-exact against the oracle."""
+    rng = np.random.default_rng(4100 + seed)
+    m, ns = int(rng.integers(4, 40)), int(rng.integers(4, 40))
+    A, b, c, rel = H.random_mixed_lp(rng, m, ns)
+    if seed % 3 == 1:          # infeasible: a row against itself
+        A = np.vstack([A, A[0]]); b = np.append(b, b[0] - 5.0 if rel[0] != -2 else b[0] + 5.0)
+        rel = np.append(rel, -2 if rel[0] != -2 else 2).astype(np.int32)
+    if seed % 3 == 2:          # redundant equalities: duplicated rows, their artificials stay basic at zero
+        A = np.vstack([A, A[1], 2.0 * A[1]]); b = np.append(b, [b[1], 2.0 * b[1]])
+        rel = np.append(rel, [3, 3]).astype(np.int32); rel[1] = 3
+    T, basis, n_art = O.build_tableau(A, b, c, rel, R=2)
+    ref = O.solve_f64(T, basis, method=O.TWOPHASE, n_art=n_art, log_cap=8192)
+    for window in (11, 1):
+        got = _solve_p2p_world1(ctx, T, basis, O.TWOPHASE, n_art, variant=variant, window=window)
+        _assert_equal(got, ref)
+        assert got["phase1_iters"] == ref["phase1_iters"]
+
+
+@pytest.mark.parametrize("method", [O.PLAIN, O.BIGM, O.TWOPHASE])
+def test_sharded_p2p_world1_bland(ctx, method):
+    """Bland's rule on the column-sharded paths (blocked and rank-1 pipeline)."""
+    rng = np.random.default_rng(77)
+    if method == O.PLAIN:
+        T, basis = O.synth_feasible(1234, 5, 60, 44)
+        n_art = 0
+    else:
+        A, b, c, rel = H.random_mixed_lp(rng, 24, 30)
+        T, basis, n_art = O.build_tableau(A, b, c, rel, R=2)
+    ref = O.solve_f64(T, basis, method=method, n_art=n_art, log_cap=8192, pricing=O.BLAND)
+    variants = [capi.BLAND, capi.BLAND | (5 << 16)] + ([capi.BLAND | capi.RANK1] if method != O.TWOPHASE else [])
+    for variant in variants:
+        got = _solve_p2p_world1(ctx, T, basis, method, n_art, variant=variant)
+        _assert_equal(got, ref)
 
 
 def test_sharded_nccl_transport_world1(ctx):

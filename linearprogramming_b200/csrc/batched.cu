@@ -5,6 +5,7 @@
 
 #include "batched_kernels.cuh"
 #include "batched_reg.cuh"
+#include "batched_regx.cuh"
 #include "ctx.h"
 
 using namespace lpgpu;
@@ -150,33 +151,42 @@ int lpgpu_batched_run(lpgpu_batched *b, const lpgpu_opts *opts, float *kernel_ms
     B.basis_out = b->basis_out; B.log = opts->log_cap > 0 ? b->log : nullptr;
     B.T_final = want_final ? b->T_final : nullptr;
 
-    // Kernel choice.  Plain method on shapes that fit a register tile: the register-resident kernel
-    // (batched_reg.cuh); everything else (Big-M, two-phase, other shapes, LPGPU_VARIANT_BATCH_SMEM): the
-    // shared-memory kernel.  Grid = a whole number of resident CTAs per SM; each CTA walks LPs
+    // Kernel choice.  Shapes that fit a register tile run register-resident: the plain method through batched_reg_kernel,
+    // Big-M / two-phase / dual / Bland through batched_regx_kernel (batched_regx.cuh); other shapes and
+    // LPGPU_VARIANT_BATCH_SMEM: the shared-memory kernel.  Grid = a whole number of resident CTAs per SM; each CTA walks LPs
     // p = blockIdx, blockIdx + grid, ...
-    const bool plain = opts->method == LPGPU_PLAIN && b->R == 1 && !(opts->variant & (LPGPU_VARIANT_BATCH_SMEM | LPGPU_VARIANT_BLAND));
-    int kind = 0;
-    if (plain && b->m <= RegSmall::MAX_M && b->n <= RegSmall::MAX_N) kind = 1;
-    else if (plain && b->m <= RegWide::MAX_M && b->n <= RegWide::MAX_N) kind = 2;
-    int occ = 0;
-    size_t smem = 0;
+    const bool bland = (opts->variant & LPGPU_VARIANT_BLAND) != 0;
+    const bool force_smem = (opts->variant & LPGPU_VARIANT_BATCH_SMEM) != 0;
+    const bool plain = opts->method == LPGPU_PLAIN && b->R == 1 && !bland;
+    const int shape = force_smem ? 0 : (b->m <= RegSmall::MAX_M && b->n <= RegSmall::MAX_N) ? 1 : (b->m <= RegWide::MAX_M && b->n <= RegWide::MAX_N) ? 2 : 0;
+    typedef void (*bkernel_t)(BatchedParams);
+    bkernel_t kern = batched_simplex_kernel;
+    size_t smem = batched_smem_bytes(b->m, b->n, b->R);
     int threads = BATCH_THREADS;
-    if (kind == 1) {
-        smem = RegSmall::smem_bytes(b->m, b->n); threads = RegSmall::THREADS;
-        LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, batched_reg_kernel<1, 32, 2>, threads, smem));
-    } else if (kind == 2) {
-        smem = RegWide::smem_bytes(b->m, b->n); threads = RegWide::THREADS;
-        LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, batched_reg_kernel<4, 16, 4>, threads, smem));
-    } else {
-        smem = batched_smem_bytes(b->m, b->n, b->R);
-        LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, batched_simplex_kernel, threads, smem));
+    if (shape && plain) {
+        kern = shape == 1 ? (bkernel_t)batched_reg_kernel<1, 32, 2> : (bkernel_t)batched_reg_kernel<4, 16, 4>;
+    } else if (shape) {
+        const int mode = opts->method == LPGPU_DUAL ? 2 : (b->R == 2 ? 1 : 0);
+        if (shape == 1)
+            kern = mode == 2 ? (bkernel_t)batched_regx_kernel<1, 32, 2, 2, false>
+                 : mode == 1 ? (bland ? (bkernel_t)batched_regx_kernel<1, 32, 2, 1, true> : (bkernel_t)batched_regx_kernel<1, 32, 2, 1, false>)
+                             : (bkernel_t)batched_regx_kernel<1, 32, 2, 0, true>;
+        else
+            kern = mode == 2 ? (bkernel_t)batched_regx_kernel<4, 16, 4, 2, false>
+                 : mode == 1 ? (bland ? (bkernel_t)batched_regx_kernel<4, 16, 4, 1, true> : (bkernel_t)batched_regx_kernel<4, 16, 4, 1, false>)
+                             : (bkernel_t)batched_regx_kernel<4, 16, 4, 0, true>;
     }
+    if (shape) {
+        smem = shape == 1 ? RegSmall::smem_bytes(b->m + b->R - 1, b->n) : RegWide::smem_bytes(b->m + b->R - 1, b->n);     // staging window of (m+R) rows
+        threads = shape == 1 ? RegSmall::THREADS : RegWide::THREADS;
+    }
+    int occ = 0;
+    LP_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, smem));
     if (occ < 1) return fail(ctx, LPGPU_EINVAL, "batched_run: kernel does not fit (smem %zu B)", smem);
     const long grid = std::min(b->n_lp, (long)ctx->sm_count * occ);
     LP_CUDA(ctx, cudaEventRecord(b->e0, ctx->stream));
-    if (kind == 1) batched_reg_kernel<1, 32, 2><<<(unsigned)grid, threads, smem, ctx->stream>>>(B);
-    else if (kind == 2) batched_reg_kernel<4, 16, 4><<<(unsigned)grid, threads, smem, ctx->stream>>>(B);
-    else batched_simplex_kernel<<<(unsigned)grid, threads, smem, ctx->stream>>>(B);
+    kern<<<(unsigned)grid, threads, smem, ctx->stream>>>(B);
     LP_LAUNCH_CHECK(ctx);
     LP_CUDA(ctx, cudaEventRecord(b->e1, ctx->stream));
     if (kernel_ms) {

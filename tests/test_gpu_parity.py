@@ -743,6 +743,95 @@ def test_batched_bigm_twophase(ctx, method):
     assert set(np.unique(got["status"])) <= {lp.OPTIMAL, lp.UNBOUNDED, lp.INFEASIBLE}
 
 
+def _same_shape_batch(build, n_lp):
+    """Stack the LPs of a generator that share the shape of the first one."""
+    Ts, Bs, na = [], [], None
+    for p in range(n_lp):
+        T0, basis, n_art = build(p)
+        if Ts and (T0.shape != Ts[0].shape or n_art != na):
+            continue
+        na = n_art
+        Ts.append(T0); Bs.append(basis)
+    return np.stack(Ts), np.stack(Bs), na
+
+
+@pytest.mark.parametrize("shape", [(6, 5), (20, 24), (40, 50)])
+@pytest.mark.parametrize("method", [O.BIGM, O.TWOPHASE])
+@pytest.mark.parametrize("bland", [False, True])
+def test_batched_register_kernels_two_objective_rows(ctx, shape, method, bland):
+    """Big-M and two-phase through the register-resident kernels (batched_regx.cuh): one warp per LP (m <= 32, n <= 64) and
+    four warps per LP (m <= 64, n <= 128), random mixed-relation LPs incl. infeasible ones and redundant equality rows
+    (two-phase drive-out); bit-exact against the oracle, and against the shared-memory kernel (force_smem) incl. the final
+    tableaux and pivot logs.  Bland's rule as well."""
+    m, ns = shape
+    rng = np.random.default_rng(1000 * m + ns)
+
+    rel = np.array([(-2, 2, 3, -2)[i % 4] for i in range(m)], np.int32)       # the same relations in every LP: one shape
+    rel[0] = rel[1] = 3
+
+    def build(p):
+        A = rng.uniform(-0.5, 1.5, size=(m, ns))
+        x0 = rng.uniform(0.0, 2.0, size=ns)
+        ax = A @ x0
+        b = np.where(rel == -2, ax + rng.uniform(0.1, 2.0, m), np.where(rel == 2, ax - rng.uniform(0.1, 2.0, m), ax))
+        c = rng.uniform(-1.0, 1.0, ns)
+        if p % 4 == 1:      # infeasible: two equality rows that contradict each other
+            A[1] = A[0]; b[1] = b[0] + 3.0
+        if p % 4 == 2:      # redundant equality rows: an artificial stays basic at level zero (two-phase drive-out)
+            A[1] = A[0]; b[1] = b[0]
+        return O.build_tableau(A, b, c, rel, R=2)
+
+    T, B, n_art = _same_shape_batch(build, 96)
+    assert T.shape[0] >= 16 and T.shape[2] - 1 <= (64 if m <= 32 else 128)
+    pricing = O.BLAND if bland else 0
+    variant = capi.BLAND if bland else 0
+    ref = O.solve_batched_f64(T, B, method=method, n_art=n_art, max_iter=2000, threads=8, log_cap=64, pricing=pricing)
+    for force_smem in (False, True):
+        b = lp.BatchedLPs(ctx, T.shape[0], m, T.shape[2] - 1, 2)
+        b.upload(T, B)
+        b.run(method=method, n_art=n_art, max_iter=2000, log_cap=64, keep_final=True, force_smem=force_smem, variant=variant)
+        got = b.download(want_log=True, want_final=True)
+        b.close()
+        _assert_batched_equal(got, ref)
+        assert np.array_equal(got["log"], ref["log"])
+        # final tableaux: status OPTIMAL / INFEASIBLE leave a complete tableau behind
+        assert np.array_equal(got["T"], ref["T"])
+    assert len(set(np.unique(ref["status"]))) >= 2
+
+
+@pytest.mark.parametrize("shape", [(10, 12), (30, 34), (50, 60)])
+def test_batched_register_kernels_dual(ctx, shape):
+    """The dual simplex through the register-resident kernels, against the oracle and the shared-memory kernel."""
+    m, ns = shape
+    rng = np.random.default_rng(31 * m + ns)
+    pairs = [H.random_dual_lp(rng, m, ns, infeasible=(q % 7 == 3))[:2] for q in range(80)]
+    T = np.stack([a for a, _ in pairs]); B = np.stack([b for _, b in pairs])
+    ref = O.solve_batched_f64(T, B, method=O.DUAL, max_iter=4000, threads=8, log_cap=32)
+    for force_smem in (False, True):
+        b = lp.BatchedLPs(ctx, T.shape[0], m, T.shape[2] - 1, 1)
+        b.upload(T, B)
+        b.run(method=O.DUAL, max_iter=4000, log_cap=32, keep_final=True, force_smem=force_smem)
+        got = b.download(want_log=True, want_final=True)
+        b.close()
+        _assert_batched_equal(got, ref)
+        assert np.array_equal(got["log"], ref["log"]) and np.array_equal(got["T"], ref["T"])
+    assert lp.OPTIMAL in ref["status"]
+
+
+@pytest.mark.parametrize("m,ns", [(32, 32), (64, 64), (17, 40)])
+def test_batched_register_kernels_bland_plain(ctx, m, ns):
+    T, basis = O.synth_feasible_batch(5, 0, 128, m, ns)
+    ref = O.solve_batched_f64(T, basis, threads=8, pricing=O.BLAND, log_cap=16)
+    for force_smem in (False, True):
+        b = lp.BatchedLPs(ctx, 128, m, m + ns, 1)
+        b.upload(T, basis)
+        b.run(log_cap=16, keep_final=True, force_smem=force_smem, variant=capi.BLAND)
+        got = b.download(want_log=True, want_final=True)
+        b.close()
+        _assert_batched_equal(got, ref)
+        assert np.array_equal(got["log"], ref["log"]) and np.array_equal(got["T"], ref["T"])
+
+
 def test_batched_edge_cases(ctx):
     # empty batch
     out = lp.solve_batched(ctx, np.zeros((0, 4, 6)), np.zeros((0, 3), np.int32))

@@ -23,6 +23,7 @@ typedef struct {
     int *basis;
     double eps;
     int method, n_art, threads, pricing;
+    double *w;       /* pricing == 2: Devex reference weights, w[1..n] (>= 1 always) */
 } lpo_ctx;
 
 #define AT(c, i, j) ((c)->T[(size_t)(i) * (c)->ld + (size_t)(j)])
@@ -35,6 +36,13 @@ static int price_single(const lpo_ctx *c, int row, int jmax) {
     double bv = 0.0;
     for (int j = 1; j <= jmax; ++j) {
         double v = AT(c, row, j);
+        if (c->pricing == 2) {                   /* Devex: largest sigma_j^2 / w_j (one multiply, one division) */
+            if (v > c->eps) {
+                const double sc = (v * v) / c->w[j];
+                if (best == 0 || sc > bv) { best = j; bv = sc; }
+            }
+            continue;
+        }
         if (v > c->eps && (best == 0 || v > bv)) {
             best = j; bv = v;
             if (c->pricing == 1) break;          /* Bland: the lowest eligible column */
@@ -54,6 +62,10 @@ static int price_bigm(const lpo_ctx *c) {
         if (fabs(p) <= c->eps) p = 0.0;
         int eligible = (p > 0.0) || (p == 0.0 && q > c->eps);
         if (!eligible) continue;
+        if (c->pricing == 2) {                   /* Devex: both levels scaled by the weight; below an M part the cost breaks ties as it is */
+            q = (p == 0.0) ? (q * q) / c->w[j] : q;
+            p = (p * p) / c->w[j];
+        }
         if (best == 0 || p > bp || (p == bp && q > bq)) { best = j; bp = p; bq = q; }
         if (c->pricing == 1) break;              /* Bland: the lowest eligible column */
     }
@@ -122,6 +134,23 @@ void lpo_pivot_f64(int rows, int n, double *T, size_t ld, int r, int k, int thre
     free(pcol);
 }
 
+/* Devex reference-framework weights (Forrest & Goldfarb; pricing == 2).  All weights start at 1.  After the pivot on
+ * (r, k), with a_rj' the scaled pivot row:  w_j <- max(w_j, (a_rj' * a_rj') * w_k)  for every column j != k (two rounded
+ * multiplies, in this order), then  w_k <- 1  (the entering column joins the basis; when it leaves again the rule above gives
+ * it max(1, w_q / a_rq^2), Devex's weight of the leaving variable).  Every pivot of a primal method updates them, the
+ * drive-out pivots between the phases too; the weights are NOT reset at the phase switch. */
+static void devex_update(lpo_ctx *c, int r, int k) {
+    const double wk = c->w[k];
+    for (int j = 1; j <= c->n; ++j) {
+        if (j == k) continue;
+        const double pr = AT(c, r, j);
+        const double t = pr * pr;
+        const double u = t * wk;
+        if (u > c->w[j]) c->w[j] = u;
+    }
+    c->w[k] = 1.0;
+}
+
 static int art_basic_positive(const lpo_ctx *c) {
     for (int i = 0; i < c->m; ++i)
         if (c->basis[i] > c->n - c->n_art && AT(c, i, 0) > c->eps) return 1;
@@ -146,9 +175,14 @@ int lpo_solve_f64(int m, int n, int R, double *T, size_t ld, int *basis,
     if (ld < (size_t)n + 1) return -1;
     if ((opts->method == LPO_PLAIN || opts->method == LPO_DUAL) != (R == 1)) return -1;
     if (opts->n_art < 0 || opts->n_art > n) return -1;
-    if (opts->pricing != 0 && (opts->pricing != 1 || opts->method == LPO_DUAL)) return -1;
+    if (opts->pricing != 0 && ((opts->pricing != 1 && opts->pricing != 2) || opts->method == LPO_DUAL)) return -1;
     lpo_ctx c = { m, n, R, T, ld, basis, opts->eps, opts->method, opts->n_art,
-                  opts->threads > 0 ? opts->threads : 1, opts->pricing };
+                  opts->threads > 0 ? opts->threads : 1, opts->pricing, NULL };
+    if (c.pricing == 2) {
+        c.w = (double *)malloc(sizeof(double) * (size_t)(n + 1));
+        if (!c.w) return -1;
+        for (int j = 0; j <= n; ++j) c.w[j] = 1.0;
+    }
     int phase = (opts->method == LPO_TWOPHASE) ? LPO_PH_ONE : LPO_PH_MAIN;
     int status = LPO_RUNNING, iters = 0, p1 = 0;
     while (status == LPO_RUNNING) {
@@ -180,11 +214,13 @@ int lpo_solve_f64(int m, int n, int R, double *T, size_t ld, int *basis,
         }
         if (iters >= opts->max_iter) { status = LPO_ITER_LIMIT; break; }
         lpo_pivot_f64(m + R, n, T, ld, r, k, c.threads);
+        if (c.pricing == 2) devex_update(&c, r, k);
         basis[r] = k;
         if (pivot_log && iters < log_cap) { pivot_log[2 * iters] = k; pivot_log[2 * iters + 1] = r; }
         ++iters;
     }
     if (phase == LPO_PH_ONE) p1 = iters;
+    free(c.w);
     res->status = status;
     res->iters = iters;
     res->phase1_iters = (opts->method == LPO_TWOPHASE) ? p1 : 0;

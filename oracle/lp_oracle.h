@@ -52,6 +52,8 @@ typedef struct {
     int threads;     /* OpenMP threads for the elimination (results do not depend)   */
     int pricing;     /* 0 = largest reduced cost, ties -> lowest column (Dantzig);
                       * 1 = Bland: the LOWEST eligible column (with the lowest-row ratio tie-break: no cycling).
+                      * 2 = Devex: largest sigma_j^2 / w_j over the eligible columns, ties -> lowest column; reference
+                      *     weights w_j as devex_update() in lp_oracle.c maintains them.
                       * fp64 primal methods only (the reference prices nothing)  */
 } lpo_opts;
 

@@ -17,7 +17,7 @@ PLAIN, BIGM, TWOPHASE, DUAL = 0, 1, 2, 3
 STATUS_NAMES = ["OPTIMAL", "UNBOUNDED", "INFEASIBLE", "ITER_LIMIT", "RUNNING", "OVERFLOW"]
 
 
-DANTZIG, BLAND = 0, 1          # lpo_opts.pricing
+DANTZIG, BLAND, DEVEX = 0, 1, 2          # lpo_opts.pricing
 
 
 class Opts(C.Structure):

@@ -372,3 +372,75 @@ def test_bland_pricing_reaches_the_same_optimum(seed):
     T, basis = O.synth_feasible(1234, seed, 10, 8)
     bl = O.solve_f64(T, basis, pricing=O.BLAND, log_cap=8)
     assert bl["log"][0][0] == 1 + int(np.argmax(T[10, 1:] > 1e-9))
+
+
+# ------------------------------------------------------------------ pricing option: Devex reference weights
+def _devex_replay(T0, basis0, log, method=O.PLAIN, n_art=0, eps=1e-9):
+    """numpy restatement of the Devex rule: replays the oracle's pivot log and checks that every entering column is the arg-max
+    of sigma_j^2 / w_j under the weight recurrence of devex_update() (lp_oracle.c)."""
+    T = np.array(T0, dtype=np.float64)
+    R = 1 if method == O.PLAIN else 2
+    m, n = T.shape[0] - R, T.shape[1] - 1
+    w = np.ones(n + 1)
+    for k, r in log:
+        sig = T[m]
+        elig = sig[1:] > eps
+        assert elig[k - 1]
+        score = np.where(elig, (sig[1:] * sig[1:]) / w[1:], -1.0)
+        assert int(np.argmax(score)) + 1 == k
+        T = O.pivot(T, r, k)
+        pr = T[r]
+        upd = (pr * pr) * w[k]
+        keep = w[k]
+        w = np.maximum(w, upd)
+        w[k] = 1.0
+        del keep
+    return T
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_devex_pricing_follows_its_recurrence_and_reaches_the_optimum(seed):
+    T, basis = O.synth_feasible(77, seed, 24, 30)
+    d = O.solve_f64(T, basis)
+    dx = O.solve_f64(T, basis, pricing=O.DEVEX)
+    assert d["status"] == dx["status"] == O.OPTIMAL
+    assert abs(d["z"] - dx["z"]) <= 1e-9 * max(1.0, abs(d["z"]))
+    Tend = _devex_replay(T, basis, dx["log"].tolist())
+    assert np.array_equal(Tend, dx["T"])
+    assert dx["log"].tolist() != d["log"].tolist()[:len(dx["log"])] or dx["iters"] == d["iters"]
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_devex_pricing_bigm_twophase_same_optimum(seed):
+    rng = np.random.default_rng(1900 + seed)
+    A, b, c, rel = H.random_mixed_lp(rng, 12, 10)
+    for method, R in ((O.BIGM, 2), (O.TWOPHASE, 2)):
+        T, basis, n_art = O.build_tableau(A, b, c, rel, R=R)
+        d = O.solve_f64(T, basis, method=method, n_art=n_art, max_iter=5000)
+        dx = O.solve_f64(T, basis, method=method, n_art=n_art, max_iter=5000, pricing=O.DEVEX)
+        assert dx["status"] == d["status"]
+        if d["status"] == O.OPTIMAL:
+            assert abs(dx["z"] - d["z"]) <= 1e-7 * max(1.0, abs(d["z"]))
+
+
+def test_devex_needs_fewer_pivots_on_badly_scaled_columns():
+    """The largest-coefficient rule depends on the scale of each column, Devex (approximately) does not: with the structural
+    columns of the synthetic family scaled by powers of two between 2^-6 and 2^6 it needs well under half the pivots."""
+    tot_d = tot_x = 0
+    for lp in range(6):
+        T, basis = O.synth_feasible(4321, lp, 96, 128)
+        T[:, 1:129] *= 2.0 ** np.random.default_rng(lp).integers(-6, 7, size=128)
+        d, x = O.solve_f64(T, basis), O.solve_f64(T, basis, pricing=O.DEVEX)
+        assert d["status"] == x["status"] == O.OPTIMAL and abs(d["z"] - x["z"]) <= 1e-9 * abs(d["z"])
+        tot_d += d["iters"]
+        tot_x += x["iters"]
+    assert 2 * tot_x < tot_d
+
+
+def test_devex_rejected_for_dual():
+    T, basis = O.synth_feasible(1, 0, 4, 4)
+    res = O.Result()
+    opts = O.Opts(1e-9, 10, O.DUAL, 0, 1, O.DEVEX)
+    import ctypes as C
+    rc = O.lib().lpo_solve_f64(4, 8, 1, O._dp(T.copy()), 9, O._ip(basis.copy()), C.byref(opts), None, 0, C.byref(res))
+    assert rc == -1

@@ -166,6 +166,21 @@ int lpgpu_dense_pivot(lpgpu_dense *d, int r, int k);
 int lpgpu_dense_download(lpgpu_dense *d, double *T, size_t ld, int *basis, int *pivot_log, double *x);
 size_t lpgpu_dense_ld(const lpgpu_dense *d);           /* device leading dimension (doubles) */
 
+/* One forced pivot on a CALLER-OWNED device tableau, allocating nothing: no cudaMalloc, cudaFree or allocating library
+ * routine is called, now or at first use.  No counterpart in the reference; added
+ * for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid it).  The
+ * allocation-free variant of lpgpu_dense_pivot: the staged pivot column and scaled pivot row live in one fixed device
+ * array inside the library (LPGPU_NOALLOC_MAX_ROWS + LPGPU_NOALLOC_MAX_COLS doubles = 1.25 MB per GPU that loads it).
+ *   T_dev   device pointer, rows x ncols doubles with leading dimension ld >= ncols: the tableau with its objective
+ *           row(s) (rows = m + R) and the b column (ncols = n + 1); updated in place, same bits as lpgpu_dense_pivot
+ *   r, k    pivot row (0 <= r < rows) and tableau column (1 <= k < ncols)
+ * Shapes beyond the maxima are rejected with LPGPU_EINVAL (lpgpu_last_error says so).  The two kernels are enqueued on the
+ * context's stream; the call does not wait for them (lpgpu_sync).  Every call on a GPU shares the array: calls that
+ * overlap on the GPU (two contexts / streams on one device) race -- keep them in one stream or order them.         */
+#define LPGPU_NOALLOC_MAX_ROWS 32768
+#define LPGPU_NOALLOC_MAX_COLS 131072
+int lpgpu_pivot_noalloc(lpgpu_ctx *ctx, double *T_dev, size_t ld, int rows, int ncols, int r, int k);
+
 /* ---- many small tableaux: one LP per CTA, resident in shared memory ---------------- */
 /* T_all: n_lp tableaux back to back, each (m+R) x (n+1), ld = n+1.  Outputs may be NULL
  * except status.  pivot_log: n_lp * 2*log_cap ints.  T_all is not modified. */

@@ -96,6 +96,7 @@ SIGNATURES = {
     "lpgpu_dense_pivot": (C.c_int, [_vp, C.c_int, C.c_int]),
     "lpgpu_dense_download": (C.c_int, [_vp, _vp, C.c_size_t, _vp, _vp, _vp]),
     "lpgpu_dense_ld": (C.c_size_t, [_vp]),
+    "lpgpu_pivot_noalloc": (C.c_int, [_vp, _vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int]),
     "lpgpu_solve_batched": (C.c_int, [_vp, C.c_long, C.c_int, C.c_int, C.c_int, _vp, _vp, C.POINTER(Opts), _vp, _vp,
                                       _vp, _vp, _vp, _vp]),
     "lpgpu_batched_create": (C.c_int, [_vp, C.c_long, C.c_int, C.c_int, C.c_int, C.POINTER(_vp)]),

@@ -65,13 +65,15 @@ extern "C" {
  *           the lowest-row tie-break of the ratio test it cannot cycle (Beale's example runs into the iteration
  *           limit under the default rule).  LPGPU_EINVAL for the dual simplex.  SURVEY.md 8 (f4): the reference has
  *           no pricing at all (Source/simplex.c:57-63).
- *   DEVEX   reference-framework pricing: sigma_j^2 / w_j is maximised, the weights w_j follow Devex's update
- *           (DESIGN.md section 3); dense path and batched shared-memory kernel, primal methods.
+ *   DEVEX   reference-framework pricing: sigma_j^2 / w_j is maximised over the eligible columns, the weights w_j (all 1
+ *           after lpgpu_dense_reset) follow Devex's update from every pivot's scaled row.  Dense
+ *           path (rank-1, blocked, pipelined) and the batched shared-memory kernel; primal methods; LPGPU_EINVAL for the
+ *           dual simplex, together with BLAND, and on the column-sharded path.
  * Dense path, which kernels run (all bit-identical):                                        */
 #define LPGPU_VARIANT_UPD_STATIC    0x1        /* rank-1 path: TMA-staged elimination, static task stride (default: work stealing) */
 #define LPGPU_VARIANT_UPD_DIRECT    0x2        /* rank-1 path: direct-load elimination kernel                                      */
 #define LPGPU_VARIANT_UPD_MASK      0xf
-#define LPGPU_VARIANT_DFMA_PASS     0x100      /* blocked path: the pass with scalar DFMAs, software-pipelined in half tiles (default: DMMA) */
+#define LPGPU_VARIANT_DMMA_PASS     0x100      /* blocked path: the pass with the FP64 matrix instruction as the FMA chain (default: scalar DFMAs, measured faster) */
 #define LPGPU_VARIANT_NO_ALTERNATE  0x200      /* rank-1 path: do not alternate the sweep direction between pivots                 */
 #define LPGPU_VARIANT_NO_PDL        0x400      /* plain stream-ordered launches (default: programmatic dependent launch)           */
 #define LPGPU_VARIANT_RANK1         0x800      /* one pass over the tableau per pivot (default: one pass per block of pivots)      */
@@ -80,7 +82,7 @@ extern "C" {
                                                /* neither bit: pipelined from about 0.4 GB of tableau on                           */
 #define LPGPU_VARIANT_WHOLE_TILE    0x4000     /* blocked path: scalar-DFMA pass that loads a whole tile before it computes          */
 #define LPGPU_VARIANT_STEP_CL8      0x8000     /* blocked path: step kernel as a portable 8-CTA cluster (default: 16 CTAs)         */
-#define LPGPU_VARIANT_STEP_LAUNCHES 0x40      /* pipelined blocks: one step-kernel launch per pivot (default: one persistent launch per block) */
+#define LPGPU_VARIANT_STEP_PERSISTENT 0x40    /* pipelined blocks: one persistent step-kernel launch per block (default: one cluster launch per pivot, measured faster) */
 #define LPGPU_VARIANT_BLOCK_K(k)    (((k) & 0x3f) << 16)   /* blocked path: pivots per block, 1..32 (0 = 32)                       */
 #define LPGPU_VARIANT_BLOCK_K_MASK  0x3f0000
 #define LPGPU_VARIANT_BLAND         0x400000

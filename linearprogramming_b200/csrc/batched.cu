@@ -35,7 +35,8 @@ bool batched_opts_ok(const lpgpu_opts *o, int n, int R) {
     if (o->method != LPGPU_PLAIN && o->method != LPGPU_BIGM && o->method != LPGPU_TWOPHASE && o->method != LPGPU_DUAL) return false;
     if ((o->method == LPGPU_PLAIN || o->method == LPGPU_DUAL) != (R == 1)) return false;
     if (o->n_art < 0 || o->n_art > n || o->max_iter < 0 || o->log_cap < 0 || !(o->eps >= 0.0)) return false;
-    if ((o->variant & LPGPU_VARIANT_BLAND) && o->method == LPGPU_DUAL) return false;      // Bland's rule: primal methods (include/lpgpu.h)
+    if ((o->variant & (LPGPU_VARIANT_BLAND | LPGPU_VARIANT_DEVEX)) && o->method == LPGPU_DUAL) return false;      // pricing rules: primal methods (include/lpgpu.h)
+    if ((o->variant & LPGPU_VARIANT_BLAND) && (o->variant & LPGPU_VARIANT_DEVEX)) return false;
     return true;
 }
 
@@ -146,7 +147,8 @@ int lpgpu_batched_run(lpgpu_batched *b, const lpgpu_opts *opts, float *kernel_ms
     BatchedParams B;
     B.T_all = b->T_all; B.basis_all = b->basis_all; B.n_lp = b->n_lp; B.m = b->m; B.n = b->n; B.R = b->R;
     B.eps = opts->eps; B.max_iter = opts->max_iter; B.method = opts->method; B.n_art = opts->n_art;
-    B.bland = (opts->variant & LPGPU_VARIANT_BLAND) ? 1 : 0;       // Bland's rule: through the shared-memory kernel (decide())
+    B.bland = (opts->variant & LPGPU_VARIANT_BLAND) ? 1 : 0;
+    B.devex = (opts->variant & LPGPU_VARIANT_DEVEX) ? 1 : 0;       // Devex: the shared-memory kernel keeps the weights next to the tableau
     B.log_cap = b->log_cap; B.status = b->status; B.iters = b->iters; B.z = b->z; B.x = b->x;
     B.basis_out = b->basis_out; B.log = opts->log_cap > 0 ? b->log : nullptr;
     B.T_final = want_final ? b->T_final : nullptr;
@@ -156,7 +158,7 @@ int lpgpu_batched_run(lpgpu_batched *b, const lpgpu_opts *opts, float *kernel_ms
     // LPGPU_VARIANT_BATCH_SMEM: the shared-memory kernel.  Grid = a whole number of resident CTAs per SM; each CTA walks LPs
     // p = blockIdx, blockIdx + grid, ...
     const bool bland = (opts->variant & LPGPU_VARIANT_BLAND) != 0;
-    const bool force_smem = (opts->variant & LPGPU_VARIANT_BATCH_SMEM) != 0;
+    const bool force_smem = (opts->variant & (LPGPU_VARIANT_BATCH_SMEM | LPGPU_VARIANT_DEVEX)) != 0;
     const bool plain = opts->method == LPGPU_PLAIN && b->R == 1 && !bland;
     const int shape = force_smem ? 0 : (b->m <= RegSmall::MAX_M && b->n <= RegSmall::MAX_N) ? 1 : (b->m <= RegWide::MAX_M && b->n <= RegWide::MAX_N) ? 2 : 0;
     typedef void (*bkernel_t)(BatchedParams);

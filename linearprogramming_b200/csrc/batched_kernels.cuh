@@ -24,6 +24,7 @@ struct BatchedParams {
     int m, n, R;
     double eps;
     int max_iter, method, n_art, bland;
+    int devex;             // 1: Devex reference weights (kept in shared memory; oracle pricing == 2)
     int log_cap;
     int *status, *iters;   // n_lp
     double *z;             // n_lp (may be null)
@@ -42,6 +43,7 @@ __host__ __device__ inline size_t batched_smem_bytes(int m, int n, int R) {
     b = (b + 15) / 16 * 16;
     b += ((size_t)n + 2) * sizeof(double);           // scaled pivot row
     b += ((size_t)m + R + 1) * sizeof(double);       // pivot column
+    b += ((size_t)n + 2) * sizeof(double);           // Devex reference weights
     b += (size_t)(BATCH_THREADS / 32) * sizeof(Cand);
     b += (size_t)m * sizeof(int);                    // basis
     return (b + 15) / 16 * 16;
@@ -59,6 +61,8 @@ __global__ void __launch_bounds__(BATCH_THREADS) batched_simplex_kernel(BatchedP
     off += ((size_t)n + 2) * sizeof(double);
     double *pcol = reinterpret_cast<double *>(smem_raw + off);
     off += ((size_t)rows + 1) * sizeof(double);
+    double *wts = reinterpret_cast<double *>(smem_raw + off);
+    off += ((size_t)n + 2) * sizeof(double);
     Cand *scratch = reinterpret_cast<Cand *>(smem_raw + off);
     off += (size_t)(BATCH_THREADS / 32) * sizeof(Cand);
     int *basis = reinterpret_cast<int *>(smem_raw + off);
@@ -84,6 +88,7 @@ __global__ void __launch_bounds__(BATCH_THREADS) batched_simplex_kernel(BatchedP
             tma_load_1d(tab_raw, reinterpret_cast<const unsigned char *>(B.T_all) + gal, nbytes, bar);
         }
         for (int i = tid; i < m; i += BATCH_THREADS) basis[i] = B.basis_all[(size_t)p * m + i];
+        if (B.devex) for (int j = tid; j <= n; j += BATCH_THREADS) wts[j] = 1.0;
         mbar_wait(bar, parity);
         parity ^= 1;
         __syncthreads();
@@ -93,6 +98,7 @@ __global__ void __launch_bounds__(BATCH_THREADS) batched_simplex_kernel(BatchedP
         P.T = S; P.ld = (size_t)ld1; P.m = m; P.n = n; P.R = R; P.basis = basis;
         P.prow = prow; P.pcol = pcol; P.pcn = 0; P.bnext = nullptr; P.st = nullptr; P.log = nullptr; P.log_cap = 0;
         P.eps = B.eps; P.max_iter = B.max_iter; P.method = B.method; P.n_art = B.n_art; P.bland = B.bland;
+        P.wts = B.devex ? wts : nullptr;
 
         int status = LPGPU_RUNNING, phase = (B.method == LPGPU_TWOPHASE) ? PH_ONE : PH_MAIN, iters = 0, p1 = 0;
         int *plog = B.log ? B.log + (size_t)p * 2 * B.log_cap : nullptr;
@@ -110,6 +116,11 @@ __global__ void __launch_bounds__(BATCH_THREADS) batched_simplex_kernel(BatchedP
                 if (plog && iters < B.log_cap) { plog[2 * iters] = k; plog[2 * iters + 1] = r; }
             }
             __syncthreads();
+            if (B.devex) {       // reference weights follow the scaled pivot row (devex_weight: the oracle's devex_update)
+                const double wk = wts[k];
+                __syncthreads();
+                for (int j = 1 + tid; j <= n; j += BATCH_THREADS) wts[j] = devex_weight(wts[j], prow[j], wk, j == k);
+            }
             // ---- rank-1 elimination: a warp per row, lanes across columns (conflict-free)
             for (int i = warp; i < rows; i += NWARP) {
                 double *row = S + (size_t)i * ld1;

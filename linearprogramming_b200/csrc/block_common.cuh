@@ -119,23 +119,37 @@ __device__ __forceinline__ KeyCand cluster_key_best(cg::cluster_group &cl, KeyCa
 // two-phase main phase), 1 = Big-M (M row first, cost row second), 2 = two-phase phase one (row m+1 alone)
 enum { PRICE_COST = 0, PRICE_BIGM = 1, PRICE_PHASE1 = 2 };
 
-// BL: Bland's rule -- every eligible column gets the same key, the arg-max's tie-break (lowest column) decides.  A template
-// parameter, not a run-time test: the step kernel sits at its register limit and the default rule must not pay for the option.
-template <bool BL = false>
-__device__ __forceinline__ void blk_price(const DenseParams &P, int mode, int j, double oc, double om, KeyCand &c) {
+// PR: pricing rule, a template parameter (the step kernels sit at their register limit and the default rule must not pay for
+// the options).  PR_DANTZIG: largest reduced cost.  PR_BLAND: every eligible column gets the same key, the arg-max's tie-break
+// (lowest column) decides.  PR_DEVEX: sigma_j^2 / w_j with the reference weight w_j >= 1 of the column (one rounded multiply,
+// one IEEE division; under Big-M both levels are scaled, below a positive M part the cost breaks ties as it is) -- the
+// oracle's price_single / price_bigm with pricing == 2.
+enum { PR_DANTZIG = 0, PR_BLAND = 1, PR_DEVEX = 2 };
+
+template <int PR = PR_DANTZIG>
+__device__ __forceinline__ void blk_price(const DenseParams &P, int mode, int j, double oc, double om, double w, KeyCand &c) {
     KeyCand t;
     t.idx = j;
     if (mode == PRICE_BIGM) {
         double p = om;
         if (fabs(p) <= P.eps) p = 0.0;
-        t.kp = BL ? 0ull : ord_key(p);
-        t.kq = BL ? 1ull : ord_key(oc);
-        if ((p > 0.0 || (p == 0.0 && oc > P.eps)) && keycand_better(t, c)) c = t;
+        if (p > 0.0 || (p == 0.0 && oc > P.eps)) {
+            if (PR == PR_DEVEX) {
+                t.kq = ord_key((p == 0.0) ? (oc * oc) / w : oc);
+                t.kp = ord_key((p * p) / w);
+            } else {
+                t.kp = (PR == PR_BLAND) ? 0ull : ord_key(p);
+                t.kq = (PR == PR_BLAND) ? 1ull : ord_key(oc);
+            }
+            if (keycand_better(t, c)) c = t;
+        }
     } else {
         const double q = (mode == PRICE_PHASE1) ? om : oc;
-        t.kp = 0;
-        t.kq = BL ? 1ull : ord_key(q);
-        if (q > P.eps && keycand_better(t, c)) c = t;
+        if (q > P.eps) {
+            t.kp = 0;
+            t.kq = (PR == PR_BLAND) ? 1ull : (PR == PR_DEVEX) ? ord_key((q * q) / w) : ord_key(q);
+            if (keycand_better(t, c)) c = t;
+        }
     }
 }
 

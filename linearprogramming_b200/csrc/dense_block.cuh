@@ -62,7 +62,7 @@ template <int CL> struct StepShape {
     static constexpr int PB = (CL == 16) ? 16 : STEP_PB;        // ... row phase (x STEP_CPT columns per thread)
 };
 
-template <int RR, bool PIPE, int CL, bool BL>
+template <int RR, bool PIPE, int CL, int BL>       // BL: pricing rule (PR_DANTZIG / PR_BLAND / PR_DEVEX, block_common.cuh)
 __global__ void __launch_bounds__(StepShape<CL>::TH)
 blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     constexpr int TH = StepShape<CL>::TH, FB = StepShape<CL>::FB, PB = StepShape<CL>::PB;
@@ -120,7 +120,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
 
     int status = status0, k = 0, r = -1, phase = phase0, p1 = st->phase1_iters;
     bool have = false;
-    double sig_c = 0.0, sig_m = 0.0;
+    double sig_c = 0.0, sig_m = 0.0, wk = 1.0;
     if (status0 == LPGPU_RUNNING && phase0 != PH_DRIVEOUT) {
         // ---- entering column: priced by the previous step (one candidate per CTA), or from scratch
         if (kn > 0) k = kn;
@@ -129,7 +129,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
             k = c.idx > 0 ? c.idx : 0;
         } else {
             KeyCand c = keycand_none();
-            for (int j = 1 + gtid; j <= jmax; j += GSTRIDE) blk_price<BL>(P, pmode, j, oc[j], (RR == 2) ? om[j] : 0.0, c);
+            for (int j = 1 + gtid; j <= jmax; j += GSTRIDE) blk_price<BL>(P, pmode, j, oc[j], (RR == 2) ? om[j] : 0.0, (BL == PR_DEVEX) ? P.wts[j] : 1.0, c);
             c = cluster_key_best<true, CL>(cl, c, scr_a, slot_a);
             k = c.idx > 0 ? c.idx : 0;
         }
@@ -150,6 +150,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
             // ---- column k as it stands after the t pivots of this block, and the ratio test on it
             sig_c = oc[k];                                        // read before the row phase rewrites objcur
             sig_m = (RR == 2) ? om[k] : 0.0;
+            if (BL == PR_DEVEX) wk = P.wts[k];                    // Devex: w_k before this pivot (rewritten in the row phase, after a cluster barrier)
             if (gtid < RR) B.Fs[(size_t)t * pcn + P.m + gtid] = oc[(size_t)gtid * P.ld + k];   // objective rows: kept eagerly, same bits
             // first row of this thread: everything it needs is requested before anyone waits
             int i = gtid;
@@ -212,16 +213,18 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
     }
 
     // ---- row r as it stands after the t pivots of this block, scaled; objective rows and next pricing
-    double av[STEP_CPT], ocv[STEP_CPT], omv[STEP_CPT];
+    double av[STEP_CPT], ocv[STEP_CPT], omv[STEP_CPT], wv[STEP_CPT];
     const size_t jb = 1 + (size_t)gtid;           // columns 1..n; column 0 (b_r') is brp, padding columns stay zero
 #pragma unroll
     for (int cth = 0; cth < STEP_CPT; ++cth) {
         const size_t j = jb + (size_t)cth * GSTRIDE;
         av[cth] = ocv[cth] = omv[cth] = 0.0;
+        wv[cth] = 1.0;
         if (j <= (size_t)P.n) {
             av[cth] = P.T[(size_t)r * P.ld + j];
             ocv[cth] = oc[j];
             if (RR == 2) omv[cth] = om[j];
+            if (BL == PR_DEVEX) wv[cth] = P.wts[j];
         }
     }
     const int s0r = blk_row_start(B.rowstamp[r], seq);
@@ -248,7 +251,7 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
 #pragma unroll
             for (int cth = 0; cth < STEP_CPT; ++cth) {
                 const size_t j = j0 + (size_t)cth * GSTRIDE;
-                if (j <= (size_t)P.n) { av[cth] = P.T[(size_t)r * P.ld + j]; ocv[cth] = oc[j]; if (RR == 2) omv[cth] = om[j]; }
+                if (j <= (size_t)P.n) { av[cth] = P.T[(size_t)r * P.ld + j]; ocv[cth] = oc[j]; if (RR == 2) omv[cth] = om[j]; if (BL == PR_DEVEX) wv[cth] = P.wts[j]; }
             }
         }
         if (rrow) {                               // the row was a pivot row earlier: restart from its scaled row
@@ -289,7 +292,12 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
                     qm = __fma_rn(-sig_m, pr, omv[cth]);
                     B.objcur[P.ld + j] = qm;
                 }
-                if (j <= (size_t)jmax) blk_price<BL>(P, pmode, (int)j, qc, qm, c);
+                double w = 1.0;
+                if (BL == PR_DEVEX) {
+                    w = devex_weight(wv[cth], pr, wk, j == (size_t)k);
+                    P.wts[j] = w;
+                }
+                if (j <= (size_t)jmax) blk_price<BL>(P, pmode, (int)j, qc, qm, w, c);
             }
         }
     }

@@ -14,6 +14,7 @@ struct lpgpu_dense {
     double *T;
     int *basis;
     double *prow, *pcol, *bnext, *xbuf;   // pcol: 2 x pcn (colbuf)
+    double *wts;            // Devex reference weights, ld doubles, all 1 after a reset (LPGPU_VARIANT_DEVEX)
     size_t pcn;
     bool la_dirty;          // tableau changed behind the lookahead's back (upload / synth / forced pivot)
     lpgpu::PivotState *st;

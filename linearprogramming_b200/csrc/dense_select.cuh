@@ -36,7 +36,16 @@ struct DenseParams {
     int n_art;
     int bland;          // 1: Bland's rule -- every eligible column gets the same key, so the arg-max's tie-break (lowest
                         // column) picks the entering column (variant bit 0x400000, primal methods)
+    double *wts;        // Devex reference weights w[0..ld) (LPGPU_VARIANT_DEVEX, primal methods), else nullptr: the entering column
+                        // maximises sigma_j^2 / w_j; every pivot updates them from its scaled pivot row (block_common.cuh devex_weight)
 };
+
+// Devex weight of column j after the pivot on (r, k): pr = the scaled pivot row entry a_rj', wk = w_k before the pivot
+// (the CPU checker restates it as devex_update: two rounded multiplies in this order, max, the entering column restarts at 1)
+__device__ __forceinline__ double devex_weight(double w, double pr, double wk, bool entering) {
+    const double u = (pr * pr) * wk;
+    return entering ? 1.0 : (u > w ? u : w);
+}
 
 constexpr int SELECT_THREADS = 1024;
 
@@ -66,7 +75,7 @@ __device__ __forceinline__ Cand price_row(const DenseParams &P, int row, int jma
         const double v = x[j];
         if (v > P.eps) {
             Cand t;
-            t.p = 0.0; t.q = P.bland ? 1.0 : v; t.idx = j;
+            t.p = 0.0; t.q = P.bland ? 1.0 : P.wts ? (v * v) / P.wts[j] : v; t.idx = j;
             if (cand_better(t, c)) c = t;
         }
     }
@@ -84,6 +93,11 @@ __device__ __forceinline__ Cand price_bigm(const DenseParams &P, Cand *scratch) 
         if (p > 0.0 || (p == 0.0 && q > P.eps)) {
             Cand t;
             t.p = P.bland ? 0.0 : p; t.q = P.bland ? 1.0 : q; t.idx = j;
+            if (P.wts) {                                 // Devex: both levels scaled by the weight (oracle price_bigm, pricing == 2)
+                const double w = P.wts[j];
+                t.q = (p == 0.0) ? (q * q) / w : q;
+                t.p = (p * p) / w;
+            }
             if (cand_better(t, c)) c = t;
         }
     }

@@ -140,7 +140,7 @@ __device__ __forceinline__ KeyCand grid_best(const StepsArgs &A, unsigned seq, K
     return r;
 }
 
-template <int RR, bool BL>
+template <int RR, int BL>          // BL: pricing rule (PR_DANTZIG / PR_BLAND / PR_DEVEX, block_common.cuh)
 __global__ void __launch_bounds__(STEPS_TH, 1) blk_steps_kernel(DenseParams P, BlockBufs B, StepsArgs A) {
     extern __shared__ __align__(128) unsigned char steps_smem[];
     __shared__ StepsShared sh;
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(STEPS_TH, 1) blk_steps_kernel(DenseParams P, B
             KeyCand c = keycand_none();
             for (int lj = tid; lj < nc; lj += TH) {
                 const long j = col0 + lj;
-                if (j >= 1 && j <= jmax) blk_price<BL>(P, pmode, (int)j, __ldcg(oc + j), (RR == 2) ? __ldcg(om + j) : 0.0, c);
+                if (j >= 1 && j <= jmax) blk_price<BL>(P, pmode, (int)j, __ldcg(oc + j), (RR == 2) ? __ldcg(om + j) : 0.0, (BL == PR_DEVEX) ? __ldcg(P.wts + j) : 1.0, c);
             }
             double d0 = 0.0, d1 = 0.0;
             c = bigm ? block_best_payload<true>(c, d0, d1, sh, 1) : block_best_payload<false>(c, d0, d1, sh, 1);
@@ -233,6 +233,7 @@ __global__ void __launch_bounds__(STEPS_TH, 1) blk_steps_kernel(DenseParams P, B
             // ================= column k as it stands after the tc pending steps, and the ratio test on it
             const double sig_c = __ldcg(oc + k);                       // read before the row phase rewrites the objective rows
             const double sig_m = (RR == 2) ? __ldcg(om + k) : 0.0;
+            const double wk = (BL == PR_DEVEX) ? __ldcg(P.wts + k) : 1.0;   // Devex: w_k before this pivot (rewritten in the row phase, after the exchange)
             if (tid < tc) s_pk[tid] = ld_hint(B.Pall + srow(tid) * P.ld + (size_t)k, pol);
             if (cta == 0 && tid < RR) B.Fs[(size_t)t * pcn + P.m + tid] = __ldcg(oc + (size_t)tid * P.ld + k);   // objective rows: kept eagerly, same bits
             KeyCand cr = keycand_none();
@@ -301,11 +302,12 @@ __global__ void __launch_bounds__(STEPS_TH, 1) blk_steps_kernel(DenseParams P, B
                 const int lj = lj0 + tid;
                 const long j = col0 + lj;
                 const bool mine = lj < nc && j >= 1 && j <= (long)P.n;
-                double av = 0.0, ocv = 0.0, omv = 0.0, pcur[BLK_KMAX];
+                double av = 0.0, ocv = 0.0, omv = 0.0, wv = 1.0, pcur[BLK_KMAX];
                 if (mine) {
                     av = P.T[(size_t)r * P.ld + (size_t)j];
                     ocv = __ldcg(oc + j);
                     if (RR == 2) omv = __ldcg(om + j);
+                    if (BL == PR_DEVEX) wv = __ldcg(P.wts + j);
 #pragma unroll
                     for (int u = 0; u < BLK_KMAX; ++u) pcur[u] = (u < t) ? ld_hint(B.Pm + (size_t)u * P.ld + (size_t)j, pol) : 0.0;
                 }
@@ -333,7 +335,12 @@ __global__ void __launch_bounds__(STEPS_TH, 1) blk_steps_kernel(DenseParams P, B
                         qm = __fma_rn(-sig_m, pr, omv);
                         __stcg(B.objcur + P.ld + j, qm);
                     }
-                    if (j <= (long)jmax) blk_price<BL>(P, pmode, (int)j, qc, qm, cp);
+                    double w = 1.0;
+                    if (BL == PR_DEVEX) {
+                        w = devex_weight(wv, pr, wk, j == (long)k);
+                        __stcg(P.wts + j, w);
+                    }
+                    if (j <= (long)jmax) blk_price<BL>(P, pmode, (int)j, qc, qm, w, cp);
                 }
             }
             if (nc <= 0) __syncthreads();

@@ -560,7 +560,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
                     qm = __fma_rn(-sig_m, pr, omv[cth]);
                     B.objcur[P.ld + j] = qm;
                 }
-                if (j <= (size_t)jmax) blk_price<BL>(P, pmode, (int)j, qc, qm, c);
+                if (j <= (size_t)jmax) blk_price<BL ? PR_BLAND : PR_DANTZIG>(P, pmode, (int)j, qc, qm, 1.0, c);
             }
         }
     }
@@ -928,6 +928,7 @@ int lpgpu_shard_reset(lpgpu_shard *s, const lpgpu_opts *opts) {
     if (!s || !opts) return LPGPU_EINVAL;
     lpgpu_ctx *ctx = s->ctx;
     if (opts->method == LPGPU_DUAL) return fail(ctx, LPGPU_EINVAL, "shard_reset: the column-sharded path runs the primal methods");
+    if (opts->variant & LPGPU_VARIANT_DEVEX) return fail(ctx, LPGPU_EINVAL, "shard_reset: Devex pricing is not available on the column-sharded path (default rule or LPGPU_VARIANT_BLAND)");
     if (opts->method == LPGPU_TWOPHASE && !(s->use_p2p && !(opts->variant & LPGPU_VARIANT_RANK1)))
         return fail(ctx, LPGPU_EINVAL, "shard_reset: the two-phase method runs on the blocked path over the peer-memory transport (lpgpu_shard_create_p2p, no LPGPU_VARIANT_RANK1)");
     if ((opts->method == LPGPU_PLAIN) != (s->R == 1) || opts->n_art < 0 || opts->n_art > s->n)

@@ -48,9 +48,10 @@ int lpf_solve_model(void *ctx, const lpf_model *mo, int method_if_needed, lpf_so
     lpgpu_default_opts(&o);
     o.method = method;
     o.n_art = n_art;
-    {   /* LPGPU_PRICING=bland: the lowest eligible column enters (anti-cycling), primal methods */
+    {   /* LPGPU_PRICING=bland: the lowest eligible column enters (anti-cycling); =devex: reference-weight pricing; primal methods */
         const char *pe = getenv("LPGPU_PRICING");
         if (pe && !strcmp(pe, "bland") && method != LPGPU_DUAL) o.variant |= LPGPU_VARIANT_BLAND;
+        if (pe && !strcmp(pe, "devex") && method != LPGPU_DUAL) o.variant |= LPGPU_VARIANT_DEVEX;
     }
     o.log_cap = 16 * (mo->m + n) + 64;
     {   /* "message, never hang": a cycling model ends with ITERATION LIMIT (LPGPU_MAX_ITER overrides the cap) */

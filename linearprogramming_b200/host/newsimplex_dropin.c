@@ -244,9 +244,10 @@ void newSimplex(LPModel *model) {
         lpgpu_default_opts(&o);
         o.method = method;
         o.n_art = n_art;
-        {   /* LPGPU_PRICING=bland: the lowest eligible column enters (anti-cycling), primal methods */
+        {   /* LPGPU_PRICING=bland: the lowest eligible column enters (anti-cycling); =devex: reference-weight pricing; primal methods */
             const char *pe = getenv("LPGPU_PRICING");
             if (pe && !strcmp(pe, "bland") && method != LPGPU_DUAL) o.variant |= LPGPU_VARIANT_BLAND;
+            if (pe && !strcmp(pe, "devex") && method != LPGPU_DUAL) o.variant |= LPGPU_VARIANT_DEVEX;
         }
         o.log_cap = 16 * (m + n) + 64;
         o.max_iter = pivot_cap(m, n);

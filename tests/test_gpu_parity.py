@@ -204,8 +204,10 @@ def test_dense_timed_run_reports_kernel_time(ctx):
 # ------------------------------------------------------------------ blocked path (delayed rank-1 applications)
 def _blocked(K=0):
     # pivots per block (0 = the default, 32), PIPELINED blocks whatever the size (the default picks them from 0.4 GB on);
-    # K >= 100: K - 100 pivots per block, blocks applied in place
-    return ((K % 100) << 16) | (capi.INPLACE if K >= 100 else capi.PIPELINED)
+    # K >= 100: K - 100 pivots per block, blocks applied in place.  Odd K: the kernels that are not the default (persistent
+    # step kernel, DMMA pass), so that every K-parametrised test covers both sets.
+    alt = (capi.STEP_PERSISTENT | capi.DMMA_PASS) if K % 2 == 1 else 0
+    return ((K % 100) << 16) | (capi.INPLACE if K >= 100 else capi.PIPELINED) | alt
 
 
 def test_log_cap_shrinks_between_calls_no_overflow(ctx):
@@ -382,9 +384,10 @@ def test_pipelined_blocks_equal_inplace_blocks_and_oracle(ctx, m, ns, K):
     _assert_dense_equal(b, ref)
     assert _same_bits(a["T"], b["T"])
     # the step kernel as a cluster of 8 CTAs (default: 16 where the device places such clusters), and the pass kernel that
-    # loads a whole tile before it computes / the scalar-DFMA pass software-pipelined in halves (default: the DMMA pass)
+    # loads a whole tile before it computes / the DMMA pass / the persistent step kernel (defaults: scalar-DFMA pass software-pipelined
+    # in halves, one step launch per pivot)
     for extra in (capi.STEP_CL8, capi.STEP_CL8 | capi.INPLACE, capi.WHOLE_TILE_PASS, capi.WHOLE_TILE_PASS | capi.INPLACE,
-                  capi.DFMA_PASS, capi.DFMA_PASS | capi.INPLACE):
+                  capi.DMMA_PASS, capi.DMMA_PASS | capi.INPLACE, capi.STEP_PERSISTENT, capi.STEP_PERSISTENT | capi.DMMA_PASS):
         c = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K) | extra)
         _assert_dense_equal(c, ref)
 
@@ -484,7 +487,7 @@ def test_pipelined_blocks_full_grid_2048x8192_bitwise(ctx):
     SMs free): 400 pivots, pipelined and in place, against the rank-1 path and the oracle."""
     m, ns, Pn = 2048, 6144, 400
     outs = []
-    for variant in (capi.RANK1, 0, capi.PIPELINED, capi.INPLACE, _blocked(24), capi.STEP_CL8 | capi.PIPELINED):
+    for variant in (capi.RANK1, 0, capi.PIPELINED, capi.INPLACE, _blocked(24), capi.STEP_CL8 | capi.PIPELINED, capi.PIPELINED | capi.STEP_PERSISTENT | capi.DMMA_PASS):
         d = lp.DenseTableau(ctx, m, m + ns, 1)
         d.synth(1234, 7, ns)
         d.reset(log_cap=Pn, variant=variant)
@@ -509,14 +512,15 @@ def test_pipelined_blocks_two_objective_rows_full_grid_bitwise(ctx, method):
     T0, basis, n_art = lp.build_tableau(A, b, c, rel, R=2)
     Pn = 500
     ref = O.solve_f64(T0, basis, method=method, n_art=n_art, max_iter=Pn, threads=16, log_cap=Pn)
-    for variant in (capi.PIPELINED, capi.INPLACE):
+    for variant in (capi.PIPELINED, capi.INPLACE, capi.PIPELINED | capi.STEP_PERSISTENT | capi.DMMA_PASS):
         got = lp.solve_dense(ctx, T0, basis, method=method, n_art=n_art, max_iter=Pn, log_cap=Pn, variant=variant)
         _assert_dense_equal(got, ref)
     assert ref["iters"] == Pn
 
 
 # ------------------------------------------------------------------ pricing option: Bland's rule
-@pytest.mark.parametrize("variant", [capi.RANK1, capi.INPLACE, capi.PIPELINED, (3 << 16) | capi.PIPELINED, capi.STEP_CL8 | capi.INPLACE])
+@pytest.mark.parametrize("variant", [capi.RANK1, capi.INPLACE, capi.PIPELINED, (3 << 16) | capi.PIPELINED, capi.STEP_CL8 | capi.INPLACE,
+                                     capi.PIPELINED | capi.STEP_PERSISTENT])
 def test_bland_pricing_dense_bitwise(ctx, variant):
     """variant bit BLAND: the lowest eligible column enters.  Rank-1 path, blocks in place and pipelined: the oracle's
     (pricing = Bland) pivot log, basis and tableau, for the plain method, Big-M and two-phase; Beale's cycling example
@@ -554,6 +558,67 @@ def test_bland_pricing_batched_and_refusals(ctx):
     d = lp.DenseTableau(ctx, 12, Td.shape[1] - 1, 1)
     with pytest.raises(Exception):
         d.reset(method=lp.DUAL, variant=capi.BLAND)                    # primal methods only
+    d.close()
+
+
+# ------------------------------------------------------------------ pricing option: Devex reference weights
+@pytest.mark.parametrize("variant", [capi.RANK1, capi.INPLACE, capi.PIPELINED, (3 << 16) | capi.PIPELINED, capi.STEP_CL8 | capi.INPLACE,
+                                     capi.PIPELINED | capi.STEP_PERSISTENT])
+def test_devex_pricing_dense_bitwise(ctx, variant):
+    """variant bit DEVEX: sigma_j^2 / w_j decides, the weights follow every pivot's scaled row.  Rank-1 path, blocks in place
+    and pipelined (persistent step kernel and per-pivot launches): the oracle's (pricing = Devex) pivot log, basis and
+    tableau, for the plain method (columns scaled by powers of two, where the rule matters), Big-M and two-phase incl.
+    the drive-out pivots; a second run call on the same object continues with the weights it left."""
+    T0, basis = O.synth_feasible(321, 2, 150, 120)
+    T0[:, 1:121] *= 2.0 ** np.random.default_rng(9).integers(-6, 7, size=120)
+    ref = O.solve_f64(T0, basis, pricing=O.DEVEX, log_cap=8192, threads=4)
+    got = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=variant | capi.DEVEX)
+    _assert_dense_equal(got, ref)
+    assert ref["status"] == O.OPTIMAL and ref["iters"] > 40
+    assert got["log"].tolist() != O.solve_f64(T0, basis, log_cap=8192)["log"].tolist()[:ref["iters"]]
+    rng = np.random.default_rng(31)
+    for seed in range(4):
+        A, b, c, rel = H.random_mixed_lp(rng, 20 + seed, 16)
+        for method in (O.BIGM, O.TWOPHASE):
+            T, bs, n_art = lp.build_tableau(A, b, c, rel, R=2)
+            ref2 = O.solve_f64(T, bs, method=method, n_art=n_art, max_iter=5000, log_cap=5000, pricing=O.DEVEX)
+            got2 = lp.solve_dense(ctx, T, bs, method=method, n_art=n_art, max_iter=5000, log_cap=5000, variant=variant | capi.DEVEX)
+            _assert_dense_equal(got2, ref2)
+    # windows: the weights live in the tableau object between run calls
+    d = lp.DenseTableau(ctx, 150, 270, 1)
+    d.upload(T0, basis)
+    d.reset(log_cap=8192, variant=variant | capi.DEVEX)
+    for _ in range(400):
+        if d.run(7)["status"] != lp.RUNNING:
+            break
+    out = d.download()
+    d.close()
+    assert np.array_equal(out["T"], ref["T"]) and out["log"][:ref["iters"]].tolist() == ref["log"].tolist()
+
+
+def test_devex_pricing_batched_and_refusals(ctx):
+    T, basis = O.synth_feasible_batch(77, 0, 300, 24, 20)
+    T[:, :, 1:21] *= 2.0 ** np.random.default_rng(3).integers(-5, 6, size=(300, 1, 20))
+    ref = O.solve_batched_f64(T, basis, threads=4, pricing=O.DEVEX)
+    got = lp.solve_batched(ctx, T, basis, variant=capi.DEVEX)          # the shared-memory kernel keeps the weights
+    _assert_batched_equal(got, ref)
+    assert not np.array_equal(ref["iters"], O.solve_batched_f64(T, basis, threads=4)["iters"])
+    rng = np.random.default_rng(6)
+    A, b, c, rel = H.random_mixed_lp(rng, 14, 12)
+    for method in (O.BIGM, O.TWOPHASE):
+        Tm, bm, n_art = lp.build_tableau(A, b, c, rel, R=2)
+        Tb = np.repeat(Tm[None], 40, axis=0).copy()
+        Tb[:, :-2, 0] *= 1.0 + 0.01 * np.arange(40)[:, None]
+        bb = np.repeat(np.asarray(bm, np.int32)[None], 40, axis=0).copy()
+        refb = O.solve_batched_f64(Tb, bb, method=method, n_art=n_art, max_iter=2000, threads=4, pricing=O.DEVEX)
+        gotb = lp.solve_batched(ctx, Tb, bb, method=method, n_art=n_art, max_iter=2000, variant=capi.DEVEX)
+        _assert_batched_equal(gotb, refb)
+    Td, bd, _ = H.random_dual_lp(rng, 12, 10)
+    d = lp.DenseTableau(ctx, 12, Td.shape[1] - 1, 1)
+    with pytest.raises(Exception):
+        d.reset(method=lp.DUAL, variant=capi.DEVEX)                    # primal methods only
+    with pytest.raises(Exception):
+        d.reset(variant=capi.DEVEX | capi.BLAND)                       # one rule at a time
     d.close()
 
 

@@ -8,8 +8,8 @@ from linearprogramming_b200 import capi
 m = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
 ctx = lp.Context(0)
 d = lp.DenseTableau(ctx, m, 2 * m, 1)
-for name, v in (("mma", 0), ("dfma_sp", capi.DFMA_PASS)):
-    for mode, mv in (("inplace", capi.INPLACE), ("pipe+launches", capi.PIPELINED | capi.STEP_LAUNCHES), ("pipe+persistent", capi.PIPELINED)):
+for name, v in (("mma", capi.DMMA_PASS), ("dfma_sp", 0)):
+    for mode, mv in (("inplace", capi.INPLACE), ("pipe+launches", capi.PIPELINED), ("pipe+persistent", capi.PIPELINED | capi.STEP_PERSISTENT)):
         for K in (32, 16):
             try:
                 d.synth(1234, 0, m)

@@ -13,6 +13,7 @@
 #include "dense_update.cuh"
 #include "dense_block.cuh"
 #include "dense_block_mma.cuh"
+#include "dense_block_ring.cuh"
 #include "dense_steps.cuh"
 
 using namespace lpgpu;
@@ -463,7 +464,7 @@ static int close_block_pipe(lpgpu_dense *d, cudaEvent_t ev0, cudaEvent_t ev1) {
     U.rowstamp = odd ? d->rowstamp2 : d->rowstamp; U.steprow = odd ? d->steprow2 : d->steprow; U.st = d->st;
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
     U.rb = d->fl_rb; U.pf = d->fl_pf;
-    const bool full = d->grid_flush >= ctx->sm_count * 2;   // a full persistent grid: every SM holds CTAs of the pass
+    const bool full = d->grid_flush >= ctx->sm_count * ((d->opts.variant & LPGPU_VARIANT_RING_PASS) ? 1 : 2);   // a full persistent grid: every SM holds CTAs of the pass
     for (int w = 0; w < 8; ++w) U.resv[w] = full ? (d->persist_on ? d->resv_steps[w] : d->resv[w]) : 0u;
     U.flag = d->flush_flag;
     U.l2first = (d->l2hint & 1) ? 1 : 0;
@@ -560,7 +561,8 @@ static int launch_block_step(lpgpu_dense *d, int first) {
 // pass in place); LPGPU_VARIANT_WHOLE_TILE = scalar DFMAs, whole tile loaded before it computes
 static int launch_pass_kernel(lpgpu_dense *d, const FlushParams &U, cudaStream_t stream) {
     lpgpu_ctx *ctx = d->ctx;
-    if (d->opts.variant & LPGPU_VARIANT_WHOLE_TILE) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
+    if (d->opts.variant & LPGPU_VARIANT_RING_PASS) blk_flush_ring_kernel<<<d->grid_flush, RG_THREADS, RG_SMEM_BYTES, stream>>>(U);
+    else if (d->opts.variant & LPGPU_VARIANT_WHOLE_TILE) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
     else if (d->opts.variant & LPGPU_VARIANT_DMMA_PASS) blk_flush_mma_kernel<<<d->grid_flush, FL_THREADS, MM_SMEM_BYTES, stream>>>(U);
     else blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
     LP_LAUNCH_CHECK(ctx);
@@ -632,13 +634,15 @@ int size_grid(lpgpu_dense *d) {
     const long nrb = (d->m + d->R + UPD_TILE_ROWS - 1) / UPD_TILE_ROWS;
     d->grid_update = (int)std::max(1L, std::min((long)ctx->sm_count * occ, nct * nrb));
     int occf = 0;
-    if ((d->opts.variant & LPGPU_VARIANT_DMMA_PASS) && !(d->opts.variant & LPGPU_VARIANT_WHOLE_TILE))
+    if (d->opts.variant & LPGPU_VARIANT_RING_PASS)
+        LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_ring_kernel, RG_THREADS, RG_SMEM_BYTES));
+    else if ((d->opts.variant & LPGPU_VARIANT_DMMA_PASS) && !(d->opts.variant & LPGPU_VARIANT_WHOLE_TILE))
         LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_mma_kernel, FL_THREADS, MM_SMEM_BYTES));
     else
         LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, (d->opts.variant & LPGPU_VARIANT_WHOLE_TILE) ? blk_flush_kernel : blk_flush_sp_kernel, FL_THREADS, FL_SMEM_BYTES));
     const long fct = (long)((d->ld + FL_COLS - 1) / FL_COLS);
     const char *erb = getenv("LPGPU_FL_RB"), *epf = getenv("LPGPU_FL_PF");      // tuning aids
-    d->fl_rb = (erb && atoi(erb) > 0) ? atoi(erb) : FL_RB;
+    d->fl_rb = (erb && atoi(erb) > 0) ? atoi(erb) : (d->opts.variant & LPGPU_VARIANT_RING_PASS) ? 2 * FL_RB : FL_RB;
     d->fl_pf = epf ? atoi(epf) : 1;
     const long fsb = ((d->m + d->R + FL_ROWS - 1) / FL_ROWS + d->fl_rb - 1) / d->fl_rb;
     d->grid_flush = (int)std::max(1L, std::min((long)ctx->sm_count * std::max(1, occf), fct * fsb));
@@ -717,6 +721,8 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
         e = cudaFuncSetAttribute(blk_flush_sp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL_SMEM_BYTES);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(blk_flush_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MM_SMEM_BYTES);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(blk_flush_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RG_SMEM_BYTES);
     if (e == cudaSuccess) e = cudaHostAlloc(&d->h_st, sizeof(PivotState), cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->T, 0, rows * d->ld * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->prow, 0, d->ld * sizeof(double), ctx->stream);

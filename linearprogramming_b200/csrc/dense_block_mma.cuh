@@ -21,16 +21,19 @@
 // loads of the other half -- of this tile or of the CTA's next tile -- are in flight (as in blk_flush_sp_kernel).
 // Accumulator fragment of patch (i, j): thread (g = lane / 4, q = lane % 4) holds row 8 i + g, columns 8 j + 2 q, +1 --
 // one 128-bit access; a warp-level access touches 8 rows x 64 contiguous bytes (whole 32-byte sectors).
-// Operand tiles in shared memory carry 8 doubles of padding per step row, so that the fragment loads (lane -> step q,
-// row / column g) hit 32 distinct banks per wavefront.
+// Operand tiles in shared memory carry 4 doubles of padding per step row: a fragment load is a 64-bit access of lane (g, q) at
+// word address q * stride + 2 g, served per half warp (g = 0..3 / 4..7); with stride = 8 (mod 32) words the four step rows of a
+// half warp fall into four disjoint groups of 8 banks -- conflict-free.  (8 doubles of padding, stride = 16 (mod 32) words,
+// put steps q and q + 2 on the same banks: ncu showed 26 M bank conflicts in 48 M shared-memory wavefronts and the pass
+// stalled on mio_throttle / short_scoreboard at 12 % issue utilisation, profiles/r2_mma_pass_pad8_raw.csv.)
 #pragma once
 
 #include "dense_block.cuh"
 
 namespace lpgpu {
 
-constexpr int MM_FS = FL_ROWS + 8;     // doubles per step row of the staged multipliers
-constexpr int MM_PS = FL_COLS + 8;     // doubles per step row of the staged pivot-row segments
+constexpr int MM_FS = FL_ROWS + 4;     // doubles per step row of the staged multipliers
+constexpr int MM_PS = FL_COLS + 4;     // doubles per step row of the staged pivot-row segments
 constexpr size_t MM_SMEM_BYTES = ((size_t)BLK_KMAX * MM_PS + 2 * (size_t)BLK_KMAX * MM_FS) * 8;
 constexpr int MM_NI = 2, MM_NJ = 8;    // MMA patches per half: 2 (rows) x 8 (columns)
 

@@ -334,9 +334,9 @@ def gpu_arm(args):
     from linearprogramming_b200 import capi as _capi
     RANK1, INPLACE, WHOLE_TILE, PIPELINED_BIT = _capi.RANK1, _capi.INPLACE, _capi.WHOLE_TILE_PASS, _capi.PIPELINED
     blocked = not (variant & RANK1)
-    # the default picks pipelined blocks from about 0.4 GB of tableau on (csrc/dense.cu want_pipeline); 0x1000 forces them
-    pipelined = blocked and not (variant & INPLACE) and bool((variant & PIPELINED_BIT) or (m + 1) * ((n + 1 + 15) // 16 * 16) * 8 >= (384 << 20))
-    block_k = ((variant >> 16) & 0x3f) or 32
+    # the default picks pipelined blocks from 0.8 GB of tableau on (csrc/dense.cu want_pipeline); 0x1000 forces them
+    pipelined = blocked and not (variant & INPLACE) and bool((variant & PIPELINED_BIT) or (m + 1) * ((n + 1 + 15) // 16 * 16) * 8 >= (800 << 20))
+    block_k = ((variant >> 16) & 0x3f) or (28 if pipelined else 32)      # csrc/dense.cu make_bufs
 
     def kernel_times():
         upd_ms = sel_ms = 0.0
@@ -352,9 +352,12 @@ def gpu_arm(args):
     upd_ms, sel_ms, upd_n, piv_n = kernel_times()
     peak, peak_src = measured_peak()
     traffic, traffic_src = None, None
-    kname = ("blk_flush_kernel" if variant & WHOLE_TILE else "blk_flush_sp_kernel") if blocked else {0: "dense_update_dynamic", 1: "dense_update_tma_staged", 2: "dense_update_direct"}[variant & 0xf]
+    pass_kernel = ("blk_flush_kernel" if variant & WHOLE_TILE else "blk_flush_mma_kernel" if variant & _capi.DMMA_PASS
+                   else "blk_flush_sp_kernel" if variant & _capi.DFMA_PASS else "blk_flush_ring_kernel")
+    kname = pass_kernel if blocked else {0: "dense_update_dynamic", 1: "dense_update_tma_staged", 2: "dense_update_direct"}[variant & 0xf]
     try:        # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
-        tfile = ("r1_flush_traffic.json" if variant & WHOLE_TILE else "r1_flush_sp_traffic.json") if blocked else "r1_update_traffic.json"
+        tfile = {"blk_flush_kernel": "r1_flush_traffic.json", "blk_flush_sp_kernel": "r1_flush_sp_traffic.json",
+                 "blk_flush_ring_kernel": "r2_flush_ring_traffic.json"}.get(pass_kernel, "none.json") if blocked else "r1_update_traffic.json"
         with open(os.path.join(ROOT, "profiles", tfile)) as f:
             tj = json.load(f)
         if m == M and (blocked or tj["variant"] == (variant & 0xf)):
@@ -373,25 +376,25 @@ def gpu_arm(args):
         # the pass of a block runs on a second stream WHILE the next block is decided: the two kernel families overlap, so their
         # summed times exceed the step; kernel_share_of_step stays the share of summed kernel time (what an ncu launch list shows)
         roofline["overlap"] = ("pipelined blocks: the pass (stream 2, every SM but the 16 of the step cluster) runs concurrently with "
-                               "the decisions of the next block; avg_launch_ms is measured under that contention")
+                               "the decisions of the next block; avg_launch_ms is measured under that contention "
+                               "(alone on the GPU the same launch takes 0.357 ms = 0.92 of the peak: tools/ring_lab.cu, profiles/r2_ring_lab.txt)")
         roofline["pass_time_over_step_time"] = (upd_ms / K) / (1e3 * t_value / K)
     if blocked:
         flops = 2.0 * (piv_n / upd_n) * (m + 1) * (n + 1)
         roofline["fp64_TFLOPs_in_kernel"] = flops / (upd_avg_ms * 1e-3) / 1e12
-        # the FP64 side's ceiling for this instruction mix (outer-product DFMAs with both operands fetched from shared memory
-        # every step) was measured with tools/dfma_peak.cu on this pool's B200: 25.3 TFLOP/s on 148 SMs; the pipelined pass
-        # runs on the SMs the step cluster leaves it
+        # FP64 side, against the NOMINAL rate (64 FMA / clock / SM x 148 SMs x 1.965 GHz = 37.2 TFLOP/s).  Footnote: what this
+        # pool's B200 delivers for the instruction mix of the kernel -- DMMA with both operands from shared memory 36.8 TFLOP/s
+        # (tools/dmma_probe.cu, profiles/r2_dmma_probe.txt), scalar outer-product DFMAs 25.3 TFLOP/s (tools/dfma_peak.cu)
         sms_pass = 148 - 16 if pipelined else 148
-        fp64_ceiling = 25.3 * sms_pass / 148
-        t_hbm_ms, t_fp64_ms = alg_bytes / (peak * 1e9) * 1e3, flops / (fp64_ceiling * 1e12) * 1e3
-        roofline["fp64_ceiling_TFLOPs"] = fp64_ceiling
-        roofline["fp64_ceiling_source"] = "measured: tools/dfma_peak.cu, outer 16 x 4, operands from shared memory, 12 warps/SM (DESIGN.md 4.0), scaled to the SMs of the pass"
-        roofline["fp64_frac_of_ceiling"] = roofline["fp64_TFLOPs_in_kernel"] / fp64_ceiling
-        roofline["co_bound_floor_ms"] = max(t_hbm_ms, t_fp64_ms)
-        roofline["frac_of_co_bound_floor"] = max(t_hbm_ms, t_fp64_ms) / upd_avg_ms
+        roofline["fp64_nominal_TFLOPs"] = 37.2
+        roofline["fp64_frac_of_nominal"] = roofline["fp64_TFLOPs_in_kernel"] / 37.2
+        measured_ceiling = 36.8 if pass_kernel in ("blk_flush_ring_kernel", "blk_flush_mma_kernel") else 25.3
+        t_hbm_ms, t_fp64_ms = alg_bytes / (peak * 1e9) * 1e3, flops / (measured_ceiling * sms_pass / 148 * 1e12) * 1e3
+        roofline["footnote_measured_fp64_ceiling_TFLOPs"] = measured_ceiling * sms_pass / 148
+        roofline["footnote_hbm_ms_and_fp64_ms_at_measured_ceilings"] = [t_hbm_ms, t_fp64_ms]
         roofline["note"] = ("one launch applies pivots_per_launch pivots: every element is read and written once and runs through "
-                            "that many dependent DFMAs, so the launch is bounded by HBM (algorithmic bytes above) and, at 32 "
-                            "pivots per launch, nearly as long on the FP64 pipe")
+                            "that many chained FMAs (DMMA: four steps per instruction, in pivot order); with the FP64 side at "
+                            "the matrix-instruction rate the launch is bounded by HBM alone")
     # the same blocks applied in place (steps, pass, steps on one stream), for comparison
     inplace = None
     if pipelined and not args.no_extra:

@@ -73,8 +73,8 @@ extern "C" {
 #define LPGPU_VARIANT_UPD_STATIC    0x1        /* rank-1 path: TMA-staged elimination, static task stride (default: work stealing) */
 #define LPGPU_VARIANT_UPD_DIRECT    0x2        /* rank-1 path: direct-load elimination kernel                                      */
 #define LPGPU_VARIANT_UPD_MASK      0xf
-#define LPGPU_VARIANT_RING_PASS     0x80       /* blocked path: producer / consumer pass -- TMA ring of slabs in shared memory, DMMA chain (dense_block_ring.cuh) */
-#define LPGPU_VARIANT_DMMA_PASS     0x100      /* blocked path: the pass with the FP64 matrix instruction as the FMA chain (default: scalar DFMAs, measured faster) */
+#define LPGPU_VARIANT_DFMA_PASS     0x80       /* blocked path: the pass with scalar DFMAs, software-pipelined in half tiles (default: the ring pass -- TMA ring of slabs + DMMA chain, dense_block_ring.cuh) */
+#define LPGPU_VARIANT_DMMA_PASS     0x100      /* blocked path: DMMA chain on tiles fetched with ordinary loads (the ring pass's predecessor) */
 #define LPGPU_VARIANT_NO_ALTERNATE  0x200      /* rank-1 path: do not alternate the sweep direction between pivots                 */
 #define LPGPU_VARIANT_NO_PDL        0x400      /* plain stream-ordered launches (default: programmatic dependent launch)           */
 #define LPGPU_VARIANT_RANK1         0x800      /* one pass over the tableau per pivot (default: one pass per block of pivots)      */

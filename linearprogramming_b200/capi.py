@@ -33,7 +33,7 @@ NO_PDL = _H["VARIANT_NO_PDL"]                  # dense: plain stream-ordered lau
 RANK1 = _H["VARIANT_RANK1"]                    # dense: one pass over the tableau per pivot (default: one pass per block of pivots)
 PIPELINED = _H["VARIANT_PIPELINED"]            # dense, blocked path: always pipeline the pass with the next block's decisions
 INPLACE = _H["VARIANT_INPLACE"]                # dense, blocked path: never pipeline (default: by size)
-RING_PASS = _H["VARIANT_RING_PASS"]            # dense, blocked path: producer / consumer pass (TMA ring of slabs + DMMA chain)
+DFMA_PASS = _H["VARIANT_DFMA_PASS"]            # dense, blocked path: the pass with scalar DFMAs (default: the ring pass, TMA ring of slabs + DMMA chain)
 DMMA_PASS = _H["VARIANT_DMMA_PASS"]            # dense, blocked path: the pass with the FP64 matrix instruction as the FMA chain (default: scalar DFMAs)
 WHOLE_TILE_PASS = _H["VARIANT_WHOLE_TILE"]     # dense, blocked path: the pass kernel that loads a whole tile before it computes
 STEP_PERSISTENT = _H["VARIANT_STEP_PERSISTENT"]  # dense, pipelined blocks: one persistent step launch per block (default: one cluster launch per pivot)

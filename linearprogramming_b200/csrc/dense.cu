@@ -203,11 +203,11 @@ static cudaError_t launch_pdl(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim
 
 // The same with the cluster shape as a launch attribute (the primal step kernel runs as 8 or 16 CTAs).
 template <typename... KArgs, typename... Args>
-static cudaError_t launch_cluster(bool pdl, int cluster, void (*kernel)(KArgs...), dim3 block, cudaStream_t stream, Args... args) {
+static cudaError_t launch_cluster(bool pdl, int cluster, size_t smem, void (*kernel)(KArgs...), dim3 block, cudaStream_t stream, Args... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(cluster);
     cfg.blockDim = block;
-    cfg.dynamicSmemBytes = 0;
+    cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
@@ -284,7 +284,8 @@ BlockBufs make_bufs(const lpgpu_dense *d) {
         B.l2keep = (d->l2hint & 2) ? 1 : 0;
     }
     const int k = (d->opts.variant & LPGPU_VARIANT_BLOCK_K_MASK) >> 16;
-    B.K = (k >= 1 && k <= BLK_KMAX) ? k : BLK_KMAX;
+    // pivots per block: 32; pipelined 28 (measured: the step kernels are the longer stage there, 56.5 k against 54.8 k pivots/s)
+    B.K = (k >= 1 && k <= BLK_KMAX) ? k : (d->pipe_on ? 28 : BLK_KMAX);
     B.dbg = d->blk_dbg ? d->blk_dbg + 8 * (size_t)(d->blk_dbg_n % 4096) : nullptr;
     return B;
 }
@@ -309,7 +310,7 @@ int launch_block_init(lpgpu_dense *d) {
 static bool want_pipeline(const lpgpu_dense *d) {
     if (!use_blocked(d) || (d->opts.variant & LPGPU_VARIANT_INPLACE) || d->opts.method == LPGPU_DUAL || getenv("LPGPU_NO_PIPELINE")) return false;
     if (d->opts.variant & LPGPU_VARIANT_PIPELINED) return true;
-    return ((size_t)d->m + d->R) * d->ld * sizeof(double) >= ((size_t)384 << 20);
+    return ((size_t)d->m + d->R) * d->ld * sizeof(double) >= ((size_t)800 << 20);
 }
 
 typedef void (*steps_kernel_t)(DenseParams, BlockBufs, StepsArgs);
@@ -430,7 +431,7 @@ static int setup_pipeline(lpgpu_dense *d) {
     // the SMs a step-kernel cluster is placed on while the device is idle: the pass leaves them free
     LP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const int cl = d->step_cl_max;
-    LP_CUDA(ctx, launch_cluster(false, cl, blk_probe_kernel, dim3(SELECT_THREADS), ctx->stream, smids));
+    LP_CUDA(ctx, launch_cluster(false, cl, 0, blk_probe_kernel, dim3(SELECT_THREADS), ctx->stream, smids));
     ctx->launches++;
     unsigned h[STEP_CLUSTER_MAX];
     LP_CUDA(ctx, cudaMemcpyAsync(h, smids, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
@@ -449,6 +450,11 @@ static int setup_pipeline(lpgpu_dense *d) {
     return LPGPU_OK;
 }
 
+enum { PASS_RING = 0, PASS_DFMA = 1, PASS_DMMA = 2, PASS_WHOLE_TILE = 3 };
+static int pass_kind(const lpgpu_dense *d) {
+    const int v = d->opts.variant;
+    return (v & LPGPU_VARIANT_WHOLE_TILE) ? PASS_WHOLE_TILE : (v & LPGPU_VARIANT_DMMA_PASS) ? PASS_DMMA : (v & LPGPU_VARIANT_DFMA_PASS) ? PASS_DFMA : PASS_RING;
+}
 static int launch_pass_kernel(lpgpu_dense *d, const FlushParams &U, cudaStream_t stream);
 
 // Close the open block: its pass goes to stream2 (after this block's steps), the next block's steps wait for the
@@ -463,8 +469,8 @@ static int close_block_pipe(lpgpu_dense *d, cudaEvent_t ev0, cudaEvent_t ev1) {
     U.ld = d->ld; U.rows = d->m + d->R; U.Fs = odd ? d->Ft2 : d->Ft; U.pcn = d->pcn; U.Pm = odd ? d->Pm2 : d->Pm;
     U.rowstamp = odd ? d->rowstamp2 : d->rowstamp; U.steprow = odd ? d->steprow2 : d->steprow; U.st = d->st;
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
-    U.rb = d->fl_rb; U.pf = d->fl_pf;
-    const bool full = d->grid_flush >= ctx->sm_count * ((d->opts.variant & LPGPU_VARIANT_RING_PASS) ? 1 : 2);   // a full persistent grid: every SM holds CTAs of the pass
+    U.rb = d->fl_rb; U.pf = d->fl_pf; U.ring_nd = d->ring_nd;
+    const bool full = d->grid_flush >= ctx->sm_count * (pass_kind(d) == PASS_RING ? 1 : 2);   // a full persistent grid: every SM holds CTAs of the pass
     for (int w = 0; w < 8; ++w) U.resv[w] = full ? (d->persist_on ? d->resv_steps[w] : d->resv[w]) : 0u;
     U.flag = d->flush_flag;
     U.l2first = (d->l2hint & 1) ? 1 : 0;
@@ -534,6 +540,7 @@ static int probe_step_cluster(lpgpu_dense *d) {
     }
     cudaGetLastError();
     if (ok) d->step_cl_max = 16;
+    cudaGetLastError();
     return LPGPU_OK;
 }
 
@@ -544,11 +551,11 @@ static int launch_block_step(lpgpu_dense *d, int first) {
     const bool pdl = !(d->opts.variant & LPGPU_VARIANT_NO_PDL) && !d->opts.time_kernels;
     if (d->opts.method == LPGPU_DUAL) {
         const int cl = step_cluster(d);
-        LP_CUDA(ctx, launch_cluster(pdl, cl, cl == 16 ? blk_dual_step_kernel<16> : blk_dual_step_kernel<8>, dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS),
+        LP_CUDA(ctx, launch_cluster(pdl, cl, 0, cl == 16 ? blk_dual_step_kernel<16> : blk_dual_step_kernel<8>, dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS),
                                     ctx->stream, make_params(d), make_bufs(d), first));
     } else {
         const int cl = step_cluster(d);
-        LP_CUDA(ctx, launch_cluster(pdl, cl, step_kernel(d->R, d->pipe_on, cl, pricing_of(d)), dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS), ctx->stream,
+        LP_CUDA(ctx, launch_cluster(pdl, cl, 0, step_kernel(d->R, d->pipe_on, cl, pricing_of(d)), dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS), ctx->stream,
                                     make_params(d), make_bufs(d), first));
     }
     if (d->blk_dbg) d->blk_dbg_n++;
@@ -556,15 +563,18 @@ static int launch_block_step(lpgpu_dense *d, int first) {
     return LPGPU_OK;
 }
 
-// which pass kernel: default = scalar DFMAs, software-pipelined in half tiles (blk_flush_sp_kernel); LPGPU_VARIANT_DMMA_PASS = the FP64
-// matrix instruction as the FMA chain (dense_block_mma.cuh: same bits, measured 1.3x slower on the B200: 0.66 against 0.51 ms per
-// pass in place); LPGPU_VARIANT_WHOLE_TILE = scalar DFMAs, whole tile loaded before it computes
+// which pass kernel: default = the ring pass (dense_block_ring.cuh: TMA ring of slabs + DMMA chain, 0.36 ms per pass alone on the GPU at
+// 8192 x 16384); LPGPU_VARIANT_DFMA_PASS = scalar DFMAs, software-pipelined in half tiles (round 1's default, 0.50 ms);
+// LPGPU_VARIANT_DMMA_PASS = DMMA chain on tiles fetched with ordinary loads (0.66 ms); LPGPU_VARIANT_WHOLE_TILE = scalar DFMAs, whole
+// tile loaded before it computes.  All bit-identical.
 static int launch_pass_kernel(lpgpu_dense *d, const FlushParams &U, cudaStream_t stream) {
     lpgpu_ctx *ctx = d->ctx;
-    if (d->opts.variant & LPGPU_VARIANT_RING_PASS) blk_flush_ring_kernel<<<d->grid_flush, RG_THREADS, RG_SMEM_BYTES, stream>>>(U);
-    else if (d->opts.variant & LPGPU_VARIANT_WHOLE_TILE) blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
-    else if (d->opts.variant & LPGPU_VARIANT_DMMA_PASS) blk_flush_mma_kernel<<<d->grid_flush, FL_THREADS, MM_SMEM_BYTES, stream>>>(U);
-    else blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U);
+    switch (pass_kind(d)) {
+        case PASS_WHOLE_TILE: blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U); break;
+        case PASS_DMMA: blk_flush_mma_kernel<<<d->grid_flush, FL_THREADS, MM_SMEM_BYTES, stream>>>(U); break;
+        case PASS_DFMA: blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U); break;
+        default: blk_flush_ring_kernel<<<d->grid_flush, RG_THREADS, RG_SMEM_BYTES, stream>>>(U); break;
+    }
     LP_LAUNCH_CHECK(ctx);
     return LPGPU_OK;
 }
@@ -576,7 +586,7 @@ int launch_block_flush(lpgpu_dense *d) {
     U.Tsrc = d->T; U.kc_ptr = &d->st->blk_t; U.seq_ptr = &d->st->blk_seq; U.flag = nullptr; U.l2first = 0;
     for (unsigned &w : U.resv) w = 0;
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
-    U.rb = d->fl_rb; U.pf = d->fl_pf;
+    U.rb = d->fl_rb; U.pf = d->fl_pf; U.ring_nd = d->ring_nd;
     {
         const int rcp = launch_pass_kernel(d, U, ctx->stream);
         if (rcp != LPGPU_OK) return rcp;
@@ -634,16 +644,15 @@ int size_grid(lpgpu_dense *d) {
     const long nrb = (d->m + d->R + UPD_TILE_ROWS - 1) / UPD_TILE_ROWS;
     d->grid_update = (int)std::max(1L, std::min((long)ctx->sm_count * occ, nct * nrb));
     int occf = 0;
-    if (d->opts.variant & LPGPU_VARIANT_RING_PASS)
-        LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_ring_kernel, RG_THREADS, RG_SMEM_BYTES));
-    else if ((d->opts.variant & LPGPU_VARIANT_DMMA_PASS) && !(d->opts.variant & LPGPU_VARIANT_WHOLE_TILE))
-        LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_mma_kernel, FL_THREADS, MM_SMEM_BYTES));
-    else
-        LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, (d->opts.variant & LPGPU_VARIANT_WHOLE_TILE) ? blk_flush_kernel : blk_flush_sp_kernel, FL_THREADS, FL_SMEM_BYTES));
+    const int pk = pass_kind(d);
+    if (pk == PASS_RING) LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_ring_kernel, RG_THREADS, RG_SMEM_BYTES));
+    else if (pk == PASS_DMMA) LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_mma_kernel, FL_THREADS, MM_SMEM_BYTES));
+    else LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, pk == PASS_WHOLE_TILE ? blk_flush_kernel : blk_flush_sp_kernel, FL_THREADS, FL_SMEM_BYTES));
     const long fct = (long)((d->ld + FL_COLS - 1) / FL_COLS);
     const char *erb = getenv("LPGPU_FL_RB"), *epf = getenv("LPGPU_FL_PF");      // tuning aids
-    d->fl_rb = (erb && atoi(erb) > 0) ? atoi(erb) : (d->opts.variant & LPGPU_VARIANT_RING_PASS) ? 2 * FL_RB : FL_RB;
+    d->fl_rb = (erb && atoi(erb) > 0) ? atoi(erb) : pk == PASS_RING ? 2 * FL_RB : FL_RB;
     d->fl_pf = epf ? atoi(epf) : 1;
+    { const char *end = getenv("LPGPU_RING_ND"); d->ring_nd = (end && atoi(end) > 0) ? atoi(end) : RG_ND; }     // tuning aid
     const long fsb = ((d->m + d->R + FL_ROWS - 1) / FL_ROWS + d->fl_rb - 1) / d->fl_rb;
     d->grid_flush = (int)std::max(1L, std::min((long)ctx->sm_count * std::max(1, occf), fct * fsb));
     d->flush_tasks = std::max(1L, fct * fsb);
@@ -900,8 +909,7 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
     if (blocked) {
         // ---- blocked path: K step kernels (decide a pivot each on lazily updated slices), then one pass over
         // the tableau that applies them all; the tableau is brought up to date before this call returns
-        const int K = make_bufs(d).K;
-        // pipelined blocks (default; variant bit 0x2000 = in place): the pass of a block overlaps the decisions of the next one
+        // pipelined blocks (default by size; variant bit 0x2000 = in place): the pass of a block overlaps the decisions of the next one
         d->pipe_on = false;
         if (want_pipeline(d)) {
             rc = setup_pipeline(d);
@@ -909,6 +917,7 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
             d->pipe_on = d->pipe_state == 1;
         }
         const bool pipe = d->pipe_on;
+        const int K = make_bufs(d).K;           // pivots per block (depends on the order chosen above)
         // pipelined blocks of the primal methods: one launch of the step cluster per pivot; LPGPU_VARIANT_STEP_PERSISTENT: one
         // persistent launch decides all the pivots of a block (dense_steps.cuh; same bits, measured slower: 42 k against 55 k pivots/s)
         d->persist_on = false;

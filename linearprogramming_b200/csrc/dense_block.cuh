@@ -301,13 +301,17 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
             }
         }
     }
-    // ---- b column
-    for (int i = gtid; i < P.m; i += GSTRIDE)
-        B.bcur[i] = (i == r) ? brp : __fma_rn(-B.Fs[(size_t)t * pcn + i], brp, B.bcur[i]);
-    stamp(4);
     // ---- this CTA's best candidate for the next pivot; the next launch reduces the SELECT_CLUSTER of them
     c = two_keys ? block_key_best<true>(c, scr_c) : block_key_best<false>(c, scr_c);
     if (threadIdx.x == 0) B.cands[rank] = c;
+    if (PIPE) {      // ... and every CTA of the cluster learns them too (split barrier: nobody waits here), see the prefetch below
+        if (threadIdx.x < CL) cl.map_shared_rank(slot_a, threadIdx.x)[rank] = c;
+        cluster_entry_arrive();
+    }
+    stamp(4);
+    // ---- b column
+    for (int i = gtid; i < P.m; i += GSTRIDE)
+        B.bcur[i] = (i == r) ? brp : __fma_rn(-B.Fs[(size_t)t * pcn + i], brp, B.bcur[i]);
     stamp(5);
 
     if (gtid == 0) {
@@ -326,6 +330,16 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
         st->blk_seq = seq;
         if (B.info) { B.info[B.par].kc = t + 1; B.info[B.par].seq = seq; }
         if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
+    }
+    if (PIPE) {
+        // Pipelined blocks: the pass streams the tableau at the HBM peak beside this kernel, and the next launch's first act is
+        // a strided read of the entering column from HBM -- several microseconds in that queue.  The column is known now
+        // (the best of the CL candidates): one 32-byte sector per row starts its way into L2 before this launch retires.
+        cluster_entry_wait();
+        const KeyCand w = two_keys ? warp_key_best<true>((threadIdx.x & 31) < CL ? slot_a[threadIdx.x & 31] : keycand_none())
+                                   : warp_key_best<false>((threadIdx.x & 31) < CL ? slot_a[threadIdx.x & 31] : keycand_none());
+        if (w.idx > 0)
+            for (int i = gtid; i < P.m; i += GSTRIDE) asm volatile("prefetch.global.L2 [%0];" ::"l"(P.T + (size_t)i * P.ld + (size_t)w.idx));
     }
     stamp(6);
 }
@@ -565,6 +579,7 @@ struct FlushParams {
     unsigned seq;
     int rb;                   // row tiles per task (FL_RB; LPGPU_FL_RB overrides it for tuning)
     int pf;                   // 1: HBM -> L2 prefetch of the next tile
+    int ring_nd;              // ring pass: data slots in use, 2 .. RG_ND (fewer = fewer bytes queued in front of the step kernels' requests)
 };
 
 constexpr size_t FL_SMEM_BYTES = (size_t)BLK_KMAX * FL_COLS * 8 + 2 * (size_t)FL_ROWS * BLK_KMAX * 8;

@@ -135,6 +135,7 @@ __global__ void __launch_bounds__(RG_THREADS, 1) blk_flush_ring_kernel(FlushPara
     const int nrt = (U.rows + FL_ROWS - 1) / FL_ROWS;
     const long ntasks = (long)nct * ((nrt + U.rb - 1) / U.rb);
     const uint64_t pol = l2_policy(U.l2first ? 1 : 0);
+    const unsigned ND = (unsigned)min(max(U.ring_nd, 2), RG_ND);     // data slots in use
     auto wait_issued = [](volatile unsigned *ctr_issued, unsigned seq) {
         unsigned spin = 0;
         while ((int)(*ctr_issued - seq) <= 0)
@@ -182,8 +183,8 @@ __global__ void __launch_bounds__(RG_THREADS, 1) blk_flush_ring_kernel(FlushPara
             const RgTask t = rg_task(U, tt, nct);
             const uint32_t rowbytes = (uint32_t)(t.ncols * 8);
             for (int q = 0; q < t.nslab; ++q, ++seq) {
-                const unsigned ds = seq % RG_ND;
-                if (seq >= (unsigned)RG_ND) mbar_wait(&empty_d[ds], (seq / RG_ND - 1u) & 1u);
+                const unsigned ds = seq % ND;
+                if (seq >= ND) mbar_wait(&empty_d[ds], (seq / ND - 1u) & 1u);
                 const int row0 = t.row0 + q * RG_SR;
                 const int nr = min(RG_SR, U.rows - row0);
                 if (lane == 0) {
@@ -214,11 +215,11 @@ __global__ void __launch_bounds__(RG_THREADS, 1) blk_flush_ring_kernel(FlushPara
         // the slabs of this task whose sequence number falls to this warp
         int q = (int)((warp + RG_NW - (int)(base % RG_NW)) % RG_NW);
         for (; q < t.nslab; q += RG_NW) {
-            const unsigned seq = base + (unsigned)q, ds = seq % RG_ND;
+            const unsigned seq = base + (unsigned)q, ds = seq % ND;
             const unsigned tseq = tbase + (unsigned)(q / RG_TS), fs = tseq % RG_NF;
             const int row0 = t.row0 + q * RG_SR;
             wait_issued(&s_issued_d, seq);
-            mbar_wait(&full_d[ds], (seq / RG_ND) & 1u);
+            mbar_wait(&full_d[ds], (seq / ND) & 1u);
             double2 acc[2][RG_NJ];
             const double *dp = sD + ((size_t)ds * RG_SR + g) * RG_DS + 2 * q4;
 #pragma unroll

@@ -27,6 +27,7 @@ struct lpgpu_dense {
     int grid_flush;         // persistent grid of the blocked path's pass
     long flush_tasks;       // tasks of one pass
     int fl_rb, fl_pf;       // its row tiles per task and L2 prefetch switch
+    int ring_nd;            // ring pass: data slots in use
     int *task_ctr;          // work-stealing counters of the elimination kernel (2 ints)
     unsigned upd_seq;       // elimination launches so far
     std::vector<cudaEvent_t> ev;

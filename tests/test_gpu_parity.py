@@ -206,7 +206,7 @@ def _blocked(K=0):
     # pivots per block (0 = the default, 32), PIPELINED blocks whatever the size (the default picks them from 0.4 GB on);
     # K >= 100: K - 100 pivots per block, blocks applied in place.  Odd K: the kernels that are not the default (persistent
     # step kernel, DMMA pass), so that every K-parametrised test covers both sets.
-    alt = (capi.STEP_PERSISTENT | capi.DMMA_PASS) if K % 2 == 1 else 0
+    alt = (capi.STEP_PERSISTENT | capi.DMMA_PASS) if K % 2 == 1 else (capi.DFMA_PASS if K % 4 == 2 else 0)
     return ((K % 100) << 16) | (capi.INPLACE if K >= 100 else capi.PIPELINED) | alt
 
 
@@ -384,11 +384,11 @@ def test_pipelined_blocks_equal_inplace_blocks_and_oracle(ctx, m, ns, K):
     _assert_dense_equal(b, ref)
     assert _same_bits(a["T"], b["T"])
     # the step kernel as a cluster of 8 CTAs (default: 16 where the device places such clusters), and the pass kernel that
-    # loads a whole tile before it computes / the DMMA pass / the persistent step kernel (defaults: scalar-DFMA pass software-pipelined
-    # in halves, one step launch per pivot)
+    # loads a whole tile before it computes / the DMMA pass on ordinary loads / the scalar-DFMA pass in halves / the persistent step
+    # kernel (defaults: the ring pass, one step launch per pivot)
     for extra in (capi.STEP_CL8, capi.STEP_CL8 | capi.INPLACE, capi.WHOLE_TILE_PASS, capi.WHOLE_TILE_PASS | capi.INPLACE,
                   capi.DMMA_PASS, capi.DMMA_PASS | capi.INPLACE, capi.STEP_PERSISTENT, capi.STEP_PERSISTENT | capi.DMMA_PASS,
-                  capi.RING_PASS, capi.RING_PASS | capi.INPLACE):
+                  capi.DFMA_PASS, capi.DFMA_PASS | capi.INPLACE):
         c = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K) | extra)
         _assert_dense_equal(c, ref)
 
@@ -489,7 +489,7 @@ def test_pipelined_blocks_full_grid_2048x8192_bitwise(ctx):
     m, ns, Pn = 2048, 6144, 400
     outs = []
     for variant in (capi.RANK1, 0, capi.PIPELINED, capi.INPLACE, _blocked(24), capi.STEP_CL8 | capi.PIPELINED, capi.PIPELINED | capi.STEP_PERSISTENT | capi.DMMA_PASS,
-                    capi.PIPELINED | capi.RING_PASS, capi.INPLACE | capi.RING_PASS):
+                    capi.PIPELINED | capi.DFMA_PASS, capi.INPLACE | capi.DFMA_PASS):
         d = lp.DenseTableau(ctx, m, m + ns, 1)
         d.synth(1234, 7, ns)
         d.reset(log_cap=Pn, variant=variant)
@@ -514,7 +514,7 @@ def test_pipelined_blocks_two_objective_rows_full_grid_bitwise(ctx, method):
     T0, basis, n_art = lp.build_tableau(A, b, c, rel, R=2)
     Pn = 500
     ref = O.solve_f64(T0, basis, method=method, n_art=n_art, max_iter=Pn, threads=16, log_cap=Pn)
-    for variant in (capi.PIPELINED, capi.INPLACE, capi.PIPELINED | capi.STEP_PERSISTENT | capi.DMMA_PASS, capi.PIPELINED | capi.RING_PASS):
+    for variant in (capi.PIPELINED, capi.INPLACE, capi.PIPELINED | capi.STEP_PERSISTENT | capi.DMMA_PASS, capi.PIPELINED | capi.DFMA_PASS):
         got = lp.solve_dense(ctx, T0, basis, method=method, n_art=n_art, max_iter=Pn, log_cap=Pn, variant=variant)
         _assert_dense_equal(got, ref)
     assert ref["iters"] == Pn

@@ -8,7 +8,7 @@ from linearprogramming_b200 import capi
 m = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
 ctx = lp.Context(0)
 d = lp.DenseTableau(ctx, m, 2 * m, 1)
-for name, v in (("ring", capi.RING_PASS), ("mma", capi.DMMA_PASS), ("dfma_sp", 0)):
+for name, v in (("ring", 0), ("mma", capi.DMMA_PASS), ("dfma_sp", capi.DFMA_PASS)):
     for mode, mv in (("inplace", capi.INPLACE), ("pipe+launches", capi.PIPELINED), ("pipe+persistent", capi.PIPELINED | capi.STEP_PERSISTENT)):
         for K in ((32, 16) if not os.environ.get("PC_K32") else (32,)):
             try:

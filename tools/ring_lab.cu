@@ -42,7 +42,7 @@ int main(int argc, char **argv) {
     FlushParams U;
     memset(&U, 0, sizeof U);
     U.Tsrc = T0; U.kc_ptr = kcp; U.seq_ptr = kcp; U.flag = nullptr; U.l2first = 1; U.ld = ld; U.rows = rows; U.Fs = Fs; U.pcn = pcn; U.Pm = Pm;
-    U.task_ctr = ctr; U.seq = 0; U.pf = 1;
+    U.task_ctr = ctr; U.seq = 0; U.pf = 1; U.ring_nd = getenv("LPGPU_RING_ND") ? atoi(getenv("LPGPU_RING_ND")) : RG_ND;
     const long nct = (long)((ld + FL_COLS - 1) / FL_COLS), nrt = (rows + FL_ROWS - 1) / FL_ROWS;
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));

@@ -332,7 +332,7 @@ def gpu_arm(args):
 
     # ---- roofline of the dominant kernel: same region, every pass over the tableau bracketed by events
     from linearprogramming_b200 import capi as _capi
-    RANK1, INPLACE, WHOLE_TILE, PIPELINED_BIT = _capi.RANK1, _capi.INPLACE, _capi.WHOLE_TILE_PASS, _capi.PIPELINED
+    RANK1, INPLACE, PIPELINED_BIT = _capi.RANK1, _capi.INPLACE, _capi.PIPELINED
     blocked = not (variant & RANK1)
     # the default picks pipelined blocks from 0.8 GB of tableau on (csrc/dense.cu want_pipeline); 0x1000 forces them
     pipelined = blocked and not (variant & INPLACE) and bool((variant & PIPELINED_BIT) or (m + 1) * ((n + 1 + 15) // 16 * 16) * 8 >= (800 << 20))
@@ -352,11 +352,11 @@ def gpu_arm(args):
     upd_ms, sel_ms, upd_n, piv_n = kernel_times()
     peak, peak_src = measured_peak()
     traffic, traffic_src = None, None
-    pass_kernel = ("blk_flush_kernel" if variant & WHOLE_TILE else "blk_flush_mma_kernel" if variant & _capi.DMMA_PASS
+    pass_kernel = ("blk_flush_mma_kernel" if variant & _capi.DMMA_PASS
                    else "blk_flush_sp_kernel" if variant & _capi.DFMA_PASS else "blk_flush_ring_kernel")
     kname = pass_kernel if blocked else {0: "dense_update_dynamic", 1: "dense_update_tma_staged", 2: "dense_update_direct"}[variant & 0xf]
     try:        # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
-        tfile = {"blk_flush_kernel": "r1_flush_traffic.json", "blk_flush_sp_kernel": "r1_flush_sp_traffic.json",
+        tfile = {"blk_flush_sp_kernel": "r1_flush_sp_traffic.json",
                  "blk_flush_ring_kernel": "r2_flush_ring_traffic.json"}.get(pass_kernel, "none.json") if blocked else "r1_update_traffic.json"
         with open(os.path.join(ROOT, "profiles", tfile)) as f:
             tj = json.load(f)

@@ -35,7 +35,6 @@ PIPELINED = _H["VARIANT_PIPELINED"]            # dense, blocked path: always pip
 INPLACE = _H["VARIANT_INPLACE"]                # dense, blocked path: never pipeline (default: by size)
 DFMA_PASS = _H["VARIANT_DFMA_PASS"]            # dense, blocked path: the pass with scalar DFMAs (default: the ring pass, TMA ring of slabs + DMMA chain)
 DMMA_PASS = _H["VARIANT_DMMA_PASS"]            # dense, blocked path: the pass with the FP64 matrix instruction as the FMA chain (default: scalar DFMAs)
-WHOLE_TILE_PASS = _H["VARIANT_WHOLE_TILE"]     # dense, blocked path: the pass kernel that loads a whole tile before it computes
 STEP_PERSISTENT = _H["VARIANT_STEP_PERSISTENT"]  # dense, pipelined blocks: one persistent step launch per block (default: one cluster launch per pivot)
 STEP_CL8 = _H["VARIANT_STEP_CL8"]              # dense, blocked path: step kernel as a portable 8-CTA cluster
 BLAND = _H["VARIANT_BLAND"]                    # Bland's rule (primal methods)

@@ -450,10 +450,10 @@ static int setup_pipeline(lpgpu_dense *d) {
     return LPGPU_OK;
 }
 
-enum { PASS_RING = 0, PASS_DFMA = 1, PASS_DMMA = 2, PASS_WHOLE_TILE = 3 };
+enum { PASS_RING = 0, PASS_DFMA = 1, PASS_DMMA = 2 };
 static int pass_kind(const lpgpu_dense *d) {
     const int v = d->opts.variant;
-    return (v & LPGPU_VARIANT_WHOLE_TILE) ? PASS_WHOLE_TILE : (v & LPGPU_VARIANT_DMMA_PASS) ? PASS_DMMA : (v & LPGPU_VARIANT_DFMA_PASS) ? PASS_DFMA : PASS_RING;
+    return (v & LPGPU_VARIANT_DMMA_PASS) ? PASS_DMMA : (v & LPGPU_VARIANT_DFMA_PASS) ? PASS_DFMA : PASS_RING;
 }
 static int launch_pass_kernel(lpgpu_dense *d, const FlushParams &U, cudaStream_t stream);
 
@@ -565,12 +565,10 @@ static int launch_block_step(lpgpu_dense *d, int first) {
 
 // which pass kernel: default = the ring pass (dense_block_ring.cuh: TMA ring of slabs + DMMA chain, 0.36 ms per pass alone on the GPU at
 // 8192 x 16384); LPGPU_VARIANT_DFMA_PASS = scalar DFMAs, software-pipelined in half tiles (round 1's default, 0.50 ms);
-// LPGPU_VARIANT_DMMA_PASS = DMMA chain on tiles fetched with ordinary loads (0.66 ms); LPGPU_VARIANT_WHOLE_TILE = scalar DFMAs, whole
-// tile loaded before it computes.  All bit-identical.
+// LPGPU_VARIANT_DMMA_PASS = DMMA chain on tiles fetched with ordinary loads (0.66 ms).  All bit-identical.
 static int launch_pass_kernel(lpgpu_dense *d, const FlushParams &U, cudaStream_t stream) {
     lpgpu_ctx *ctx = d->ctx;
     switch (pass_kind(d)) {
-        case PASS_WHOLE_TILE: blk_flush_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U); break;
         case PASS_DMMA: blk_flush_mma_kernel<<<d->grid_flush, FL_THREADS, MM_SMEM_BYTES, stream>>>(U); break;
         case PASS_DFMA: blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U); break;
         default: blk_flush_ring_kernel<<<d->grid_flush, RG_THREADS, RG_SMEM_BYTES, stream>>>(U); break;
@@ -647,7 +645,7 @@ int size_grid(lpgpu_dense *d) {
     const int pk = pass_kind(d);
     if (pk == PASS_RING) LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_ring_kernel, RG_THREADS, RG_SMEM_BYTES));
     else if (pk == PASS_DMMA) LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_mma_kernel, FL_THREADS, MM_SMEM_BYTES));
-    else LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, pk == PASS_WHOLE_TILE ? blk_flush_kernel : blk_flush_sp_kernel, FL_THREADS, FL_SMEM_BYTES));
+    else LP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, blk_flush_sp_kernel, FL_THREADS, FL_SMEM_BYTES));
     const long fct = (long)((d->ld + FL_COLS - 1) / FL_COLS);
     const char *erb = getenv("LPGPU_FL_RB"), *epf = getenv("LPGPU_FL_PF");      // tuning aids
     d->fl_rb = (erb && atoi(erb) > 0) ? atoi(erb) : pk == PASS_RING ? 2 * FL_RB : FL_RB;
@@ -657,6 +655,209 @@ int size_grid(lpgpu_dense *d) {
     d->grid_flush = (int)std::max(1L, std::min((long)ctx->sm_count * std::max(1, occf), fct * fsb));
     d->flush_tasks = std::max(1L, fct * fsb);
     return LPGPU_OK;
+}
+
+// ---- one lpgpu_dense_run call: what its loops share
+struct RunCall {
+    lpgpu_dense *d = nullptr;
+    int max_pivots = 0;
+    bool timed = false, dirty = false;
+    int launched = 0;           // pivots enqueued (and known to have been applied) so far
+    int done_updates = 0;       // passes over the tableau
+    int iters_before = 0;
+    double upd_ms = 0.0, sel_ms = 0.0;
+    std::vector<int> kinds;     // timed mode: 0 = step, 1 = pass, in launch order (events 2 i, 2 i + 1)
+    bool pipe = false, persist = false;
+    int K = BLK_KMAX;
+};
+
+// blocked path: enqueue one step launch (kind 0; the persistent kernel: nsteps pivots) or the pass that closes the block (kind 1)
+int run_enqueue(RunCall &R, int kind, int first, int nsteps = 1) {
+    lpgpu_dense *d = R.d;
+    lpgpu_ctx *ctx = d->ctx;
+    const size_t e = 2 * R.kinds.size();
+    const bool pass_on_stream2 = kind && R.pipe;
+    if (R.timed) {
+        while (d->ev.size() < e + 2) {
+            cudaEvent_t ev;
+            LP_CUDA(ctx, cudaEventCreate(&ev));
+            d->ev.push_back(ev);
+        }
+        if (!pass_on_stream2) LP_CUDA(ctx, cudaEventRecord(d->ev[e], ctx->stream));
+    }
+    int rc;
+    if (pass_on_stream2) rc = close_block_pipe(d, R.timed ? d->ev[e] : nullptr, R.timed ? d->ev[e + 1] : nullptr);
+    else rc = kind ? launch_block_flush(d) : (R.persist ? launch_block_steps(d, nsteps, first) : launch_block_step(d, first));
+    if (rc != LPGPU_OK) return rc;
+    if (R.timed) {
+        if (!pass_on_stream2) LP_CUDA(ctx, cudaEventRecord(d->ev[e + 1], ctx->stream));
+        R.kinds.push_back(kind);
+    }
+    return LPGPU_OK;
+}
+
+int run_flush(RunCall &R) {
+    const int rc = run_enqueue(R, 1, 0);
+    R.d->blk_open = false;
+    R.d->blk_steps = 0;
+    ++R.done_updates;
+    return rc;
+}
+
+// the tableau in d->T is brought up to date (in stream order): open block closed, pass in flight waited for
+int run_settle(RunCall &R) {
+    if (R.d->blk_open) { const int rc = run_flush(R); if (rc != LPGPU_OK) return rc; }
+    return R.pipe ? drain_pipe(R.d) : LPGPU_OK;
+}
+
+// timed mode: add up the event pairs recorded since the last call
+int run_collect(RunCall &R) {
+    lpgpu_dense *d = R.d;
+    lpgpu_ctx *ctx = d->ctx;
+    if (R.pipe && !R.kinds.empty()) LP_CUDA(ctx, cudaStreamSynchronize(d->stream2));
+    for (size_t i = 0; i < R.kinds.size(); ++i) {
+        float ms = 0.f;
+        LP_CUDA(ctx, cudaEventElapsedTime(&ms, d->ev[2 * i], d->ev[2 * i + 1]));
+        (R.kinds[i] ? R.upd_ms : R.sel_ms) += ms;
+    }
+    R.kinds.clear();
+    return LPGPU_OK;
+}
+
+// two-phase: the drive-out pivots between the phases are decided by the rank-1 path's full decision (it scans tableau rows),
+// a few pivots at a time, on a tableau brought up to date first; afterwards the blocked path re-reads its objective rows and
+// b column and carries on in the main phase
+int run_driveout(RunCall &R) {
+    lpgpu_dense *d = R.d;
+    while (d->h_st->status == LPGPU_RUNNING && d->h_st->phase == PH_DRIVEOUT && R.launched < R.max_pivots) {
+        const int chunk = std::min(8, R.max_pivots - R.launched);
+        for (int c = 0; c < chunk; ++c) {
+            int rc = launch_select(d, -1, 0);
+            if (rc == LPGPU_OK) rc = launch_update(d, nullptr);
+            if (rc != LPGPU_OK) return rc;
+        }
+        R.launched += chunk;
+        const int rc = read_state(d);
+        if (rc != LPGPU_OK) return rc;
+    }
+    return launch_block_init(d);
+}
+
+// ---- blocked path: K step kernels (decide a pivot each on lazily updated slices), then one pass over the tableau that applies
+// them all -- in place, or pipelined with the decisions of the next block
+int run_blocked(RunCall &R) {
+    lpgpu_dense *d = R.d;
+    int rc = LPGPU_OK;
+    // pipelined blocks (default by size; LPGPU_VARIANT_INPLACE = never): the pass of a block overlaps the decisions of the next one
+    d->pipe_on = false;
+    if (want_pipeline(d)) {
+        rc = setup_pipeline(d);
+        if (rc != LPGPU_OK) return rc;
+        d->pipe_on = d->pipe_state == 1;
+    }
+    R.pipe = d->pipe_on;
+    R.K = make_bufs(d).K;             // pivots per block (depends on the order chosen above)
+    // pipelined blocks of the primal methods: one launch of the step cluster per pivot; LPGPU_VARIANT_STEP_PERSISTENT: one
+    // persistent launch decides all the pivots of a block (dense_steps.cuh; same bits, measured slower: 42 k against 55 k pivots/s)
+    d->persist_on = false;
+    if (R.pipe && d->opts.method != LPGPU_DUAL && (d->opts.variant & LPGPU_VARIANT_STEP_PERSISTENT)) {
+        rc = setup_steps(d);
+        if (rc != LPGPU_OK) return rc;
+        d->persist_on = d->steps_state == 1;
+    }
+    R.persist = d->persist_on;
+    if (R.dirty) { rc = launch_block_init(d); if (rc != LPGPU_OK) return rc; }
+    if (d->h_st->phase == PH_DRIVEOUT) { rc = run_settle(R); if (rc == LPGPU_OK) rc = run_driveout(R); if (rc != LPGPU_OK) return rc; }
+    const int chunk_max = d->opts.check_every;
+    while (R.launched < R.max_pivots && d->h_st->status == LPGPU_RUNNING) {
+        const int chunk = std::min(chunk_max, R.max_pivots - R.launched);
+        for (int c = 0; c < chunk;) {
+            const int nst = R.persist ? std::min(chunk - c, R.K - d->blk_steps) : 1;     // persistent: all the pivots the block still has room for
+            rc = run_enqueue(R, 0, d->blk_open ? 0 : 1, nst);
+            if (rc != LPGPU_OK) return rc;
+            d->blk_open = true;
+            d->blk_steps += nst;
+            c += nst;
+            if (d->blk_steps >= R.K) { rc = run_flush(R); if (rc != LPGPU_OK) return rc; }
+        }
+        rc = read_state(d);
+        if (rc == LPGPU_OK && R.timed) rc = run_collect(R);
+        if (rc != LPGPU_OK) return rc;
+        // launches after a phase switch (or a terminal status) were no-ops: only the applied pivots count
+        R.launched += (d->h_st->status == LPGPU_RUNNING && d->h_st->phase == PH_DRIVEOUT) ? d->h_st->iters - R.iters_before : chunk;
+        R.iters_before = d->h_st->iters;
+        if (d->h_st->status != LPGPU_RUNNING) break;
+        if (d->h_st->phase == PH_DRIVEOUT) {
+            rc = run_settle(R);
+            if (rc == LPGPU_OK) rc = run_driveout(R);
+            if (rc != LPGPU_OK) return rc;
+            R.iters_before = d->h_st->iters;
+        }
+    }
+    // pipelined and still running: the open block and the pass in flight stay pending, so that the next run call continues the
+    // pipeline (z comes from the eagerly kept objective rows; download / reset / upload / ... settle first)
+    const bool keep_pending = R.pipe && !R.timed && d->h_st->status == LPGPU_RUNNING && d->h_st->phase != PH_DRIVEOUT;
+    if (!keep_pending) { rc = run_settle(R); if (rc != LPGPU_OK) return rc; }
+    if (d->h_st->status == LPGPU_RUNNING) {
+        // decision only (budget is spent): settles a terminal status
+        rc = (d->h_st->phase == PH_DRIVEOUT) ? launch_select(d, -1, 0)
+             : R.persist ? launch_block_steps(d, 0, d->blk_open ? 0 : 1) : launch_block_step(d, d->blk_open ? 0 : 1);
+        if (rc != LPGPU_OK) return rc;
+    }
+    rc = read_state(d);
+    if (rc == LPGPU_OK && R.timed) rc = run_collect(R);
+    if (rc != LPGPU_OK) return rc;
+    // the decision-only step may have found a terminal status (or the end of phase one): nothing stays pending then
+    if (d->h_st->status != LPGPU_RUNNING || d->h_st->phase == PH_DRIVEOUT) rc = run_settle(R);
+    return rc;
+}
+
+// ---- rank-1 path: (select, eliminate) pairs, one pass over the tableau per pivot
+int run_rank1(RunCall &R) {
+    lpgpu_dense *d = R.d;
+    lpgpu_ctx *ctx = d->ctx;
+    const int chunk_max = d->opts.check_every;
+    int rc = LPGPU_OK;
+    while (d->ev.size() < (size_t)3 * chunk_max && R.timed) {
+        cudaEvent_t e;
+        LP_CUDA(ctx, cudaEventCreate(&e));
+        d->ev.push_back(e);
+    }
+    while (R.launched < R.max_pivots) {
+        const int chunk = std::min(chunk_max, R.max_pivots - R.launched);
+        for (int c = 0; c < chunk; ++c) {
+            if (R.timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c], ctx->stream));
+            rc = launch_select(d, -1, 0);
+            if (rc != LPGPU_OK) return rc;
+            if (R.timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c + 1], ctx->stream));
+            rc = launch_update(d, nullptr);
+            if (rc != LPGPU_OK) return rc;
+            if (R.timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c + 2], ctx->stream));
+        }
+        R.launched += chunk;
+        rc = read_state(d);
+        if (rc != LPGPU_OK) return rc;
+        const int did = d->h_st->iters - R.iters_before;      // pivots applied in this chunk
+        R.iters_before = d->h_st->iters;
+        R.done_updates += did;
+        if (R.timed) {
+            for (int c = 0; c < did && c < chunk; ++c) {
+                float a = 0.f, b = 0.f;
+                LP_CUDA(ctx, cudaEventElapsedTime(&a, d->ev[3 * c], d->ev[3 * c + 1]));
+                LP_CUDA(ctx, cudaEventElapsedTime(&b, d->ev[3 * c + 1], d->ev[3 * c + 2]));
+                R.sel_ms += a;
+                R.upd_ms += b;
+            }
+        }
+        if (d->h_st->status != LPGPU_RUNNING) break;
+    }
+    if (d->h_st->status == LPGPU_RUNNING) {
+        // budget spent: one decision-only select settles a terminal status (optimal, iteration limit, ...) without applying a
+        // pivot, so a run of exactly the needed pivots reports it
+        rc = launch_select(d, -1, 0);
+        if (rc == LPGPU_OK) rc = read_state(d);
+    }
+    return rc;
 }
 
 bool opts_ok(const lpgpu_opts *o, int n, int R) {
@@ -724,8 +925,6 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     if (e == cudaSuccess) e = cudaMemsetAsync(d->Ft, 0, 2 * pcn * BLK_KMAX * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->Pm, 0, 2 * (size_t)BLK_KMAX * d->ld * sizeof(double), ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d->rowstamp, 0, pcn * sizeof(int), ctx->stream);
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(blk_flush_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL_SMEM_BYTES);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(blk_flush_sp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL_SMEM_BYTES);
     if (e == cudaSuccess)
@@ -883,190 +1082,23 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
     if (!d || !res || max_pivots < 0) return LPGPU_EINVAL;
     lpgpu_ctx *ctx = d->ctx;
     LP_CUDA(ctx, cudaSetDevice(ctx->device));
-    const bool timed = d->opts.time_kernels != 0;
-    const int chunk_max = d->opts.check_every;
-    if (timed && d->ev.size() < (size_t)3 * chunk_max) {
-        while (d->ev.size() < (size_t)3 * chunk_max) {
-            cudaEvent_t e;
-            LP_CUDA(ctx, cudaEventCreate(&e));
-            d->ev.push_back(e);
-        }
-    }
+    RunCall R;
+    R.d = d; R.max_pivots = max_pivots; R.timed = d->opts.time_kernels != 0;
     // a pipelined run call leaves its last block(s) pending; anything but another pipelined run call needs the tableau itself
     int rc = LPGPU_OK;
-    if (d->up_pending || !(use_blocked(d) && want_pipeline(d) && d->pipe_state == 1 && d->pipe_on && !timed)) rc = settle_dense(d);
+    if (d->up_pending || !(use_blocked(d) && want_pipeline(d) && d->pipe_state == 1 && d->pipe_on && !R.timed)) rc = settle_dense(d);
     if (rc == LPGPU_OK) rc = read_state(d);
     if (rc != LPGPU_OK) return rc;
     d->h_st->budget = max_pivots;
-    const bool dirty = d->la_dirty;
-    if (dirty) d->h_st->k_next = 0;             // never trust a lookahead across an upload / synth / forced pivot
+    R.dirty = d->la_dirty;
+    if (R.dirty) d->h_st->k_next = 0;             // never trust a lookahead across an upload / synth / forced pivot
     d->la_dirty = false;
     LP_CUDA(ctx, cudaMemcpyAsync(d->st, d->h_st, sizeof(PivotState), cudaMemcpyHostToDevice, ctx->stream));
-    int launched = 0, done_updates = 0;
-    double upd_ms = 0.0, sel_ms = 0.0;
-    int iters_before = d->h_st->iters;
-    const bool blocked = use_blocked(d);
-    if (blocked) {
-        // ---- blocked path: K step kernels (decide a pivot each on lazily updated slices), then one pass over
-        // the tableau that applies them all; the tableau is brought up to date before this call returns
-        // pipelined blocks (default by size; variant bit 0x2000 = in place): the pass of a block overlaps the decisions of the next one
-        d->pipe_on = false;
-        if (want_pipeline(d)) {
-            rc = setup_pipeline(d);
-            if (rc != LPGPU_OK) return rc;
-            d->pipe_on = d->pipe_state == 1;
-        }
-        const bool pipe = d->pipe_on;
-        const int K = make_bufs(d).K;           // pivots per block (depends on the order chosen above)
-        // pipelined blocks of the primal methods: one launch of the step cluster per pivot; LPGPU_VARIANT_STEP_PERSISTENT: one
-        // persistent launch decides all the pivots of a block (dense_steps.cuh; same bits, measured slower: 42 k against 55 k pivots/s)
-        d->persist_on = false;
-        if (pipe && d->opts.method != LPGPU_DUAL && (d->opts.variant & LPGPU_VARIANT_STEP_PERSISTENT)) {
-            rc = setup_steps(d);
-            if (rc != LPGPU_OK) return rc;
-            d->persist_on = d->steps_state == 1;
-        }
-        const bool persist = d->persist_on;
-        if (dirty) { rc = launch_block_init(d); if (rc != LPGPU_OK) return rc; }
-        std::vector<int> kinds;                 // timed mode: 0 = step, 1 = flush, in launch order
-        auto enqueue = [&](int kind, int first, int nsteps = 1) -> int {
-            const size_t e = 2 * kinds.size();
-            if (timed) {
-                while (d->ev.size() < e + 2) {
-                    cudaEvent_t ev;
-                    LP_CUDA(ctx, cudaEventCreate(&ev));
-                    d->ev.push_back(ev);
-                }
-                if (!(kind && pipe)) LP_CUDA(ctx, cudaEventRecord(d->ev[e], ctx->stream));
-            }
-            int rc2;
-            if (kind && pipe) { rc2 = close_block_pipe(d, timed ? d->ev[e] : nullptr, timed ? d->ev[e + 1] : nullptr); }
-            else rc2 = kind ? launch_block_flush(d) : (persist ? launch_block_steps(d, nsteps, first) : launch_block_step(d, first));
-            if (rc2 != LPGPU_OK) return rc2;
-            if (timed) { if (!(kind && pipe)) LP_CUDA(ctx, cudaEventRecord(d->ev[e + 1], ctx->stream)); kinds.push_back(kind); }
-            return LPGPU_OK;
-        };
-        auto flush = [&]() -> int {
-            const int rc2 = enqueue(1, 0);
-            d->blk_open = false;
-            d->blk_steps = 0;
-            ++done_updates;
-            return rc2;
-        };
-        // the tableau in d->T is brought up to date (in stream order): open block closed, pass in flight waited for
-        auto settle = [&]() -> int {
-            if (d->blk_open) { const int rc2 = flush(); if (rc2 != LPGPU_OK) return rc2; }
-            return pipe ? drain_pipe(d) : LPGPU_OK;
-        };
-        auto collect = [&]() -> int {
-            if (pipe && !kinds.empty()) LP_CUDA(ctx, cudaStreamSynchronize(d->stream2));
-            for (size_t i = 0; i < kinds.size(); ++i) {
-                float ms = 0.f;
-                LP_CUDA(ctx, cudaEventElapsedTime(&ms, d->ev[2 * i], d->ev[2 * i + 1]));
-                (kinds[i] ? upd_ms : sel_ms) += ms;
-            }
-            kinds.clear();
-            return LPGPU_OK;
-        };
-        // two-phase: the drive-out pivots between the phases are decided by the rank-1 path's full decision
-        // (it scans tableau rows), a few pivots at a time, on a tableau brought up to date first; afterwards the
-        // blocked path re-reads its objective rows and b column and carries on in the main phase
-        auto driveout = [&]() -> int {
-            while (d->h_st->status == LPGPU_RUNNING && d->h_st->phase == PH_DRIVEOUT && launched < max_pivots) {
-                const int chunk = std::min(8, max_pivots - launched);
-                for (int c = 0; c < chunk; ++c) {
-                    int rc2 = launch_select(d, -1, 0);
-                    if (rc2 == LPGPU_OK) rc2 = launch_update(d, nullptr);
-                    if (rc2 != LPGPU_OK) return rc2;
-                }
-                launched += chunk;
-                const int rc2 = read_state(d);
-                if (rc2 != LPGPU_OK) return rc2;
-            }
-            return launch_block_init(d);
-        };
-        if (d->h_st->phase == PH_DRIVEOUT) { rc = settle(); if (rc == LPGPU_OK) rc = driveout(); if (rc != LPGPU_OK) return rc; }
-        while (launched < max_pivots && d->h_st->status == LPGPU_RUNNING) {
-            const int chunk = std::min(chunk_max, max_pivots - launched);
-            for (int c = 0; c < chunk;) {
-                const int nst = persist ? std::min(chunk - c, K - d->blk_steps) : 1;     // persistent: all the pivots the block still has room for
-                rc = enqueue(0, d->blk_open ? 0 : 1, nst);
-                if (rc != LPGPU_OK) return rc;
-                d->blk_open = true;
-                d->blk_steps += nst;
-                c += nst;
-                if (d->blk_steps >= K) { rc = flush(); if (rc != LPGPU_OK) return rc; }
-            }
-            rc = read_state(d);
-            if (rc == LPGPU_OK && timed) rc = collect();
-            if (rc != LPGPU_OK) return rc;
-            // launches after a phase switch (or a terminal status) were no-ops: only the applied pivots count
-            launched += (d->h_st->status == LPGPU_RUNNING && d->h_st->phase == PH_DRIVEOUT) ? d->h_st->iters - iters_before : chunk;
-            iters_before = d->h_st->iters;
-            if (d->h_st->status != LPGPU_RUNNING) break;
-            if (d->h_st->phase == PH_DRIVEOUT) {
-                rc = settle();
-                if (rc != LPGPU_OK) return rc;
-                rc = driveout();
-                if (rc != LPGPU_OK) return rc;
-                iters_before = d->h_st->iters;
-            }
-        }
-        // pipelined and still running: the open block and the pass in flight stay pending, so that the next run call
-        // continues the pipeline (z comes from the eagerly kept objective rows; download / reset / upload / ... settle first)
-        const bool keep_pending = pipe && !timed && d->h_st->status == LPGPU_RUNNING && d->h_st->phase != PH_DRIVEOUT;
-        if (!keep_pending) { rc = settle(); if (rc != LPGPU_OK) return rc; }
-        if (d->h_st->status == LPGPU_RUNNING) {
-            // decision only (budget is spent): settles a terminal status
-            rc = (d->h_st->phase == PH_DRIVEOUT) ? launch_select(d, -1, 0)
-                 : persist ? launch_block_steps(d, 0, d->blk_open ? 0 : 1) : launch_block_step(d, d->blk_open ? 0 : 1);
-            if (rc != LPGPU_OK) return rc;
-        }
-        rc = read_state(d);
-        if (rc == LPGPU_OK && timed) rc = collect();
-        if (rc != LPGPU_OK) return rc;
-        // the decision-only step may have found a terminal status (or the end of phase one): nothing stays pending then
-        if (d->h_st->status != LPGPU_RUNNING || d->h_st->phase == PH_DRIVEOUT) { rc = settle(); if (rc != LPGPU_OK) return rc; }
-    }
-    while (!blocked && launched < max_pivots) {
-        const int chunk = std::min(chunk_max, max_pivots - launched);
-        for (int c = 0; c < chunk; ++c) {
-            if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c], ctx->stream));
-            rc = launch_select(d, -1, 0);
-            if (rc != LPGPU_OK) return rc;
-            if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c + 1], ctx->stream));
-            rc = launch_update(d, nullptr);
-            if (rc != LPGPU_OK) return rc;
-            if (timed) LP_CUDA(ctx, cudaEventRecord(d->ev[3 * c + 2], ctx->stream));
-        }
-        launched += chunk;
-        rc = read_state(d);
-        if (rc != LPGPU_OK) return rc;
-        const int did = d->h_st->iters - iters_before;      // pivots applied in this chunk
-        iters_before = d->h_st->iters;
-        done_updates += did;
-        if (timed) {
-            for (int c = 0; c < did && c < chunk; ++c) {
-                float a = 0.f, b = 0.f;
-                LP_CUDA(ctx, cudaEventElapsedTime(&a, d->ev[3 * c], d->ev[3 * c + 1]));
-                LP_CUDA(ctx, cudaEventElapsedTime(&b, d->ev[3 * c + 1], d->ev[3 * c + 2]));
-                sel_ms += a;
-                upd_ms += b;
-            }
-        }
-        if (d->h_st->status != LPGPU_RUNNING) break;
-    }
-    if (!blocked && d->h_st->status == LPGPU_RUNNING) {
-        // budget spent: one decision-only select settles a terminal status (optimal, iteration
-        // limit, ...) without applying a pivot, so a run of exactly the needed pivots reports it
-        rc = launch_select(d, -1, 0);
-        if (rc != LPGPU_OK) return rc;
-        rc = read_state(d);
-        if (rc != LPGPU_OK) return rc;
-    }
-    // objective cells
+    R.iters_before = d->h_st->iters;
+    rc = use_blocked(d) ? run_blocked(R) : run_rank1(R);
+    if (rc != LPGPU_OK) return rc;
+    // objective cells: with blocks pending the tableau's own objective cells are behind, the eagerly kept objective rows hold the same bits
     double zc[2] = {0.0, 0.0};
-    // with blocks pending the tableau's own objective cells are behind: the eagerly kept objective rows hold the same bits
     const double *zsrc = (d->pend || d->blk_open) ? d->objcur : d->T + (size_t)d->m * d->ld;
     LP_CUDA(ctx, cudaMemcpyAsync(&zc[0], zsrc, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     if (d->R == 2)
@@ -1080,9 +1112,9 @@ int lpgpu_dense_run(lpgpu_dense *d, int max_pivots, lpgpu_result *res) {
     res->z = -zc[0];
     res->zM = (d->R == 2) ? -zc[1] : 0.0;
     res->n_logged = std::min(res->iters, d->log_cap);
-    res->update_launches = done_updates;
-    res->update_ms = (float)upd_ms;
-    res->select_ms = (float)sel_ms;
+    res->update_launches = R.done_updates;
+    res->update_ms = (float)R.upd_ms;
+    res->select_ms = (float)R.sel_ms;
     return LPGPU_OK;
 }
 

@@ -10,7 +10,7 @@
 //     ratio test            on the eagerly maintained b column  bcur                   -> r_t
 //     row r_t, current      = T[r_t,:] run through the pivots s < t, divided by a_rk   -> P[t,:]
 //     objcur, bcur          updated with (F[:,t], P[t,:]);  next entering column priced
-//   per block (blk_flush_kernel, persistent grid):
+//   per block (the pass: blk_flush_ring_kernel, persistent grid):
 //     a_ij <- fma(-F[i,K-1], P[K-1,j], ... fma(-F[i,0], P[0,j], a_ij))   every element, once
 //     (a row that was the pivot row of step s restarts from P[s,j] and runs the steps after s)
 //
@@ -591,205 +591,8 @@ struct FlTile {
     int rt;             // row tile index
 };
 
-__device__ __forceinline__ void fl_load_tile(const FlushParams &U, const FlTile &t, int wr, int jc, double2 (&acc)[FL_TR][2]) {
-    const int i0 = t.rt * FL_ROWS + FL_TR * wr;
-    const double *tp = U.Tsrc + (size_t)i0 * U.ld + t.j0 + jc;
-    const bool ok0 = jc < t.ncols, ok1 = jc + 64 < t.ncols;
-#pragma unroll
-    for (int rr = 0; rr < FL_TR; ++rr) {
-        const bool rowok = i0 + rr < U.rows;
-        acc[rr][0] = (ok0 && rowok) ? ld_stream2(tp + (size_t)rr * U.ld) : make_double2(0.0, 0.0);
-        acc[rr][1] = (ok1 && rowok) ? ld_stream2(tp + (size_t)rr * U.ld + 64) : make_double2(0.0, 0.0);
-    }
-}
-
-// HBM -> L2 prefetch of a tile (no registers involved): thread i < FL_ROWS asks for row i's segment.
-__device__ __forceinline__ void fl_prefetch_tile(const FlushParams &U, const FlTile &t) {
-    const int i = t.rt * FL_ROWS + (int)threadIdx.x;
-    if ((int)threadIdx.x < FL_ROWS && i < U.rows)
-        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(U.Tsrc + (size_t)i * U.ld + t.j0), "r"(t.ncols * 8) : "memory");
-}
-
-// the chain of kc steps on one thread's 16 x 4 elements, then the store
-// fw: this warp's 16 multipliers of step 0 in the staged tile sF[s][FL_ROWS] (row pairs = one LDS.128)
-__device__ __forceinline__ void fl_chain_tile(int kc, const double *fw, const double *pw, double2 (&acc)[FL_TR][2]) {
-    int s = 0;
-    for (; s + 1 < kc; s += 2) {
-        double2 p[2][2];                                  // [step][column pair]
-#pragma unroll
-        for (int e = 0; e < 2; ++e)
-#pragma unroll
-            for (int q = 0; q < 2; ++q) p[e][q] = *reinterpret_cast<const double2 *>(pw + (size_t)(s + e) * FL_COLS + 64 * q);
-#pragma unroll
-        for (int rg = 0; rg < FL_TR; rg += FL_RG) {
-            double2 f[2][FL_RG / 2];                  // [step][row pair]: multipliers of FL_RG rows (broadcast loads)
-#pragma unroll
-            for (int e = 0; e < 2; ++e)
-#pragma unroll
-                for (int u = 0; u < FL_RG / 2; ++u) f[e][u] = *reinterpret_cast<const double2 *>(fw + (size_t)(s + e) * FL_ROWS + rg + 2 * u);
-#pragma unroll
-            for (int e = 0; e < 2; ++e)
-#pragma unroll
-                for (int u = 0; u < FL_RG / 2; ++u)
-#pragma unroll
-                    for (int q = 0; q < 2; ++q) {
-                        acc[rg + 2 * u][q].x = __fma_rn(-f[e][u].x, p[e][q].x, acc[rg + 2 * u][q].x);
-                        acc[rg + 2 * u][q].y = __fma_rn(-f[e][u].x, p[e][q].y, acc[rg + 2 * u][q].y);
-                        acc[rg + 2 * u + 1][q].x = __fma_rn(-f[e][u].y, p[e][q].x, acc[rg + 2 * u + 1][q].x);
-                        acc[rg + 2 * u + 1][q].y = __fma_rn(-f[e][u].y, p[e][q].y, acc[rg + 2 * u + 1][q].y);
-                    }
-            asm volatile("" ::: "memory");            // keeps the next group's loads from being hoisted (register budget)
-        }
-    }
-    if (s < kc) {                                  // odd number of steps: the last one alone
-        double2 p[2];
-#pragma unroll
-        for (int q = 0; q < 2; ++q) p[q] = *reinterpret_cast<const double2 *>(pw + (size_t)s * FL_COLS + 64 * q);
-#pragma unroll
-        for (int rr = 0; rr < FL_TR; ++rr) {
-            const double f = fw[(size_t)s * FL_ROWS + rr];
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                acc[rr][q].x = __fma_rn(-f, p[q].x, acc[rr][q].x);
-                acc[rr][q].y = __fma_rn(-f, p[q].y, acc[rr][q].y);
-            }
-        }
-    }
-}
-
-__device__ __forceinline__ void fl_store_tile(const FlushParams &U, const FlTile &t, int wr, int jc, double2 (&acc)[FL_TR][2]) {
-    const int i0 = t.rt * FL_ROWS + FL_TR * wr;
-    double *tp = U.T + (size_t)i0 * U.ld + t.j0 + jc;
-    const bool ok0 = jc < t.ncols, ok1 = jc + 64 < t.ncols;
-#pragma unroll
-    for (int rr = 0; rr < FL_TR; ++rr) {
-        const bool rowok = i0 + rr < U.rows;
-        if (ok0 && rowok) st_stream2(tp + (size_t)rr * U.ld, acc[rr][0]);
-        if (ok1 && rowok) st_stream2(tp + (size_t)rr * U.ld + 64, acc[rr][1]);
-    }
-}
-
-__device__ __forceinline__ void fl_apply_tile(const FlushParams &U, const FlTile &t, int wr, int jc, int kc, const double *fw,
-                                              const double *pw, double2 (&acc)[FL_TR][2]) {
-    fl_chain_tile(kc, fw, pw, acc);
-    fl_store_tile(U, t, wr, jc, acc);
-}
-
-// Three CTAs of four warps per SM (170 registers each: 64 accumulators, 32 operands, no spills): while one
-// CTA waits for its tile of the tableau, the others keep the FP64 pipe busy.
-__global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_kernel(FlushParams U) {
-    extern __shared__ __align__(128) unsigned char fl_smem[];
-    double *sP = reinterpret_cast<double *>(fl_smem);                                 // [BLK_KMAX][FL_COLS]
-    double *sF = sP + (size_t)BLK_KMAX * FL_COLS;                                     // [2][BLK_KMAX][FL_ROWS]
-    __shared__ __align__(8) uint64_t bar_p, bar_f[2];
-    __shared__ long s_task[2];
-
-    if (threadIdx.x == 0) {
-        mbar_init(&bar_p, 1);
-        mbar_init(&bar_f[0], 1);
-        mbar_init(&bar_f[1], 1);
-        fence_mbar_init();
-    }
-    pdl_wait();
-    int *ctr = U.task_ctr + (U.seq & 1u);
-    if (blockIdx.x == 0 && threadIdx.x == 0) U.task_ctr[(U.seq & 1u) ^ 1u] = 0;
-    if (U.flag) {
-        // Pipelined blocks: the SMs in U.resv are left to the step kernels of the next block.  A CTA that lands on one
-        // leaves as soon as it knows that some CTA of this launch works elsewhere (any one worker finishes the pass:
-        // tasks are claimed from a counter); if none shows up within 20 us it works after all -- placement only ever
-        // costs time, never the result.
-        unsigned smid;
-        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-        const int want = (int)(U.seq + 1u);
-        if ((U.resv[(smid >> 5) & 7u] >> (smid & 31u)) & 1u) {         // the same for every thread of the CTA
-            __shared__ int s_leave;
-            if (threadIdx.x == 0) {
-                unsigned long long t0, now;
-                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-                bool leave = false;
-                do {
-                    leave = (*(volatile int *)U.flag - want) >= 0;
-                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-                } while (!leave && now - t0 < 20000ull);
-                s_leave = leave ? 1 : 0;
-            }
-            __syncthreads();
-            if (s_leave) return;
-        } else if (threadIdx.x == 0) atomicMax(U.flag, want);
-    }
-    const int kc = *U.kc_ptr;
-    if (kc <= 0 && U.Tsrc == U.T) return;                              // nothing to apply (out of place: a plain copy)
-
-    const int nct = (int)((U.ld + FL_COLS - 1) / FL_COLS);
-    const int nrt = (U.rows + FL_ROWS - 1) / FL_ROWS;                  // row tiles
-    const int nsb = (nrt + U.rb - 1) / U.rb;                           // row super-blocks
-    const long ntasks = (long)nct * nsb;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int wr = warp;                                               // 4 warps stacked over 64 rows x 128 columns
-    const int jc = 2 * lane;                                           // this thread's first column pair inside the tile
-    const uint32_t FBYTES = (uint32_t)(kc * FL_ROWS * 8);
-    auto issue_f = [&](int rt, int fb) {           // thread 0: kc x (FL_ROWS multipliers) of one row tile
-        mbar_arrive_expect_tx(&bar_f[fb], FBYTES);
-        for (int s = 0; s < kc; ++s)
-            tma_load_1d(sF + ((size_t)fb * BLK_KMAX + s) * FL_ROWS, U.Fs + (size_t)s * U.pcn + (size_t)rt * FL_ROWS, (uint32_t)(FL_ROWS * 8), &bar_f[fb]);
-    };
-
-    if (threadIdx.x == 0) s_task[0] = (long)atomicAdd(ctr, 1);
-    __syncthreads();
-    uint32_t par_p = 0, par_f = 0;               // bit fb of par_f = parity of F buffer fb
-    for (int it = 0;; ++it) {
-        const long tt = s_task[it & 1];
-        if (tt >= ntasks) break;
-        FlTile t;
-        t.j0 = (size_t)(tt % nct) * FL_COLS;
-        t.ncols = (int)min((size_t)FL_COLS, U.ld - t.j0);              // a multiple of 16 (ld % 16 == 0)
-        const int rt0 = (int)(tt / nct) * U.rb, rt1 = min(rt0 + U.rb, nrt);
-        if (threadIdx.x == 0) {
-            s_task[(it & 1) ^ 1] = (long)atomicAdd(ctr, 1);            // next task; visible after the barriers below
-            mbar_arrive_expect_tx(&bar_p, (uint32_t)(kc * t.ncols * 8));
-            for (int s = 0; s < kc; ++s) tma_load_1d(sP + (size_t)s * FL_COLS, U.Pm + (size_t)s * U.ld + t.j0, (uint32_t)(t.ncols * 8), &bar_p);
-            issue_f(rt0, 0);
-        }
-        for (int rt = rt0; rt < rt1; ++rt) {
-            const int fb = (rt - rt0) & 1;
-            t.rt = rt;
-            double2 acc[FL_TR][2];
-            fl_load_tile(U, t, wr, jc, acc);
-            if (threadIdx.x == 0 && rt + 1 < rt1) issue_f(rt + 1, fb ^ 1);   // that F buffer was released by the barrier that ended tile rt-1
-            // the tile after this one starts its way from HBM into L2 now, so that DRAM keeps streaming while this
-            // CTA (and its neighbours on the SM) are busy on the FP64 pipe
-            {
-                const int dist = (U.pf >= 2) ? 2 : 1;          // how many tiles ahead (LPGPU_FL_PF)
-                for (int dd = (U.pf >= 2 && rt == rt0) ? 1 : dist; dd <= dist; ++dd) {
-                    FlTile nx = t;
-                    bool have = true;
-                    if (rt + dd < rt1) nx.rt = rt + dd;
-                    else {
-                        const long nt = s_task[(it & 1) ^ 1];   // claimed at the start of this task; visible since tile rt0's barrier
-                        const int over = rt + dd - rt1;           // tile index inside the next task
-                        have = (rt > rt0) && nt < ntasks && over < U.rb;
-                        if (have) {
-                            nx.j0 = (size_t)(nt % nct) * FL_COLS;
-                            nx.ncols = (int)min((size_t)FL_COLS, U.ld - nx.j0);
-                            nx.rt = (int)(nt / nct) * U.rb + over;
-                            have = nx.rt < nrt;
-                        }
-                    }
-                    if (have && U.pf) fl_prefetch_tile(U, nx);
-                }
-            }
-            if (rt == rt0) { mbar_wait(&bar_p, par_p); par_p ^= 1; }
-            mbar_wait(&bar_f[fb], (par_f >> fb) & 1u);
-            par_f ^= 1u << fb;
-            fl_apply_tile(U, t, wr, jc, kc, sF + (size_t)fb * BLK_KMAX * FL_ROWS + FL_TR * wr, sP + jc, acc);
-            __syncthreads();       // sF[fb] may be refilled (two tiles ahead), and at the last tile sP and s_task
-        }
-    }
-}
-
-// ------------------------------------------------------------------ the pass, software-pipelined in half tiles (default)
-// Same tiles, same operands, same chain as blk_flush_kernel; what changes is WHEN a thread's tableau loads are issued.
-// There a CTA loads its whole 64 x 128 tile (32 LDG.128 per thread), waits, runs the chain on it and stores it: memory
+// ------------------------------------------------------------------ the scalar pass, software-pipelined in half tiles (round 1's default; LPGPU_VARIANT_DFMA_PASS)
+// A CTA that loads its whole 64 x 128 tile (32 LDG.128 per thread), waits, runs the chain on it and stores it: memory
 // idles while the CTA computes and the FP64 pipe idles while it loads, and three CTAs per SM in arbitrary phase only
 // partly cover for one another (ncu: DRAM 50 %, FP64 pipe 53 % busy).  Here a thread's 16 rows are two halves of 8:
 // while the chain runs on one half (32 accumulator registers) the loads of the other half -- of this tile, or of the
@@ -884,7 +687,7 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_sp_kernel(FlushParams
     pdl_wait();
     int *ctr = U.task_ctr + (U.seq & 1u);
     if (blockIdx.x == 0 && threadIdx.x == 0) U.task_ctr[(U.seq & 1u) ^ 1u] = 0;
-    if (U.flag) {       // pipelined blocks: see blk_flush_kernel
+    if (U.flag) {       // pipelined blocks: see blk_flush_ring_kernel
         unsigned smid;
         asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
         const int want = (int)(U.seq + 1u);

@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(FL_THREADS, 3) blk_flush_mma_kernel(FlushParam
     pdl_wait();
     int *ctr = U.task_ctr + (U.seq & 1u);
     if (blockIdx.x == 0 && threadIdx.x == 0) U.task_ctr[(U.seq & 1u) ^ 1u] = 0;
-    if (U.flag) {       // pipelined blocks: CTAs that land on the SMs reserved for the step cluster leave (see blk_flush_kernel)
+    if (U.flag) {       // pipelined blocks: CTAs that land on the SMs reserved for the step cluster leave (see blk_flush_ring_kernel)
         unsigned smid;
         asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
         const int want = (int)(U.seq + 1u);

@@ -99,7 +99,11 @@ __global__ void __launch_bounds__(RG_THREADS, 1) blk_flush_ring_kernel(FlushPara
     pdl_wait();
     int *ctr = U.task_ctr + (U.seq & 1u);
     if (blockIdx.x == 0 && threadIdx.x == 0) U.task_ctr[(U.seq & 1u) ^ 1u] = 0;
-    if (U.flag) {       // pipelined blocks: CTAs that land on the SMs reserved for the step kernels leave (see blk_flush_kernel)
+    if (U.flag) {
+        // Pipelined blocks: the SMs in U.resv are left to the step kernels of the next block.  A CTA that lands on one
+        // leaves as soon as it knows that some CTA of this launch works elsewhere (any one worker finishes the pass:
+        // tasks are claimed from a counter); if none shows up within 20 us it works after all -- placement only ever
+        // costs time, never the result.
         unsigned smid;
         asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
         const int want = (int)(U.seq + 1u);

@@ -92,7 +92,7 @@ def test_header_constants_match_the_ctypes_mirror():
         assert defs[name] == getattr(capi, name), name
     # every option bit of lpgpu_opts.variant is a #define of the header; capi.py reads them from there
     for cname, hname in (("BLAND", "VARIANT_BLAND"), ("DEVEX", "VARIANT_DEVEX"), ("RANK1", "VARIANT_RANK1"), ("PIPELINED", "VARIANT_PIPELINED"),
-                         ("INPLACE", "VARIANT_INPLACE"), ("WHOLE_TILE_PASS", "VARIANT_WHOLE_TILE"), ("DMMA_PASS", "VARIANT_DMMA_PASS"), ("DFMA_PASS", "VARIANT_DFMA_PASS"), ("STEP_PERSISTENT", "VARIANT_STEP_PERSISTENT"), ("STEP_CL8", "VARIANT_STEP_CL8"),
+                         ("INPLACE", "VARIANT_INPLACE"), ("DMMA_PASS", "VARIANT_DMMA_PASS"), ("DFMA_PASS", "VARIANT_DFMA_PASS"), ("STEP_PERSISTENT", "VARIANT_STEP_PERSISTENT"), ("STEP_CL8", "VARIANT_STEP_CL8"),
                          ("NO_PDL", "VARIANT_NO_PDL"), ("NO_ALTERNATE", "VARIANT_NO_ALTERNATE"), ("STATIC", "VARIANT_UPD_STATIC"),
                          ("DIRECT", "VARIANT_UPD_DIRECT"), ("KEEP_FINAL", "VARIANT_BATCH_KEEP_FINAL"), ("FORCE_SMEM", "VARIANT_BATCH_SMEM")):
         assert defs[hname] == getattr(capi, cname), cname

@@ -383,10 +383,9 @@ def test_pipelined_blocks_equal_inplace_blocks_and_oracle(ctx, m, ns, K):
     _assert_dense_equal(a, ref)
     _assert_dense_equal(b, ref)
     assert _same_bits(a["T"], b["T"])
-    # the step kernel as a cluster of 8 CTAs (default: 16 where the device places such clusters), and the pass kernel that
-    # loads a whole tile before it computes / the DMMA pass on ordinary loads / the scalar-DFMA pass in halves / the persistent step
+    # the step kernel as a cluster of 8 CTAs (default: 16 where the device places such clusters), and the DMMA pass on ordinary loads / the scalar-DFMA pass in halves / the persistent step
     # kernel (defaults: the ring pass, one step launch per pivot)
-    for extra in (capi.STEP_CL8, capi.STEP_CL8 | capi.INPLACE, capi.WHOLE_TILE_PASS, capi.WHOLE_TILE_PASS | capi.INPLACE,
+    for extra in (capi.STEP_CL8, capi.STEP_CL8 | capi.INPLACE,
                   capi.DMMA_PASS, capi.DMMA_PASS | capi.INPLACE, capi.STEP_PERSISTENT, capi.STEP_PERSISTENT | capi.DMMA_PASS,
                   capi.DFMA_PASS, capi.DFMA_PASS | capi.INPLACE):
         c = lp.solve_dense(ctx, T0, basis, log_cap=8192, variant=_blocked(K) | extra)

@@ -574,6 +574,37 @@ def gpu_arm(args):
                                              "workload": f"one dense tableau {lm}x{ln} fp64 ({(lm + 1) * (ln + 1) * 8 / 1e9:.2f} GB) resident on one GPU, default path",
                                              "pivots": lpv, "us_per_pivot": 1e6 * t_big / lpv, "iters_after": r_big["iters"]}
 
+    # ---- extra (rank 0): the dual simplex (the reference's menu stub Source/router.c:32-34) on a 3000 x 5000
+    # dual-feasible LP: max c.x with c <= 0, about half the rows '>=' rows turned into '<=' rows with a negative b
+    if rank == 0 and not args.no_extra and m == M:
+        rng = np.random.default_rng(77)
+        dm, dns = 3000, 2000
+        A = rng.uniform(0.0, 1.5, size=(dm, dns))
+        A[rng.random((dm, dns)) < 0.2] = 0.0
+        ge = rng.random(dm) < 0.5
+        ax = A @ rng.uniform(0.0, 2.0, size=dns)
+        bb = np.where(ge, np.maximum(ax - rng.uniform(0.1, 1.0, dm), 0.05), ax + rng.uniform(0.1, 2.0, dm))
+        sgn = np.where(ge, -1.0, 1.0)
+        Td = np.zeros((dm + 1, dns + dm + 1))
+        Td[:dm, 0] = sgn * bb
+        Td[:dm, 1:dns + 1] = sgn[:, None] * A
+        Td[:dm, dns + 1:] = np.eye(dm)
+        Td[dm, 1:dns + 1] = -rng.uniform(0.1, 1.0, size=dns)
+        dd = lp.DenseTableau(ctx, dm, dns + dm, 1)
+        dd.upload(Td, (dns + 1 + np.arange(dm)).astype(np.int32))
+        dd.reset(method=lp.DUAL, check_every=256)
+        dd.run(32)
+        torch.cuda.synchronize()
+        ed0, ed1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ed0.record(stream)
+        r_d = dd.run(1 << 20)
+        ed1.record(stream)
+        torch.cuda.synchronize()
+        dd.close()
+        extra["dual_simplex"] = {"metric": "pivots_per_sec", "value": (r_d["iters"] - 32) / (ed0.elapsed_time(ed1) * 1e-3), "unit": "pivots/s",
+                                 "workload": f"dual simplex, {dm} x {dns + dm} fp64 dual-feasible LP, blocked path in place", "iters": r_d["iters"],
+                                 "status": lp.STATUS_NAMES[r_d["status"]]}
+
     # ---- extra (N > 1): BASELINE config 5b, ONE 16384 x 65536 tableau column-sharded over the ranks,
     # candidate + entering-column exchange per pivot over our own NCCL communicator
     if world > 1 and not args.no_extra:
@@ -635,6 +666,8 @@ def gpu_arm(args):
         big_n1 = bn1[0]
     if big_n1 is not None:
         sec["cfg5b_one_gpu"] = {"pivots_per_s": r3(big_n1)}
+    if "dual_simplex" in extra:
+        sec["dual_3000x5000"] = {"pivots_per_s": r3(extra["dual_simplex"]["value"]), "iters": extra["dual_simplex"]["iters"], "status": extra["dual_simplex"]["status"]}
     if "column_sharded" in extra:
         cs = extra["column_sharded"]
         sec["column_sharded"] = {"pivots_per_s": r3(cs["value"]), "us_per_pivot": r3(cs["us_per_pivot"]),

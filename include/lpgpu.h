@@ -80,7 +80,7 @@ extern "C" {
 #define LPGPU_VARIANT_RANK1         0x800      /* one pass over the tableau per pivot (default: one pass per block of pivots)      */
 #define LPGPU_VARIANT_PIPELINED     0x1000     /* blocked path: always pipeline the pass of a block with the next block's decisions */
 #define LPGPU_VARIANT_INPLACE       0x2000     /* blocked path: never pipeline (steps, pass, steps, ... on one stream, in place)    */
-                                               /* neither bit: pipelined from about 0.4 GB of tableau on                           */
+                                               /* neither bit: pipelined from 0.8 GB of tableau on                                 */
 #define LPGPU_VARIANT_STEP_CL8      0x8000     /* blocked path: step kernel as a portable 8-CTA cluster (default: 16 CTAs)         */
 #define LPGPU_VARIANT_STEP_PERSISTENT 0x40    /* pipelined blocks: one persistent step-kernel launch per block (default: one cluster launch per pivot, measured faster) */
 #define LPGPU_VARIANT_BLOCK_K(k)    (((k) & 0x3f) << 16)   /* blocked path: pivots per block, 1..32 (0 = 32)                       */

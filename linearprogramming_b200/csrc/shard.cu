@@ -344,6 +344,14 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
     const int gtid = crank * SELECT_THREADS + (int)threadIdx.x;
     constexpr int GSTRIDE = SELECT_CLUSTER * SELECT_THREADS;
 
+    auto stamp = [&](int slot) {        // LPGPU_BLK_DEBUG=1: phase times of a step (printed when the tableau object is destroyed)
+        if (B.dbg && gtid == 0) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            B.dbg[slot] = now;
+        }
+    };
+    stamp(0);
     cluster_entry_arrive();     // DSMEM rule: no remote access before every CTA of the cluster has started
     PivotState *st = P.st;
     const int status0 = st->status, iters = st->iters, budget = st->budget;
@@ -394,6 +402,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
             return;
         }
     }
+    stamp(1);                   // every rank's candidate has arrived
     int owner = 0;
     const Cand best = best_pair(xptr<double>(S.peer_x[S.rank], XLayout::pairs(ppar)), S.world, &owner);
     const int k = best.idx > 0 ? best.idx : 0;              // GLOBAL column
@@ -447,6 +456,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
                 if (gtid < S.world) st_release_sys(xptr<unsigned>(S.peer_x[gtid], XLayout::col_flag(par)), S.iter + 1u);
             }
             // ---- every rank: the column of this pivot has landed in its region
+            stamp(2);           // (owner: column computed, stored to every rank and flagged)
             if (threadIdx.x == 0) s_flag = spin_until(xptr<unsigned>(S.peer_x[S.rank], XLayout::col_flag(par)), S.iter + 1u, XCHG_TIMEOUT_NS) ? 1 : 0;
             __syncthreads();
             if (!s_flag) {
@@ -454,6 +464,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
                 if (gtid == 0) { st->status = LPGPU_EXCHANGE_TIMEOUT; st->do_pivot = 0; }
                 return;
             }
+            stamp(3);           // the column has arrived
             KeyCand c = keycand_none();
             for (int i = gtid; i < rows; i += GSTRIDE) {
                 const double a = __ldcg(mycol + i);
@@ -489,6 +500,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
         return;
     }
 
+    stamp(4);                   // ratio test done
     // ---- this rank's slice of row r, brought up to date and scaled; objective rows; local pricing
     const double sig_c = __ldcg(mycol + P.m);
     const double sig_m = (RR == 2) ? __ldcg(mycol + P.m + 1) : 0.0;
@@ -566,6 +578,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
     }
     for (int i = gtid; i < P.m; i += GSTRIDE)
         B.bcur[i] = (i == r) ? brp : __fma_rn(-B.Fs[(size_t)t * pcn + i], brp, B.bcur[i]);
+    stamp(5);                   // row, objective rows, b column done
     // ---- this rank's candidate for the next pivot -> every rank
     c = bigm ? cluster_key_best<true>(cl, c, scr_c, slot_c) : cluster_key_best<false>(cl, c, scr_c, slot_c);
     if (gtid < 32 && !forced) {                             // first warp of CTA 0: one lane per peer (a forced step posts nothing:
@@ -605,6 +618,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
         st->phase1_iters = (phase0 == PH_ONE) ? iters + 1 : p1;
         if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
     }
+    stamp(6);
 }
 
 __global__ void shard_synth_kernel(double *T, size_t ld, int m, int ns, int col0, int ncols, int *basis,
@@ -1026,6 +1040,7 @@ static int shard_run_blocked(lpgpu_shard *s, int max_pivots, lpgpu_result *res) 
                               : (bland ? shard_blk_step_kernel<1, true> : shard_blk_step_kernel<1, false>);
         kern<<<SELECT_CLUSTER, SELECT_THREADS, 0, ctx->stream>>>(S, make_bufs(d), first);
         LP_LAUNCH_CHECK(ctx);
+        if (d->blk_dbg) d->blk_dbg_n++;
         return LPGPU_OK;
     };
     int passes = 0;

@@ -332,8 +332,7 @@ constexpr int SSTEP_PB = 8, SSTEP_CPT = 2;
 // row, the lowest global column wins, its owner ships the column, and the row is pivoted without a ratio test.
 // BL: Bland's rule (every eligible column gets the same key; the lowest global column wins the exchange).
 template <int RR, bool BL>
-__global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
-shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
+__device__ __forceinline__ void shard_blk_step_body(const ShardParams &S, const BlockBufs &B, int first) {
     __shared__ KeyCand scr_b[SELECT_THREADS / 32], scr_c[SELECT_THREADS / 32];
     __shared__ KeyCand slot_b[SELECT_CLUSTER], slot_c[SELECT_CLUSTER];
     __shared__ double s_pk[BLK_KMAX], s_fr[BLK_KMAX];
@@ -354,14 +353,14 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
     stamp(0);
     cluster_entry_arrive();     // DSMEM rule: no remote access before every CTA of the cluster has started
     PivotState *st = P.st;
-    const int status0 = st->status, iters = st->iters, budget = st->budget;
-    const int t = first ? 0 : st->blk_t, seq = st->blk_seq + (first ? 1 : 0);
+    const int status0 = __ldcg(&st->status), iters = __ldcg(&st->iters), budget = __ldcg(&st->budget);
+    const int t = first ? 0 : __ldcg(&st->blk_t), seq = __ldcg(&st->blk_seq) + (first ? 1 : 0);
     const bool bigm = (P.method == LPGPU_BIGM);
     const double *oc = B.objcur, *om = B.objcur + P.ld;
     const size_t pcn = P.pcn;
     const int rows = P.m + RR;
-    const int phase0 = st->phase;
-    int phase = phase0, p1 = st->phase1_iters;
+    const int phase0 = __ldcg(&st->phase);
+    int phase = phase0, p1 = __ldcg(&st->phase1_iters);
     const bool forced = S.forced_r >= 0;
     const int pmode = bigm ? PRICE_BIGM : (phase0 == PH_ONE ? PRICE_PHASE1 : PRICE_COST);
     // local columns that may be priced: all of them, or (main phase of the two-phase method) the non-artificial ones
@@ -423,7 +422,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
             if (bigm || phase0 == PH_ONE) {
                 const int nreal = S.n_global - S.n_art;
                 for (int i = (int)threadIdx.x; i < P.m; i += blockDim.x)
-                    if (P.basis[i] > nreal && B.bcur[i] > P.eps) f = 1;
+                    if (__ldcg(P.basis + i) > nreal && __ldcg(B.bcur + i) > P.eps) f = 1;
             }
             f = __syncthreads_or(f);                                               // every CTA scans all rows: same answer
             if (f) status = LPGPU_INFEASIBLE;
@@ -432,13 +431,13 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
         } else {
             // ---- the owner: column k as it stands after the t pivots of this block -> every rank's region
             if (mine) {
-                if ((int)threadIdx.x < t) s_pk[threadIdx.x] = B.Pm[(size_t)threadIdx.x * P.ld + (size_t)kl];
+                if ((int)threadIdx.x < t) s_pk[threadIdx.x] = __ldcg(B.Pm + (size_t)threadIdx.x * P.ld + (size_t)kl);
                 __syncthreads();
                 for (int i = gtid; i < rows; i += GSTRIDE) {
                     double a;
-                    if (i >= P.m) a = oc[(size_t)(i - P.m) * P.ld + kl];           // objective rows are kept eagerly: same bits
+                    if (i >= P.m) a = __ldcg(oc + (size_t)(i - P.m) * P.ld + kl);   // objective rows are kept eagerly: same bits
                     else {
-                        const int s0 = blk_row_start(B.rowstamp[i], seq);
+                        const int s0 = blk_row_start(__ldcg(B.rowstamp + i), seq);
                         a = s0 ? s_pk[s0 - 1] : P.T[(size_t)i * P.ld + (size_t)kl];
                         for (int sb = s0; sb < t; sb += 8) {
                             double fv[8];
@@ -472,7 +471,7 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
                 if (i < P.m && a > P.eps) {
                     KeyCand x;
                     x.kp = 0;
-                    x.kq = ord_key(-(B.bcur[i] / a));
+                    x.kq = ord_key(-(__ldcg(B.bcur + i) / a));
                     x.idx = i;
                     if (keycand_better(x, c)) c = x;
                 }
@@ -517,9 +516,9 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
             if (RR == 2) omv[cth] = om[j];
         }
     }
-    const int s0r = blk_row_start(B.rowstamp[r], seq);
-    const double b_r = B.bcur[r];
-    if ((int)threadIdx.x < t) s_fr[threadIdx.x] = B.Fs[(size_t)threadIdx.x * pcn + r];
+    const int s0r = blk_row_start(__ldcg(B.rowstamp + r), seq);
+    const double b_r = __ldcg(B.bcur + r);
+    if ((int)threadIdx.x < t) s_fr[threadIdx.x] = __ldcg(B.Fs + (size_t)threadIdx.x * pcn + r);
     __syncthreads();
     double *pt = B.Pm + (size_t)t * P.ld;
     const double brp = div_skip_zero(b_r, piv);
@@ -619,6 +618,12 @@ shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
         if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
     }
     stamp(6);
+}
+
+template <int RR, bool BL>
+__global__ void __cluster_dims__(SELECT_CLUSTER, 1, 1) __launch_bounds__(SELECT_THREADS)
+shard_blk_step_kernel(ShardParams S, BlockBufs B, int first) {
+    shard_blk_step_body<RR, BL>(S, B, first);
 }
 
 __global__ void shard_synth_kernel(double *T, size_t ld, int m, int ns, int col0, int ncols, int *basis,

@@ -50,6 +50,7 @@ struct ShardParams {
     void *const *peer_x;     // world pointers: every rank's exchange region, own included
     unsigned iter;           // pipeline iteration, counted identically on every rank
     int post;                // 0: decide only, post nothing (the extra select that ends a run call)
+    int ll;                  // 1: flag-in-payload exchange (blocked path over peer memory; shard_p2p.cuh), 0: data + release flag
     int forced_r;            // blocked path, two-phase drive-out: >= 0 = pivot in THIS row on its lowest eligible (non-artificial,
                              // |a| > eps) global column, found and agreed on inside the step kernel; -1 = the normal decision
 };
@@ -99,6 +100,24 @@ __device__ __forceinline__ void store_pair(double *dst, const Cand &c, int col0)
     dst[3] = 0.0;
 }
 
+// flag-in-payload form of the same message: 5 words (p, q as two halves each, the global column) per sender
+__device__ __forceinline__ void ll_post_pair_to(const ShardParams &S, int g, const double *v, unsigned iter) {
+    unsigned long long *dst = xptr<unsigned long long>(S.peer_x[g], XLayout::ll_pairs((int)(iter & 1u), S.P.pcn)) + (size_t)S.rank * 8;
+    ll_put_f64(dst, v[0], iter + 1u);
+    ll_put_f64(dst + 2, v[1], iter + 1u);
+    ll_put(dst + 4, (unsigned)(int)v[2], iter + 1u);
+}
+// this rank's candidate (4 doubles as store_pair leaves them) -> every rank; one thread
+__device__ __forceinline__ void post_cand(const ShardParams &S, const double *v) {
+    if (S.ll) { for (int g = 0; g < S.world; ++g) ll_post_pair_to(S, g, v, S.iter); }
+    else post_pair(S);
+}
+// ... one lane per peer (first warp of a CTA, all 32 lanes)
+__device__ __forceinline__ void post_cand_lanes(const ShardParams &S, const double (&v)[PAIR_DOUBLES]) {
+    if (S.ll) { for (int g = (int)(threadIdx.x & 31); g < S.world; g += 32) ll_post_pair_to(S, g, v, S.iter); }
+    else post_pair_lanes(S, v);
+}
+
 // arg-max over the gathered candidates; idx = GLOBAL column, owner through *owner
 __device__ __forceinline__ Cand best_pair(const double *pairs, int world, int *owner) {
     Cand best = cand_none();
@@ -128,7 +147,7 @@ __global__ void __launch_bounds__(SELECT_THREADS) shard_price_kernel(ShardParams
     }
     if (threadIdx.x == 0) {
         store_pair(S.sendpair, c, S.col0);
-        if (S.peer_x) post_pair(S);
+        if (S.peer_x) post_cand(S, S.sendpair);
     }
 }
 
@@ -388,10 +407,19 @@ __device__ __forceinline__ void shard_blk_step_body(const ShardParams &S, const 
             store_pair(v, out, S.col0);
             ShardParams Sp = S;
             Sp.iter = pit;
-            post_pair_lanes(Sp, v);
+            post_cand_lanes(Sp, v);
         }
     }
-    {
+    __shared__ double s_cand[XMAXW * PAIR_DOUBLES];
+    if (S.ll) {                 // flag-in-payload words: thread g collects rank g's candidate (a dead peer traps the kernel)
+        if (threadIdx.x < (unsigned)S.world) {
+            const unsigned long long *src = xptr<unsigned long long>(S.peer_x[S.rank], XLayout::ll_pairs(ppar, pcn)) + (size_t)threadIdx.x * 8;
+            s_cand[threadIdx.x * PAIR_DOUBLES] = ll_wait_f64(src, pit + 1u);
+            s_cand[threadIdx.x * PAIR_DOUBLES + 1] = ll_wait_f64(src + 2, pit + 1u);
+            s_cand[threadIdx.x * PAIR_DOUBLES + 2] = (double)(int)ll_wait(src + 4, pit + 1u);
+        }
+        __syncthreads();
+    } else {
         int ok = 1;
         if (threadIdx.x < (unsigned)S.world)
             ok = spin_until(xptr<unsigned>(S.peer_x[S.rank], XLayout::pair_flag(ppar)) + threadIdx.x, pit + 1u, XCHG_TIMEOUT_NS);
@@ -403,7 +431,14 @@ __device__ __forceinline__ void shard_blk_step_body(const ShardParams &S, const 
     }
     stamp(1);                   // every rank's candidate has arrived
     int owner = 0;
-    const Cand best = best_pair(xptr<double>(S.peer_x[S.rank], XLayout::pairs(ppar)), S.world, &owner);
+    Cand best = cand_none();
+    if (S.ll) {
+        for (int g = 0; g < S.world; ++g) {
+            Cand c2;
+            c2.p = s_cand[g * PAIR_DOUBLES]; c2.q = s_cand[g * PAIR_DOUBLES + 1]; c2.idx = (int)s_cand[g * PAIR_DOUBLES + 2];
+            if (c2.idx > 0 && cand_better(c2, best)) { best = c2; owner = g; }
+        }
+    } else best = best_pair(xptr<double>(S.peer_x[S.rank], XLayout::pairs(ppar)), S.world, &owner);
     const int k = best.idx > 0 ? best.idx : 0;              // GLOBAL column
     const bool mine = (k > 0) && (owner == S.rank);
     const int kl = mine ? k - S.col0 + 1 : 0;
@@ -448,25 +483,34 @@ __device__ __forceinline__ void shard_blk_step_body(const ShardParams &S, const 
                                 if (sb + u < t) a = __fma_rn(-fv[u], s_pk[sb + u], a);
                         }
                     }
-                    for (int g = 0; g < S.world; ++g) xptr<double>(S.peer_x[g], XLayout::cols(par, pcn))[i] = a;
+                    if (S.ll) {                              // every element is its own message: no fence, no flag
+                        for (int g = 0; g < S.world; ++g) ll_put_f64(xptr<unsigned long long>(S.peer_x[g], XLayout::ll_cols(par, pcn)) + 2 * (size_t)i, a, S.iter + 1u);
+                    } else {
+                        for (int g = 0; g < S.world; ++g) xptr<double>(S.peer_x[g], XLayout::cols(par, pcn))[i] = a;
+                    }
                 }
-                __threadfence_system();                     // this thread's stores into the peers, before the flag below
-                cl.sync();
-                if (gtid < S.world) st_release_sys(xptr<unsigned>(S.peer_x[gtid], XLayout::col_flag(par)), S.iter + 1u);
+                if (!S.ll) {
+                    __threadfence_system();                 // this thread's stores into the peers, before the flag below
+                    cl.sync();
+                    if (gtid < S.world) st_release_sys(xptr<unsigned>(S.peer_x[gtid], XLayout::col_flag(par)), S.iter + 1u);
+                }
             }
             // ---- every rank: the column of this pivot has landed in its region
             stamp(2);           // (owner: column computed, stored to every rank and flagged)
-            if (threadIdx.x == 0) s_flag = spin_until(xptr<unsigned>(S.peer_x[S.rank], XLayout::col_flag(par)), S.iter + 1u, XCHG_TIMEOUT_NS) ? 1 : 0;
-            __syncthreads();
-            if (!s_flag) {
-                cl.sync();
-                if (gtid == 0) { st->status = LPGPU_EXCHANGE_TIMEOUT; st->do_pivot = 0; }
-                return;
+            if (!S.ll) {
+                if (threadIdx.x == 0) s_flag = spin_until(xptr<unsigned>(S.peer_x[S.rank], XLayout::col_flag(par)), S.iter + 1u, XCHG_TIMEOUT_NS) ? 1 : 0;
+                __syncthreads();
+                if (!s_flag) {
+                    cl.sync();
+                    if (gtid == 0) { st->status = LPGPU_EXCHANGE_TIMEOUT; st->do_pivot = 0; }
+                    return;
+                }
             }
             stamp(3);           // the column has arrived
+            const unsigned long long *llcol = xptr<unsigned long long>(S.peer_x[S.rank], XLayout::ll_cols(par, pcn));
             KeyCand c = keycand_none();
             for (int i = gtid; i < rows; i += GSTRIDE) {
-                const double a = __ldcg(mycol + i);
+                const double a = S.ll ? ll_wait_f64(llcol + 2 * (size_t)i, S.iter + 1u) : __ldcg(mycol + i);
                 B.Fs[(size_t)t * pcn + i] = a;
                 if (i < P.m && a > P.eps) {
                     KeyCand x;
@@ -494,16 +538,17 @@ __device__ __forceinline__ void shard_blk_step_body(const ShardParams &S, const 
             st->blk_seq = seq;
             st->phase = phase;
             st->phase1_iters = p1;
-            if (S.post && !forced) post_pair(S);            // the same candidate again: peers expect one every iteration
+            if (S.post && !forced) post_cand(S, S.sendpair);    // the same candidate again: peers expect one every iteration
         }
         return;
     }
 
     stamp(4);                   // ratio test done
     // ---- this rank's slice of row r, brought up to date and scaled; objective rows; local pricing
-    const double sig_c = __ldcg(mycol + P.m);
-    const double sig_m = (RR == 2) ? __ldcg(mycol + P.m + 1) : 0.0;
-    const double piv = __ldcg(mycol + r);
+    // (the column of this pivot, as every thread of the cluster stored it into F[t] above, before the ratio test's cluster barrier)
+    const double sig_c = __ldcg(B.Fs + (size_t)t * pcn + P.m);
+    const double sig_m = (RR == 2) ? __ldcg(B.Fs + (size_t)t * pcn + P.m + 1) : 0.0;
+    const double piv = __ldcg(B.Fs + (size_t)t * pcn + r);
     double av[SSTEP_CPT], ocv[SSTEP_CPT], omv[SSTEP_CPT];
     const size_t jb = 1 + (size_t)gtid;
 #pragma unroll
@@ -599,7 +644,7 @@ __device__ __forceinline__ void shard_blk_step_body(const ShardParams &S, const 
         double v[PAIR_DOUBLES];
         store_pair(v, out, S.col0);
         if (gtid == 0) store_pair(S.sendpair, out, S.col0); // kept for the re-post of an iteration without a pivot
-        post_pair_lanes(S, v);
+        post_cand_lanes(S, v);
     }
     if (gtid == 0) {
         P.basis[r] = k;
@@ -703,6 +748,8 @@ ShardParams shard_params(const lpgpu_shard *s, const ShardRank &r) {
     S.rank = r.rank; S.world = s->world; S.col0 = r.col0; S.n_global = s->n; S.n_art = s->opts.n_art;
     S.sh = r.sh; S.sendpair = r.sendpair; S.pairs = r.pairs; S.sendcol = r.sendcol; S.gathered = r.gathered;
     S.peer_x = s->use_p2p ? s->peer_dev : nullptr; S.iter = s->iter; S.post = 1; S.forced_r = -1;
+    // blocked path over peer memory: flag-in-payload exchange (LPGPU_SHARD_FLAGS=1: data + release flag, as in round 1)
+    S.ll = (s->use_p2p && !(s->opts.variant & LPGPU_VARIANT_RANK1) && !getenv("LPGPU_SHARD_FLAGS")) ? 1 : 0;
     return S;
 }
 

@@ -302,13 +302,13 @@ int launch_block_init(lpgpu_dense *d) {
 }
 
 // ---- pipelined blocks: the pass of block b runs on a second stream, out of place (T -> T2), while the step kernels of
-// block b+1 decide on T (the tableau BEFORE block b) through the slices of block b and their own.  Primal methods.
+// block b+1 decide on T (the tableau BEFORE block b) through the slices of block b and their own.  All four methods.
 // Default: by size -- the longer chains cost each step about 8 us, the hidden pass saves 2 x bytes / 4.3 TB/s per block,
 // which pays from about 0.4 GB of tableau on (measured on 2 m = n tableaux: in place 1.27x / 1.12x faster at m = 1024 /
 // 4096, pipelined 1.12x / 1.45x faster at m = 6144 / 8192).  variant bit 0x1000 forces pipelined blocks, 0x2000 (or no
 // room for the second tableau buffer) the in-place order: steps, pass, steps, ...
 static bool want_pipeline(const lpgpu_dense *d) {
-    if (!use_blocked(d) || (d->opts.variant & LPGPU_VARIANT_INPLACE) || d->opts.method == LPGPU_DUAL || getenv("LPGPU_NO_PIPELINE")) return false;
+    if (!use_blocked(d) || (d->opts.variant & LPGPU_VARIANT_INPLACE) || getenv("LPGPU_NO_PIPELINE")) return false;
     if (d->opts.variant & LPGPU_VARIANT_PIPELINED) return true;
     return ((size_t)d->m + d->R) * d->ld * sizeof(double) >= ((size_t)800 << 20);
 }
@@ -527,7 +527,8 @@ static int probe_step_cluster(lpgpu_dense *d) {
             for (int pr = 0; pr <= 2 && ok; ++pr)
                 ok = cudaFuncSetAttribute(step_kernel(R, pipe != 0, 16, pr), cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
     if (ok) ok = cudaFuncSetAttribute(blk_probe_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
-    if (ok) ok = cudaFuncSetAttribute(blk_dual_step_kernel<16>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
+    if (ok) ok = cudaFuncSetAttribute(blk_dual_step_kernel<16, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
+                 cudaFuncSetAttribute(blk_dual_step_kernel<16, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
     if (ok) {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(16); cfg.blockDim = dim3(SELECT_THREADS / 2);
@@ -551,7 +552,8 @@ static int launch_block_step(lpgpu_dense *d, int first) {
     const bool pdl = !(d->opts.variant & LPGPU_VARIANT_NO_PDL) && !d->opts.time_kernels;
     if (d->opts.method == LPGPU_DUAL) {
         const int cl = step_cluster(d);
-        LP_CUDA(ctx, launch_cluster(pdl, cl, 0, cl == 16 ? blk_dual_step_kernel<16> : blk_dual_step_kernel<8>, dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS),
+        LP_CUDA(ctx, launch_cluster(pdl, cl, 0, cl == 16 ? (d->pipe_on ? blk_dual_step_kernel<16, true> : blk_dual_step_kernel<16, false>)
+                                                         : (d->pipe_on ? blk_dual_step_kernel<8, true> : blk_dual_step_kernel<8, false>), dim3(cl == 16 ? SELECT_THREADS / 2 : SELECT_THREADS),
                                     ctx->stream, make_params(d), make_bufs(d), first));
     } else {
         const int cl = step_cluster(d);

@@ -349,13 +349,13 @@ blk_step_kernel(DenseParams P, BlockBufs B, int first) {
 // of the NEXT pivot are left per CTA at the end of a step, as in the primal kernel), row r brought up to
 // date lazily, entering column = min sigma_j / a_rj over a_rj < -eps on it, column k brought up to date
 // lazily -> F[t], row scaled by a_rk = F[t][r] -> P[t], objective row and b updated.
-template <int CL>
+template <int CL, bool PIPE>        // PIPE: pipelined blocks -- the chains run through the pending block's steps first (see blk_step_kernel)
 __global__ void __launch_bounds__(StepShape<CL>::TH)
 blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
     constexpr int TH = StepShape<CL>::TH, FB = StepShape<CL>::FB, PB = StepShape<CL>::PB;      // cluster shape: see blk_step_kernel
     __shared__ KeyCand scr_a[TH / 32], scr_b[TH / 32], scr_c[TH / 32];
     __shared__ KeyCand slot_a[CL], slot_b[CL];
-    __shared__ double s_pk[BLK_KMAX], s_fr[BLK_KMAX];
+    __shared__ double s_pk[2 * BLK_KMAX], s_fr[2 * BLK_KMAX];      // the pending block's steps first, then this block's
     cg::cluster_group cl = cg::this_cluster();
     const int rank = (int)cl.block_rank();
     const int gtid = rank * TH + (int)threadIdx.x;
@@ -376,6 +376,16 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
     }
     const double *oc = B.objcur;
     const size_t pcn = P.pcn;
+    // pipelined blocks: P.T is the tableau before the pending block; combined step index c < Kp = the pending block's step c
+    const int Kp = (PIPE && B.pend) ? B.info[B.par ^ 1].kc : 0;
+    const int seqp = (PIPE && B.pend) ? B.info[B.par ^ 1].seq : -1;
+    const int tc = Kp + t;
+    const int offP = PIPE ? (B.par ^ 1) * BLK_KMAX : 0, offC = PIPE ? B.par * BLK_KMAX - Kp : 0;
+    auto srow = [&](int cc) -> size_t { return (size_t)((cc < Kp ? offP : offC) + cc); };
+    auto row_start = [&](int i) -> int {       // where row i's chain starts: after its last turn as a pivot row (this block, else the pending one)
+        const int s0 = blk_row_start(B.rowstamp[i], seq);
+        return s0 ? Kp + s0 : (Kp ? blk_row_start(B.stamp_prev[i], seqp) : 0);
+    };
 
     int status = status0, k = 0, r = -1;
     bool have = false;
@@ -399,14 +409,14 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
         if (r < 0) status = LPGPU_OPTIMAL;
         else {
             // ---- row r as it stands after the t pivots of this block; entering column on it
-            const int s0r = blk_row_start(B.rowstamp[r], seq);
+            const int s0r = row_start(r);
 #pragma unroll
             for (int cth = 0; cth < STEP_CPT; ++cth) {
                 const size_t j = jb + (size_t)cth * GSTRIDE;
                 av[cth] = ocv[cth] = 0.0;
                 if (j <= (size_t)P.n) { av[cth] = P.T[(size_t)r * P.ld + j]; ocv[cth] = oc[j]; }
             }
-            if ((int)threadIdx.x < t) s_fr[threadIdx.x] = B.Fs[(size_t)threadIdx.x * pcn + r];
+            if ((int)threadIdx.x < tc) s_fr[threadIdx.x] = B.Fall[srow((int)threadIdx.x) * pcn + r];
             __syncthreads();
             KeyCand c = keycand_none();
             // n <= STEP_CPT * GSTRIDE columns are kept in registers across the column phase; wider tableaux recompute
@@ -418,19 +428,19 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
                     aw[cth] = ow[cth] = 0.0;
                     if (j0 == jb) { aw[cth] = av[cth]; ow[cth] = ocv[cth]; }
                     else if (j <= (size_t)P.n) { aw[cth] = P.T[(size_t)r * P.ld + j]; ow[cth] = oc[j]; }
-                    if (s0r > 0 && j <= (size_t)P.n) aw[cth] = B.Pm[(size_t)(s0r - 1) * P.ld + j];
+                    if (s0r > 0 && j <= (size_t)P.n) aw[cth] = B.Pall[srow(s0r - 1) * P.ld + j];
                 }
-                for (int sb = s0r; sb < t; sb += PB) {
+                for (int sb = s0r; sb < tc; sb += PB) {
                     double pv[STEP_CPT][PB];
 #pragma unroll
                     for (int cth = 0; cth < STEP_CPT; ++cth) {
                         const size_t j = j0 + (size_t)cth * GSTRIDE;
 #pragma unroll
-                        for (int u = 0; u < PB; ++u) pv[cth][u] = (sb + u < t && j <= (size_t)P.n) ? B.Pm[(size_t)(sb + u) * P.ld + j] : 0.0;
+                        for (int u = 0; u < PB; ++u) pv[cth][u] = (sb + u < tc && j <= (size_t)P.n) ? B.Pall[srow(sb + u) * P.ld + j] : 0.0;
                     }
 #pragma unroll
                     for (int u = 0; u < PB; ++u)
-                        if (sb + u < t) {
+                        if (sb + u < tc) {
 #pragma unroll
                             for (int cth = 0; cth < STEP_CPT; ++cth) aw[cth] = __fma_rn(-s_fr[sb + u], pv[cth][u], aw[cth]);
                         }
@@ -460,6 +470,7 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
             st->blk_t = t;
             st->blk_seq = seq;
             st->k_next = 0;                       // the leaving row is looked for again from bcur
+            if (B.info) { B.info[B.par].kc = t; B.info[B.par].seq = seq; }
         }
         return;
     }
@@ -467,23 +478,23 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
     // ---- column k as it stands after the t pivots of this block -> F[t]
     const double sig = oc[k];
     if (gtid == 0) B.Fs[(size_t)t * pcn + P.m] = sig;
-    if ((int)threadIdx.x < t) s_pk[threadIdx.x] = B.Pm[(size_t)threadIdx.x * P.ld + (size_t)k];
+    if ((int)threadIdx.x < tc) s_pk[threadIdx.x] = B.Pall[srow((int)threadIdx.x) * P.ld + (size_t)k];
     __syncthreads();
     for (int i = gtid; i < P.m; i += GSTRIDE) {
-        const int s0 = blk_row_start(B.rowstamp[i], seq);
+        const int s0 = row_start(i);
         double a = s0 ? s_pk[s0 - 1] : P.T[(size_t)i * P.ld + (size_t)k];
-        for (int sb = s0; sb < t; sb += FB) {
+        for (int sb = s0; sb < tc; sb += FB) {
             double fv[FB];
 #pragma unroll
-            for (int u = 0; u < FB; ++u) fv[u] = (sb + u < t) ? B.Fs[(size_t)(sb + u) * pcn + i] : 0.0;
+            for (int u = 0; u < FB; ++u) fv[u] = (sb + u < tc) ? B.Fall[srow(sb + u) * pcn + i] : 0.0;
 #pragma unroll
             for (int u = 0; u < FB; ++u)
-                if (sb + u < t) a = __fma_rn(-fv[u], s_pk[sb + u], a);
+                if (sb + u < tc) a = __fma_rn(-fv[u], s_pk[sb + u], a);
         }
         B.Fs[(size_t)t * pcn + i] = a;
     }
     const double b_r = B.bcur[r];
-    const int s0r = blk_row_start(B.rowstamp[r], seq);
+    const int s0r = row_start(r);
     cl.sync();                                    // F[t] is complete (the pivot element among it)
     const double piv = __ldcg(B.Fs + (size_t)t * pcn + r);
 
@@ -502,8 +513,8 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
             double a, o;
             if (j0 == jb) { a = av[cth]; o = ocv[cth]; }
             else {                                // wide tableau: the row slice again (rare; same chain, same bits)
-                a = s0r ? B.Pm[(size_t)(s0r - 1) * P.ld + j] : P.T[(size_t)r * P.ld + j];
-                for (int s = s0r; s < t; ++s) a = __fma_rn(-s_fr[s], B.Pm[(size_t)s * P.ld + j], a);
+                a = s0r ? B.Pall[srow(s0r - 1) * P.ld + j] : P.T[(size_t)r * P.ld + j];
+                for (int s = s0r; s < tc; ++s) a = __fma_rn(-s_fr[s], B.Pall[srow(s) * P.ld + j], a);
                 o = oc[j];
             }
             const double pr = div_skip_zero(a, piv);
@@ -536,6 +547,7 @@ blk_dual_step_kernel(DenseParams P, BlockBufs B, int first) {
         st->k_next = -2;
         st->blk_t = t + 1;
         st->blk_seq = seq;
+        if (B.info) { B.info[B.par].kc = t + 1; B.info[B.par].seq = seq; }
         if (iters < P.log_cap) { P.log[2 * iters] = k; P.log[2 * iters + 1] = r; }
     }
 }

@@ -644,6 +644,7 @@ def test_dual_simplex_midsize_and_batched(ctx):
     got = lp.solve_dense(ctx, T, basis, method=lp.DUAL, log_cap=4096)
     _assert_dense_equal(got, ref)
     assert ref["status"] == O.OPTIMAL and ref["iters"] > 20
+    _assert_dense_equal(lp.solve_dense(ctx, T, basis, method=lp.DUAL, log_cap=4096, variant=capi.PIPELINED), ref)      # pipelined blocks
     # batched: the shared-memory kernel takes the dual method through the same decide()
     Ts, Bs = zip(*[H.random_dual_lp(rng, 10, 12)[:2] for _ in range(200)])
     Tb, Bb = np.stack(Ts), np.stack(Bs)
@@ -652,10 +653,11 @@ def test_dual_simplex_midsize_and_batched(ctx):
     _assert_batched_equal(gotb, refb)
 
 
-@pytest.mark.parametrize("variant", [0, 4 << 16, capi.STEP_CL8, (4 << 16) | capi.STEP_CL8, capi.RANK1])
+@pytest.mark.parametrize("variant", [0, 4 << 16, capi.STEP_CL8, (4 << 16) | capi.STEP_CL8, capi.RANK1, capi.PIPELINED, (5 << 16) | capi.PIPELINED,
+                                     capi.PIPELINED | capi.STEP_CL8, (3 << 16) | capi.PIPELINED | capi.DFMA_PASS])
 def test_dual_simplex_blocked_windows_and_rank1(ctx, variant):
-    """Dual simplex through the blocked path (default; blocks of 32 and of 4 pivots; step kernel as a cluster of 16 x 512
-    and of 8 x 1024 threads) and through the rank-1 path, in windows of 7 pivots: all leave the oracle's bits."""
+    """Dual simplex through the blocked path (in place and pipelined; blocks of 32 / 28, 5, 4 and 3 pivots; step kernel as a cluster
+    of 16 x 512 and of 8 x 1024 threads) and through the rank-1 path, in windows of 7 pivots: all leave the oracle's bits."""
     rng = np.random.default_rng(555)
     for (m, ns, infeasible) in [(120, 90, False), (40, 70, False), (30, 30, True)]:
         T, basis, _ = H.random_dual_lp(rng, m, ns, infeasible=infeasible)

@@ -14,7 +14,7 @@ rng = np.random.default_rng(77)
 T, basis, _ = H.random_dual_lp(rng, m, ns)
 ctx = lp.Context(0)
 ref = None
-for name, variant in (("cl16", 0), ("cl8", capi.STEP_CL8), ("rank1", capi.RANK1)):
+for name, variant in (("cl16", 0), ("pipelined", capi.PIPELINED), ("cl8", capi.STEP_CL8), ("rank1", capi.RANK1)):
     d = lp.DenseTableau(ctx, m, T.shape[1] - 1, 1)
     d.upload(T, basis)
     d.reset(method=lp.DUAL, log_cap=1 << 16, check_every=256, variant=variant)

@@ -83,7 +83,7 @@ extern "C" {
                                                /* neither bit: pipelined from 0.8 GB of tableau on                                 */
 #define LPGPU_VARIANT_STEP_CL8      0x8000     /* blocked path: step kernel as a portable 8-CTA cluster (default: 16 CTAs)         */
 #define LPGPU_VARIANT_STEP_PERSISTENT 0x40    /* pipelined blocks: one persistent step-kernel launch per block (default: one cluster launch per pivot, measured faster) */
-#define LPGPU_VARIANT_BLOCK_K(k)    (((k) & 0x3f) << 16)   /* blocked path: pivots per block, 1..32 (0 = 32)                       */
+#define LPGPU_VARIANT_BLOCK_K(k)    (((k) & 0x3f) << 16)   /* blocked path: pivots per block, 1..32 (0 = 32 in place, 28 pipelined) */
 #define LPGPU_VARIANT_BLOCK_K_MASK  0x3f0000
 #define LPGPU_VARIANT_BLAND         0x400000
 #define LPGPU_VARIANT_DEVEX         0x800000

@@ -3,13 +3,15 @@
 // blk_flush_sp_kernel and blk_flush_mma_kernel fetch their tiles with ordinary loads: a CTA's accumulators ARE its loads in
 // flight, a warp that waits for them does nothing else, and both kernels end up serialising memory and arithmetic
 // (ncu of the DMMA pass, profiles/r2_mma_pass_raw.csv: the DMMA pipe is busy 37 % of the time, every warp spends 85 % of
-// its life waiting for its tile, 3.4 TB/s).  Here ONE persistent CTA per SM is split into a producer warp and
+// its life waiting for its tile, 3.4 TB/s).  Here ONE persistent CTA per SM is split into two producer warps and
 // RG_NW compute warps:
-//   * the producer claims tasks (column tile x row super-block, the same global counter as the other pass kernels) and
-//     keeps a ring of shared-memory slots full with TMA bulk copies: per slab of 16 rows x 128 columns one 1 KB copy per
-//     row plus the slab's multipliers (kc x 128 B), per task the kc pivot-row segments of the column tile (double
-//     buffered).  Nothing it moves ever touches a register, and it runs ahead of the arithmetic by RG_ND slabs
-//     (5 x 17 KB per SM: more than the bandwidth-latency product of the SM's share of HBM);
+//   * the OPERAND producer claims tasks (column tile x row super-block, the same global counter as the other pass kernels)
+//     and fetches, with TMA bulk copies, the kc pivot-row segments of the column tile (double buffered across tasks) and the
+//     multipliers of each 64-row tile (RG_NF slots, kc x 512 B each);
+//   * the DATA producer keeps a ring of RG_ND slabs of 16 rows x 128 columns full: one 1 KB bulk copy per row, issued by
+//     16 lanes at once (one lane issuing them in turn capped the pass at 4.8 TB/s).  Nothing the producers move ever touches
+//     a register, and the ring runs ahead of the arithmetic by 5 x 16 KB per SM -- more than the bandwidth-latency product of
+//     the SM's share of HBM;
 //   * a compute warp takes the next slab that is complete (mbarrier), pulls it into registers as DMMA accumulator
 //     fragments (conflict-free LDS.128: rows are padded to 1088 B), hands the data slot back at once, runs the chain with
 //     mma.sync.m8n8k4.f64 -- four consecutive steps of the pivot chain per instruction, in pivot order, one rounding per

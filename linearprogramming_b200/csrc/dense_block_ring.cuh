@@ -141,6 +141,7 @@ __global__ void __launch_bounds__(RG_THREADS, 1) blk_flush_ring_kernel(FlushPara
     const int nrt = (U.rows + FL_ROWS - 1) / FL_ROWS;
     const long ntasks = (long)nct * ((nrt + U.rb - 1) / U.rb);
     const uint64_t pol = l2_policy(U.l2first ? 1 : 0);
+    const uint64_t pol_keep = l2_policy(U.l2first ? 2 : 0);      // the slices: the step kernels re-read them all the time (evict last)
     const unsigned ND = (unsigned)min(max(U.ring_nd, 2), RG_ND);     // data slots in use
     auto wait_issued = [](volatile unsigned *ctr_issued, unsigned seq) {
         unsigned spin = 0;
@@ -163,7 +164,7 @@ __global__ void __launch_bounds__(RG_THREADS, 1) blk_flush_ring_kernel(FlushPara
             const uint32_t rowbytes = (uint32_t)(t.ncols * 8);
             mbar_arrive_expect_tx(&full_p[pb], (uint32_t)kc * rowbytes);
             for (int s = 0; s < kc; ++s)
-                tma_load_1d(sP + ((size_t)pb * BLK_KMAX + s) * RG_PS, U.Pm + (size_t)s * U.ld + t.j0, rowbytes, &full_p[pb]);
+                tma_load_1d_hint(sP + ((size_t)pb * BLK_KMAX + s) * RG_PS, U.Pm + (size_t)s * U.ld + t.j0, rowbytes, &full_p[pb], pol_keep);
             const int ntile = (t.nslab + RG_TS - 1) / RG_TS;
             for (int ti = 0; ti < ntile; ++ti, ++tseq) {
                 const unsigned fs = tseq % RG_NF;
@@ -173,7 +174,7 @@ __global__ void __launch_bounds__(RG_THREADS, 1) blk_flush_ring_kernel(FlushPara
                 s_issued_f = tseq + 1u;
                 const double *src = U.Fs + (size_t)(t.row0 + ti * FL_ROWS);
                 for (int s = 0; s < kc; ++s)
-                    tma_load_1d(sF + ((size_t)fs * BLK_KMAX + s) * RG_FS, src + (size_t)s * U.pcn, (uint32_t)(FL_ROWS * 8), &full_f[fs]);
+                    tma_load_1d_hint(sF + ((size_t)fs * BLK_KMAX + s) * RG_FS, src + (size_t)s * U.pcn, (uint32_t)(FL_ROWS * 8), &full_f[fs], pol_keep);
             }
         }
         return;

@@ -375,7 +375,7 @@ def gpu_arm(args):
     if pipelined:
         # the pass of a block runs on a second stream WHILE the next block is decided: the two kernel families overlap, so their
         # summed times exceed the step; kernel_share_of_step stays the share of summed kernel time (what an ncu launch list shows)
-        roofline["overlap"] = ("pipelined blocks: the pass (stream 2, every SM but the 16 of the step cluster) runs concurrently with "
+        roofline["overlap"] = ("pipelined blocks: the pass (stream 2 in a green context over every SM but the 16 of the step cluster) runs concurrently with "
                                "the decisions of the next block; avg_launch_ms is measured under that contention "
                                "(alone on the GPU the same launch takes 0.357 ms = 0.92 of the peak: tools/ring_lab.cu, profiles/r2_ring_lab.txt)")
         roofline["pass_time_over_step_time"] = (upd_ms / K) / (1e3 * t_value / K)

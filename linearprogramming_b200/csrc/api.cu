@@ -41,6 +41,7 @@ int lpgpu_create(lpgpu_ctx **out, int device, void *stream) {
     ctx->hbm_bytes = prop.totalGlobalMem;
     ctx->launches = 0;
     ctx->solve_cache = nullptr;
+    ctx->green_pass = nullptr; ctx->green_sms = 0; ctx->green_state = 0;
     ctx->err[0] = '\0';
     if (stream) {
         ctx->stream = reinterpret_cast<cudaStream_t>(stream);
@@ -61,6 +62,14 @@ void lpgpu_destroy(lpgpu_ctx *ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->solve_cache) lpgpu_dense_destroy(ctx->solve_cache);
+    if (ctx->green_pass) {          // the green context of the pipelined pass (dense.cu); its streams went with the tableau objects
+        typedef int (*fn_gdestroy)(void *);
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuGreenCtxDestroy", &f, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess && f)
+            reinterpret_cast<fn_gdestroy>(f)(ctx->green_pass);
+        cudaGetLastError();
+    }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -17,6 +17,9 @@ struct lpgpu_ctx {
     int cc_major, cc_minor;
     size_t hbm_bytes;
     long launches;
+    void *green_pass;           // green context (driver API) over the SMs the step kernels do NOT get: the pipelined pass runs in it
+    int green_sms;              // SMs in it
+    int green_state;            // 0 = not tried yet, 1 = ready, -1 = unavailable
     lpgpu_dense *solve_cache;   // tableau object kept between lpgpu_solve_dense calls of one shape (1 GB cudaMalloc / cudaFree per call otherwise)
     char err[512];
 };

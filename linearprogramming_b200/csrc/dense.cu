@@ -9,6 +9,8 @@
 #include <new>
 #include <vector>
 
+#include <cuda.h>
+
 #include "dense_internal.h"
 #include "dense_update.cuh"
 #include "dense_block.cuh"
@@ -332,7 +334,7 @@ static int setup_steps(lpgpu_dense *d) {
     if (d->steps_state != 0) return LPGPU_OK;
     lpgpu_ctx *ctx = d->ctx;
     d->steps_state = -1;
-    int G = 32;
+    int G = d->green ? 16 : 32;       // under the green-context partition the pass leaves exactly 16 SMs
     { const char *e = getenv("LPGPU_STEP_CTAS"); if (e && atoi(e) > 0) G = atoi(e); }      // tuning aid
     G = std::max(1, std::min(G, std::min(STEPS_GMAX, ctx->sm_count / 2)));
     const int rpc = (int)((((size_t)d->m + G - 1) / G + 1) & ~(size_t)1);
@@ -397,6 +399,55 @@ static void free_pipeline(lpgpu_dense *d) {
     if (d->ev_flush) { cudaEventDestroy(d->ev_flush); d->ev_flush = nullptr; }
 }
 
+// SM partition through the driver's green contexts instead of the %smid probe: the SMs of the device are split into a group of
+// 16 (one step cluster, 8-SM granularity, MAX_POTENTIAL_CLUSTER_SIZE so that a 16-CTA cluster fits it) and the rest; the
+// pipelined pass runs on a stream of a green context over THE REST, so it can never occupy the step kernels' SMs and nothing
+// has to be probed or vacated.  Entry points come from cudaGetDriverEntryPoint (the library does not link libcuda).
+// Measured: 58.3 k against 56.6 k pivots/s with the probe + vacate reservation (tools/green_ab.sh).  LPGPU_GREEN=0, or the API
+// being unavailable / failing, falls back to that reservation.
+static cudaStream_t green_pass_stream(lpgpu_ctx *ctx) {
+    const char *ge = getenv("LPGPU_GREEN");
+    if ((ge && atoi(ge) == 0) || ctx->green_state < 0) return nullptr;
+    typedef CUresult (*fn_devget)(CUdevice *, int);
+    typedef CUresult (*fn_getres)(CUdevice, CUdevResource *, CUdevResourceType);
+    typedef CUresult (*fn_split)(CUdevResource *, unsigned int *, const CUdevResource *, CUdevResource *, unsigned int, unsigned int);
+    typedef CUresult (*fn_desc)(CUdevResourceDesc *, CUdevResource *, unsigned int);
+    typedef CUresult (*fn_gcreate)(CUgreenCtx *, CUdevResourceDesc, CUdevice, unsigned int);
+    typedef CUresult (*fn_gstream)(CUstream *, CUgreenCtx, unsigned int, int);
+    auto entry = [](const char *name) -> void * {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint(name, &f, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) { cudaGetLastError(); return nullptr; }
+        return f;
+    };
+    fn_gstream gstream = (fn_gstream)entry("cuGreenCtxStreamCreate");
+    if (ctx->green_state == 0) {
+        ctx->green_state = -1;
+        fn_devget devget = (fn_devget)entry("cuDeviceGet");
+        fn_getres getres = (fn_getres)entry("cuDeviceGetDevResource");
+        fn_split split = (fn_split)entry("cuDevSmResourceSplitByCount");
+        fn_desc desc = (fn_desc)entry("cuDevResourceGenerateDesc");
+        fn_gcreate gcreate = (fn_gcreate)entry("cuGreenCtxCreate");
+        if (!devget || !getres || !split || !desc || !gcreate || !gstream) return nullptr;
+        CUdevice dev;
+        CUdevResource all, grp, rest;
+        unsigned int ng = 1;
+        CUdevResourceDesc rd;
+        CUgreenCtx g;
+        if (devget(&dev, ctx->device) != CUDA_SUCCESS || getres(dev, &all, CU_DEV_RESOURCE_TYPE_SM) != CUDA_SUCCESS) return nullptr;
+        if (split(&grp, &ng, &all, &rest, CU_DEV_SM_RESOURCE_SPLIT_MAX_POTENTIAL_CLUSTER_SIZE, 16) != CUDA_SUCCESS || ng < 1) return nullptr;
+        if (rest.sm.smCount < 64) return nullptr;
+        if (desc(&rd, &rest, 1) != CUDA_SUCCESS || gcreate(&g, rd, dev, CU_GREEN_CTX_DEFAULT_STREAM) != CUDA_SUCCESS) return nullptr;
+        ctx->green_pass = g;
+        ctx->green_sms = (int)rest.sm.smCount;
+        ctx->green_state = 1;
+        if (getenv("LPGPU_BLK_DEBUG")) fprintf(stderr, "[lpgpu] green context: step group %u SMs, pass %u SMs\n", grp.sm.smCount, rest.sm.smCount);
+    }
+    CUstream st = nullptr;
+    if (!gstream || gstream(&st, (CUgreenCtx)ctx->green_pass, CU_STREAM_NON_BLOCKING, 0) != CUDA_SUCCESS) return nullptr;
+    return (cudaStream_t)st;
+}
+
 // Buffers, stream and events of the pipelined path, once per tableau object.  Not having room for the second tableau
 // buffer is not an error: the in-place order is used instead (pipe_state = -1).
 static int setup_pipeline(lpgpu_dense *d) {
@@ -412,7 +463,8 @@ static int setup_pipeline(lpgpu_dense *d) {
     if (e == cudaSuccess) e = cudaMalloc(&d->info, 2 * sizeof(BlkInfo));
     if (e == cudaSuccess) e = cudaMalloc(&d->flush_flag, sizeof(int));
     if (e == cudaSuccess) e = cudaMalloc(&smids, STEP_CLUSTER_MAX * sizeof(unsigned));
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d->stream2, cudaStreamNonBlocking);
+    if (e == cudaSuccess) { d->stream2 = green_pass_stream(ctx); d->green = d->stream2 != nullptr; }
+    if (e == cudaSuccess && !d->green) e = cudaStreamCreateWithFlags(&d->stream2, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->ev_steps, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->ev_flush, cudaEventDisableTiming);
     if (e != cudaSuccess) {
@@ -471,7 +523,7 @@ static int close_block_pipe(lpgpu_dense *d, cudaEvent_t ev0, cudaEvent_t ev1) {
     U.task_ctr = d->task_ctr; U.seq = d->upd_seq++;
     U.rb = d->fl_rb; U.pf = d->fl_pf; U.ring_nd = d->ring_nd;
     const bool full = d->grid_flush >= ctx->sm_count * (pass_kind(d) == PASS_RING ? 1 : 2);   // a full persistent grid: every SM holds CTAs of the pass
-    for (int w = 0; w < 8; ++w) U.resv[w] = full ? (d->persist_on ? d->resv_steps[w] : d->resv[w]) : 0u;
+    for (int w = 0; w < 8; ++w) U.resv[w] = (full && !d->green) ? (d->persist_on ? d->resv_steps[w] : d->resv[w]) : 0u;     // green context: nothing to vacate
     U.flag = d->flush_flag;
     U.l2first = (d->l2hint & 1) ? 1 : 0;
     LP_CUDA(ctx, cudaEventRecord(d->ev_steps, ctx->stream));
@@ -570,10 +622,13 @@ static int launch_block_step(lpgpu_dense *d, int first) {
 // LPGPU_VARIANT_DMMA_PASS = DMMA chain on tiles fetched with ordinary loads (0.66 ms).  All bit-identical.
 static int launch_pass_kernel(lpgpu_dense *d, const FlushParams &U, cudaStream_t stream) {
     lpgpu_ctx *ctx = d->ctx;
+    int grid = d->grid_flush;
+    if (d->green && stream == d->stream2)        // the persistent grid fits the SMs of the green context it runs in
+        grid = std::max(1, std::min(grid, grid / ctx->sm_count > 0 ? grid / ctx->sm_count * ctx->green_sms : ctx->green_sms));
     switch (pass_kind(d)) {
-        case PASS_DMMA: blk_flush_mma_kernel<<<d->grid_flush, FL_THREADS, MM_SMEM_BYTES, stream>>>(U); break;
-        case PASS_DFMA: blk_flush_sp_kernel<<<d->grid_flush, FL_THREADS, FL_SMEM_BYTES, stream>>>(U); break;
-        default: blk_flush_ring_kernel<<<d->grid_flush, RG_THREADS, RG_SMEM_BYTES, stream>>>(U); break;
+        case PASS_DMMA: blk_flush_mma_kernel<<<grid, FL_THREADS, MM_SMEM_BYTES, stream>>>(U); break;
+        case PASS_DFMA: blk_flush_sp_kernel<<<grid, FL_THREADS, FL_SMEM_BYTES, stream>>>(U); break;
+        default: blk_flush_ring_kernel<<<grid, RG_THREADS, RG_SMEM_BYTES, stream>>>(U); break;
     }
     LP_LAUNCH_CHECK(ctx);
     return LPGPU_OK;
@@ -893,7 +948,7 @@ int lpgpu_dense_create(lpgpu_ctx *ctx, int m, int n, int R, lpgpu_dense **out) {
     d->up_stream = nullptr; d->ev_up = d->ev_up_ready = nullptr; d->up_pending = false;
     { const char *eh = getenv("LPGPU_L2HINT"); d->l2hint = eh ? atoi(eh) : 3; }
     d->T2 = d->Ft2 = d->Pm2 = nullptr; d->rowstamp2 = d->steprow2 = nullptr; d->info = nullptr; d->flush_flag = nullptr;
-    d->stream2 = nullptr; d->ev_steps = d->ev_flush = nullptr;
+    d->stream2 = nullptr; d->ev_steps = d->ev_flush = nullptr; d->green = false;
     for (unsigned &w : d->resv) w = 0;
     lpgpu_default_opts(&d->opts);
     d->opts.method = (R == 1) ? LPGPU_PLAIN : LPGPU_BIGM;

@@ -50,6 +50,7 @@ struct lpgpu_dense {
     int *rowstamp2, *steprow2;
     lpgpu::BlkInfo *info;   // [2]
     int *flush_flag;        // a pass's CTAs on reserved SMs leave once a worker CTA is known to exist
+    bool green;             // stream2 belongs to the green context of the SMs the step kernels do not get (no reservation needed)
     cudaStream_t stream2;
     cudaEvent_t ev_steps, ev_flush;
     unsigned resv[8];       // SMs left to the step kernels while a pass runs (bit per %smid)
